@@ -1,0 +1,235 @@
+/*
+ * rtb200.h — C-ABI of the B200-native per-frame ray-tracing hot path.
+ *
+ * Drop-in boundary for the all-static C++ class `renderer::Renderer` of
+ * 3169651074/real-time-gpu-ray-tracer (reference include/Global/Renderer.cuh:109-146).
+ * Each entry point names the reference interface it replaces (file:line, relative to the
+ * reference root).  Plain pointers and sizes only; no C++/torch types cross this boundary.
+ *
+ * Threading: a context is single-threaded (one host thread drives one rt_ctx at a time).
+ * Errors: every function returns 0 on success or a negative rt_status; nothing exits or throws
+ *         (the reference exit()s: include/Global/Global.cuh:242,253; src/Global/Global.cu:14-42).
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes (reference exit codes kept where they exist) -------------------------- */
+enum rt_status {
+    RT_OK            = 0,
+    RT_ERR_IO        = -1,   /* reference: exit(-1) on file errors, src/Global/Renderer.cu:399-422 */
+    RT_ERR_ARGUMENT  = -2,
+    RT_ERR_STATE     = -3,   /* call order violated (e.g. render before build)                    */
+    RT_ERR_CUDA      = -200, /* reference: CUDA_ERROR_EXIT_CODE, include/Global/Global.cuh:253    */
+    RT_ERR_NCCL      = -300
+};
+
+/* ---- enums: values identical to the reference (include/Basic/BasicTypes.cuh:9-16) -------- */
+enum rt_primitive_type { RT_SPHERE = 0, RT_PARALLELOGRAM = 1, RT_TRIANGLE = 2 };
+enum rt_material_type  { RT_ROUGH = 0, RT_METAL = 1, RT_DIELECTRIC = 2 /* extension, not in the reference */ };
+
+typedef struct rt_vec3 { float x, y, z; } rt_vec3;
+
+/* ---- geometry inputs: the constructor arguments of the reference classes ---------------- */
+/* Sphere(materialType, materialIndex, center, radius)    include/Geometry/Sphere.cuh:27-28   */
+typedef struct rt_sphere {
+    rt_vec3  center;
+    float    radius;
+    uint32_t material_type;
+    uint32_t material_index;
+} rt_sphere;
+
+/* Parallelogram(materialType, materialIndex, q, u, v)    include/Geometry/Parallelogram.cuh:26-39
+ * (area, normalVector, d are derived inside the library exactly as that constructor does)      */
+typedef struct rt_parallelogram {
+    rt_vec3  q, u, v;
+    uint32_t material_type;
+    uint32_t material_index;
+} rt_parallelogram;
+
+/* Triangle(materialType, materialIndex, vertexes[, vertexNormals])  include/Geometry/Triangle.cuh:26-46
+ * has_normals == 0 selects the 3-vertex constructor (flat normal unit(e1 x e2) on all vertices). */
+typedef struct rt_triangle {
+    rt_vec3  v[3];
+    rt_vec3  n[3];
+    uint32_t material_type;
+    uint32_t material_index;
+    uint32_t has_normals;
+    uint32_t _pad;
+} rt_triangle;
+
+/* ---- materials (include/Material/Rough.cuh:11-12, include/Material/Metal.cuh:11-13) ------- */
+typedef struct rt_rough      { rt_vec3 albedo; } rt_rough;
+typedef struct rt_metal      { rt_vec3 albedo; float fuzz; } rt_metal;
+typedef struct rt_dielectric { rt_vec3 albedo; float ior; } rt_dielectric;   /* extension */
+
+/* ---- instances ---------------------------------------------------------------------------
+ * The reference's instance map carries (PrimitiveType, index) (include/Global/Renderer.cuh:123-126);
+ * multi-primitive instances exist only for VTK particles (src/Global/VTKReader.cu:203-209), which
+ * pre-fill primitiveCount, boundingBox and centroid.  prim_count <= 1 means "single primitive":
+ * count/box/centroid come from the primitive (src/Global/RenderPin.cu:124-140).  For prim_count > 1
+ * the caller may pass the local box/centroid (has_bounds = 1, as VTKReader does); otherwise the
+ * library uses the merged primitive boxes and the box centre.                                     */
+typedef struct rt_instance_desc {
+    uint32_t type;         /* rt_primitive_type                                                  */
+    uint32_t has_bounds;
+    uint64_t first_prim;   /* Instance::primitiveIndex  include/AS/Instance.cuh:29               */
+    uint64_t prim_count;   /* Instance::primitiveCount  include/AS/Instance.cuh:31               */
+    float    bounds_min[3], bounds_max[3];
+    float    centroid[3];
+    uint32_t _pad;
+} rt_instance_desc;
+
+/* Arguments of Instance::updateTransformArguments (include/AS/Instance.cuh:53, src/AS/Instance.cu:4-17):
+ * M = T(shift) * Rx * Ry * Rz * S(scale), rotation in degrees.                                    */
+typedef struct rt_instance_xform {
+    rt_vec3 shift;
+    rt_vec3 rotate_deg;
+    rt_vec3 scale;
+} rt_instance_xform;
+
+/* Per-frame instance update callback; replaces
+ * void (*updateInstances)(Instance*, size_t, size_t)  include/Global/Renderer.cuh:94.
+ * It writes transform arguments; matrices, inverse, boxes are derived inside the library.         */
+typedef void (*rt_update_cb)(rt_instance_xform *xforms, size_t instance_count, size_t frame, void *user);
+
+/* ---- window + camera (include/Global/Renderer.cuh:46-64) --------------------------------- */
+typedef struct rt_window { uint32_t width, height; } rt_window;
+
+typedef struct rt_camera_input {
+    rt_vec3  background;
+    rt_vec3  center;
+    rt_vec3  target;
+    float    fov;               /* horizontal, degrees (src/Global/RenderPin.cu:76-78)            */
+    rt_vec3  up;
+    float    focus_disk_radius;
+    float    sample_range;      /* carried, unused by the reference kernel                        */
+    uint64_t sample_count;      /* floored to a perfect square (src/Global/RenderPin.cu:93)       */
+    uint64_t ray_trace_depth;
+} rt_camera_input;
+
+/* ---- options ----------------------------------------------------------------------------- */
+enum rt_flags {
+    RT_FLAG_NONE                    = 0,
+    /* The reference's Parallelogram::constructBoundingBox is wrong (src/Geometry/Parallelogram.cu:48-50)
+     * and culls most of the quad.  Default = bug-compatible (results identical to the reference).  */
+    RT_FLAG_FIX_PARALLELOGRAM_BBOX  = 1u << 0,
+    /* Record primary-hit AOVs (t, instance, primitive) of each pixel's first sample.              */
+    RT_FLAG_RECORD_PRIMARY_AOV      = 1u << 1,
+    /* Keep the binary LBVH arrays after the wide collapse so rt_read_lbvh can return them.        */
+    RT_FLAG_KEEP_LBVH               = 1u << 2
+};
+
+typedef struct rt_frame_out {
+    uint64_t rays;            /* closest-hit queries traced (= TLAS::hit calls, src/Global/Kernel.cu:68) */
+    uint64_t primary_rays;    /* W*H*spp of this context's shard                                         */
+    float    render_ms;       /* CUDA-event time, first launch of the frame .. framebuffer ready          */
+    float    tlas_ms;         /* CUDA-event time of the per-frame instance update + TLAS rebuild           */
+    float    rng_ms;          /* CUDA-event time of the per-pixel XORWOW initialisation                    */
+    float    trace_ms;        /* CUDA-event time of the trace/shade kernel                                 */
+    uint32_t kernel_launches; /* kernels launched for this frame                                           */
+    uint32_t stack_overflow;  /* != 0 if a traversal stack overflowed (reference has no check, Q15)         */
+} rt_frame_out;
+
+typedef struct rt_build_stats {
+    float    blas_ms;          /* triangles resident -> wide BVH ready (CUDA events)              */
+    float    tlas_ms;
+    uint64_t blas_count;
+    uint64_t primitive_count;
+    uint64_t lbvh_nodes;       /* binary internal nodes                                            */
+    uint64_t wide_nodes;
+    uint64_t node_bytes;       /* bytes of traversable node memory                                 */
+    uint64_t prim_bytes;       /* bytes of traversable primitive memory                            */
+    uint32_t kernel_launches;
+    uint32_t _pad;
+} rt_build_stats;
+
+enum rt_buffer_kind {
+    RT_BUFFER_RGBA8       = 0, /* uchar4, row 0 = bottom scan-line (src/Global/RenderPin.cu:91)   */
+    RT_BUFFER_RADIANCE    = 1, /* float3 per pixel, mean over samples before gamma               */
+    RT_BUFFER_PRIMARY_T   = 2, /* float per pixel, +inf on miss                                   */
+    RT_BUFFER_PRIMARY_INSTANCE = 3, /* int32 per pixel, -1 on miss                                */
+    RT_BUFFER_PRIMARY_PRIM     = 4  /* int32 per pixel: (type << 28) | index, -1 on miss          */
+};
+
+typedef struct rt_ctx rt_ctx;
+
+/* ---- life cycle -------------------------------------------------------------------------- */
+int  rt_create(rt_ctx **out, int cuda_device, uint32_t flags);
+/* Renderer::cleanup  include/Global/Renderer.cuh:143-145, src/Global/Renderer.cu:368-392 */
+int  rt_cleanup(rt_ctx *ctx);
+const char *rt_last_error(const rt_ctx *ctx);
+const char *rt_version(void);
+/* sizeof() of a struct of this header by name ("rt_triangle", ...), 0 if unknown: lets an FFI binding
+ * verify its mirror of the layouts at load time.                                                   */
+size_t rt_struct_size(const char *struct_name);
+
+/* ---- scene commits (inputs are copied; caller keeps ownership) ----------------------------- */
+/* Renderer::commitGeometryData  include/Global/Renderer.cuh:116, src/Global/Renderer.cu:9-43 */
+int rt_commit_geometry(rt_ctx *ctx,
+                       const rt_sphere *spheres, size_t sphere_count,
+                       const rt_parallelogram *parallelograms, size_t parallelogram_count,
+                       const rt_triangle *triangles, size_t triangle_count);
+/* Renderer::commitMaterialData  include/Global/Renderer.cuh:119, src/Global/Renderer.cu:45-69 */
+int rt_commit_materials(rt_ctx *ctx,
+                        const rt_rough *roughs, size_t rough_count,
+                        const rt_metal *metals, size_t metal_count);
+int rt_commit_dielectrics(rt_ctx *ctx, const rt_dielectric *dielectrics, size_t count); /* extension */
+/* Renderer::configureInstances  include/Global/Renderer.cuh:123-126, src/Global/Renderer.cu:71-121.
+ * initial_xforms may be NULL (identity) — the callback, if given, is invoked with frame 0.      */
+int rt_configure_instances(rt_ctx *ctx, const rt_instance_desc *instances, size_t instance_count,
+                           const rt_instance_xform *initial_xforms, rt_update_cb update, void *user);
+/* Renderer::buildAccelerationStructure  include/Global/Renderer.cuh:129-130, src/Global/Renderer.cu:123-155.
+ * Device LBVH build of every BLAS (one per distinct (type, first_prim, prim_count)) + TLAS.       */
+int rt_build_acceleration_structure(rt_ctx *ctx);
+int rt_get_build_stats(const rt_ctx *ctx, rt_build_stats *out);
+/* Renderer::configureCamera  include/Global/Renderer.cuh:133, src/Global/Renderer.cu:157-178 */
+int rt_configure_camera(rt_ctx *ctx, const rt_window *window, const rt_camera_input *camera);
+
+/* ---- per frame ---------------------------------------------------------------------------
+ * One iteration of Renderer::startRender's loop (src/Global/Renderer.cu:232-338) minus SDL/GL:
+ * update callback -> instance transforms -> TLAS rebuild -> render kernel(s) -> framebuffer.
+ * `seed` replaces clock64() in curand_init(pixelIndex ^ clock64(), pixelIndex, 0) (src/Global/Kernel.cu:114). */
+int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_out *out);
+/* Set instance transforms directly (no callback); takes effect at the next rt_render_frame.       */
+int rt_set_instance_xforms(rt_ctx *ctx, const rt_instance_xform *xforms, size_t instance_count);
+
+/* Headless replacement of the CUDA-GL surface (src/Global/SDL_OpenGLWindow.cu:258-270):
+ * copy a framebuffer plane to host memory.  Rows are bottom-up like the reference surface.         */
+int rt_read_framebuffer(rt_ctx *ctx, int kind, void *host_dst, size_t dst_bytes);
+/* Device pointer of a plane (for NCCL / peer access by the caller); size in bytes via *bytes.      */
+int rt_framebuffer_device_ptr(rt_ctx *ctx, int kind, void **dev_ptr, size_t *bytes);
+/* Write the RGBA8 plane as a binary PPM (top-down, flipped) — the headless "display".              */
+int rt_write_ppm(rt_ctx *ctx, const char *path);
+
+/* ---- multi-GPU image-tile sharding ---------------------------------------------------------
+ * This context renders only tile rows t with (t % world) == rank, a tile being `tile_rows` scan-lines.
+ * Pixel RNG streams are keyed by the global pixel index, so the union over ranks is bit-identical to
+ * a single-GPU frame.  Shard planes are packed: local tile k holds global tile k*world + rank.
+ * If peer_rgba8 != NULL the final RGBA8 texels are stored straight into that (peer-mapped, full-size)
+ * buffer instead of the local packed plane (fused gather over NVLink).                              */
+int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_rows, void *peer_rgba8);
+
+/* ---- acceleration-structure introspection (parity tests) ----------------------------------- */
+/* Binary LBVH of BLAS `blas_index` as built on the device: sorted Morton keys, sorted primitive
+ * ids, Karras child/parent arrays.  Any output pointer may be NULL; *n_prims is always written.
+ * Children: value >= 0 -> internal node, value < 0 -> leaf ~value (position in sorted order).      */
+int rt_read_lbvh(rt_ctx *ctx, size_t blas_index, size_t *n_prims,
+                 uint64_t *sorted_keys, uint32_t *sorted_prim_ids,
+                 int32_t *left, int32_t *right, int32_t *parent, float *node_bounds /* 6 per node */);
+
+/* ---- VTK particle-mesh series (Renderer::configureVTKFiles include/Global/Renderer.cuh:113,
+ *      src/Global/Renderer.cu:394-443; VTKReader src/Global/VTKReader.cu:16-220) ------------------ */
+int rt_load_vtk_series(rt_ctx *ctx, const char *series_path, size_t *frame_count);
+int rt_set_vtk_frame(rt_ctx *ctx, size_t frame);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB200_H */

@@ -1,0 +1,139 @@
+"""ctypes loader for the CPU checkers (oracle/oracle_api.h).  TEST INFRASTRUCTURE ONLY:
+imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs."""
+from __future__ import annotations
+
+import ctypes as C
+import importlib
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+pkg = importlib.import_module("real-time-gpu-ray-tracer_b200.abi")
+abi = pkg
+
+PORT_PATH = os.path.join(HERE, "liboracle_port.so")
+REF_PATH = os.path.join(HERE, "_ref", "libref_oracle.so")
+
+
+class OracleScene(C.Structure):
+    _fields_ = [("spheres", C.c_void_p), ("sphere_count", C.c_size_t),
+                ("parallelograms", C.c_void_p), ("parallelogram_count", C.c_size_t),
+                ("triangles", C.c_void_p), ("triangle_count", C.c_size_t),
+                ("roughs", C.c_void_p), ("rough_count", C.c_size_t),
+                ("metals", C.c_void_p), ("metal_count", C.c_size_t),
+                ("instances", C.c_void_p), ("xforms", C.c_void_p), ("instance_count", C.c_size_t),
+                ("window", abi.Window), ("camera", abi.CameraInput), ("build_seed", C.c_uint64)]
+
+
+class OracleTiming(C.Structure):
+    _fields_ = [("blas_build_ms", C.c_double), ("xform_ms", C.c_double), ("tlas_build_ms", C.c_double),
+                ("blas_nodes", C.c_uint64), ("tlas_nodes", C.c_uint64)]
+
+
+class Oracle:
+    """One of the two checkers: kind = 'port' (restatement) or 'ref' (reference sources compiled as C++)."""
+
+    def __init__(self, kind: str = "port"):
+        path = PORT_PATH if kind == "port" else REF_PATH
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"{path} not built (make -C oracle {kind})")
+        self.kind = kind
+        self.prefix = "port_" if kind == "port" else "ref_"
+        self.lib = C.CDLL(path)
+        vp, sz, u64, i32 = C.c_void_p, C.c_size_t, C.c_uint64, C.c_int
+        self._fn("create", [C.POINTER(OracleScene), C.POINTER(OracleTiming)], vp)
+        self._fn("destroy", [vp], None)
+        self._fn("render", [vp, u64, i32, i32, i32, vp, vp, C.POINTER(u64)], None)
+        self._fn("primary", [vp, u64, i32, i32, i32, vp, vp, vp], None)
+        self._fn("trace", [vp, vp, sz, C.c_float, vp, vp, vp, vp], None)
+        self._fn("camera", [vp, vp], None)
+        self._fn("instances", [vp, vp], None)
+        self._fn("uniforms", [u64, u64, sz, vp], None)
+        self._fn("describe", [], C.c_char_p)
+        if kind == "ref":
+            self._fn("render_kernel", [vp, u64, i32, vp], None)
+
+    def _fn(self, name, argtypes, restype):
+        f = getattr(self.lib, self.prefix + name)
+        f.argtypes = argtypes
+        f.restype = restype
+        setattr(self, "_" + name, f)
+
+    def describe(self) -> str:
+        return self._describe().decode()
+
+    def uniforms(self, seed: int, subsequence: int, n: int) -> np.ndarray:
+        out = np.zeros(n, np.float32)
+        self._uniforms(seed, subsequence, n, abi.ptr(out))
+        return out
+
+    def scene(self, sc, build_seed: int = 1234) -> "OracleSceneHandle":
+        return OracleSceneHandle(self, sc, build_seed)
+
+
+class OracleSceneHandle:
+    def __init__(self, oracle: Oracle, sc, build_seed: int):
+        self.o = oracle
+        self.sc = sc  # keeps the numpy arrays alive
+        s = OracleScene(abi.ptr(sc.spheres), len(sc.spheres), abi.ptr(sc.parallelograms), len(sc.parallelograms),
+                        abi.ptr(sc.triangles), len(sc.triangles), abi.ptr(sc.roughs), len(sc.roughs),
+                        abi.ptr(sc.metals), len(sc.metals), abi.ptr(sc.instances), abi.ptr(sc.xforms), len(sc.instances),
+                        sc.window(), sc.camera_input(), build_seed)
+        self.timing = OracleTiming()
+        self.h = oracle._create(C.byref(s), C.byref(self.timing))
+        self.W, self.H = sc.width, sc.height
+
+    def close(self):
+        if self.h:
+            self.o._destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def render(self, seed: int, y0: int = 0, y1: int | None = None, threads: int | None = None, rgba8=True, radiance=True):
+        y1 = self.H if y1 is None else y1
+        threads = threads or os.cpu_count() or 1
+        img = np.zeros((self.H, self.W, 4), np.uint8) if rgba8 else None
+        rad = np.zeros((self.H, self.W, 3), np.float32) if radiance else None
+        rays = C.c_uint64(0)
+        self.o._render(self.h, seed, y0, y1, threads, abi.ptr(img), abi.ptr(rad), C.byref(rays))
+        return img, rad, rays.value
+
+    def render_kernel(self, seed: int, threads: int | None = None):
+        img = np.zeros((self.H, self.W, 4), np.uint8)
+        self.o._render_kernel(self.h, seed, threads or os.cpu_count() or 1, abi.ptr(img))
+        return img
+
+    def primary(self, seed: int, y0: int = 0, y1: int | None = None, threads: int | None = None):
+        y1 = self.H if y1 is None else y1
+        t = np.full((self.H, self.W), np.inf, np.float32)
+        inst = np.full((self.H, self.W), -1, np.int32)
+        prim = np.full((self.H, self.W), -1, np.int32)
+        self.o._primary(self.h, seed, y0, y1, threads or os.cpu_count() or 1, abi.ptr(t), abi.ptr(inst), abi.ptr(prim))
+        return t, inst, prim
+
+    def trace(self, rays: np.ndarray, tmin: float = 0.001):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        n = len(rays)
+        t = np.zeros(n, np.float32)
+        inst = np.zeros(n, np.int32)
+        prim = np.zeros(n, np.int32)
+        nrm = np.zeros((n, 3), np.float32)
+        self.o._trace(self.h, abi.ptr(rays), n, tmin, abi.ptr(t), abi.ptr(inst), abi.ptr(prim), abi.ptr(nrm))
+        return t, inst, prim, nrm
+
+    def camera(self) -> np.ndarray:
+        out = np.zeros(20, np.float32)
+        self.o._camera(self.h, abi.ptr(out))
+        return out
+
+    def instances(self) -> np.ndarray:
+        out = np.zeros((len(self.sc.instances), 33), np.float32)
+        self.o._instances(self.h, abi.ptr(out))
+        return out

@@ -1,0 +1,138 @@
+"""Host-side mirror of the reference's public API (renderer::Renderer, include/Global/Renderer.cuh:109-146)
+over the C-ABI of librtb200.so.  Method names follow the reference; startRender's loop body is
+``renderFrame`` (one iteration, src/Global/Renderer.cu:232-338, headless)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+class RtError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"rtb200 error {code}: {msg}")
+        self.code = code
+
+
+class Renderer:
+    def __init__(self, device: int = 0, flags: int = 0):
+        self.lib = abi.load_library()
+        self.ctx = C.c_void_p()
+        rc = self.lib.rt_create(C.byref(self.ctx), device, flags)
+        if rc != 0:
+            raise RtError(rc, "rt_create failed (no CUDA device?)")
+        self._keep = []
+        self.width = self.height = 0
+
+    # -- plumbing ------------------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != 0:
+            raise RtError(rc, (self.lib.rt_last_error(self.ctx) or b"").decode())
+
+    # -- Renderer::commitGeometryData ------------------------------------------------------------
+    def commitGeometryData(self, spheres=None, parallelograms=None, triangles=None):
+        n = lambda a: 0 if a is None else len(a)
+        self._check(self.lib.rt_commit_geometry(self.ctx, abi.ptr(spheres), n(spheres), abi.ptr(parallelograms), n(parallelograms),
+                                                abi.ptr(triangles), n(triangles)))
+
+    # -- Renderer::commitMaterialData ------------------------------------------------------------
+    def commitMaterialData(self, roughs=None, metals=None, dielectrics=None):
+        n = lambda a: 0 if a is None else len(a)
+        self._check(self.lib.rt_commit_materials(self.ctx, abi.ptr(roughs), n(roughs), abi.ptr(metals), n(metals)))
+        if dielectrics is not None and len(dielectrics):
+            self._check(self.lib.rt_commit_dielectrics(self.ctx, abi.ptr(dielectrics), len(dielectrics)))
+
+    # -- Renderer::configureInstances ------------------------------------------------------------
+    def configureInstances(self, instances: np.ndarray, xforms: np.ndarray | None = None, update=None):
+        """update(xforms_view: np.ndarray, frame: int) mutates the transform arguments in place
+        (the reference's updateInstances callback, include/Global/Renderer.cuh:94)."""
+        cb = None
+        if update is not None:
+            n_inst = len(instances)
+
+            def _cb(xf_ptr, n, frame, _user):
+                buf = (C.c_char * (n * abi.instance_xform_dt.itemsize)).from_address(xf_ptr)
+                update(np.frombuffer(buf, abi.instance_xform_dt, count=n), int(frame))
+            cb = abi.UPDATE_CB(_cb)
+            self._keep.append(cb)
+            assert n_inst >= 0
+        self._check(self.lib.rt_configure_instances(self.ctx, abi.ptr(instances), len(instances), abi.ptr(xforms),
+                                                    C.cast(cb, C.c_void_p) if cb else None, None))
+
+    # -- Renderer::buildAccelerationStructure ------------------------------------------------------
+    def buildAccelerationStructure(self) -> abi.BuildStats:
+        self._check(self.lib.rt_build_acceleration_structure(self.ctx))
+        st = abi.BuildStats()
+        self._check(self.lib.rt_get_build_stats(self.ctx, C.byref(st)))
+        return st
+
+    # -- Renderer::configureCamera ---------------------------------------------------------------
+    def configureCamera(self, window: abi.Window, camera: abi.CameraInput):
+        self.width, self.height = window.width, window.height
+        self._check(self.lib.rt_configure_camera(self.ctx, C.byref(window), C.byref(camera)))
+
+    def commitScene(self, sc, update=None):
+        """Convenience: the whole start-up sequence of src/Global/Main.cu:111-123 for a scenes.Scene."""
+        self.commitGeometryData(sc.spheres, sc.parallelograms, sc.triangles)
+        self.commitMaterialData(sc.roughs, sc.metals)
+        self.configureInstances(sc.instances, sc.xforms, update)
+        st = self.buildAccelerationStructure()
+        self.configureCamera(sc.window(), sc.camera_input())
+        return st
+
+    # -- one iteration of Renderer::startRender ----------------------------------------------------
+    def renderFrame(self, frame: int = 0, seed: int = 0x5EED) -> abi.FrameOut:
+        out = abi.FrameOut()
+        self._check(self.lib.rt_render_frame(self.ctx, frame, seed, C.byref(out)))
+        return out
+
+    def setInstanceTransforms(self, xforms: np.ndarray):
+        self._check(self.lib.rt_set_instance_xforms(self.ctx, abi.ptr(xforms), len(xforms)))
+
+    def setTileShard(self, rank: int, world: int, tile_rows: int = 8, peer_rgba8: int | None = None):
+        self._check(self.lib.rt_set_tile_shard(self.ctx, rank, world, tile_rows, peer_rgba8))
+
+    def devicePointer(self, kind: int):
+        p, n = C.c_void_p(), C.c_size_t()
+        self._check(self.lib.rt_framebuffer_device_ptr(self.ctx, kind, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def readFramebuffer(self, kind: int = abi.BUF_RGBA8, out: np.ndarray | None = None) -> np.ndarray:
+        _, nbytes = self.devicePointer(kind)
+        if out is None:
+            out = np.empty(nbytes, np.uint8)
+        self._check(self.lib.rt_read_framebuffer(self.ctx, kind, out.ctypes.data_as(C.c_void_p), out.nbytes))
+        dt = {abi.BUF_RGBA8: np.uint8, abi.BUF_RADIANCE: np.float32, abi.BUF_PRIMARY_T: np.float32,
+              abi.BUF_PRIMARY_INSTANCE: np.int32, abi.BUF_PRIMARY_PRIM: np.int32}[kind]
+        return out.view(dt)
+
+    def writePPM(self, path: str):
+        self._check(self.lib.rt_write_ppm(self.ctx, path.encode()))
+
+    def readLBVH(self, blas_index: int = 0):
+        n = C.c_size_t()
+        self._check(self.lib.rt_read_lbvh(self.ctx, blas_index, C.byref(n), None, None, None, None, None, None))
+        n = n.value
+        keys = np.zeros(n, np.uint64)
+        ids = np.zeros(n, np.uint32)
+        m = max(n - 1, 0)
+        left, right, parent = np.zeros(m, np.int32), np.zeros(m, np.int32), np.zeros(m, np.int32)
+        bounds = np.zeros((m, 6), np.float32)
+        nn = C.c_size_t()
+        self._check(self.lib.rt_read_lbvh(self.ctx, blas_index, C.byref(nn), abi.ptr(keys), abi.ptr(ids), abi.ptr(left), abi.ptr(right),
+                                          abi.ptr(parent), abi.ptr(bounds)))
+        return dict(keys=keys, prim_ids=ids, left=left, right=right, parent=parent, bounds=bounds)
+
+    # -- Renderer::cleanup -----------------------------------------------------------------------
+    def cleanup(self):
+        if self.ctx:
+            self.lib.rt_cleanup(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.cleanup()
+        except Exception:
+            pass

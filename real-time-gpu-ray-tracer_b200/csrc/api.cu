@@ -1,0 +1,439 @@
+// api.cu — the C-ABI of include/rtb200.h: an opaque context that owns every host/device resource, mirrors
+// the reference's Renderer::* entry points and returns error codes instead of exiting.
+#include "../../include/rtb200.h"
+
+#include "build.h"
+#include "host_scene.h"
+#include "render.h"
+#include "vtk_reader.h"
+
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <string>
+#include <tuple>
+#include <vector>
+
+struct rt_ctx {
+    int device = 0;
+    uint32_t flags = 0;
+    std::string err;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[5] = {};
+    int sm_count = 148;
+
+    HostScene hs;                            // host half: validated inputs + device-layout records
+    rt_update_cb update_cb = nullptr;
+    void *update_user = nullptr;
+
+    // device scene
+    DeviceBuffer<float> d_tri_verts;
+    DeviceBuffer<TriShade> d_tri_shade;
+    DeviceBuffer<SphereD> d_spheres;
+    DeviceBuffer<QuadD> d_quads;
+    DeviceBuffer<float4> d_roughs, d_metals, d_dielectrics;
+    DeviceBuffer<InstanceD> d_instances;
+    DeviceBuffer<InstanceXformIn> d_xform_in;
+    DeviceBuffer<float4> d_wcentroid;
+    PinnedBuffer<InstanceXformIn> h_xform_in;
+    LbvhBuilder blas, tlas;
+    bool geometry_committed = false, materials_committed = false, instances_configured = false, built = false, camera_set = false;
+    rt_build_stats build_stats{};
+
+    // camera / frame
+    uint32_t shard_rank = 0, shard_world = 1, tile_rows = 8, local_rows = 0;
+    void *peer_rgba8 = nullptr;
+    DeviceBuffer<uint8_t> d_rgba8;
+    DeviceBuffer<float> d_radiance, d_aov_t;
+    DeviceBuffer<int> d_aov_inst, d_aov_prim;
+    DeviceBuffer<RngState> d_rng;
+    DeviceBuffer<unsigned long long> d_counters;   // [0] rays, [1] overflow flag (low word)
+    PinnedBuffer<unsigned long long> h_counters;
+
+    // VTK series
+    std::unique_ptr<VtkSeries> vtk;
+};
+
+namespace {
+
+int fail(rt_ctx *ctx, int code, const std::string &msg) {
+    if (ctx) ctx->err = msg;
+    return code;
+}
+
+#define RT_API_BEGIN(ctx)                                   \
+    if (!(ctx)) return RT_ERR_ARGUMENT;                     \
+    try {                                                   \
+        if (cudaSetDevice((ctx)->device) != cudaSuccess) return fail(ctx, RT_ERR_CUDA, "cudaSetDevice failed");
+#define RT_API_END(ctx)                                     \
+    } catch (const CudaError &e) {                          \
+        cudaGetLastError();                                 \
+        return fail(ctx, RT_ERR_CUDA, e.what());            \
+    } catch (const std::exception &e) {                     \
+        return fail(ctx, RT_ERR_ARGUMENT, e.what());        \
+    }                                                       \
+    return RT_OK;
+
+void compute_local_rows(rt_ctx *c) {
+    const uint32_t H = c->hs.window.height;
+    const uint32_t tiles = (H + c->tile_rows - 1) / c->tile_rows;
+    const uint32_t local_tiles = c->shard_rank < tiles ? (tiles - c->shard_rank + c->shard_world - 1) / c->shard_world : 0;
+    c->local_rows = c->shard_world == 1 ? H : local_tiles * c->tile_rows;
+}
+
+void alloc_frame(rt_ctx *c) {
+    compute_local_rows(c);
+    const size_t px = (size_t) c->hs.window.width * c->local_rows;
+    c->d_rgba8.reserve(px * 4 + 4);
+    c->d_radiance.reserve(px * 3 + 3);
+    c->d_rng.reserve(px + 1);
+    if (c->flags & RT_FLAG_RECORD_PRIMARY_AOV) { c->d_aov_t.reserve(px + 1); c->d_aov_inst.reserve(px + 1); c->d_aov_prim.reserve(px + 1); }
+    c->d_counters.reserve(2);
+    c->h_counters.reserve(2);
+}
+
+void update_instances_and_tlas(rt_ctx *c) {
+    const int n = (int) c->hs.inst_desc.size();
+    c->hs.fill_xform_in(c->h_xform_in.get(), c->blas.seg_root_host);
+    CUDA_CHECK(cudaMemcpyAsync(c->d_xform_in.get(), c->h_xform_in.get(), (size_t) n * sizeof(InstanceXformIn), cudaMemcpyHostToDevice, c->stream));
+    launch_instance_update(c->d_xform_in.get(), n, c->d_instances.get(), c->tlas.prim_lo(), c->tlas.prim_hi(), c->d_wcentroid.get(),
+                           c->tlas.bounds(), c->stream);
+    c->tlas.build_tlas(n, morton_bits_for((size_t) n), c->stream, c->sm_count);
+}
+
+} // namespace
+
+extern "C" {
+
+const char *rt_version(void) { return "rtb200 0.1 (sm_100a)"; }
+
+size_t rt_struct_size(const char *name) {
+    if (!name) return 0;
+#define RT_SZ(T) if (strcmp(name, #T) == 0) return sizeof(T);
+    RT_SZ(rt_vec3) RT_SZ(rt_sphere) RT_SZ(rt_parallelogram) RT_SZ(rt_triangle) RT_SZ(rt_rough) RT_SZ(rt_metal) RT_SZ(rt_dielectric)
+    RT_SZ(rt_instance_desc) RT_SZ(rt_instance_xform) RT_SZ(rt_window) RT_SZ(rt_camera_input) RT_SZ(rt_frame_out) RT_SZ(rt_build_stats)
+#undef RT_SZ
+    return 0;
+}
+
+int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
+    if (!out) return RT_ERR_ARGUMENT;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || cuda_device < 0 || cuda_device >= count) { cudaGetLastError(); return RT_ERR_CUDA; }
+    if (cudaSetDevice(cuda_device) != cudaSuccess) return RT_ERR_CUDA;
+    rt_ctx *c = new rt_ctx();
+    c->device = cuda_device;
+    c->flags = flags;
+    c->hs.flags = flags;
+    try {
+        CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        for (auto &e: c->ev) CUDA_CHECK(cudaEventCreate(&e));
+        CUDA_CHECK(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, cuda_device));
+    } catch (const std::exception &) {
+        delete c;
+        return RT_ERR_CUDA;
+    }
+    *out = c;
+    return RT_OK;
+}
+
+int rt_cleanup(rt_ctx *ctx) {
+    if (!ctx) return RT_ERR_ARGUMENT;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) { cudaStreamSynchronize(ctx->stream); }
+    for (auto &e: ctx->ev) if (e) cudaEventDestroy(e);
+    cudaStream_t s = ctx->stream;
+    delete ctx;   // frees device buffers
+    if (s) cudaStreamDestroy(s);
+    return RT_OK;
+}
+
+const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int rt_commit_geometry(rt_ctx *ctx, const rt_sphere *spheres, size_t sphere_count, const rt_parallelogram *parallelograms,
+                       size_t parallelogram_count, const rt_triangle *triangles, size_t triangle_count) {
+    RT_API_BEGIN(ctx)
+    const std::string e = ctx->hs.commit_geometry(spheres, sphere_count, parallelograms, parallelogram_count, triangles, triangle_count);
+    if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    ctx->built = false;
+    ctx->d_spheres.upload(ctx->hs.sphere_rec.data(), ctx->hs.sphere_rec.size(), ctx->stream);
+    ctx->d_quads.upload(ctx->hs.quad_rec.data(), ctx->hs.quad_rec.size(), ctx->stream);
+    ctx->d_tri_verts.upload(ctx->hs.tri_verts.data(), ctx->hs.tri_verts.size(), ctx->stream);
+    ctx->d_tri_shade.upload(ctx->hs.tri_shade.data(), ctx->hs.tri_shade.size(), ctx->stream);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    ctx->geometry_committed = true;
+    RT_API_END(ctx)
+}
+
+int rt_commit_materials(rt_ctx *ctx, const rt_rough *roughs, size_t rough_count, const rt_metal *metals, size_t metal_count) {
+    RT_API_BEGIN(ctx)
+    const std::string e = ctx->hs.commit_materials(roughs, rough_count, metals, metal_count);
+    if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    ctx->d_roughs.upload(ctx->hs.roughs.data(), ctx->hs.roughs.size(), ctx->stream);
+    ctx->d_metals.upload(ctx->hs.metals.data(), ctx->hs.metals.size(), ctx->stream);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    ctx->materials_committed = true;
+    RT_API_END(ctx)
+}
+
+int rt_commit_dielectrics(rt_ctx *ctx, const rt_dielectric *d, size_t count) {
+    RT_API_BEGIN(ctx)
+    const std::string e = ctx->hs.commit_dielectrics(d, count);
+    if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    ctx->d_dielectrics.upload(ctx->hs.dielectrics.data(), ctx->hs.dielectrics.size(), ctx->stream);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    RT_API_END(ctx)
+}
+
+int rt_configure_instances(rt_ctx *ctx, const rt_instance_desc *instances, size_t instance_count, const rt_instance_xform *initial_xforms,
+                           rt_update_cb update, void *user) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->geometry_committed) return fail(ctx, RT_ERR_STATE, "rt_configure_instances: commit geometry first");
+    const std::string e = ctx->hs.configure_instances(instances, instance_count, initial_xforms);
+    if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    ctx->update_cb = update;
+    ctx->update_user = user;
+    if (update) update(ctx->hs.xforms.data(), instance_count, 0, user);   // reference src/Global/Renderer.cu:111
+    ctx->instances_configured = true;
+    ctx->built = false;
+    RT_API_END(ctx)
+}
+
+int rt_set_instance_xforms(rt_ctx *ctx, const rt_instance_xform *xforms, size_t instance_count) {
+    RT_API_BEGIN(ctx)
+    if (!xforms || instance_count != ctx->hs.xforms.size()) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_instance_xforms: count mismatch");
+    std::copy(xforms, xforms + instance_count, ctx->hs.xforms.begin());
+    RT_API_END(ctx)
+}
+
+int rt_build_acceleration_structure(rt_ctx *ctx) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->geometry_committed || !ctx->instances_configured) return fail(ctx, RT_ERR_STATE, "rt_build_acceleration_structure: commit geometry and instances first");
+    HostScene &hs = ctx->hs;
+    const std::string e = hs.plan_blas();
+    if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    const size_t n_inst = hs.inst_desc.size();
+    const GeometryD geo{ctx->d_tri_verts.get(), ctx->d_spheres.get(), ctx->d_quads.get()};
+    const size_t n_prims = hs.seg_offset.back();
+    CUDA_CHECK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    ctx->blas.build_blas(geo, hs.seg_offset, hs.seg_type, hs.seg_first, morton_bits_for(n_prims / std::max<size_t>(1, hs.seg_type.size())),
+                         ctx->stream, ctx->sm_count);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    // TLAS (also rebuilt every frame)
+    ctx->d_instances.reserve(n_inst);
+    ctx->d_xform_in.reserve(n_inst);
+    ctx->d_wcentroid.reserve(n_inst);
+    ctx->h_xform_in.reserve(n_inst);
+    ctx->tlas.prepare_tlas((int) n_inst);
+    update_instances_and_tlas(ctx);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    rt_build_stats &st = ctx->build_stats;
+    CUDA_CHECK(cudaEventElapsedTime(&st.blas_ms, ctx->ev[0], ctx->ev[1]));
+    CUDA_CHECK(cudaEventElapsedTime(&st.tlas_ms, ctx->ev[1], ctx->ev[2]));
+    st.blas_count = hs.seg_type.size();
+    st.primitive_count = n_prims;
+    st.lbvh_nodes = n_prims > 0 ? n_prims - 1 : 0;
+    st.wide_nodes = st.lbvh_nodes;
+    st.node_bytes = ctx->blas.node_bytes() + ctx->tlas.node_bytes();
+    st.prim_bytes = hs.prim_bytes();
+    st.kernel_launches = ctx->blas.launches + ctx->tlas.launches + 2;
+    ctx->built = true;
+    RT_API_END(ctx)
+}
+
+int rt_get_build_stats(const rt_ctx *ctx, rt_build_stats *out) {
+    if (!ctx || !out) return RT_ERR_ARGUMENT;
+    *out = ctx->build_stats;
+    return RT_OK;
+}
+
+int rt_configure_camera(rt_ctx *ctx, const rt_window *window, const rt_camera_input *camera) {
+    RT_API_BEGIN(ctx)
+    if (!window || !camera) return fail(ctx, RT_ERR_ARGUMENT, "rt_configure_camera: null argument");
+    const std::string e = ctx->hs.configure_camera(*window, *camera);
+    if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    alloc_frame(ctx);
+    ctx->camera_set = true;
+    RT_API_END(ctx)
+}
+
+int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_rows, void *peer_rgba8) {
+    RT_API_BEGIN(ctx)
+    if (world == 0 || rank >= world || tile_rows == 0) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_tile_shard: bad rank/world/tile_rows");
+    ctx->shard_rank = rank; ctx->shard_world = world; ctx->tile_rows = tile_rows; ctx->peer_rgba8 = peer_rgba8;
+    if (ctx->camera_set) alloc_frame(ctx);
+    RT_API_END(ctx)
+}
+
+int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_out *out) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->built || !ctx->camera_set || !ctx->materials_committed) return fail(ctx, RT_ERR_STATE, "rt_render_frame: scene not built / camera or materials missing");
+    cudaStream_t s = ctx->stream;
+    if (ctx->update_cb) ctx->update_cb(ctx->hs.xforms.data(), ctx->hs.xforms.size(), (size_t) frame_index, ctx->update_user);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[0], s));
+    update_instances_and_tlas(ctx);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[1], s));
+
+    SceneD sc{};
+    sc.tlas_nodes = ctx->tlas.nodes();
+    sc.blas_nodes = ctx->blas.nodes();
+    sc.instances = ctx->d_instances.get();
+    sc.leaf_tris = ctx->blas.leaf_tris();
+    sc.leaf_prims = ctx->blas.leaf_prims();
+    sc.tri_shade = ctx->d_tri_shade.get();
+    sc.spheres = ctx->d_spheres.get();
+    sc.quads = ctx->d_quads.get();
+    sc.roughs = ctx->d_roughs.get();
+    sc.metals = ctx->d_metals.get();
+    sc.dielectrics = ctx->d_dielectrics.get();
+    sc.tlas_root_ref = ctx->hs.inst_desc.size() > 1 ? 0 : make_leaf_ref(0u, 0u);
+
+    FrameD fr{};
+    fr.rgba8 = ctx->peer_rgba8 ? (uint8_t *) ctx->peer_rgba8 : ctx->d_rgba8.get();
+    fr.rgba8_is_full_frame = ctx->peer_rgba8 ? 1u : 0u;
+    fr.radiance = ctx->d_radiance.get();
+    const bool aov = ctx->flags & RT_FLAG_RECORD_PRIMARY_AOV;
+    fr.aov_t = aov ? ctx->d_aov_t.get() : nullptr;
+    fr.aov_inst = aov ? ctx->d_aov_inst.get() : nullptr;
+    fr.aov_prim = aov ? ctx->d_aov_prim.get() : nullptr;
+    fr.rng = ctx->d_rng.get();
+    fr.ray_counter = ctx->d_counters.get();
+    fr.overflow_flag = reinterpret_cast<unsigned int *>(ctx->d_counters.get() + 1);
+    fr.shard_rank = ctx->shard_rank; fr.shard_world = ctx->shard_world; fr.tile_rows = ctx->tile_rows; fr.local_rows = ctx->local_rows;
+
+    CUDA_CHECK(cudaMemsetAsync(ctx->d_counters.get(), 0, 2 * sizeof(unsigned long long), s));
+    launch_rng_init(ctx->d_rng.get(), seed, ctx->hs.cam, fr, s);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[2], s));
+    launch_render(sc, ctx->hs.cam, fr, s);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[3], s));
+    CUDA_CHECK(cudaMemcpyAsync(ctx->h_counters.get(), ctx->d_counters.get(), 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    if (out) {
+        memset(out, 0, sizeof(*out));
+        out->rays = ctx->h_counters.get()[0];
+        out->stack_overflow = (uint32_t) ctx->h_counters.get()[1];
+        uint64_t rows = 0;
+        for (uint32_t ly = 0; ly < ctx->local_rows; ly++) {
+            const uint32_t gy = ((ly / ctx->tile_rows) * ctx->shard_world + ctx->shard_rank) * ctx->tile_rows + (ly % ctx->tile_rows);
+            if (gy < ctx->hs.cam.height) rows++;
+        }
+        out->primary_rays = rows * ctx->hs.cam.width * ctx->hs.cam.sqrtSamples * ctx->hs.cam.sqrtSamples;
+        CUDA_CHECK(cudaEventElapsedTime(&out->render_ms, ctx->ev[0], ctx->ev[3]));
+        CUDA_CHECK(cudaEventElapsedTime(&out->tlas_ms, ctx->ev[0], ctx->ev[1]));
+        CUDA_CHECK(cudaEventElapsedTime(&out->rng_ms, ctx->ev[1], ctx->ev[2]));
+        CUDA_CHECK(cudaEventElapsedTime(&out->trace_ms, ctx->ev[2], ctx->ev[3]));
+        out->kernel_launches = ctx->tlas.launches + 2 /*instance update*/ + 2 /*rng + render*/;
+    }
+    RT_API_END(ctx)
+}
+
+static int plane_info(rt_ctx *ctx, int kind, void **ptr, size_t *bytes) {
+    const size_t px = (size_t) ctx->hs.window.width * ctx->local_rows;
+    switch (kind) {
+        case RT_BUFFER_RGBA8: *ptr = ctx->d_rgba8.get(); *bytes = px * 4; return RT_OK;
+        case RT_BUFFER_RADIANCE: *ptr = ctx->d_radiance.get(); *bytes = px * 12; return RT_OK;
+        case RT_BUFFER_PRIMARY_T: *ptr = ctx->d_aov_t.get(); *bytes = px * 4; break;
+        case RT_BUFFER_PRIMARY_INSTANCE: *ptr = ctx->d_aov_inst.get(); *bytes = px * 4; break;
+        case RT_BUFFER_PRIMARY_PRIM: *ptr = ctx->d_aov_prim.get(); *bytes = px * 4; break;
+        default: return fail(ctx, RT_ERR_ARGUMENT, "unknown buffer kind");
+    }
+    if (!(ctx->flags & RT_FLAG_RECORD_PRIMARY_AOV)) return fail(ctx, RT_ERR_STATE, "primary AOVs need RT_FLAG_RECORD_PRIMARY_AOV");
+    return RT_OK;
+}
+
+int rt_framebuffer_device_ptr(rt_ctx *ctx, int kind, void **dev_ptr, size_t *bytes) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->camera_set) return fail(ctx, RT_ERR_STATE, "configure the camera first");
+    void *p = nullptr;
+    size_t n = 0;
+    const int rc = plane_info(ctx, kind, &p, &n);
+    if (rc != RT_OK) return rc;
+    if (dev_ptr) *dev_ptr = p;
+    if (bytes) *bytes = n;
+    RT_API_END(ctx)
+}
+
+int rt_read_framebuffer(rt_ctx *ctx, int kind, void *host_dst, size_t dst_bytes) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->camera_set) return fail(ctx, RT_ERR_STATE, "configure the camera first");
+    void *p = nullptr;
+    size_t n = 0;
+    const int rc = plane_info(ctx, kind, &p, &n);
+    if (rc != RT_OK) return rc;
+    if (!host_dst || dst_bytes < n) return fail(ctx, RT_ERR_ARGUMENT, "rt_read_framebuffer: destination too small");
+    CUDA_CHECK(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    RT_API_END(ctx)
+}
+
+int rt_write_ppm(rt_ctx *ctx, const char *path) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->camera_set || !path) return fail(ctx, RT_ERR_STATE, "rt_write_ppm: no frame");
+    const uint32_t W = ctx->hs.window.width, H = ctx->local_rows;
+    std::vector<uint8_t> img((size_t) W * H * 4);
+    CUDA_CHECK(cudaMemcpyAsync(img.data(), ctx->d_rgba8.get(), img.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    FILE *f = fopen(path, "wb");
+    if (!f) return fail(ctx, RT_ERR_IO, std::string("cannot open ") + path);
+    fprintf(f, "P6\n%u %u\n255\n", W, H);
+    std::vector<uint8_t> row((size_t) W * 3);
+    for (uint32_t y = 0; y < H; y++) {   // row 0 of the framebuffer is the bottom scan-line: flip
+        const uint8_t *src = &img[(size_t) (H - 1 - y) * W * 4];
+        for (uint32_t x = 0; x < W; x++) { row[3 * x] = src[4 * x]; row[3 * x + 1] = src[4 * x + 1]; row[3 * x + 2] = src[4 * x + 2]; }
+        fwrite(row.data(), 1, row.size(), f);
+    }
+    fclose(f);
+    RT_API_END(ctx)
+}
+
+int rt_read_lbvh(rt_ctx *ctx, size_t which, size_t *n_prims, uint64_t *sorted_keys, uint32_t *sorted_prim_ids, int32_t *left, int32_t *right,
+                 int32_t *parent, float *node_bounds) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->built) return fail(ctx, RT_ERR_STATE, "rt_read_lbvh: build first");
+    if (which > 1) return fail(ctx, RT_ERR_ARGUMENT, "rt_read_lbvh: which = 0 (BLAS batch) or 1 (TLAS)");
+    LbvhBuilder &b = which == 0 ? ctx->blas : ctx->tlas;
+    const size_t n = (size_t) b.n_prims();
+    if (n_prims) *n_prims = n;
+    const size_t m = n > 1 ? n - 1 : 0;
+    cudaStream_t s = ctx->stream;
+    if (sorted_keys) CUDA_CHECK(cudaMemcpyAsync(sorted_keys, b.sorted_keys(), n * 8, cudaMemcpyDeviceToHost, s));
+    if (sorted_prim_ids) CUDA_CHECK(cudaMemcpyAsync(sorted_prim_ids, b.sorted_vals(), n * 4, cudaMemcpyDeviceToHost, s));
+    if (left && m) CUDA_CHECK(cudaMemcpyAsync(left, b.left(), m * 4, cudaMemcpyDeviceToHost, s));
+    if (right && m) CUDA_CHECK(cudaMemcpyAsync(right, b.right(), m * 4, cudaMemcpyDeviceToHost, s));
+    if (parent && m) CUDA_CHECK(cudaMemcpyAsync(parent, b.parent(), m * 4, cudaMemcpyDeviceToHost, s));
+    if (node_bounds && m) {
+        std::vector<float4> lo(m), hi(m);
+        CUDA_CHECK(cudaMemcpyAsync(lo.data(), b.node_lo(), m * 16, cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(hi.data(), b.node_hi(), m * 16, cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        for (size_t i = 0; i < m; i++) {
+            node_bounds[6 * i] = lo[i].x; node_bounds[6 * i + 1] = lo[i].y; node_bounds[6 * i + 2] = lo[i].z;
+            node_bounds[6 * i + 3] = hi[i].x; node_bounds[6 * i + 4] = hi[i].y; node_bounds[6 * i + 5] = hi[i].z;
+        }
+    }
+    CUDA_CHECK(cudaStreamSynchronize(s));
+    RT_API_END(ctx)
+}
+
+int rt_load_vtk_series(rt_ctx *ctx, const char *series_path, size_t *frame_count) {
+    RT_API_BEGIN(ctx)
+    if (!series_path) return fail(ctx, RT_ERR_ARGUMENT, "rt_load_vtk_series: null path");
+    auto series = std::make_unique<VtkSeries>();
+    std::string err;
+    if (!series->load(series_path, err)) return fail(ctx, RT_ERR_IO, err);
+    if (frame_count) *frame_count = series->files.size();
+    ctx->vtk = std::move(series);
+    RT_API_END(ctx)
+}
+
+int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
+    RT_API_BEGIN(ctx)
+    (void) frame;
+    return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: not implemented yet");
+    RT_API_END(ctx)
+}
+
+} // extern "C"

@@ -1,0 +1,83 @@
+// build.h — host-side drivers of the device LBVH pipeline (replaces the reference's single-threaded host
+// builders BLAS::constructBLAS / TLAS::constructTLAS, src/AS/BLAS.cu:4-117, src/AS/TLAS.cu:4-129).
+#pragma once
+
+#include "device_util.h"
+#include "rt_build_core.h"
+
+#include <algorithm>
+#include <cstdint>
+#include <vector>
+
+class RadixSorter {
+public:
+    // Sorts n (key, value) pairs by the low `key_bits` bits of the key.  On return `keys`/`vals` point at the
+    // sorted arrays and `keys_alt`/`vals_alt` at the scratch copies (the pairs ping-pong between them).
+    void sort(uint64_t *&keys, uint64_t *&keys_alt, uint32_t *&vals, uint32_t *&vals_alt, int n, int key_bits,
+              cudaStream_t stream, int sm_count, uint32_t &launches);
+private:
+    DeviceBuffer<uint32_t> scratch_;
+};
+
+// Geometry sources of a BLAS batch (device pointers, original order)
+struct GeometryD {
+    const float *tri_verts;     // 9 floats per triangle
+    const SphereD *spheres;
+    const QuadD *quads;
+};
+
+// One batched LBVH build: all segments (BLASes) of the batch share one sort and one Karras pass; segment s
+// owns leaf positions [seg_offset[s], seg_offset[s+1]) and the subtree rooted at seg_root[s].
+class LbvhBuilder {
+public:
+    // ---- BLAS batch.  seg_* are host arrays of n_segs (+1 for offsets) entries. -------------------------
+    void build_blas(const GeometryD &geo, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type,
+                    const std::vector<uint32_t> &seg_first, int morton_bits, cudaStream_t stream, int sm_count);
+    // ---- TLAS: one segment over instance world boxes already written to prim_lo()/prim_hi() and bounds() --
+    void prepare_tlas(int n_instances);
+    void build_tlas(int n_instances, int morton_bits, cudaStream_t stream, int sm_count);
+
+    // results (device)
+    const BvhNode2 *nodes() const { return nodes_.get(); }
+    const TriIsect *leaf_tris() const { return leaf_tris_.get(); }
+    const uint32_t *leaf_prims() const { return leaf_prims_.get(); }
+    const int *seg_root_dev() const { return seg_root_.get(); }
+    std::vector<int> seg_root_host;          // filled by build_blas (synchronises the stream once)
+    int root_ref_host = 0;                   // TLAS root (filled by build_tlas via *_dev below, no sync)
+    // scratch the instance-update kernel writes into (TLAS mode)
+    float4 *prim_lo() const { return prim_lo_.get(); }
+    float4 *prim_hi() const { return prim_hi_.get(); }
+    uint32_t *bounds() const { return seg_bounds_.get(); }   // 6 ordered-uint words per segment
+    // introspection for parity tests (valid after a build)
+    int n_prims() const { return n_; }
+    const uint64_t *sorted_keys() const { return keys_; }
+    const uint32_t *sorted_vals() const { return vals_; }
+    const int *left() const { return left_.get(); }
+    const int *right() const { return right_.get(); }
+    const int *parent() const { return parent_.get(); }
+    const float4 *node_lo() const { return node_lo_.get(); }
+    const float4 *node_hi() const { return node_hi_.get(); }
+    uint32_t launches = 0;
+    size_t node_bytes() const { return (size_t) (n_ > 1 ? n_ - 1 : 0) * sizeof(BvhNode2); }
+
+private:
+    void reserve(int n, int n_segs, bool tris);
+    void run_tree(int n, int n_segs, int key_bits, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count);
+    int n_ = 0, n_segs_ = 0;
+    RadixSorter sorter_;
+    DeviceBuffer<float4> prim_lo_, prim_hi_, node_lo_, node_hi_;
+    DeviceBuffer<uint32_t> seg_bounds_, seg_offset_, seg_type_, seg_first_;
+    DeviceBuffer<uint64_t> keys_a_, keys_b_;
+    DeviceBuffer<uint32_t> vals_a_, vals_b_;
+    DeviceBuffer<int> left_, right_, parent_, leaf_parent_, flags_, seg_root_;
+    DeviceBuffer<BvhNode2> nodes_;
+    DeviceBuffer<TriIsect> leaf_tris_;
+    DeviceBuffer<uint32_t> leaf_prims_;
+    uint64_t *keys_ = nullptr, *keys_alt_ = nullptr;
+    uint32_t *vals_ = nullptr, *vals_alt_ = nullptr;
+};
+
+// per-frame instance update (device restatement of Instance::updateTransformArguments); writes InstanceD
+// records plus the TLAS builder's prim boxes and scene bounds.
+void launch_instance_update(const InstanceXformIn *in, int n, InstanceD *out, float4 *wlo, float4 *whi, float4 *wcentroid,
+                            uint32_t *bounds, cudaStream_t stream);

@@ -1,0 +1,262 @@
+#include "host_scene.h"
+
+#include <algorithm>
+#include <cmath>
+#include <map>
+#include <tuple>
+
+namespace {
+
+constexpr float PI_F = (float) M_PI;   // reference include/Global/Global.cuh:149
+
+inline f3 V(const rt_vec3 &v) { return mk3(v.x, v.y, v.z); }
+
+// BoundingBox(Point3, Point3) (reference include/AS/BoundingBox.cuh:40-46): per-axis ordering + ensureVolume
+HostBox ref_box_from_points(const f3 &a, const f3 &b) {
+    HostBox r;
+    for (int i = 0; i < 3; i++) {
+        const float x = comp3(a, i), y = comp3(b, i);
+        r.lo[i] = x < y ? x : y;
+        r.hi[i] = x < y ? y : x;
+        ensure_volume(r.lo[i], r.hi[i]);
+    }
+    return r;
+}
+HostBox ref_box_merge(const HostBox &a, const HostBox &b) {   // BoundingBox(b1, b2), BoundingBox.cuh:49-54
+    HostBox r;
+    for (int i = 0; i < 3; i++) { r.lo[i] = a.lo[i] < b.lo[i] ? a.lo[i] : b.lo[i]; r.hi[i] = a.hi[i] > b.hi[i] ? a.hi[i] : b.hi[i]; }
+    return r;
+}
+
+struct BlasKey {
+    uint32_t type; uint64_t first, count;
+    bool operator<(const BlasKey &o) const { return std::tie(type, first, count) < std::tie(o.type, o.first, o.count); }
+};
+
+} // namespace
+
+int morton_bits_for(size_t n) {
+    // bits per axis: fine enough that cells hold O(1) primitives, coarse enough to keep the sort short
+    if (n <= (1u << 12)) return 8;
+    if (n <= (1u << 18)) return 10;
+    if (n <= (1u << 22)) return 13;
+    return 16;
+}
+
+std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_parallelogram *p, size_t np, const rt_triangle *t, size_t nt) {
+    if ((ns && !s) || (np && !p) || (nt && !t)) return "rt_commit_geometry: null array with non-zero count";
+    if (nt > RT_REF_POS_MASK || ns > RT_REF_POS_MASK || np > RT_REF_POS_MASK) return "rt_commit_geometry: more than 2^29 primitives of one type";
+    spheres.assign(s, s + ns);
+    quads.assign(p, p + np);
+    n_tris = nt;
+    sphere_rec.resize(ns);
+    for (size_t i = 0; i < ns; i++) {
+        sphere_rec[i].c_r = make_float4(s[i].center.x, s[i].center.y, s[i].center.z, s[i].radius);
+        sphere_rec[i].mat_type = s[i].material_type; sphere_rec[i].mat_index = s[i].material_index;
+        sphere_rec[i]._p0 = sphere_rec[i]._p1 = 0;
+    }
+    quad_rec.resize(np);
+    for (size_t i = 0; i < np; i++) {
+        // Parallelogram constructor (reference include/Geometry/Parallelogram.cuh:26-39)
+        const rt_parallelogram &g = p[i];
+        const f3 n = unit3(cross3(V(g.u), V(g.v)));
+        float d = 0.0f;
+        d += n.x * g.q.x; d += n.y * g.q.y; d += n.z * g.q.z;
+        const bool compat = !(flags & RT_FLAG_FIX_PARALLELOGRAM_BBOX);
+        const f3 h = (V(g.u) + V(g.v)) * 0.5f;                                    // Parallelogram.cu:48-50 (Q10)
+        const HostBox rb = ref_box_from_points(V(g.q) + h, V(g.q) - h);
+        QuadD &o = quad_rec[i];
+        o.q_d = make_float4(g.q.x, g.q.y, g.q.z, d);
+        o.u = make_float4(g.u.x, g.u.y, g.u.z, 0.0f);
+        o.v = make_float4(g.v.x, g.v.y, g.v.z, 0.0f);
+        o.n_flag = make_float4(n.x, n.y, n.z, compat ? 1.0f : 0.0f);
+        o.rb_lo = make_float4(rb.lo[0], rb.lo[1], rb.lo[2], 0.0f);
+        o.rb_hi = make_float4(rb.hi[0], rb.hi[1], rb.hi[2], 0.0f);
+        o.mat_type = g.material_type; o.mat_index = g.material_index; o._p0 = o._p1 = 0;
+    }
+    tri_verts.resize(nt * 9);
+    tri_shade.resize(nt);
+    for (size_t i = 0; i < nt; i++) {
+        // Triangle constructors (reference include/Geometry/Triangle.cuh:26-46)
+        const rt_triangle &g = t[i];
+        float *v = &tri_verts[i * 9];
+        for (int k = 0; k < 3; k++) { v[3 * k] = g.v[k].x; v[3 * k + 1] = g.v[k].y; v[3 * k + 2] = g.v[k].z; }
+        f3 n0, n1, n2;
+        if (g.has_normals) { n0 = V(g.n[0]); n1 = V(g.n[1]); n2 = V(g.n[2]); }
+        else {
+            const f3 e1 = V(g.v[1]) - V(g.v[0]), e2 = V(g.v[2]) - V(g.v[0]);
+            n0 = n1 = n2 = unit3(cross3(e1, e2));
+        }
+        tri_shade[i].n0_mt = make_float4(n0.x, n0.y, n0.z, u2f(g.material_type));
+        tri_shade[i].n1_mi = make_float4(n1.x, n1.y, n1.z, u2f(g.material_index));
+        tri_shade[i].n2 = make_float4(n2.x, n2.y, n2.z, 0.0f);
+    }
+    return "";
+}
+
+std::string HostScene::commit_materials(const rt_rough *r, size_t nr, const rt_metal *m, size_t nm) {
+    if ((nr && !r) || (nm && !m)) return "rt_commit_materials: null array with non-zero count";
+    roughs.resize(nr);
+    metals.resize(nm);
+    for (size_t i = 0; i < nr; i++) roughs[i] = make_float4(r[i].albedo.x, r[i].albedo.y, r[i].albedo.z, 0.0f);
+    for (size_t i = 0; i < nm; i++) metals[i] = make_float4(m[i].albedo.x, m[i].albedo.y, m[i].albedo.z, m[i].fuzz);
+    return "";
+}
+
+std::string HostScene::commit_dielectrics(const rt_dielectric *d, size_t n) {
+    if (n && !d) return "rt_commit_dielectrics: null array";
+    dielectrics.resize(n);
+    for (size_t i = 0; i < n; i++) dielectrics[i] = make_float4(d[i].albedo.x, d[i].albedo.y, d[i].albedo.z, d[i].ior);
+    return "";
+}
+
+std::string HostScene::configure_instances(const rt_instance_desc *d, size_t n, const rt_instance_xform *x) {
+    if (!d || n == 0) return "rt_configure_instances: no instances";
+    if (n > RT_REF_POS_MASK) return "rt_configure_instances: too many instances";
+    for (size_t i = 0; i < n; i++) {
+        const uint64_t cnt = d[i].prim_count <= 1 ? 1 : d[i].prim_count;
+        const uint64_t limit = d[i].type == RT_SPHERE ? spheres.size() : d[i].type == RT_PARALLELOGRAM ? quads.size() : d[i].type == RT_TRIANGLE ? n_tris : 0;
+        if (d[i].type > RT_TRIANGLE || d[i].first_prim + cnt > limit) return "rt_configure_instances: primitive range out of bounds";
+    }
+    inst_desc.assign(d, d + n);
+    xforms.resize(n);
+    for (size_t i = 0; i < n; i++) xforms[i] = x ? x[i] : rt_instance_xform{{0, 0, 0}, {0, 0, 0}, {1, 1, 1}};
+    return "";
+}
+
+std::string HostScene::plan_blas() {
+    // one BLAS per distinct primitive range (the reference's intent, src/Global/RenderPin.cu:143-172; Q11 not replicated)
+    const size_t n_inst = inst_desc.size();
+    std::map<BlasKey, int> blas_of;
+    seg_offset.assign(1, 0u);
+    seg_type.clear();
+    seg_first.clear();
+    inst_blas.resize(n_inst);
+    inst_box.resize(n_inst);
+    inst_centroid.resize(n_inst);
+    for (size_t i = 0; i < n_inst; i++) {
+        const rt_instance_desc &d = inst_desc[i];
+        const uint64_t cnt = d.prim_count <= 1 ? 1 : d.prim_count;
+        const BlasKey key{d.type, d.first_prim, cnt};
+        auto it = blas_of.find(key);
+        if (it == blas_of.end()) {
+            it = blas_of.emplace(key, (int) seg_type.size()).first;
+            seg_type.push_back(d.type);
+            seg_first.push_back((uint32_t) d.first_prim);
+            if ((uint64_t) seg_offset.back() + cnt > RT_REF_POS_MASK) return "BLAS batch exceeds 2^29 primitives";
+            seg_offset.push_back(seg_offset.back() + (uint32_t) cnt);
+        }
+        inst_blas[i] = it->second;
+
+        // local box + centroid, reference semantics (src/Global/RenderPin.cu:124-140 for single primitives;
+        // caller-provided bounds as src/Global/VTKReader.cu:206-207; else merged boxes + box centre)
+        auto prim_box = [&](uint64_t k) -> HostBox {
+            if (d.type == RT_SPHERE) {
+                const rt_sphere &s = spheres[k];
+                const f3 e = mk3(s.radius, s.radius, s.radius);                   // Sphere.cu:51-55
+                return ref_box_from_points(V(s.center) - e, V(s.center) + e);
+            }
+            if (d.type == RT_PARALLELOGRAM) {
+                const rt_parallelogram &p = quads[k];
+                if (flags & RT_FLAG_FIX_PARALLELOGRAM_BBOX) {
+                    const Aabb b = quad_aabb(quad_rec[k]);
+                    return ref_box_from_points(b.lo, b.hi);
+                }
+                const f3 h = (V(p.u) + V(p.v)) * 0.5f;
+                return ref_box_from_points(V(p.q) + h, V(p.q) - h);
+            }
+            const float *v = &tri_verts[k * 9];                                   // Triangle.cu:46-62
+            const f3 lo = mk3(std::min({v[0], v[3], v[6]}), std::min({v[1], v[4], v[7]}), std::min({v[2], v[5], v[8]}));
+            const f3 hi = mk3(std::max({v[0], v[3], v[6]}), std::max({v[1], v[4], v[7]}), std::max({v[2], v[5], v[8]}));
+            return ref_box_from_points(lo, hi);
+        };
+        HostBox &box = inst_box[i];
+        f3 &centroid = inst_centroid[i];
+        if (d.prim_count <= 1) {
+            box = prim_box(d.first_prim);
+            if (d.type == RT_SPHERE) centroid = V(spheres[d.first_prim].center);
+            else if (d.type == RT_PARALLELOGRAM) {
+                const rt_parallelogram &p = quads[d.first_prim];
+                centroid = (V(p.q) + V(p.u) * 0.5f) + V(p.v) * 0.5f;              // Parallelogram.cuh:45-47
+            } else {
+                const float *v = &tri_verts[d.first_prim * 9];                    // Triangle.cuh:52-60
+                float cc[3];
+                for (int a = 0; a < 3; a++) { cc[a] = v[a] + v[3 + a] + v[6 + a]; cc[a] /= 3.0f; }
+                centroid = mk3(cc[0], cc[1], cc[2]);
+            }
+        } else if (d.has_bounds) {
+            for (int a = 0; a < 3; a++) { box.lo[a] = d.bounds_min[a]; box.hi[a] = d.bounds_max[a]; ensure_volume(box.lo[a], box.hi[a]); }
+            centroid = mk3(d.centroid[0], d.centroid[1], d.centroid[2]);
+        } else {
+            box = prim_box(d.first_prim);
+            for (uint64_t k = 1; k < d.prim_count; k++) box = ref_box_merge(box, prim_box(d.first_prim + k));
+            centroid = mk3(0.5f * (box.lo[0] + box.hi[0]), 0.5f * (box.lo[1] + box.hi[1]), 0.5f * (box.lo[2] + box.hi[2]));
+        }
+    }
+    return "";
+}
+
+// RendererImpl::calculateCameraProperties (reference src/Global/RenderPin.cu:73-95), same operation order
+std::string HostScene::configure_camera(const rt_window &w, const rt_camera_input &in) {
+    if (w.width == 0 || w.height == 0) return "rt_configure_camera: bad window";
+    if (in.sample_count == 0) return "rt_configure_camera: sample_count must be >= 1";
+    window = w;
+    const f3 center = V(in.center), target = V(in.target), up = V(in.up);
+    float d2 = 0.0f;
+    d2 += (center.x - target.x) * (center.x - target.x);
+    d2 += (center.y - target.y) * (center.y - target.y);
+    d2 += (center.z - target.z) * (center.z - target.z);
+    const float focusDistance = std::sqrt(d2);
+    const float theta = in.fov * PI_F / 180.0f;
+    const float vW = 2.0f * std::tan(theta / 2.0f) * focusDistance;
+    const float vH = vW / (static_cast<float>(w.width) * 1.0f / static_cast<float>(w.height));
+    const f3 camW = unit3(target - center);
+    const f3 camU = unit3(cross3(camW, up));
+    const f3 camV = unit3(cross3(camU, camW));
+    const f3 vpX = camU * vW, vpY = camV * vH;
+    const float fw = static_cast<float>(w.width), fh = static_cast<float>(w.height);
+    cam.pixelDx = mk3(vpX.x / fw, vpX.y / fw, vpX.z / fw);
+    cam.pixelDy = mk3(vpY.x / fh, vpY.y / fh, vpY.z / fh);
+    const f3 vpOrigin = ((center + camW * focusDistance) - vpX * 0.5f) - vpY * 0.5f;
+    cam.pixelOrigin = (vpOrigin + cam.pixelDx * 0.5f) + cam.pixelDy * 0.5f;
+    cam.background = V(in.background);
+    cam.center = center;
+    cam.camU = camU;
+    cam.camV = camV;
+    cam.focusRadius = in.focus_disk_radius;
+    cam.sqrtSamples = (uint32_t) static_cast<size_t>(std::sqrt((double) in.sample_count));
+    cam.rcpSqrtSamples = 1.0f / static_cast<float>(cam.sqrtSamples);
+    cam.depth = (uint32_t) in.ray_trace_depth;
+    cam.width = w.width;
+    cam.height = w.height;
+    cam.pitch = ((w.width + 15u) / 16u) * 16u;   // gridDim.x * blockDim.x of the reference launch (src/Global/Kernel.cu:109)
+    return "";
+}
+
+void HostScene::fill_xform_in(InstanceXformIn *out, const std::vector<int> &seg_root) const {
+    const size_t n = inst_desc.size();
+    for (size_t i = 0; i < n; i++) {
+        const rt_instance_xform &x = xforms[i];
+        InstanceXformIn &o = out[i];
+        o.shift[0] = x.shift.x; o.shift[1] = x.shift.y; o.shift[2] = x.shift.z;
+        o.scale[0] = x.scale.x; o.scale[1] = x.scale.y; o.scale[2] = x.scale.z;
+        // MathHelper::degreeToRadian + cos/sin as Matrix::constructRotateMatrix (reference src/Util/Matrix.cu:209-243)
+        const float tx = x.rotate_deg.x * PI_F / 180.0f, ty = x.rotate_deg.y * PI_F / 180.0f, tz = x.rotate_deg.z * PI_F / 180.0f;
+        o.trig[0] = std::cos(tx); o.trig[1] = std::sin(tx);
+        o.trig[2] = std::cos(ty); o.trig[3] = std::sin(ty);
+        o.trig[4] = std::cos(tz); o.trig[5] = std::sin(tz);
+        for (int a = 0; a < 3; a++) { o.box_lo[a] = inst_box[i].lo[a]; o.box_hi[a] = inst_box[i].hi[a]; }
+        o.centroid[0] = inst_centroid[i].x; o.centroid[1] = inst_centroid[i].y; o.centroid[2] = inst_centroid[i].z;
+        o.root_ref = seg_root[inst_blas[i]];
+        o.blas = inst_blas[i];
+    }
+}
+
+size_t HostScene::prim_bytes() const {
+    size_t b = 0;
+    for (size_t s = 0; s < seg_type.size(); s++) {
+        const size_t cnt = seg_offset[s + 1] - seg_offset[s];
+        b += cnt * (seg_type[s] == RT_TRIANGLE ? sizeof(TriIsect) : seg_type[s] == RT_SPHERE ? sizeof(SphereD) : sizeof(QuadD));
+    }
+    return b;
+}

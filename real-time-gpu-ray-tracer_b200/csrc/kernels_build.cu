@@ -1,0 +1,322 @@
+// kernels_build.cu — device LBVH pipeline: primitive bounds -> Morton keys -> onesweep radix sort ->
+// Karras hierarchy -> atomic bottom-up refit -> node emission (+ leaf-order triangle records).
+// One thread per element everywhere; grids are sized to the element count (>= 148 SMs * resident CTAs for
+// the configs that matter).  All of it is HBM-bound streaming work: algorithmic bytes per primitive are
+// listed in DESIGN.md ("LBVH build roofline").
+#include "build.h"
+
+namespace {
+
+constexpr int BT = 256;   // threads per block for the element-wise kernels
+
+__device__ __forceinline__ int find_segment(const uint32_t *__restrict__ seg_offset, int n_segs, uint32_t j) {
+    // largest s with seg_offset[s] <= j
+    int lo = 0, hi = n_segs - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(&seg_offset[mid]) <= j) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(BT) init_bounds_kernel(uint32_t *bounds, int n_segs) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_segs * 6) bounds[i] = (i % 6) < 3 ? 0xFFFFFFFFu : 0u;   // lo = +max, hi = -max in ordered space
+}
+
+// TLAS: one segment [0, n) — written by a kernel so the per-frame rebuild needs no host->device copy
+__global__ void set_single_segment_kernel(uint32_t *seg_offset, uint32_t *seg_type, uint32_t n) {
+    seg_offset[0] = 0u;
+    seg_offset[1] = n;
+    seg_type[0] = 0u;
+}
+
+__device__ __forceinline__ void atomic_bounds(uint32_t *b, const Aabb &box) {
+    atomicMin(&b[0], float_to_ordered(box.lo.x)); atomicMin(&b[1], float_to_ordered(box.lo.y)); atomicMin(&b[2], float_to_ordered(box.lo.z));
+    atomicMax(&b[3], float_to_ordered(box.hi.x)); atomicMax(&b[4], float_to_ordered(box.hi.y)); atomicMax(&b[5], float_to_ordered(box.hi.z));
+}
+
+// K1: per build-primitive box (padded) + per-segment bounds.  Warps whose lanes all belong to one segment
+// reduce with shuffles and issue one atomic set per warp.
+__global__ void __launch_bounds__(BT) prim_bounds_kernel(GeometryD geo, const uint32_t *__restrict__ seg_offset, const uint32_t *__restrict__ seg_type,
+                                                         const uint32_t *__restrict__ seg_first, int n_segs, int n,
+                                                         float4 *__restrict__ prim_lo, float4 *__restrict__ prim_hi, uint32_t *bounds) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = j < n;
+    int seg = -1;
+    Aabb box;
+    box.lo = mk3(RT_INF, RT_INF, RT_INF);
+    box.hi = mk3(-RT_INF, -RT_INF, -RT_INF);
+    if (valid) {
+        seg = find_segment(seg_offset, n_segs, (uint32_t) j);
+        const uint32_t type = __ldg(&seg_type[seg]);
+        const uint32_t prim = __ldg(&seg_first[seg]) + ((uint32_t) j - __ldg(&seg_offset[seg]));
+        if (type == 2u) {
+            float v9[9];
+            const float *src = geo.tri_verts + (size_t) prim * 9;
+#pragma unroll
+            for (int k = 0; k < 9; k++) v9[k] = __ldg(src + k);
+            box = tri_aabb(v9);
+        } else if (type == 0u) {
+            box = sphere_aabb(geo.spheres[prim]);
+        } else {
+            box = quad_aabb(geo.quads[prim]);
+        }
+        box = aabb_pad(box);
+        prim_lo[j] = make_float4(box.lo.x, box.lo.y, box.lo.z, 0.0f);
+        prim_hi[j] = make_float4(box.hi.x, box.hi.y, box.hi.z, 0.0f);
+    }
+    const int seg0 = __shfl_sync(0xffffffffu, seg, 0);
+    const bool uniform = __all_sync(0xffffffffu, seg == seg0 || !valid) && seg0 >= 0;
+    if (uniform) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            box.lo.x = fminf(box.lo.x, __shfl_xor_sync(0xffffffffu, box.lo.x, off));
+            box.lo.y = fminf(box.lo.y, __shfl_xor_sync(0xffffffffu, box.lo.y, off));
+            box.lo.z = fminf(box.lo.z, __shfl_xor_sync(0xffffffffu, box.lo.z, off));
+            box.hi.x = fmaxf(box.hi.x, __shfl_xor_sync(0xffffffffu, box.hi.x, off));
+            box.hi.y = fmaxf(box.hi.y, __shfl_xor_sync(0xffffffffu, box.hi.y, off));
+            box.hi.z = fmaxf(box.hi.z, __shfl_xor_sync(0xffffffffu, box.hi.z, off));
+        }
+        if ((threadIdx.x & 31) == 0) atomic_bounds(bounds + 6 * seg0, box);
+    } else if (valid) {
+        atomic_bounds(bounds + 6 * seg, box);
+    }
+}
+
+// K2: key = (segment << 3*bits) | morton(box centre within segment bounds); payload = build-primitive index
+__global__ void __launch_bounds__(BT) morton_kernel(const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi,
+                                                    const uint32_t *__restrict__ seg_offset, int n_segs, const uint32_t *__restrict__ bounds,
+                                                    int n, int bits, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int seg = n_segs > 1 ? find_segment(seg_offset, n_segs, (uint32_t) j) : 0;
+    const uint32_t *b = bounds + 6 * seg;
+    Aabb scene;
+    scene.lo = mk3(ordered_to_float(__ldg(b + 0)), ordered_to_float(__ldg(b + 1)), ordered_to_float(__ldg(b + 2)));
+    scene.hi = mk3(ordered_to_float(__ldg(b + 3)), ordered_to_float(__ldg(b + 4)), ordered_to_float(__ldg(b + 5)));
+    const float4 lo = prim_lo[j], hi = prim_hi[j];
+    Aabb box;
+    box.lo = mk3(lo.x, lo.y, lo.z);
+    box.hi = mk3(hi.x, hi.y, hi.z);
+    keys[j] = ((uint64_t) seg << (3 * bits)) | morton_code(box, scene, bits);
+    vals[j] = (uint32_t) j;
+}
+
+// K3: Karras hierarchy over the sorted keys
+__global__ void __launch_bounds__(BT) karras_kernel(const uint64_t *__restrict__ keys, int n, const uint32_t *__restrict__ seg_offset, int n_segs,
+                                                    int *__restrict__ left, int *__restrict__ right, int *__restrict__ parent,
+                                                    int *__restrict__ leaf_parent, int *__restrict__ seg_root) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const KarrasNode k = karras_node(keys, n, i);
+    left[i] = k.left;
+    right[i] = k.right;
+    if (k.left >= 0) parent[k.left] = i; else leaf_parent[~k.left] = i;
+    if (k.right >= 0) parent[k.right] = i; else leaf_parent[~k.right] = i;
+    if (i == 0) parent[0] = -1;
+    // subtree that covers exactly one segment = that BLAS's root
+    const int seg = n_segs > 1 ? find_segment(seg_offset, n_segs, (uint32_t) k.first) : 0;
+    if ((uint32_t) k.first == __ldg(&seg_offset[seg]) && (uint32_t) k.last + 1u == __ldg(&seg_offset[seg + 1])) seg_root[seg] = i;
+}
+
+// segments with a single primitive have no inner node: their root is the leaf itself
+__global__ void __launch_bounds__(BT) single_prim_roots_kernel(const uint32_t *__restrict__ seg_offset, const uint32_t *__restrict__ seg_type,
+                                                               int n_segs, int leaf_mode, const uint32_t *__restrict__ vals, int *__restrict__ seg_root) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_segs) return;
+    if (seg_offset[s + 1] - seg_offset[s] == 1u) {
+        const uint32_t pos = seg_offset[s];
+        seg_root[s] = leaf_mode == 0 ? make_leaf_ref(seg_type[s], pos) : make_leaf_ref(0u, vals[pos]);
+    }
+}
+
+// K4: bottom-up refit; the second child to arrive at a node computes its box
+__global__ void __launch_bounds__(BT) refit_kernel(const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi, const uint32_t *__restrict__ vals,
+                                                   const int *__restrict__ left, const int *__restrict__ right, const int *__restrict__ parent,
+                                                   const int *__restrict__ leaf_parent, int n, int *flags, float4 *node_lo, float4 *node_hi) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    int cur = leaf_parent[pos];
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(&flags[cur], 1) == 0) return;
+        __threadfence();
+        const int l = left[cur], r = right[cur];
+        float4 llo, lhi, rlo, rhi;
+        if (l >= 0) { llo = __ldcg(&node_lo[l]); lhi = __ldcg(&node_hi[l]); } else { const uint32_t p = vals[~l]; llo = prim_lo[p]; lhi = prim_hi[p]; }
+        if (r >= 0) { rlo = __ldcg(&node_lo[r]); rhi = __ldcg(&node_hi[r]); } else { const uint32_t p = vals[~r]; rlo = prim_lo[p]; rhi = prim_hi[p]; }
+        __stcg(&node_lo[cur], make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), 0.0f));
+        __stcg(&node_hi[cur], make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), 0.0f));
+        cur = parent[cur];
+    }
+}
+
+__device__ __forceinline__ Aabb load_box(const float4 *lo, const float4 *hi, int i) {
+    const float4 a = lo[i], b = hi[i];
+    Aabb r;
+    r.lo = mk3(a.x, a.y, a.z);
+    r.hi = mk3(b.x, b.y, b.z);
+    return r;
+}
+
+// K5a: traversal nodes (both child boxes in the parent)
+__global__ void __launch_bounds__(BT) emit_nodes_kernel(const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi, const uint32_t *__restrict__ vals,
+                                                        const int *__restrict__ left, const int *__restrict__ right,
+                                                        const float4 *__restrict__ node_lo, const float4 *__restrict__ node_hi,
+                                                        const uint32_t *__restrict__ seg_offset, const uint32_t *__restrict__ seg_type, int n_segs,
+                                                        int n, int leaf_mode, BvhNode2 *__restrict__ nodes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int l = left[i], r = right[i];
+    Aabb b[2];
+    int ref[2];
+    const int child[2] = {l, r};
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+        if (child[c] >= 0) {
+            b[c] = load_box(node_lo, node_hi, child[c]);
+            ref[c] = child[c];
+        } else {
+            const uint32_t pos = (uint32_t) ~child[c];
+            const uint32_t p = vals[pos];
+            b[c] = load_box(prim_lo, prim_hi, (int) p);
+            if (leaf_mode == 0) {
+                const int seg = n_segs > 1 ? find_segment(seg_offset, n_segs, pos) : 0;
+                ref[c] = make_leaf_ref(__ldg(&seg_type[seg]), pos);
+            } else {
+                ref[c] = make_leaf_ref(0u, p);
+            }
+        }
+    }
+    nodes[i] = make_node2(b[0], ref[0], b[1], ref[1]);
+}
+
+// K5b: leaf-order primitive ids and triangle intersection records (e1/e2 as the reference's constructor)
+__global__ void __launch_bounds__(BT) emit_leaves_kernel(GeometryD geo, const uint32_t *__restrict__ vals,
+                                                         const uint32_t *__restrict__ seg_offset, const uint32_t *__restrict__ seg_type,
+                                                         const uint32_t *__restrict__ seg_first, int n_segs, int n,
+                                                         uint32_t *__restrict__ leaf_prims, TriIsect *__restrict__ leaf_tris) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    const int seg = n_segs > 1 ? find_segment(seg_offset, n_segs, (uint32_t) pos) : 0;
+    const uint32_t prim = __ldg(&seg_first[seg]) + (vals[pos] - __ldg(&seg_offset[seg]));
+    leaf_prims[pos] = prim;
+    if (__ldg(&seg_type[seg]) == 2u) {
+        const float *s = geo.tri_verts + (size_t) prim * 9;
+        const f3 v0 = mk3(__ldg(s), __ldg(s + 1), __ldg(s + 2));
+        const f3 v1 = mk3(__ldg(s + 3), __ldg(s + 4), __ldg(s + 5));
+        const f3 v2 = mk3(__ldg(s + 6), __ldg(s + 7), __ldg(s + 8));
+        const f3 e1 = v1 - v0, e2 = v2 - v0;
+        TriIsect t;
+        t.v0_id = make_float4(v0.x, v0.y, v0.z, __uint_as_float(prim));
+        t.e1 = make_float4(e1.x, e1.y, e1.z, 0.0f);
+        t.e2 = make_float4(e2.x, e2.y, e2.z, 0.0f);
+        leaf_tris[pos] = t;
+    }
+}
+
+__global__ void __launch_bounds__(BT) instance_update_kernel(const InstanceXformIn *__restrict__ in, int n, InstanceD *__restrict__ out,
+                                                             float4 *__restrict__ wlo, float4 *__restrict__ whi, float4 *__restrict__ wcentroid,
+                                                             uint32_t *bounds) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    InstanceD o;
+    Aabb box;
+    f3 c;
+    instance_update(in[i], o, box, c);
+    out[i] = o;
+    // the TLAS culls with a padded copy of the reference's transformedBoundingBox
+    const Aabb padded = aabb_pad(box);
+    wlo[i] = make_float4(padded.lo.x, padded.lo.y, padded.lo.z, 0.0f);
+    whi[i] = make_float4(padded.hi.x, padded.hi.y, padded.hi.z, 0.0f);
+    wcentroid[i] = make_float4(c.x, c.y, c.z, 0.0f);
+    atomic_bounds(bounds, padded);
+}
+
+} // namespace
+
+void launch_instance_update(const InstanceXformIn *in, int n, InstanceD *out, float4 *wlo, float4 *whi, float4 *wcentroid,
+                            uint32_t *bounds, cudaStream_t stream) {
+    init_bounds_kernel<<<1, BT, 0, stream>>>(bounds, 1);
+    instance_update_kernel<<<div_up(n, 64), 64, 0, stream>>>(in, n, out, wlo, whi, wcentroid, bounds);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void LbvhBuilder::reserve(int n, int n_segs, bool tris) {
+    prim_lo_.reserve(n); prim_hi_.reserve(n);
+    seg_bounds_.reserve((size_t) n_segs * 6);
+    seg_offset_.reserve(n_segs + 1); seg_type_.reserve(n_segs); seg_first_.reserve(n_segs);
+    keys_a_.reserve(n); keys_b_.reserve(n); vals_a_.reserve(n); vals_b_.reserve(n);
+    const int m = n > 1 ? n - 1 : 1;
+    left_.reserve(m); right_.reserve(m); parent_.reserve(m); flags_.reserve(m);
+    node_lo_.reserve(m); node_hi_.reserve(m); nodes_.reserve(m);
+    leaf_parent_.reserve(n); seg_root_.reserve(n_segs);
+    leaf_prims_.reserve(n);
+    if (tris) leaf_tris_.reserve(n);
+}
+
+void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count) {
+    keys_ = keys_a_.get(); keys_alt_ = keys_b_.get(); vals_ = vals_a_.get(); vals_alt_ = vals_b_.get();
+    if (n > 1) {
+        sorter_.sort(keys_, keys_alt_, vals_, vals_alt_, n, key_bits, stream, sm_count, launches);
+        CUDA_CHECK(cudaMemsetAsync(flags_.get(), 0, (size_t) (n - 1) * sizeof(int), stream));
+        karras_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(keys_, n, seg_offset_.get(), n_segs, left_.get(), right_.get(), parent_.get(),
+                                                           leaf_parent_.get(), seg_root_.get());
+        refit_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(), parent_.get(),
+                                                      leaf_parent_.get(), n, flags_.get(), node_lo_.get(), node_hi_.get());
+        emit_nodes_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(),
+                                                               node_lo_.get(), node_hi_.get(), seg_offset_.get(), seg_type_.get(), n_segs, n, leaf_mode,
+                                                               nodes_.get());
+        launches += 3;
+    }
+    single_prim_roots_kernel<<<div_up(n_segs, BT), BT, 0, stream>>>(seg_offset_.get(), seg_type_.get(), n_segs, leaf_mode, vals_, seg_root_.get());
+    launches++;
+    if (leaf_mode == 0) {
+        emit_leaves_kernel<<<div_up(n, BT), BT, 0, stream>>>(*geo, vals_, seg_offset_.get(), seg_type_.get(), seg_first_.get(), n_segs, n,
+                                                            leaf_prims_.get(), leaf_tris_.get());
+        launches++;
+    }
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void LbvhBuilder::build_blas(const GeometryD &geo, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type,
+                             const std::vector<uint32_t> &seg_first, int morton_bits, cudaStream_t stream, int sm_count) {
+    const int n_segs = (int) seg_type.size();
+    const int n = (int) seg_offset.back();
+    n_ = n; n_segs_ = n_segs; launches = 0;
+    bool tris = false;
+    for (uint32_t t: seg_type) tris |= (t == 2u);
+    reserve(n, n_segs, tris);
+    seg_offset_.upload(seg_offset.data(), seg_offset.size(), stream);
+    seg_type_.upload(seg_type.data(), seg_type.size(), stream);
+    seg_first_.upload(seg_first.data(), seg_first.size(), stream);
+    int seg_bits = 0;
+    while ((1 << seg_bits) < n_segs) seg_bits++;
+    if (3 * morton_bits + seg_bits > 64) morton_bits = (64 - seg_bits) / 3;
+    init_bounds_kernel<<<div_up((size_t) n_segs * 6, BT), BT, 0, stream>>>(seg_bounds_.get(), n_segs);
+    prim_bounds_kernel<<<div_up(n, BT), BT, 0, stream>>>(geo, seg_offset_.get(), seg_type_.get(), seg_first_.get(), n_segs, n,
+                                                        prim_lo_.get(), prim_hi_.get(), seg_bounds_.get());
+    morton_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), seg_offset_.get(), n_segs, seg_bounds_.get(), n, morton_bits,
+                                                   keys_a_.get(), vals_a_.get());
+    launches += 3;
+    run_tree(n, n_segs, 3 * morton_bits + seg_bits, 0, &geo, stream, sm_count);
+    seg_root_host.resize(n_segs);
+    CUDA_CHECK(cudaMemcpyAsync(seg_root_host.data(), seg_root_.get(), n_segs * sizeof(int), cudaMemcpyDeviceToHost, stream));
+    CUDA_CHECK(cudaStreamSynchronize(stream));
+}
+
+void LbvhBuilder::prepare_tlas(int n_instances) {
+    reserve(n_instances, 1, false);
+}
+
+void LbvhBuilder::build_tlas(int n_instances, int morton_bits, cudaStream_t stream, int sm_count) {
+    const int n = n_instances;
+    n_ = n; n_segs_ = 1; launches = 0;
+    set_single_segment_kernel<<<1, 1, 0, stream>>>(seg_offset_.get(), seg_type_.get(), (uint32_t) n);
+    launches++;
+    morton_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), seg_offset_.get(), 1, seg_bounds_.get(), n, morton_bits,
+                                                   keys_a_.get(), vals_a_.get());
+    launches++;
+    run_tree(n, 1, 3 * morton_bits, 1, nullptr, stream, sm_count);
+}

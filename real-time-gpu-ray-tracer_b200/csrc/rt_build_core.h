@@ -1,0 +1,214 @@
+// rt_build_core.h — per-element logic of the LBVH build (Morton codes, Karras 2012 hierarchy, refit, node
+// emission) and of the per-instance transform update.  The CUDA kernels in kernels_build.cu call these once
+// per thread; the CPU twin used by the `not gpu` tests calls them in serial loops, so device topology can be
+// compared bit-for-bit against a serial execution of the same definition.
+#pragma once
+
+#include "rt_types.h"
+
+// ---- boxes ------------------------------------------------------------------------------------------
+struct Aabb { f3 lo, hi; };
+RT_HD Aabb aabb_union(const Aabb &a, const Aabb &b) {
+    Aabb r;
+    r.lo = mk3(rt_min(a.lo.x, b.lo.x), rt_min(a.lo.y, b.lo.y), rt_min(a.lo.z, b.lo.z));
+    r.hi = mk3(rt_max(a.hi.x, b.hi.x), rt_max(a.hi.y, b.hi.y), rt_max(a.hi.z, b.hi.z));
+    return r;
+}
+// Conservative padding so that the fma-based slab test can never cull a true hit on the box surface.
+// The reference pads only degenerate axes by 1e-6 (ensureVolume, include/AS/BoundingBox.cuh:24-28).
+RT_HD Aabb aabb_pad(const Aabb &a) {
+    Aabb r;
+    r.lo = mk3(a.lo.x - (fabsf(a.lo.x) * 4e-7f + 1e-6f), a.lo.y - (fabsf(a.lo.y) * 4e-7f + 1e-6f), a.lo.z - (fabsf(a.lo.z) * 4e-7f + 1e-6f));
+    r.hi = mk3(a.hi.x + (fabsf(a.hi.x) * 4e-7f + 1e-6f), a.hi.y + (fabsf(a.hi.y) * 4e-7f + 1e-6f), a.hi.z + (fabsf(a.hi.z) * 4e-7f + 1e-6f));
+    return r;
+}
+RT_HD Aabb tri_aabb(const float *v9) {
+    Aabb r;
+    r.lo = mk3(rt_min(rt_min(v9[0], v9[3]), v9[6]), rt_min(rt_min(v9[1], v9[4]), v9[7]), rt_min(rt_min(v9[2], v9[5]), v9[8]));
+    r.hi = mk3(rt_max(rt_max(v9[0], v9[3]), v9[6]), rt_max(rt_max(v9[1], v9[4]), v9[7]), rt_max(rt_max(v9[2], v9[5]), v9[8]));
+    return r;
+}
+RT_HD Aabb sphere_aabb(const SphereD &s) {
+    Aabb r;
+    r.lo = mk3(s.c_r.x - s.c_r.w, s.c_r.y - s.c_r.w, s.c_r.z - s.c_r.w);
+    r.hi = mk3(s.c_r.x + s.c_r.w, s.c_r.y + s.c_r.w, s.c_r.z + s.c_r.w);
+    return r;
+}
+RT_HD Aabb quad_aabb(const QuadD &p) {   // TRUE box of the four corners (the reference's box is a filter, Q10)
+    const f3 q = mk3(p.q_d.x, p.q_d.y, p.q_d.z), u = mk3(p.u.x, p.u.y, p.u.z), v = mk3(p.v.x, p.v.y, p.v.z);
+    const f3 c1 = q + u, c2 = q + v, c3 = (q + u) + v;
+    Aabb r;
+    r.lo = mk3(rt_min(rt_min(q.x, c1.x), rt_min(c2.x, c3.x)), rt_min(rt_min(q.y, c1.y), rt_min(c2.y, c3.y)), rt_min(rt_min(q.z, c1.z), rt_min(c2.z, c3.z)));
+    r.hi = mk3(rt_max(rt_max(q.x, c1.x), rt_max(c2.x, c3.x)), rt_max(rt_max(q.y, c1.y), rt_max(c2.y, c3.y)), rt_max(rt_max(q.z, c1.z), rt_max(c2.z, c3.z)));
+    return r;
+}
+
+// order-preserving float <-> uint mapping for atomicMin/atomicMax on bounds
+RT_HD uint32_t float_to_ordered(float f) { const uint32_t u = f2u(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+RT_HD float ordered_to_float(uint32_t o) { return u2f((o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o); }
+
+// ---- Morton keys ---------------------------------------------------------------------------------------
+// 3*bits-bit Morton code of the box centre, normalised to the segment (BLAS) bounds; bits <= 21.
+RT_HD uint64_t expand_bits21(uint64_t v) {
+    v &= 0x1FFFFFull;
+    v = (v | (v << 32)) & 0x1F00000000FFFFull;
+    v = (v | (v << 16)) & 0x1F0000FF0000FFull;
+    v = (v | (v << 8)) & 0x100F00F00F00F00Full;
+    v = (v | (v << 4)) & 0x10C30C30C30C30C3ull;
+    v = (v | (v << 2)) & 0x1249249249249249ull;
+    return v;
+}
+RT_HD uint64_t morton_code(const Aabb &prim, const Aabb &scene, int bits) {
+    const float scale = (float) (1u << bits);
+    uint64_t q[3];
+    for (int a = 0; a < 3; a++) {
+        const float lo = comp3(scene.lo, a), hi = comp3(scene.hi, a);
+        const float c = 0.5f * (comp3(prim.lo, a) + comp3(prim.hi, a));
+        const float ext = hi - lo;
+        float n = ext > 0.0f ? (c - lo) / ext : 0.0f;
+        n = rt_min(rt_max(n * scale, 0.0f), scale - 1.0f);
+        q[a] = (uint64_t) n;
+    }
+    const uint64_t code21 = (expand_bits21(q[0]) << 2) | (expand_bits21(q[1]) << 1) | expand_bits21(q[2]);
+    // q has `bits` significant bits per axis -> interleaved code has 3*bits significant bits
+    return code21;
+}
+
+// ---- Karras 2012: internal node i of a radix tree over n sorted keys (ties broken by position) ------------
+RT_HD int clz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clzll((long long) x);
+#else
+    return x == 0 ? 64 : __builtin_clzll(x);
+#endif
+}
+RT_HD int clz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __clz((int) x);
+#else
+    return x == 0 ? 32 : __builtin_clz(x);
+#endif
+}
+RT_HD int karras_delta(const uint64_t *keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + clz32((uint32_t) i ^ (uint32_t) j);
+    return clz64(a ^ b);
+}
+struct KarrasNode { int left, right, first, last; };   // children: >= 0 inner node, < 0 leaf ~position
+RT_HD KarrasNode karras_node(const uint64_t *keys, int n, int i) {
+    const int d = (karras_delta(keys, n, i, i + 1) - karras_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = karras_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (karras_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (karras_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = karras_delta(keys, n, i, j);
+    int s = 0;
+    for (int div = 2, t = (l + 1) / 2;; div <<= 1, t = (l + div - 1) / div) {
+        if (karras_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t <= 1) break;
+    }
+    const int gamma = i + s * d + (d < 0 ? -1 : 0);
+    KarrasNode k;
+    k.first = i < j ? i : j;
+    k.last = i < j ? j : i;
+    k.left = (k.first == gamma) ? ~gamma : gamma;
+    k.right = (k.last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    return k;
+}
+
+// ---- node emission ----------------------------------------------------------------------------------------
+RT_HD BvhNode2 make_node2(const Aabb &b0, int ref0, const Aabb &b1, int ref1) {
+    BvhNode2 n;
+    n.xy0 = make_float4(b0.lo.x, b0.hi.x, b0.lo.y, b0.hi.y);
+    n.xy1 = make_float4(b1.lo.x, b1.hi.x, b1.lo.y, b1.hi.y);
+    n.z01 = make_float4(b0.lo.z, b0.hi.z, b1.lo.z, b1.hi.z);
+    n.refs = make_int4(ref0, ref1, 0, 0);
+    return n;
+}
+
+// ---- instance transform update ---------------------------------------------------------------------------
+// Instance::updateTransformArguments (reference src/AS/Instance.cu:4-17) with the reference's generic
+// Matrix arithmetic restated on plain 4x4 arrays: M = T * (Rx * Ry * Rz) * S  (src/Util/Matrix.cu:71-86,
+// 183-250), inverse by Gauss-Jordan with partial pivoting on a 4x8 scratch (Matrix.cu:4-69,101-130; singular
+// input is returned unchanged, Q14), world box from the 8 corners (src/AS/BoundingBox.cu:4-32) and the
+// centroid.  sin/cos of the three angles are evaluated on the host (glibc) and passed in `trig`.
+struct InstanceXformIn {
+    float shift[3], scale[3];
+    float trig[6];          // cos x, sin x, cos y, sin y, cos z, sin z
+    float box_lo[3], box_hi[3], centroid[3];
+    int root_ref, blas;
+};
+RT_HD void mat4_mul(const float a[4][4], const float b[4][4], float r[4][4]) {
+    for (int i = 0; i < 4; i++)
+        for (int j = 0; j < 4; j++) {
+            float sum = 0.0f;
+            for (int k = 0; k < 4; k++) sum += a[i][k] * b[k][j];
+            r[i][j] = sum;
+        }
+}
+RT_HD void mat4_identity(float m[4][4]) {
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) m[i][j] = i == j ? 1.0f : 0.0f;
+}
+RT_HD bool mat4_inverse(const float a[4][4], float out[4][4]) {
+    float w[4][8];
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 8; j++) w[i][j] = j < 4 ? a[i][j] : (j - 4 == i ? 1.0f : 0.0f);
+    for (int i = 0; i < 4; i++) {
+        float pivot = fabsf(w[i][i]);
+        int maxRow = i;
+        for (int p = i + 1; p < 4; p++) if (fabsf(w[p][i]) > pivot) { pivot = fabsf(w[p][i]); maxRow = p; }
+        if (near_zero(pivot)) return false;
+        if (maxRow != i) for (int j = 0; j < 8; j++) { const float t = w[maxRow][j]; w[maxRow][j] = w[i][j]; w[i][j] = t; }
+        for (int j = i + 1; j < 4; j++) {
+            const float factor = w[j][i] / w[i][i];
+            for (int k = i; k < 8; k++) w[j][k] -= factor * w[i][k];
+        }
+    }
+    for (int i = 3; i >= 0; i--) {
+        if (near_zero(w[i][i])) return false;
+        float factor = 1.0f / w[i][i];
+        for (int p = i; p < 8; p++) w[i][p] *= factor;
+        for (int j = i - 1; j >= 0; j--) {
+            factor = w[j][i];
+            for (int k = j; k < 8; k++) w[j][k] -= factor * w[i][k];
+        }
+    }
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) out[i][j] = w[i][4 + j];
+    return true;
+}
+// Range::length / BoundingBox::ensureVolume on one axis (reference include/Util/Range.cuh:59-65, BoundingBox.cuh:24-28)
+RT_HD void ensure_volume(float &lo, float &hi) {
+    const float len = (lo >= hi || feq(lo, hi)) ? 0.0f : hi - lo;
+    if (len < RT_EPS) { lo -= RT_EPS; hi += RT_EPS; }
+}
+RT_HD void instance_update(const InstanceXformIn &in, InstanceD &out, Aabb &wbox, f3 &wcentroid) {
+    float T[4][4], S[4][4], Rx[4][4], Ry[4][4], Rz[4][4], Rxy[4][4], R[4][4], TR[4][4], M[4][4], Minv[4][4];
+    mat4_identity(T); T[0][3] = in.shift[0]; T[1][3] = in.shift[1]; T[2][3] = in.shift[2];
+    mat4_identity(S); S[0][0] = in.scale[0]; S[1][1] = in.scale[1]; S[2][2] = in.scale[2];
+    mat4_identity(Rx); Rx[1][1] = in.trig[0]; Rx[1][2] = -in.trig[1]; Rx[2][1] = in.trig[1]; Rx[2][2] = in.trig[0];
+    mat4_identity(Ry); Ry[0][0] = in.trig[2]; Ry[0][2] = in.trig[3]; Ry[2][0] = -in.trig[3]; Ry[2][2] = in.trig[2];
+    mat4_identity(Rz); Rz[0][0] = in.trig[4]; Rz[0][1] = -in.trig[5]; Rz[1][0] = in.trig[5]; Rz[1][1] = in.trig[4];
+    mat4_mul(Rx, Ry, Rxy);
+    mat4_mul(Rxy, Rz, R);
+    mat4_mul(T, R, TR);
+    mat4_mul(TR, S, M);
+    if (!mat4_inverse(M, Minv)) for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) Minv[i][j] = M[i][j];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 4; j++) { out.fwd[4 * i + j] = M[i][j]; out.inv[4 * i + j] = Minv[i][j]; }
+    out.root_ref = in.root_ref; out.blas = in.blas; out._p0 = 0; out._p1 = 0;
+    // 8-corner world box; the point transform includes the reference's 4th-row terms only through rows 1..3
+    f3 lo = mk3(RT_INF, RT_INF, RT_INF), hi = mk3(-RT_INF, -RT_INF, -RT_INF);
+    for (int i = 0; i < 2; i++) for (int j = 0; j < 2; j++) for (int k = 0; k < 2; k++) {
+        const float x = i * in.box_hi[0] + (1.0f - i) * in.box_lo[0];
+        const float y = j * in.box_hi[1] + (1.0f - j) * in.box_lo[1];
+        const float z = k * in.box_hi[2] + (1.0f - k) * in.box_lo[2];
+        const f3 p = xf_point(out.fwd, mk3(x, y, z));
+        lo = mk3(rt_min(lo.x, p.x), rt_min(lo.y, p.y), rt_min(lo.z, p.z));
+        hi = mk3(rt_max(hi.x, p.x), rt_max(hi.y, p.y), rt_max(hi.z, p.z));
+    }
+    ensure_volume(lo.x, hi.x); ensure_volume(lo.y, hi.y); ensure_volume(lo.z, hi.z);
+    wbox.lo = lo; wbox.hi = hi;
+    wcentroid = xf_point(out.fwd, mk3(in.centroid[0], in.centroid[1], in.centroid[2]));
+}

@@ -1,0 +1,278 @@
+/*
+ * emul.cpp — TEST INFRASTRUCTURE ONLY (never part of librtb200.so, never used by the product path).
+ *
+ * Serial CPU execution of the product's OWN per-element device code: the headers under
+ * real-time-gpu-ray-tracer_b200/csrc/ are written __host__ __device__, so g++ compiles the very same
+ * Morton/Karras/refit/emit, traversal, intersection, RNG and shading functions that the CUDA kernels call.
+ * Purpose (there is no GPU in the development container):
+ *   1. `not gpu` tests check this code against the oracle before any GPU time is spent;
+ *   2. `gpu` tests use it as the "CPU twin" of the LBVH build: device topology must equal the serial result
+ *      bit for bit (same keys, same order, same children, same boxes).
+ */
+#define QUALIFIERS static inline
+#include <cuda_runtime.h>
+#include <curand_kernel.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <numeric>
+#include <thread>
+#include <vector>
+
+#include "../../real-time-gpu-ray-tracer_b200/csrc/host_scene.h"
+#include "../../real-time-gpu-ray-tracer_b200/csrc/rt_trace_core.h"
+#include "../../oracle/oracle_api.h"
+
+namespace {
+
+struct Lbvh {
+    int n = 0;
+    std::vector<Aabb> prim_box;
+    std::vector<uint64_t> keys;
+    std::vector<uint32_t> vals;
+    std::vector<int> left, right, parent, leaf_parent;
+    std::vector<Aabb> node_box;
+    std::vector<BvhNode2> nodes;
+    std::vector<int> seg_root;
+};
+
+int find_segment(const std::vector<uint32_t> &off, uint32_t j) {
+    int lo = 0, hi = (int) off.size() - 2;
+    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (off[mid] <= j) lo = mid; else hi = mid - 1; }
+    return lo;
+}
+
+// serial twin of LbvhBuilder::run_tree
+void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type, int leaf_mode) {
+    const int n = b.n;
+    const int n_segs = (int) seg_type.size();
+    std::vector<uint32_t> order(n);
+    std::iota(order.begin(), order.end(), 0u);
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t c) { return b.keys[a] < b.keys[c]; });
+    std::vector<uint64_t> sk(n);
+    for (int i = 0; i < n; i++) sk[i] = b.keys[order[i]];
+    b.keys = sk;
+    b.vals = order;
+    b.seg_root.assign(n_segs, 0);
+    const int m = n > 1 ? n - 1 : 0;
+    b.left.assign(m, 0); b.right.assign(m, 0); b.parent.assign(m, -1); b.leaf_parent.assign(n, -1);
+    b.node_box.resize(m); b.nodes.resize(m);
+    for (int i = 0; i < m; i++) {
+        const KarrasNode k = karras_node(b.keys.data(), n, i);
+        b.left[i] = k.left; b.right[i] = k.right;
+        if (k.left >= 0) b.parent[k.left] = i; else b.leaf_parent[~k.left] = i;
+        if (k.right >= 0) b.parent[k.right] = i; else b.leaf_parent[~k.right] = i;
+        const int seg = find_segment(seg_offset, (uint32_t) k.first);
+        if ((uint32_t) k.first == seg_offset[seg] && (uint32_t) k.last + 1u == seg_offset[seg + 1]) b.seg_root[seg] = i;
+    }
+    for (int s = 0; s < n_segs; s++)
+        if (seg_offset[s + 1] - seg_offset[s] == 1u)
+            b.seg_root[s] = leaf_mode == 0 ? make_leaf_ref(seg_type[s], seg_offset[s]) : make_leaf_ref(0u, b.vals[seg_offset[s]]);
+    // refit in post-order (explicit stack)
+    if (m > 0) {
+        std::vector<char> done(m, 0);
+        std::vector<int> st{0};
+        auto child_box = [&](int c) { return c >= 0 ? b.node_box[c] : b.prim_box[b.vals[~c]]; };
+        while (!st.empty()) {
+            const int i = st.back();
+            const int l = b.left[i], r = b.right[i];
+            const bool lready = l < 0 || done[l], rready = r < 0 || done[r];
+            if (lready && rready) {
+                b.node_box[i] = aabb_union(child_box(l), child_box(r));
+                done[i] = 1;
+                st.pop_back();
+            } else {
+                if (!lready) st.push_back(l);
+                if (!rready) st.push_back(r);
+            }
+        }
+        // nodes that belong to no segment (junk above the BLAS roots) are also reachable from node 0: done.
+        for (int i = 0; i < m; i++) {
+            Aabb bx[2];
+            int ref[2];
+            const int child[2] = {b.left[i], b.right[i]};
+            for (int c = 0; c < 2; c++) {
+                if (child[c] >= 0) { bx[c] = b.node_box[child[c]]; ref[c] = child[c]; }
+                else {
+                    const uint32_t pos = (uint32_t) ~child[c];
+                    bx[c] = b.prim_box[b.vals[pos]];
+                    ref[c] = leaf_mode == 0 ? make_leaf_ref(seg_type[find_segment(seg_offset, pos)], pos) : make_leaf_ref(0u, b.vals[pos]);
+                }
+            }
+            b.nodes[i] = make_node2(bx[0], ref[0], bx[1], ref[1]);
+        }
+    }
+}
+
+struct Emul {
+    HostScene hs;
+    Lbvh blas, tlas;
+    std::vector<TriIsect> leaf_tris;
+    std::vector<uint32_t> leaf_prims;
+    std::vector<InstanceD> instances;
+    std::vector<Aabb> wbox;
+    std::vector<f3> wcentroid;
+    SceneD sc{};
+};
+
+template<class F>
+void parallel_rows(int y0, int y1, int threads, F f) {
+    if (threads < 1) threads = 1;
+    std::atomic<int> next{y0};
+    std::vector<std::thread> pool;
+    for (int k = 0; k < threads; k++) pool.emplace_back([&]() { for (;;) { const int y = next.fetch_add(1); if (y >= y1) break; f(y); } });
+    for (auto &t: pool) t.join();
+}
+
+} // namespace
+
+extern "C" {
+
+void *emul_create(const oracle_scene *s, uint32_t flags) {
+    auto *e = new Emul();
+    HostScene &hs = e->hs;
+    hs.flags = flags;
+    if (!hs.commit_geometry(s->spheres, s->sphere_count, s->parallelograms, s->parallelogram_count, s->triangles, s->triangle_count).empty() ||
+        !hs.commit_materials(s->roughs, s->rough_count, s->metals, s->metal_count).empty() ||
+        !hs.configure_instances(s->instances, s->instance_count, s->xforms).empty() || !hs.plan_blas().empty() ||
+        !hs.configure_camera(s->window, s->camera).empty()) { delete e; return nullptr; }
+
+    // ---- BLAS batch (twin of LbvhBuilder::build_blas)
+    Lbvh &b = e->blas;
+    const int n = (int) hs.seg_offset.back(), n_segs = (int) hs.seg_type.size();
+    b.n = n;
+    b.prim_box.resize(n);
+    std::vector<Aabb> seg_bounds(n_segs);
+    for (auto &sb: seg_bounds) { sb.lo = mk3(RT_INF, RT_INF, RT_INF); sb.hi = mk3(-RT_INF, -RT_INF, -RT_INF); }
+    for (int j = 0; j < n; j++) {
+        const int seg = find_segment(hs.seg_offset, (uint32_t) j);
+        const uint32_t prim = hs.seg_first[seg] + ((uint32_t) j - hs.seg_offset[seg]);
+        Aabb box = hs.seg_type[seg] == 2u ? tri_aabb(&hs.tri_verts[(size_t) prim * 9]) : hs.seg_type[seg] == 0u ? sphere_aabb(hs.sphere_rec[prim]) : quad_aabb(hs.quad_rec[prim]);
+        box = aabb_pad(box);
+        b.prim_box[j] = box;
+        seg_bounds[seg] = aabb_union(seg_bounds[seg], box);
+    }
+    int seg_bits = 0;
+    while ((1 << seg_bits) < n_segs) seg_bits++;
+    int bits = morton_bits_for((size_t) n / std::max(1, n_segs));
+    if (3 * bits + seg_bits > 64) bits = (64 - seg_bits) / 3;
+    b.keys.resize(n);
+    for (int j = 0; j < n; j++) {
+        const int seg = find_segment(hs.seg_offset, (uint32_t) j);
+        b.keys[j] = ((uint64_t) seg << (3 * bits)) | morton_code(b.prim_box[j], seg_bounds[seg], bits);
+    }
+    build_tree(b, hs.seg_offset, hs.seg_type, 0);
+    e->leaf_prims.resize(n);
+    e->leaf_tris.resize(n);
+    for (int pos = 0; pos < n; pos++) {
+        const int seg = find_segment(hs.seg_offset, (uint32_t) pos);
+        const uint32_t prim = hs.seg_first[seg] + (b.vals[pos] - hs.seg_offset[seg]);
+        e->leaf_prims[pos] = prim;
+        if (hs.seg_type[seg] == 2u) {
+            const float *v = &hs.tri_verts[(size_t) prim * 9];
+            const f3 v0 = mk3(v[0], v[1], v[2]), e1 = mk3(v[3], v[4], v[5]) - v0, e2 = mk3(v[6], v[7], v[8]) - v0;
+            e->leaf_tris[pos].v0_id = make_float4(v0.x, v0.y, v0.z, u2f(prim));
+            e->leaf_tris[pos].e1 = make_float4(e1.x, e1.y, e1.z, 0.0f);
+            e->leaf_tris[pos].e2 = make_float4(e2.x, e2.y, e2.z, 0.0f);
+        }
+    }
+
+    // ---- instances + TLAS (twin of update_instances_and_tlas)
+    const int ni = (int) hs.inst_desc.size();
+    std::vector<InstanceXformIn> xin(ni);
+    hs.fill_xform_in(xin.data(), b.seg_root);
+    e->instances.resize(ni); e->wbox.resize(ni); e->wcentroid.resize(ni);
+    Lbvh &t = e->tlas;
+    t.n = ni;
+    t.prim_box.resize(ni);
+    Aabb scene;
+    scene.lo = mk3(RT_INF, RT_INF, RT_INF); scene.hi = mk3(-RT_INF, -RT_INF, -RT_INF);
+    for (int i = 0; i < ni; i++) {
+        instance_update(xin[i], e->instances[i], e->wbox[i], e->wcentroid[i]);
+        t.prim_box[i] = aabb_pad(e->wbox[i]);
+        scene = aabb_union(scene, t.prim_box[i]);
+    }
+    const int tbits = morton_bits_for((size_t) ni);
+    t.keys.resize(ni);
+    for (int i = 0; i < ni; i++) t.keys[i] = morton_code(t.prim_box[i], scene, tbits);
+    const std::vector<uint32_t> toff{0u, (uint32_t) ni}, ttype{0u};
+    build_tree(t, toff, ttype, 1);
+
+    SceneD &sc = e->sc;
+    sc.tlas_nodes = t.nodes.data(); sc.blas_nodes = b.nodes.data(); sc.instances = e->instances.data();
+    sc.leaf_tris = e->leaf_tris.data(); sc.leaf_prims = e->leaf_prims.data(); sc.tri_shade = hs.tri_shade.data();
+    sc.spheres = hs.sphere_rec.data(); sc.quads = hs.quad_rec.data();
+    sc.roughs = hs.roughs.data(); sc.metals = hs.metals.data(); sc.dielectrics = hs.dielectrics.data();
+    sc.tlas_root_ref = ni > 1 ? 0 : make_leaf_ref(0u, 0u);
+    return e;
+}
+
+void emul_destroy(void *h) { delete (Emul *) h; }
+
+// out: per pixel like the product planes; returns stack-overflow flag
+uint32_t emul_render(void *h, uint64_t seed, int y0, int y1, int threads, uint8_t *rgba8, float *radiance, uint64_t *rays,
+                     float *aov_t, int32_t *aov_inst, int32_t *aov_prim) {
+    Emul &e = *(Emul *) h;
+    const CameraD &cam = e.hs.cam;
+    std::atomic<uint64_t> total{0};
+    std::atomic<uint32_t> ovf{0};
+    parallel_rows(y0, y1, threads, [&](int y) {
+        uint64_t segs = 0;
+        for (uint32_t x = 0; x < cam.width; x++) {
+            const uint32_t pixelIndex = cam.pitch * (uint32_t) y + x;
+            curandStateXORWOW_t st;
+            curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &st);
+            RngState r{st.d, st.v[0], st.v[1], st.v[2], st.v[3], st.v[4]};
+            uint32_t overflow = 0;
+            const PixelOut o = render_pixel(e.sc, cam, x, (uint32_t) y, r, overflow);
+            if (overflow) ovf = 1;
+            segs += o.rays;
+            const size_t p = (size_t) y * cam.width + x;
+            if (radiance) { radiance[3 * p] = o.radiance.x; radiance[3 * p + 1] = o.radiance.y; radiance[3 * p + 2] = o.radiance.z; }
+            if (rgba8) { rgba8[4 * p] = to_byte(o.radiance.x); rgba8[4 * p + 1] = to_byte(o.radiance.y); rgba8[4 * p + 2] = to_byte(o.radiance.z); rgba8[4 * p + 3] = 255; }
+            if (aov_t) { aov_t[p] = o.aov_t; aov_inst[p] = o.aov_inst; aov_prim[p] = o.aov_prim; }
+        }
+        total += segs;
+    });
+    if (rays) *rays += total.load();
+    return ovf.load();
+}
+
+void emul_instances(void *h, float *o) {
+    Emul &e = *(Emul *) h;
+    for (size_t i = 0; i < e.instances.size(); i++) {
+        float *p = o + 33 * i;
+        memcpy(p, e.instances[i].fwd, 48);
+        memcpy(p + 12, e.instances[i].inv, 48);
+        p[24] = e.wbox[i].lo.x; p[25] = e.wbox[i].lo.y; p[26] = e.wbox[i].lo.z;
+        p[27] = e.wbox[i].hi.x; p[28] = e.wbox[i].hi.y; p[29] = e.wbox[i].hi.z;
+        p[30] = e.wcentroid[i].x; p[31] = e.wcentroid[i].y; p[32] = e.wcentroid[i].z;
+    }
+}
+
+void emul_camera(void *h, float *o) {
+    const CameraD &c = ((Emul *) h)->hs.cam;
+    const float v[20] = {c.pixelOrigin.x, c.pixelOrigin.y, c.pixelOrigin.z, c.pixelDx.x, c.pixelDx.y, c.pixelDx.z, c.pixelDy.x, c.pixelDy.y, c.pixelDy.z,
+                         c.camU.x, c.camU.y, c.camU.z, c.camV.x, c.camV.y, c.camV.z, 0, 0, 0, c.rcpSqrtSamples, (float) c.sqrtSamples};
+    memcpy(o, v, sizeof(v));
+}
+
+// LBVH arrays of the BLAS batch (which = 0) or the TLAS (which = 1); same layout as rt_read_lbvh
+void emul_lbvh(void *h, int which, size_t *n_prims, uint64_t *keys, uint32_t *vals, int32_t *left, int32_t *right, int32_t *parent, float *bounds) {
+    Emul &e = *(Emul *) h;
+    const Lbvh &b = which == 0 ? e.blas : e.tlas;
+    if (n_prims) *n_prims = (size_t) b.n;
+    const size_t m = b.n > 1 ? b.n - 1 : 0;
+    if (keys) memcpy(keys, b.keys.data(), (size_t) b.n * 8);
+    if (vals) memcpy(vals, b.vals.data(), (size_t) b.n * 4);
+    if (left && m) memcpy(left, b.left.data(), m * 4);
+    if (right && m) memcpy(right, b.right.data(), m * 4);
+    if (parent && m) memcpy(parent, b.parent.data(), m * 4);
+    if (bounds) for (size_t i = 0; i < m; i++) {
+        bounds[6 * i] = b.node_box[i].lo.x; bounds[6 * i + 1] = b.node_box[i].lo.y; bounds[6 * i + 2] = b.node_box[i].lo.z;
+        bounds[6 * i + 3] = b.node_box[i].hi.x; bounds[6 * i + 4] = b.node_box[i].hi.y; bounds[6 * i + 5] = b.node_box[i].hi.z;
+    }
+}
+
+} // extern "C"

@@ -1,0 +1,89 @@
+"""ctypes loader of tests/emul/libemul.so — the g++ build of the product's __host__ __device__ cores.
+TEST INFRASTRUCTURE ONLY (see tests/emul/emul.cpp)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+import oracle_ctypes as oc  # noqa: E402
+
+abi = oc.abi
+LIB = os.path.join(HERE, "emul", "libemul.so")
+
+
+def load():
+    if not os.path.exists(LIB):
+        subprocess.check_call(["make", "-C", os.path.join(HERE, "emul")])
+    lib = C.CDLL(LIB)
+    vp, u64, i32, sz = C.c_void_p, C.c_uint64, C.c_int, C.c_size_t
+    lib.emul_create.argtypes = [C.POINTER(oc.OracleScene), C.c_uint32]
+    lib.emul_create.restype = vp
+    lib.emul_destroy.argtypes = [vp]
+    lib.emul_render.argtypes = [vp, u64, i32, i32, i32, vp, vp, C.POINTER(u64), vp, vp, vp]
+    lib.emul_render.restype = C.c_uint32
+    lib.emul_instances.argtypes = [vp, vp]
+    lib.emul_camera.argtypes = [vp, vp]
+    lib.emul_lbvh.argtypes = [vp, i32, C.POINTER(sz), vp, vp, vp, vp, vp, vp]
+    return lib
+
+
+class Emul:
+    def __init__(self, sc, flags: int = 0):
+        self.lib = load()
+        self.sc = sc
+        s = oc.OracleScene(abi.ptr(sc.spheres), len(sc.spheres), abi.ptr(sc.parallelograms), len(sc.parallelograms),
+                           abi.ptr(sc.triangles), len(sc.triangles), abi.ptr(sc.roughs), len(sc.roughs),
+                           abi.ptr(sc.metals), len(sc.metals), abi.ptr(sc.instances), abi.ptr(sc.xforms), len(sc.instances),
+                           sc.window(), sc.camera_input(), 0)
+        self.h = self.lib.emul_create(C.byref(s), flags)
+        assert self.h, "emul_create failed"
+        self.W, self.H = sc.width, sc.height
+
+    def render(self, seed, threads=None):
+        img = np.zeros((self.H, self.W, 4), np.uint8)
+        rad = np.zeros((self.H, self.W, 3), np.float32)
+        t = np.zeros((self.H, self.W), np.float32)
+        inst = np.zeros((self.H, self.W), np.int32)
+        prim = np.zeros((self.H, self.W), np.int32)
+        rays = C.c_uint64(0)
+        ovf = self.lib.emul_render(self.h, seed, 0, self.H, threads or os.cpu_count() or 1, abi.ptr(img), abi.ptr(rad), C.byref(rays),
+                                   abi.ptr(t), abi.ptr(inst), abi.ptr(prim))
+        return dict(rgba8=img, radiance=rad, rays=rays.value, t=t, inst=inst, prim=prim, overflow=ovf)
+
+    def instances(self):
+        out = np.zeros((len(self.sc.instances), 33), np.float32)
+        self.lib.emul_instances(self.h, abi.ptr(out))
+        return out
+
+    def camera(self):
+        out = np.zeros(20, np.float32)
+        self.lib.emul_camera(self.h, abi.ptr(out))
+        return out
+
+    def lbvh(self, which=0):
+        nn = C.c_size_t()
+        self.lib.emul_lbvh(self.h, which, C.byref(nn), None, None, None, None, None, None)
+        n = nn.value
+        m = max(n - 1, 0)
+        keys, vals = np.zeros(n, np.uint64), np.zeros(n, np.uint32)
+        left, right, parent = np.zeros(m, np.int32), np.zeros(m, np.int32), np.zeros(m, np.int32)
+        bounds = np.zeros((m, 6), np.float32)
+        self.lib.emul_lbvh(self.h, which, C.byref(nn), abi.ptr(keys), abi.ptr(vals), abi.ptr(left), abi.ptr(right), abi.ptr(parent), abi.ptr(bounds))
+        return dict(keys=keys, prim_ids=vals, left=left, right=right, parent=parent, bounds=bounds)
+
+    def close(self):
+        if self.h:
+            self.lib.emul_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()

@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py — the reference's headline metric (Mrays/s, ms/frame at 1080p fixed spp; LBVH build ms) on BASELINE.json's
+config 2: synthetic 1 000 000-triangle mesh scene, 1920x1080, 64 spp, depth 10, rough/metal path tracing.
+
+  python bench.py --gpus 1 --steps K --warmup W            # our arm (CUDA, through the C-ABI)
+  torchrun ... bench.py --gpus N ...                       # N ranks: image tiles sharded, framebuffer gathered with NCCL
+  python bench.py --impl reference ...                     # reference arm: the reference's own CPU code on the host cores
+
+A step = one frame of the hot path (= one iteration of Renderer::startRender's loop, headless): per-frame instance
+update + TLAS rebuild + per-pixel RNG init + trace/shade + framebuffer.  Prints ONE JSON line (rank 0).
+"""
+from __future__ import annotations
+
+import argparse
+import concurrent.futures as cf
+import ctypes as C
+import importlib
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+SEED = 0x5EED
+METRIC = "Mrays/s (1M-triangle scene, 1920x1080, 64 spp, depth 10)"
+
+
+def workload(args):
+    pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    sc = pkg.scenes.c2(width=args.width, height=args.height, spp=args.spp, depth=args.depth, nx=args.nx, nz=args.nz)
+    cfg = {"workload": f"configs[1]: synthetic {len(sc.triangles)}-triangle height-field, {sc.width}x{sc.height}, {sc.sample_count} spp, "
+                       f"depth {sc.ray_trace_depth}, rough+metal, camera (0,6,9)->(0,0,0) fov 60, frame seed 0x5EED, XORWOW per-pixel streams",
+           "triangles": int(len(sc.triangles)), "width": sc.width, "height": sc.height, "spp": sc.sample_count, "depth": sc.ray_trace_depth,
+           "l2": "BVH + triangle records (~100 MB) exceed/approach L2 and every step re-traverses with 2M independent pixel streams; no L2 flush needed between steps (inputs larger than L2 slices touched per step)"}
+    return pkg, sc, cfg
+
+
+# ---------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, gpu_index: int):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for k, nme in enumerate(names):
+                    if r[3 + k].lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+class DevPtr:
+    """Zero-copy view of a librtb200 device plane for torch (plumbing for the NCCL gather)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def cpu_reference_sample(sc, rows, kind="ref"):
+    """Time the reference's own CPU implementation (oracle/_ref, else the port) on `rows` scan-lines of the
+    workload spread evenly over the image, one host thread per row.  Returns (rays, seconds, cores, build_ms, kind)."""
+    import oracle_ctypes as oc
+    if kind == "ref" and not os.path.exists(oc.REF_PATH):
+        kind = "port"
+    o = oc.Oracle(kind)
+    t0 = time.perf_counter()
+    h = o.scene(sc, 1234)
+    build_s = time.perf_counter() - t0
+    cores = os.cpu_count() or 1
+    ys = sorted(set(int(round(v)) for v in np.linspace(0, sc.height - 1, rows)))
+    rays_total = [0]
+
+    def one(y):
+        r = C.c_uint64(0)
+        o._render(h.h, SEED, y, y + 1, 1, None, None, C.byref(r))
+        return r.value
+    t0 = time.perf_counter()
+    with cf.ThreadPoolExecutor(max_workers=cores) as ex:
+        for v in ex.map(one, ys):
+            rays_total[0] += v
+    dt = time.perf_counter() - t0
+    timing = h.timing
+    info = {"blas_build_ms_1core": timing.blas_build_ms, "tlas_build_ms_1core": timing.tlas_build_ms, "scene_setup_s": build_s}
+    h.close()
+    return rays_total[0], dt, min(cores, len(ys)), info, ("reference" if kind == "ref" else "port"), len(ys)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pkg, sc, cfg = workload(args)
+    cores = os.cpu_count() or 1
+    budget = 150.0 / max(1, args.steps + args.warmup)           # seconds per step
+    rows = int(max(1, min(2 * cores, round(cores * budget / 5.0))))
+    import oracle_ctypes as oc
+    kind = "ref" if os.path.exists(oc.REF_PATH) else "port"
+    o = oc.Oracle(kind)
+    h = o.scene(sc, 1234)
+    ys_all = np.linspace(0, sc.height - 1, rows * (args.steps + args.warmup)).round().astype(int)
+
+    def step(k):
+        ys = ys_all[k * rows:(k + 1) * rows]
+        total = 0
+
+        def one(y):
+            r = C.c_uint64(0)
+            o._render(h.h, SEED, int(y), int(y) + 1, 1, None, None, C.byref(r))
+            return r.value
+        t0 = time.perf_counter()
+        with cf.ThreadPoolExecutor(max_workers=cores) as ex:
+            for v in ex.map(one, ys):
+                total += v
+        return total, time.perf_counter() - t0
+    for k in range(args.warmup):
+        step(k)
+    rays, secs = 0, 0.0
+    for k in range(args.warmup, args.warmup + args.steps):
+        r, s = step(k)
+        rays += r
+        secs += s
+    value = rays / secs / 1e6
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": min(cores, rows), "kind": "reference" if kind == "ref" else "port",
+                             "sample": f"{rows} full scan-lines ({sc.width} px x {sc.sample_count} spp, all bounces) per step, spread evenly over the frame, one host thread per line; "
+                                       f"host BLAS build {h.timing.blas_build_ms:.0f} ms on 1 core (not in the timed region)"},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    distributed = world > 1
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (our arm) needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if distributed:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg, sc, cfg = workload(args)
+    abi = pkg.abi
+
+    r = pkg.Renderer(device=local)
+    t0 = time.perf_counter()
+    st = r.commitScene(sc)
+    commit_s = time.perf_counter() - t0
+    tile_rows = args.tile_rows
+    if distributed:
+        r.setTileShard(rank, world, tile_rows)
+    W, H = sc.width, sc.height
+    ptr, nbytes = r.devicePointer(abi.BUF_RGBA8)
+    local_plane = torch.as_tensor(DevPtr(ptr, nbytes), device=f"cuda:{local}")
+    gathered = [torch.empty_like(local_plane) for _ in range(world)] if (distributed and rank == 0) else None
+    host_fb = torch.empty(W * H * 4, dtype=torch.uint8).pin_memory()
+    xf = sc.xforms.copy()
+
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def frame(k, read_back):
+        """one step; returns (rays, device_ms incl. gather, FrameOut)"""
+        if read_back:
+            r.setInstanceTransforms(xf)          # per-frame host input (reference: updateInstances + H2D, Renderer.cu:269-291)
+        out = r.renderFrame(k, SEED)
+        ms = out.render_ms
+        if distributed:
+            ev0.record()
+            dist.gather(local_plane, gathered, dst=0)
+            ev1.record()
+            ev1.synchronize()
+            ms += ev0.elapsed_time(ev1)
+        if read_back and rank == 0:
+            if distributed:
+                # tiles of rank q are rows [(k*world+q)*tile_rows ...): de-interleave on the device, one D2H copy
+                full = torch.stack(gathered).view(world, -1, tile_rows, W * 4).permute(1, 0, 2, 3).reshape(-1, W * 4)[:H].contiguous()
+                host_fb.copy_(full.view(-1), non_blocking=True)
+                torch.cuda.synchronize()
+            else:
+                r.lib.rt_read_framebuffer(r.ctx, abi.BUF_RGBA8, C.c_void_p(host_fb.data_ptr()), host_fb.numel())
+        return out.rays, ms, out
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-timed, inputs resident -------------------------------------------------------------------
+    for k in range(args.warmup):
+        frame(k, False)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    rays = 0
+    dev_ms = 0.0
+    trace_ms, rng_ms, tlas_ms = [], [], []
+    launches = 0
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        n, ms, out = frame(args.warmup + k, False)
+        rays += n
+        dev_ms += ms
+        trace_ms.append(out.trace_ms)
+        rng_ms.append(out.rng_ms)
+        tlas_ms.append(out.tlas_ms)
+        launches += out.kernel_launches
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- e2e: same steps through the public API with host buffers: transforms H2D, framebuffer D2H ---------------
+    barrier()
+    e_rays = 0
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        n, _, _ = frame(args.warmup + k, True)
+        e_rays += n
+    barrier()
+    e2e_s = time.perf_counter() - t0
+
+    tot = torch.tensor([float(rays), float(e_rays)], dtype=torch.float64, device=f"cuda:{local}")
+    mx = torch.tensor([dev_ms, e2e_s, wall_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if distributed:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    tot_rays, tot_e_rays = tot.tolist()
+    max_dev_ms, max_e2e_s, max_wall_ms = mx.tolist()
+
+    if rank == 0:
+        value = tot_rays / (max_dev_ms * 1e-3) / 1e6
+        e2e = tot_e_rays / max_e2e_s / 1e6
+        # ---- roofline of the dominant kernel (trace/shade): algorithmic bytes from an instrumented pass ----------
+        roof = None
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak, peak_src = float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        if world == 1:
+            rc = pkg.Renderer(device=local, flags=abi.FLAG_COUNT_TRAVERSAL)
+            rc.commitScene(sc)
+            co = rc.renderFrame(0, SEED)
+            rc.cleanup()
+            node_b, prim_b, inst_b, io_b = 64, 48, 64, 24 + 16 + 12
+            alg = co.node_fetches * node_b + co.prim_fetches * prim_b + co.instance_fetches * inst_b + W * H * io_b
+            t_kernel = statistics.mean(trace_ms) * 1e-3
+            achieved = alg / t_kernel / 1e9
+            traffic = None
+            tp = os.path.join(ROOT, "profiles", "traffic_latest.json")
+            if os.path.exists(tp):
+                try:
+                    traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+                except Exception:
+                    traffic = None
+            roof = {"bound": "hbm", "kernel": "render_pixels_kernel (trace+shade)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": alg, "kernel_ms": t_kernel * 1e3,
+                    "per_ray": {"node_fetches": co.node_fetches / co.rays, "prim_fetches": co.prim_fetches / co.rays,
+                                "instance_fetches": co.instance_fetches / co.rays, "bytes": alg / co.rays},
+                    "record_bytes": {"node": node_b, "triangle": prim_b, "instance": inst_b, "pixel_io": io_b}}
+        # ---- CPU baseline: the reference's own code on this box's host cores, bounded sample ---------------------
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            c_rays, c_s, c_cores, info, kind, nrows = cpu_reference_sample(sc, rows=max(4, min(4 * cores, 256)))
+            cpu = {"value": c_rays / c_s / 1e6, "unit": "Mrays/s", "cores": c_cores, "kind": kind,
+                   "sample": f"{nrows} full scan-lines ({W} px x {sc.sample_count} spp, all bounces) spread evenly over the frame, one host thread per line, {c_s:.1f} s",
+                   "host_bvh_build_ms_1core": info["blas_build_ms_1core"]}
+        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": max_dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": {**cfg, "parallelism": f"image tiles ({tile_rows} rows) x{world}, scene replicated, NCCL gather" if world > 1 else "single GPU"},
+                "rays_per_frame": tot_rays / args.steps, "wall_ms_per_step": max_wall_ms / args.steps,
+                "stage_ms": {"tlas_rebuild": statistics.mean(tlas_ms), "rng_init": statistics.mean(rng_ms), "trace": statistics.mean(trace_ms)},
+                "lbvh_build_ms": {"blas_1M_tris": st.blas_ms, "tlas": st.tlas_ms, "kernel_launches": st.kernel_launches,
+                                  "bytes_per_prim_algorithmic": 280, "achieved_gbs": 280 * st.primitive_count / max(st.blas_ms, 1e-6) / 1e6},
+                "commit_s": commit_s,
+                "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": int(len(sc.instances) * 92), "d2h_bytes_per_step": int(W * H * 4 + 64),
+                        "ms_per_step": 1e3 * max_e2e_s / args.steps,
+                        "what": "rt_set_instance_xforms(host) + rt_render_frame + rt_read_framebuffer(RGBA8 -> pinned host), host wall clock"},
+                "gpu_launches": int(launches), "clocks": clocks}
+        if roof:
+            line["roofline"] = roof
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    r.cleanup()
+    if distributed:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--spp", type=int, default=64)
+    ap.add_argument("--depth", type=int, default=10)
+    ap.add_argument("--nx", type=int, default=1000)
+    ap.add_argument("--nz", type=int, default=500)
+    ap.add_argument("--tile-rows", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -123,7 +123,10 @@ enum rt_flags {
     /* Record primary-hit AOVs (t, instance, primitive) of each pixel's first sample.              */
     RT_FLAG_RECORD_PRIMARY_AOV      = 1u << 1,
     /* Keep the binary LBVH arrays after the wide collapse so rt_read_lbvh can return them.        */
-    RT_FLAG_KEEP_LBVH               = 1u << 2
+    RT_FLAG_KEEP_LBVH               = 1u << 2,
+    /* Run the instrumented trace kernel: rt_frame_out.{node,prim,instance}_fetches are filled (the roofline's
+     * algorithmic-bytes figure).  Slower; never set for timed runs.                                  */
+    RT_FLAG_COUNT_TRAVERSAL         = 1u << 3
 };
 
 typedef struct rt_frame_out {
@@ -135,6 +138,9 @@ typedef struct rt_frame_out {
     float    trace_ms;        /* CUDA-event time of the trace/shade kernel                                 */
     uint32_t kernel_launches; /* kernels launched for this frame                                           */
     uint32_t stack_overflow;  /* != 0 if a traversal stack overflowed (reference has no check, Q15)         */
+    uint64_t node_fetches;    /* BVH node records fetched      (only with RT_FLAG_COUNT_TRAVERSAL)                  */
+    uint64_t prim_fetches;    /* primitive records fetched     (only with RT_FLAG_COUNT_TRAVERSAL)                  */
+    uint64_t instance_fetches;/* instance records fetched      (only with RT_FLAG_COUNT_TRAVERSAL)                  */
 } rt_frame_out;
 
 typedef struct rt_build_stats {
@@ -217,10 +223,11 @@ int rt_write_ppm(rt_ctx *ctx, const char *path);
 int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_rows, void *peer_rgba8);
 
 /* ---- acceleration-structure introspection (parity tests) ----------------------------------- */
-/* Binary LBVH of BLAS `blas_index` as built on the device: sorted Morton keys, sorted primitive
- * ids, Karras child/parent arrays.  Any output pointer may be NULL; *n_prims is always written.
+/* Binary LBVH as built on the device, for `which` = 0 (the BLAS batch: all BLASes share one sort and one
+ * Karras pass, segment id in the key's high bits) or 1 (the TLAS): sorted Morton keys, sorted build-primitive
+ * ids, Karras child/parent arrays, node boxes.  Any output pointer may be NULL; *n_prims is always written.
  * Children: value >= 0 -> internal node, value < 0 -> leaf ~value (position in sorted order).      */
-int rt_read_lbvh(rt_ctx *ctx, size_t blas_index, size_t *n_prims,
+int rt_read_lbvh(rt_ctx *ctx, size_t which, size_t *n_prims,
                  uint64_t *sorted_keys, uint32_t *sorted_prim_ids,
                  int32_t *left, int32_t *right, int32_t *parent, float *node_bounds /* 6 per node */);
 

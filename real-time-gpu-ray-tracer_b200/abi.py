@@ -21,6 +21,7 @@ ROUGH, METAL, DIELECTRIC = 0, 1, 2
 FLAG_FIX_PARALLELOGRAM_BBOX = 1 << 0
 FLAG_RECORD_PRIMARY_AOV = 1 << 1
 FLAG_KEEP_LBVH = 1 << 2
+FLAG_COUNT_TRAVERSAL = 1 << 3
 
 BUF_RGBA8, BUF_RADIANCE, BUF_PRIMARY_T, BUF_PRIMARY_INSTANCE, BUF_PRIMARY_PRIM = range(5)
 
@@ -60,7 +61,8 @@ class CameraInput(C.Structure):
 
 class FrameOut(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("primary_rays", C.c_uint64), ("render_ms", C.c_float), ("tlas_ms", C.c_float),
-                ("rng_ms", C.c_float), ("trace_ms", C.c_float), ("kernel_launches", C.c_uint32), ("stack_overflow", C.c_uint32)]
+                ("rng_ms", C.c_float), ("trace_ms", C.c_float), ("kernel_launches", C.c_uint32), ("stack_overflow", C.c_uint32),
+                ("node_fetches", C.c_uint64), ("prim_fetches", C.c_uint64), ("instance_fetches", C.c_uint64)]
 
 
 class BuildStats(C.Structure):

@@ -89,8 +89,8 @@ void alloc_frame(rt_ctx *c) {
     c->d_radiance.reserve(px * 3 + 3);
     c->d_rng.reserve(px + 1);
     if (c->flags & RT_FLAG_RECORD_PRIMARY_AOV) { c->d_aov_t.reserve(px + 1); c->d_aov_inst.reserve(px + 1); c->d_aov_prim.reserve(px + 1); }
-    c->d_counters.reserve(2);
-    c->h_counters.reserve(2);
+    c->d_counters.reserve(8);
+    c->h_counters.reserve(8);
 }
 
 void update_instances_and_tlas(rt_ctx *c) {
@@ -302,19 +302,23 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     fr.rng = ctx->d_rng.get();
     fr.ray_counter = ctx->d_counters.get();
     fr.overflow_flag = reinterpret_cast<unsigned int *>(ctx->d_counters.get() + 1);
+    fr.count_traversal = (ctx->flags & RT_FLAG_COUNT_TRAVERSAL) ? 1u : 0u;
     fr.shard_rank = ctx->shard_rank; fr.shard_world = ctx->shard_world; fr.tile_rows = ctx->tile_rows; fr.local_rows = ctx->local_rows;
 
-    CUDA_CHECK(cudaMemsetAsync(ctx->d_counters.get(), 0, 2 * sizeof(unsigned long long), s));
+    CUDA_CHECK(cudaMemsetAsync(ctx->d_counters.get(), 0, 8 * sizeof(unsigned long long), s));
     launch_rng_init(ctx->d_rng.get(), seed, ctx->hs.cam, fr, s);
     CUDA_CHECK(cudaEventRecord(ctx->ev[2], s));
     launch_render(sc, ctx->hs.cam, fr, s);
     CUDA_CHECK(cudaEventRecord(ctx->ev[3], s));
-    CUDA_CHECK(cudaMemcpyAsync(ctx->h_counters.get(), ctx->d_counters.get(), 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CUDA_CHECK(cudaMemcpyAsync(ctx->h_counters.get(), ctx->d_counters.get(), 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     CUDA_CHECK(cudaStreamSynchronize(s));
     if (out) {
         memset(out, 0, sizeof(*out));
         out->rays = ctx->h_counters.get()[0];
         out->stack_overflow = (uint32_t) ctx->h_counters.get()[1];
+        out->node_fetches = ctx->h_counters.get()[2];
+        out->prim_fetches = ctx->h_counters.get()[3];
+        out->instance_fetches = ctx->h_counters.get()[4];
         uint64_t rows = 0;
         for (uint32_t ly = 0; ly < ctx->local_rows; ly++) {
             const uint32_t gy = ((ly / ctx->tile_rows) * ctx->shard_world + ctx->shard_rank) * ctx->tile_rows + (ly % ctx->tile_rows);

@@ -25,6 +25,7 @@ __global__ void __launch_bounds__(256) rng_init_kernel(RngState *__restrict__ st
 }
 
 // v1: one thread per pixel, 8x4-pixel warps, all samples and bounces of the pixel in the thread
+template<bool COUNT>
 __global__ void __launch_bounds__(128) render_pixels_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
                                                             const __grid_constant__ FrameD fr) {
     // block = 4 warps, each warp an 8x4 pixel tile; blocks tile the (local) image in 16x8 pixel groups
@@ -34,12 +35,14 @@ __global__ void __launch_bounds__(128) render_pixels_kernel(const __grid_constan
     const uint32_t lx = bx * 16 + (warp & 1) * 8 + (lane & 7);
     const uint32_t ly = by * 8 + (warp >> 1) * 4 + (lane >> 3);
     uint32_t rays = 0, overflow = 0;
+    TravStats stats{0, 0, 0};
     if (lx < cam.width && ly < fr.local_rows) {
         const uint32_t gy = ((ly / fr.tile_rows) * fr.shard_world + fr.shard_rank) * fr.tile_rows + (ly % fr.tile_rows);
         if (gy < cam.height) {
             const uint32_t lp = ly * cam.width + lx;
-            const PixelOut o = render_pixel(sc, cam, lx, gy, fr.rng[lp], overflow);
+            const PixelOut o = render_pixel<COUNT>(sc, cam, lx, gy, fr.rng[lp], overflow);
             rays = o.rays;
+            stats = o.stats;
             fr.radiance[3 * (size_t) lp + 0] = o.radiance.x;
             fr.radiance[3 * (size_t) lp + 1] = o.radiance.y;
             fr.radiance[3 * (size_t) lp + 2] = o.radiance.z;
@@ -54,9 +57,22 @@ __global__ void __launch_bounds__(128) render_pixels_kernel(const __grid_constan
         rays += __shfl_xor_sync(0xffffffffu, rays, off);
         overflow |= __shfl_xor_sync(0xffffffffu, overflow, off);
     }
+    if (COUNT) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            stats.nodes += __shfl_xor_sync(0xffffffffu, stats.nodes, off);
+            stats.prims += __shfl_xor_sync(0xffffffffu, stats.prims, off);
+            stats.insts += __shfl_xor_sync(0xffffffffu, stats.insts, off);
+        }
+    }
     if (lane == 0) {
         if (rays) atomicAdd(fr.ray_counter, (unsigned long long) rays);
         if (overflow) atomicOr(fr.overflow_flag, 1u);
+        if (COUNT) {
+            atomicAdd(fr.ray_counter + 2, (unsigned long long) stats.nodes);
+            atomicAdd(fr.ray_counter + 3, (unsigned long long) stats.prims);
+            atomicAdd(fr.ray_counter + 4, (unsigned long long) stats.insts);
+        }
     }
 }
 
@@ -70,6 +86,7 @@ void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &c
 
 void launch_render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream) {
     const uint32_t tiles_x = (cam.width + 15) / 16, tiles_y = (fr.local_rows + 7) / 8;
-    render_pixels_kernel<<<tiles_x * tiles_y, 128, 0, stream>>>(sc, cam, fr);
+    if (fr.count_traversal) render_pixels_kernel<true><<<tiles_x * tiles_y, 128, 0, stream>>>(sc, cam, fr);
+    else render_pixels_kernel<false><<<tiles_x * tiles_y, 128, 0, stream>>>(sc, cam, fr);
     CUDA_CHECK(cudaGetLastError());
 }

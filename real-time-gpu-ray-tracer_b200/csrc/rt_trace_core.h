@@ -14,6 +14,9 @@ struct HitD {
 
 struct RaySlabs { f3 idir, ood; };
 
+// record fetches of one path/pixel, for the roofline's algorithmic-bytes figure (instrumented variant only)
+struct TravStats { uint32_t nodes, prims, insts; };
+
 RT_HD float safe_rcp(float d) {
     // BVH culling only (not parity-critical): keep 1/d finite so 0 * inf never appears in the slab test
     const float a = fabsf(d) < 1e-20f ? (d < 0.0f ? -1e-20f : 1e-20f) : d;
@@ -106,7 +109,8 @@ RT_HD void load_instance_inv(const SceneD &sc, int inst, float *inv, int &root) 
 
 // Closest hit of a world ray over [tmin, +inf): the job of TLAS::hit -> Instance::hit -> BLAS::hit
 // (reference src/AS/TLAS.cu:131-201, src/AS/Instance.cu:19-50, src/AS/BLAS.cu:119-206) on our own BVH.
-RT_HD void trace_closest(const SceneD &sc, const RayD &wray, float tmin, HitD &hit, uint32_t &overflow) {
+template<bool COUNT>
+RT_HD void trace_closest(const SceneD &sc, const RayD &wray, float tmin, HitD &hit, uint32_t &overflow, TravStats &stats) {
     hit.t = RT_INF; hit.u = 0.0f; hit.v = 0.0f; hit.inst = -1; hit.leaf = 0;
     int stack[RT_STACK_SIZE];
     int sp = 0;
@@ -117,6 +121,7 @@ RT_HD void trace_closest(const SceneD &sc, const RayD &wray, float tmin, HitD &h
     for (;;) {
         if (cur >= 0) {
             const BvhNode2 n = load_node2(inst < 0 ? sc.tlas_nodes : sc.blas_nodes, cur);
+            if (COUNT) stats.nodes++;
             float tn0, tf0, tn1, tf1;
             node2_test(n, slabs, tmin, hit.t, tn0, tf0, tn1, tf1);
             const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
@@ -137,6 +142,7 @@ RT_HD void trace_closest(const SceneD &sc, const RayD &wray, float tmin, HitD &h
         } else if (inst < 0) {
             // TLAS leaf: enter the instance
             inst = (int) ref_pos(cur);
+            if (COUNT) stats.insts++;
             float inv[12];
             int root;
             load_instance_inv(sc, inst, inv, root);
@@ -147,6 +153,7 @@ RT_HD void trace_closest(const SceneD &sc, const RayD &wray, float tmin, HitD &h
             cur = root;
             continue;
         } else {
+            if (COUNT) stats.prims++;
             leaf_test(sc, cur, ray, tmin, inst, hit);
         }
         if (sp == 0) break;
@@ -236,11 +243,13 @@ RT_HD uint8_t to_byte(float c) {
     return (uint8_t) (256.0f * g);
 }
 
-struct PixelOut { f3 radiance; uint32_t rays; float aov_t; int aov_inst, aov_prim; };
+struct PixelOut { f3 radiance; uint32_t rays; float aov_t; int aov_inst, aov_prim; TravStats stats; };
 
 // One pixel of the reference's `render` kernel (src/Global/Kernel.cu:116-143): all samples, all bounces.
+template<bool COUNT>
 RT_HD PixelOut render_pixel(const SceneD &sc, const CameraD &cam, uint32_t x, uint32_t y, RngState rng, uint32_t &overflow) {
     PixelOut out;
+    out.stats.nodes = 0; out.stats.prims = 0; out.stats.insts = 0;
     out.radiance = mk3(0.0f, 0.0f, 0.0f);
     out.rays = 0; out.aov_t = RT_INF; out.aov_inst = -1; out.aov_prim = -1;
     for (uint32_t si = 0; si < cam.sqrtSamples; si++) {
@@ -249,7 +258,7 @@ RT_HD PixelOut render_pixel(const SceneD &sc, const CameraD &cam, uint32_t x, ui
             f3 thr = mk3(1.0f, 1.0f, 1.0f);
             for (uint32_t depth = 0; depth < cam.depth; depth++) {
                 HitD hit;
-                trace_closest(sc, ray, RT_TMIN, hit, overflow);
+                trace_closest<COUNT>(sc, ray, RT_TMIN, hit, overflow, out.stats);
                 out.rays++;
                 if (si == 0 && sj == 0 && depth == 0 && hit.inst >= 0) {
                     out.aov_t = hit.t; out.aov_inst = hit.inst;

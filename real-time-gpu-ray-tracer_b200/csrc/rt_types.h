@@ -98,8 +98,9 @@ struct FrameD {
     int *aov_inst;
     int *aov_prim;
     const RngState *rng;   // per local pixel
-    unsigned long long *ray_counter;
+    unsigned long long *ray_counter;   // [0] rays [1] overflow flag [2] node fetches [3] primitive fetches [4] instance fetches
     unsigned int *overflow_flag;
+    uint32_t count_traversal;          // 1: run the instrumented variant (fills counters [2..4])
     // tile sharding: local row r -> global row
     uint32_t shard_rank, shard_world, tile_rows, local_rows;
     uint32_t rgba8_is_full_frame;   // 1: rgba8 indexed by GLOBAL pixel (peer store), 0: by local pixel

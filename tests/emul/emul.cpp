@@ -225,7 +225,7 @@ uint32_t emul_render(void *h, uint64_t seed, int y0, int y1, int threads, uint8_
             curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &st);
             RngState r{st.d, st.v[0], st.v[1], st.v[2], st.v[3], st.v[4]};
             uint32_t overflow = 0;
-            const PixelOut o = render_pixel(e.sc, cam, x, (uint32_t) y, r, overflow);
+            const PixelOut o = render_pixel<false>(e.sc, cam, x, (uint32_t) y, r, overflow);
             if (overflow) ovf = 1;
             segs += o.rays;
             const size_t p = (size_t) y * cam.width + x;

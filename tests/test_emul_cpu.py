@@ -1,0 +1,59 @@
+"""`not gpu` tests of the product's host logic and of its __host__ __device__ cores compiled by g++
+(tests/emul): the same traversal / intersection / shading / LBVH functions the CUDA kernels call must reproduce the
+oracle, so kernel bugs are separated from algorithm bugs before GPU time is spent."""
+import numpy as np
+import pytest
+
+import emul_ctypes as ec
+from conftest import parity_scenes
+
+SEED = 0x5EED
+
+
+@pytest.mark.parametrize("idx", range(5))
+def test_cores_match_oracle(pkg, port, idx):
+    sc = parity_scenes(pkg.scenes)[idx]
+    e = ec.Emul(sc)
+    r = e.render(SEED)
+    h = port.scene(sc, 5)
+    img, rad, rays = h.render(SEED)
+    t, inst, prim = h.primary(SEED)
+    assert r["overflow"] == 0 and r["rays"] == rays
+    assert np.array_equal(r["rgba8"], img) and np.array_equal(r["radiance"], rad)
+    assert np.array_equal(r["inst"], inst) and np.array_equal(r["prim"], prim) and np.array_equal(r["t"], t)
+    # host restatement of Instance::updateTransformArguments and calculateCameraProperties
+    assert np.array_equal(e.instances(), h.instances())
+    cam_e, cam_o = e.camera(), h.camera()
+    keep = [i for i in range(20) if i not in (15, 16, 17)]      # cameraW is not kept by the product
+    assert np.array_equal(cam_e[keep], cam_o[keep])
+
+
+@pytest.mark.parametrize("idx", [0, 2, 3, 4])
+def test_lbvh_invariants(pkg, idx):
+    sc = parity_scenes(pkg.scenes)[idx]
+    e = ec.Emul(sc)
+    for which in (0, 1):
+        b = e.lbvh(which)
+        n = len(b["keys"])
+        assert (np.diff(b["keys"].astype(np.uint64)) >= 0).all() if n > 1 else True          # sorted
+        assert sorted(b["prim_ids"].tolist()) == list(range(n))                                # a permutation
+        if n < 2:
+            continue
+        left, right, parent, bounds = b["left"], b["right"], b["parent"], b["bounds"]
+        leaves = sorted([~c for c in np.concatenate([left, right]) if c < 0])
+        assert leaves == list(range(n))                                                        # every primitive in exactly one leaf
+        inner = sorted([c for c in np.concatenate([left, right]) if c >= 0])
+        assert inner == list(range(1, n - 1))                                                  # every inner node has one parent
+        assert parent[0] == -1
+        for i in range(n - 1):
+            for c in (left[i], right[i]):
+                if c >= 0:
+                    assert parent[c] == i
+                    assert (bounds[c, :3] >= bounds[i, :3]).all() and (bounds[c, 3:] <= bounds[i, 3:]).all()   # parent box contains child
+
+
+def test_parallelogram_bbox_flag(pkg):
+    sc = pkg.scenes.c1b(width=64, height=36, spp=1, depth=1)
+    compat = ec.Emul(sc).render(SEED)
+    fixed = ec.Emul(sc, flags=pkg.abi.FLAG_FIX_PARALLELOGRAM_BBOX).render(SEED)
+    assert (fixed["inst"] == 0).sum() > (compat["inst"] == 0).sum()

@@ -189,7 +189,8 @@ def run_ours(args):
     pkg, sc, cfg = workload(args)
     abi = pkg.abi
 
-    r = pkg.Renderer(device=local)
+    base_flags = abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0
+    r = pkg.Renderer(device=local, flags=base_flags)
     t0 = time.perf_counter()
     st = r.commitScene(sc)
     commit_s = time.perf_counter() - t0
@@ -285,11 +286,11 @@ def run_ours(args):
         except Exception:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
         if world == 1:
-            rc = pkg.Renderer(device=local, flags=abi.FLAG_COUNT_TRAVERSAL)
+            rc = pkg.Renderer(device=local, flags=abi.FLAG_COUNT_TRAVERSAL | base_flags)
             rc.commitScene(sc)
             co = rc.renderFrame(0, SEED)
             rc.cleanup()
-            node_b, prim_b, inst_b, io_b = 64, 48, 64, 24 + 16 + 12
+            node_b, prim_b, inst_b, io_b = (64 if args.bvh2 else 80), 48, 64, 24 + 16 + 12
             alg = co.node_fetches * node_b + co.prim_fetches * prim_b + co.instance_fetches * inst_b + W * H * io_b
             t_kernel = statistics.mean(trace_ms) * 1e-3
             achieved = alg / t_kernel / 1e9
@@ -350,6 +351,7 @@ def main():
     ap.add_argument("--nz", type=int, default=500)
     ap.add_argument("--tile-rows", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--bvh2", action="store_true", help="comparison mode: traverse the binary LBVH instead of the wide BVH")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -126,7 +126,12 @@ enum rt_flags {
     RT_FLAG_KEEP_LBVH               = 1u << 2,
     /* Run the instrumented trace kernel: rt_frame_out.{node,prim,instance}_fetches are filled (the roofline's
      * algorithmic-bytes figure).  Slower; never set for timed runs.                                  */
-    RT_FLAG_COUNT_TRAVERSAL         = 1u << 3
+    RT_FLAG_COUNT_TRAVERSAL         = 1u << 3,
+    /* Comparison mode: traverse the binary LBVH (64-byte two-box nodes) instead of the compressed 8-wide BVH. */
+    RT_FLAG_TRAVERSE_BVH2           = 1u << 4,
+    /* Comparison mode: one thread per pixel runs all samples and bounces (the reference's kernel structure,
+     * src/Global/Kernel.cu:105-147) instead of the wavefront (shade/generate + persistent trace kernels).          */
+    RT_FLAG_MEGAKERNEL              = 1u << 5
 };
 
 typedef struct rt_frame_out {
@@ -138,6 +143,8 @@ typedef struct rt_frame_out {
     float    trace_ms;        /* CUDA-event time of the trace/shade kernel                                 */
     uint32_t kernel_launches; /* kernels launched for this frame                                           */
     uint32_t stack_overflow;  /* != 0 if a traversal stack overflowed (reference has no check, Q15)         */
+    uint32_t waves;           /* wavefront iterations of this frame (0 in megakernel mode)                  */
+    uint32_t _pad;
     uint64_t node_fetches;    /* BVH node records fetched      (only with RT_FLAG_COUNT_TRAVERSAL)                  */
     uint64_t prim_fetches;    /* primitive records fetched     (only with RT_FLAG_COUNT_TRAVERSAL)                  */
     uint64_t instance_fetches;/* instance records fetched      (only with RT_FLAG_COUNT_TRAVERSAL)                  */
@@ -230,6 +237,11 @@ int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_
 int rt_read_lbvh(rt_ctx *ctx, size_t which, size_t *n_prims,
                  uint64_t *sorted_keys, uint32_t *sorted_prim_ids,
                  int32_t *left, int32_t *right, int32_t *parent, float *node_bounds /* 6 per node */);
+
+/* Compressed 8-wide BVH as traversed by the render kernels, `which` as above.  nodes: 80 bytes per node (layout in
+ * csrc/rt_types.h BvhNode8), leaf_prims: per leaf-order position the original primitive index (BLAS batch) or the
+ * instance index (TLAS).  Roots: node s for BLAS s of the batch, node 0 for the TLAS.  Either pointer may be NULL. */
+int rt_read_wide_bvh(rt_ctx *ctx, size_t which, size_t *n_nodes, size_t *n_leaf_prims, void *nodes, uint32_t *leaf_prims);
 
 /* ---- VTK particle-mesh series (Renderer::configureVTKFiles include/Global/Renderer.cuh:113,
  *      src/Global/Renderer.cu:394-443; VTKReader src/Global/VTKReader.cu:16-220) ------------------ */

@@ -22,6 +22,8 @@ FLAG_FIX_PARALLELOGRAM_BBOX = 1 << 0
 FLAG_RECORD_PRIMARY_AOV = 1 << 1
 FLAG_KEEP_LBVH = 1 << 2
 FLAG_COUNT_TRAVERSAL = 1 << 3
+FLAG_TRAVERSE_BVH2 = 1 << 4
+FLAG_MEGAKERNEL = 1 << 5
 
 BUF_RGBA8, BUF_RADIANCE, BUF_PRIMARY_T, BUF_PRIMARY_INSTANCE, BUF_PRIMARY_PRIM = range(5)
 
@@ -62,7 +64,7 @@ class CameraInput(C.Structure):
 class FrameOut(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("primary_rays", C.c_uint64), ("render_ms", C.c_float), ("tlas_ms", C.c_float),
                 ("rng_ms", C.c_float), ("trace_ms", C.c_float), ("kernel_launches", C.c_uint32), ("stack_overflow", C.c_uint32),
-                ("node_fetches", C.c_uint64), ("prim_fetches", C.c_uint64), ("instance_fetches", C.c_uint64)]
+                ("waves", C.c_uint32), ("_pad", C.c_uint32), ("node_fetches", C.c_uint64), ("prim_fetches", C.c_uint64), ("instance_fetches", C.c_uint64)]
 
 
 class BuildStats(C.Structure):
@@ -87,7 +89,7 @@ EXPORTS = [
     "rt_commit_geometry", "rt_commit_materials", "rt_commit_dielectrics", "rt_configure_instances",
     "rt_build_acceleration_structure", "rt_get_build_stats", "rt_configure_camera",
     "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm",
-    "rt_set_tile_shard", "rt_read_lbvh", "rt_load_vtk_series", "rt_set_vtk_frame",
+    "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame",
 ]
 
 _lib = None
@@ -125,6 +127,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_write_ppm.argtypes = [vp, C.c_char_p]
     lib.rt_set_tile_shard.argtypes = [vp, u32, u32, u32, vp]
     lib.rt_read_lbvh.argtypes = [vp, sz, C.POINTER(sz), vp, vp, vp, vp, vp, vp]
+    lib.rt_read_wide_bvh.argtypes = [vp, sz, C.POINTER(sz), C.POINTER(sz), vp, vp]
     lib.rt_load_vtk_series.argtypes = [vp, C.c_char_p, C.POINTER(sz)]
     lib.rt_set_vtk_frame.argtypes = [vp, sz]
     for name in EXPORTS:
@@ -145,3 +148,31 @@ def ptr(a: np.ndarray | None):
         return None
     assert a.flags["C_CONTIGUOUS"]
     return a.ctypes.data_as(C.c_void_p)
+
+
+def canonical_wide_bvh(nodes: np.ndarray, leaf_prims: np.ndarray, roots) -> list:
+    """Layout-independent form of a compressed 8-wide BVH (csrc/rt_types.h BvhNode8): a pre-order walk from `roots`
+    listing, per node, the 18 words that do not depend on memory placement (origin, exponents/imask, meta, quantised
+    boxes) and the primitive ids of its leaf children in slot order.  nodes: (N, 20) uint32."""
+    out = []
+    stack = list(reversed(list(roots)))
+    while stack:
+        i = stack.pop()
+        n = nodes[i]
+        child_base, prim_base = int(n[4]), int(n[5])
+        meta = [(int(n[6 + (s >> 2)]) >> (8 * (s & 3))) & 0xFF for s in range(8)]
+        imask = int(n[3]) >> 24
+        prims, kids = [], []
+        for s in range(8):
+            m = meta[s]
+            if m == 0:
+                continue
+            if imask & (1 << s):
+                kids.append(child_base + bin(imask & ((1 << s) - 1)).count("1"))
+            else:
+                cnt = bin(m >> 5).count("1")
+                off = m & 0x1F
+                prims.append(tuple(int(v) for v in leaf_prims[prim_base + off: prim_base + off + cnt]))
+        out.append((tuple(int(v) for v in n[[0, 1, 2, 3, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17, 18, 19]]), tuple(prims)))
+        stack.extend(reversed(kids))
+    return out

@@ -6,6 +6,7 @@
 #include "host_scene.h"
 #include "render.h"
 #include "vtk_reader.h"
+#include "wave.h"
 
 #include <cmath>
 #include <cstring>
@@ -38,6 +39,7 @@ struct rt_ctx {
     DeviceBuffer<float4> d_wcentroid;
     PinnedBuffer<InstanceXformIn> h_xform_in;
     LbvhBuilder blas, tlas;
+    WaveRenderer wave;
     bool geometry_committed = false, materials_committed = false, instances_configured = false, built = false, camera_set = false;
     rt_build_stats build_stats{};
 
@@ -135,6 +137,9 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
         delete c;
         return RT_ERR_CUDA;
     }
+    if (const char *e = getenv("RTB200_SLOTS")) c->wave.slots_override = (uint32_t) strtoul(e, nullptr, 0);
+    if (const char *e = getenv("RTB200_REFILL_MIN")) c->wave.refill_min = atoi(e);
+    if (const char *e = getenv("RTB200_NODE_MIN")) c->wave.node_min = atoi(e);
     *out = c;
     return RT_OK;
 }
@@ -236,8 +241,11 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     st.blas_count = hs.seg_type.size();
     st.primitive_count = n_prims;
     st.lbvh_nodes = n_prims > 0 ? n_prims - 1 : 0;
-    st.wide_nodes = st.lbvh_nodes;
-    st.node_bytes = ctx->blas.node_bytes() + ctx->tlas.node_bytes();
+    uint32_t wc[4] = {0, 0, 0, 0}, wt[4] = {0, 0, 0, 0};
+    CUDA_CHECK(cudaMemcpy(wc, ctx->blas.wide_counters(), sizeof(wc), cudaMemcpyDeviceToHost));
+    CUDA_CHECK(cudaMemcpy(wt, ctx->tlas.wide_counters(), sizeof(wt), cudaMemcpyDeviceToHost));
+    st.wide_nodes = wc[0];
+    st.node_bytes = (uint64_t) (wc[0] + wt[0]) * sizeof(BvhNode8);
     st.prim_bytes = hs.prim_bytes();
     st.kernel_launches = ctx->blas.launches + ctx->tlas.launches + 2;
     ctx->built = true;
@@ -290,6 +298,11 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     sc.metals = ctx->d_metals.get();
     sc.dielectrics = ctx->d_dielectrics.get();
     sc.tlas_root_ref = ctx->hs.inst_desc.size() > 1 ? 0 : make_leaf_ref(0u, 0u);
+    sc.tlas_nodes8 = ctx->tlas.nodes8();
+    sc.blas_nodes8 = ctx->blas.nodes8();
+    sc.tlas_leaf_inst = ctx->tlas.leaf_prims8();
+    sc.leaf_tris8 = ctx->blas.leaf_tris8();
+    sc.leaf_prims8 = ctx->blas.leaf_prims8();
 
     FrameD fr{};
     fr.rgba8 = ctx->peer_rgba8 ? (uint8_t *) ctx->peer_rgba8 : ctx->d_rgba8.get();
@@ -303,18 +316,27 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     fr.ray_counter = ctx->d_counters.get();
     fr.overflow_flag = reinterpret_cast<unsigned int *>(ctx->d_counters.get() + 1);
     fr.count_traversal = (ctx->flags & RT_FLAG_COUNT_TRAVERSAL) ? 1u : 0u;
+    fr.traverse_bvh2 = (ctx->flags & RT_FLAG_TRAVERSE_BVH2) ? 1u : 0u;
     fr.shard_rank = ctx->shard_rank; fr.shard_world = ctx->shard_world; fr.tile_rows = ctx->tile_rows; fr.local_rows = ctx->local_rows;
 
     CUDA_CHECK(cudaMemsetAsync(ctx->d_counters.get(), 0, 8 * sizeof(unsigned long long), s));
     launch_rng_init(ctx->d_rng.get(), seed, ctx->hs.cam, fr, s);
     CUDA_CHECK(cudaEventRecord(ctx->ev[2], s));
-    launch_render(sc, ctx->hs.cam, fr, s);
+    WaveStats ws{};
+    const bool mega = ctx->flags & RT_FLAG_MEGAKERNEL;
+    if (mega) {
+        launch_render(sc, ctx->hs.cam, fr, s);
+    } else {
+        ctx->wave.mode = 0;   // TODO wide trace kernel
+        ctx->wave.render(sc, ctx->hs.cam, fr, s, ctx->sm_count, ws);
+    }
     CUDA_CHECK(cudaEventRecord(ctx->ev[3], s));
     CUDA_CHECK(cudaMemcpyAsync(ctx->h_counters.get(), ctx->d_counters.get(), 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     CUDA_CHECK(cudaStreamSynchronize(s));
     if (out) {
         memset(out, 0, sizeof(*out));
-        out->rays = ctx->h_counters.get()[0];
+        out->rays = mega ? ctx->h_counters.get()[0] : ws.rays;
+        out->waves = ws.waves;
         out->stack_overflow = (uint32_t) ctx->h_counters.get()[1];
         out->node_fetches = ctx->h_counters.get()[2];
         out->prim_fetches = ctx->h_counters.get()[3];
@@ -329,7 +351,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
         CUDA_CHECK(cudaEventElapsedTime(&out->tlas_ms, ctx->ev[0], ctx->ev[1]));
         CUDA_CHECK(cudaEventElapsedTime(&out->rng_ms, ctx->ev[1], ctx->ev[2]));
         CUDA_CHECK(cudaEventElapsedTime(&out->trace_ms, ctx->ev[2], ctx->ev[3]));
-        out->kernel_launches = ctx->tlas.launches + 2 /*instance update*/ + 2 /*rng + render*/;
+        out->kernel_launches = ctx->tlas.launches + 2 /*instance update*/ + 1 /*rng*/ + (mega ? 1 : ws.launches);
     }
     RT_API_END(ctx)
 }
@@ -419,6 +441,22 @@ int rt_read_lbvh(rt_ctx *ctx, size_t which, size_t *n_prims, uint64_t *sorted_ke
         }
     }
     CUDA_CHECK(cudaStreamSynchronize(s));
+    RT_API_END(ctx)
+}
+
+int rt_read_wide_bvh(rt_ctx *ctx, size_t which, size_t *n_nodes, size_t *n_leaf_prims, void *nodes, uint32_t *leaf_prims) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->built) return fail(ctx, RT_ERR_STATE, "rt_read_wide_bvh: build first");
+    if (which > 1) return fail(ctx, RT_ERR_ARGUMENT, "rt_read_wide_bvh: which = 0 (BLAS batch) or 1 (TLAS)");
+    LbvhBuilder &b = which == 0 ? ctx->blas : ctx->tlas;
+    uint32_t wc[4];
+    CUDA_CHECK(cudaMemcpyAsync(wc, b.wide_counters(), sizeof(wc), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    if (n_nodes) *n_nodes = wc[0];
+    if (n_leaf_prims) *n_leaf_prims = (size_t) b.n_prims();
+    if (nodes) CUDA_CHECK(cudaMemcpyAsync(nodes, b.nodes8(), (size_t) wc[0] * sizeof(BvhNode8), cudaMemcpyDeviceToHost, ctx->stream));
+    if (leaf_prims) CUDA_CHECK(cudaMemcpyAsync(leaf_prims, b.leaf_prims8(), (size_t) b.n_prims() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     RT_API_END(ctx)
 }
 

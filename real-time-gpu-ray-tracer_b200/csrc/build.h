@@ -4,6 +4,7 @@
 
 #include "device_util.h"
 #include "rt_build_core.h"
+#include "rt_wide_core.h"
 
 #include <algorithm>
 #include <cstdint>
@@ -37,7 +38,13 @@ public:
     void prepare_tlas(int n_instances);
     void build_tlas(int n_instances, int morton_bits, cudaStream_t stream, int sm_count);
 
-    // results (device)
+    // results (device): the compressed 8-wide BVH the render kernels traverse (root of segment s = node s) ...
+    const BvhNode8 *nodes8() const { return nodes8_.get(); }
+    const TriIsect *leaf_tris8() const { return leaf_tris8_.get(); }
+    const uint32_t *leaf_prims8() const { return leaf_prims8_.get(); }   // BLAS: original primitive index; TLAS: instance index
+    const uint32_t *wide_counters() const { return wide_counters_.get(); } // [0] wide nodes, [1] leaf primitives, [2] finished
+    size_t node8_capacity() const { return (size_t) n_ + (size_t) n_segs_; }
+    // ... and the binary LBVH it was collapsed from (kept for introspection and the BVH2 comparison kernel)
     const BvhNode2 *nodes() const { return nodes_.get(); }
     const TriIsect *leaf_tris() const { return leaf_tris_.get(); }
     const uint32_t *leaf_prims() const { return leaf_prims_.get(); }
@@ -63,6 +70,7 @@ public:
 private:
     void reserve(int n, int n_segs, bool tris);
     void run_tree(int n, int n_segs, int key_bits, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count);
+    void collapse_wide(int n, int n_segs, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count);   // kernels_wide.cu
     int n_ = 0, n_segs_ = 0;
     RadixSorter sorter_;
     DeviceBuffer<float4> prim_lo_, prim_hi_, node_lo_, node_hi_;
@@ -71,6 +79,12 @@ private:
     DeviceBuffer<uint32_t> vals_a_, vals_b_;
     DeviceBuffer<int> left_, right_, parent_, leaf_parent_, flags_, seg_root_;
     DeviceBuffer<BvhNode2> nodes_;
+    DeviceBuffer<int2> range_;
+    DeviceBuffer<int> queue_;
+    DeviceBuffer<uint32_t> wide_counters_, leaf_pos8_, leaf_prims8_;
+    DeviceBuffer<BvhNode8> nodes8_;
+    DeviceBuffer<TriIsect> leaf_tris8_;
+    int collapse_blocks_per_sm_ = 0;
     DeviceBuffer<TriIsect> leaf_tris_;
     DeviceBuffer<uint32_t> leaf_prims_;
     uint64_t *keys_ = nullptr, *keys_alt_ = nullptr;

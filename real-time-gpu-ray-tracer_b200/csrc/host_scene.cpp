@@ -249,6 +249,8 @@ void HostScene::fill_xform_in(InstanceXformIn *out, const std::vector<int> &seg_
         o.centroid[0] = inst_centroid[i].x; o.centroid[1] = inst_centroid[i].y; o.centroid[2] = inst_centroid[i].z;
         o.root_ref = seg_root[inst_blas[i]];
         o.blas = inst_blas[i];
+        o.root8 = inst_blas[i];                 // the wide root of BLAS s is wide node s (kernels_wide.cu)
+        o.prim_type = (int) inst_desc[i].type;
     }
 }
 

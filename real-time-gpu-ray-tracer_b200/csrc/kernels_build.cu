@@ -106,12 +106,13 @@ __global__ void __launch_bounds__(BT) morton_kernel(const float4 *__restrict__ p
 // K3: Karras hierarchy over the sorted keys
 __global__ void __launch_bounds__(BT) karras_kernel(const uint64_t *__restrict__ keys, int n, const uint32_t *__restrict__ seg_offset, int n_segs,
                                                     int *__restrict__ left, int *__restrict__ right, int *__restrict__ parent,
-                                                    int *__restrict__ leaf_parent, int *__restrict__ seg_root) {
+                                                    int *__restrict__ leaf_parent, int *__restrict__ seg_root, int2 *__restrict__ range) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     const KarrasNode k = karras_node(keys, n, i);
     left[i] = k.left;
     right[i] = k.right;
+    range[i] = make_int2(k.first, k.last);
     if (k.left >= 0) parent[k.left] = i; else leaf_parent[~k.left] = i;
     if (k.right >= 0) parent[k.right] = i; else leaf_parent[~k.right] = i;
     if (i == 0) parent[0] = -1;
@@ -254,6 +255,12 @@ void LbvhBuilder::reserve(int n, int n_segs, bool tris) {
     leaf_parent_.reserve(n); seg_root_.reserve(n_segs);
     leaf_prims_.reserve(n);
     if (tris) leaf_tris_.reserve(n);
+    range_.reserve(m);
+    queue_.reserve((size_t) n + n_segs);
+    nodes8_.reserve((size_t) n + n_segs);
+    wide_counters_.reserve(4);
+    leaf_pos8_.reserve(n); leaf_prims8_.reserve(n);
+    if (tris) leaf_tris8_.reserve(n);
 }
 
 void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count) {
@@ -262,7 +269,7 @@ void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const
         sorter_.sort(keys_, keys_alt_, vals_, vals_alt_, n, key_bits, stream, sm_count, launches);
         CUDA_CHECK(cudaMemsetAsync(flags_.get(), 0, (size_t) (n - 1) * sizeof(int), stream));
         karras_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(keys_, n, seg_offset_.get(), n_segs, left_.get(), right_.get(), parent_.get(),
-                                                           leaf_parent_.get(), seg_root_.get());
+                                                           leaf_parent_.get(), seg_root_.get(), range_.get());
         refit_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(), parent_.get(),
                                                       leaf_parent_.get(), n, flags_.get(), node_lo_.get(), node_hi_.get());
         emit_nodes_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(),
@@ -278,6 +285,7 @@ void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const
         launches++;
     }
     CUDA_CHECK(cudaGetLastError());
+    collapse_wide(n, n_segs, leaf_mode, geo, stream, sm_count);
 }
 
 void LbvhBuilder::build_blas(const GeometryD &geo, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type,

@@ -3,7 +3,7 @@
 
 #include <curand_kernel.h>
 
-#include "rt_trace_core.h"
+#include "rt_pixel.h"
 
 namespace {
 
@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) rng_init_kernel(RngState *__restrict__ st
 }
 
 // v1: one thread per pixel, 8x4-pixel warps, all samples and bounces of the pixel in the thread
-template<bool COUNT>
+template<bool COUNT, bool WIDE>
 __global__ void __launch_bounds__(128) render_pixels_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
                                                             const __grid_constant__ FrameD fr) {
     // block = 4 warps, each warp an 8x4 pixel tile; blocks tile the (local) image in 16x8 pixel groups
@@ -36,11 +36,13 @@ __global__ void __launch_bounds__(128) render_pixels_kernel(const __grid_constan
     const uint32_t ly = by * 8 + (warp >> 1) * 4 + (lane >> 3);
     uint32_t rays = 0, overflow = 0;
     TravStats stats{0, 0, 0};
+    // per-thread traversal stacks interleaved in shared memory: entry k of thread t at [k * 128 + t]
+    __shared__ uint2 stack_mem[WIDE ? RT_WIDE_STACK * 128 : 1];
     if (lx < cam.width && ly < fr.local_rows) {
         const uint32_t gy = ((ly / fr.tile_rows) * fr.shard_world + fr.shard_rank) * fr.tile_rows + (ly % fr.tile_rows);
         if (gy < cam.height) {
             const uint32_t lp = ly * cam.width + lx;
-            const PixelOut o = render_pixel<COUNT>(sc, cam, lx, gy, fr.rng[lp], overflow);
+            const PixelOut o = render_pixel<COUNT, WIDE>(sc, cam, lx, gy, fr.rng[lp], overflow, stack_mem + (WIDE ? threadIdx.x : 0), 128);
             rays = o.rays;
             stats = o.stats;
             fr.radiance[3 * (size_t) lp + 0] = o.radiance.x;
@@ -86,7 +88,13 @@ void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &c
 
 void launch_render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream) {
     const uint32_t tiles_x = (cam.width + 15) / 16, tiles_y = (fr.local_rows + 7) / 8;
-    if (fr.count_traversal) render_pixels_kernel<true><<<tiles_x * tiles_y, 128, 0, stream>>>(sc, cam, fr);
-    else render_pixels_kernel<false><<<tiles_x * tiles_y, 128, 0, stream>>>(sc, cam, fr);
+    const unsigned grid = tiles_x * tiles_y;
+    if (fr.traverse_bvh2) {
+        if (fr.count_traversal) render_pixels_kernel<true, false><<<grid, 128, 0, stream>>>(sc, cam, fr);
+        else render_pixels_kernel<false, false><<<grid, 128, 0, stream>>>(sc, cam, fr);
+    } else {
+        if (fr.count_traversal) render_pixels_kernel<true, true><<<grid, 128, 0, stream>>>(sc, cam, fr);
+        else render_pixels_kernel<false, true><<<grid, 128, 0, stream>>>(sc, cam, fr);
+    }
     CUDA_CHECK(cudaGetLastError());
 }

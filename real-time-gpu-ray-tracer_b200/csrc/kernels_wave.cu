@@ -1,0 +1,340 @@
+// kernels_wave.cu — wavefront path tracer: per wave one SHADE/GENERATE kernel (thread per slot) and one persistent
+// TRACE kernel (warps pull rays from the wave's queue, lanes are refilled as their rays finish).
+//
+//   wave_shade : consumes the hit of the slot's previous ray — hit record, Rough/Metal::scatter, rayColor's
+//                bookkeeping (reference src/Global/Kernel.cu:64-100), sample accumulation and stratified primary-ray
+//                generation (Kernel.cu:119-143), pixel write-out (Color3::castToUchar4) — then queues the slot's next
+//                ray.  The per-pixel XORWOW stream is advanced exactly in the reference's order.
+//   wave_trace : closest hit (the job of TLAS::hit, src/AS/TLAS.cu:131-201) for every queued ray.
+#include "wave.h"
+
+#include "rt_pixel.h"
+
+#include <algorithm>
+
+namespace {
+
+constexpr int SHADE_THREADS = 256;
+constexpr uint32_t SLOT_IDLE = 0xFFFFFFFFu;
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+// tile-major pixel id -> local pixel coordinates (8x4 tiles, so that a warp's 32 consecutive ids form one tile)
+__device__ __forceinline__ void pixel_coords(uint32_t pid, uint32_t tiles_x, uint32_t &lx, uint32_t &ly) {
+    const uint32_t tile = pid >> 5, in = pid & 31u;
+    lx = (tile % tiles_x) * 8u + (in & 7u);
+    ly = (tile / tiles_x) * 4u + (in >> 3);
+}
+__device__ __forceinline__ uint32_t global_row(const FrameD &fr, uint32_t ly) {
+    return ((ly / fr.tile_rows) * fr.shard_world + fr.shard_rank) * fr.tile_rows + (ly % fr.tile_rows);
+}
+
+// warp-aggregated append: every lane with `want` gets a distinct index from *counter (one atomic per warp)
+__device__ __forceinline__ uint32_t warp_append(uint32_t *counter, bool want) {
+    const uint32_t mask = __ballot_sync(0xffffffffu, want);
+    if (mask == 0u) return 0u;
+    const uint32_t leader = __ffs(mask) - 1u;
+    uint32_t base = 0;
+    if (lane_id() == leader) base = atomicAdd(counter, (uint32_t) __popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t) __popc(mask & ((1u << lane_id()) - 1u));
+}
+
+template<bool FIRST, bool WIDE>
+__global__ void __launch_bounds__(SHADE_THREADS) wave_shade_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
+                                                                   const __grid_constant__ FrameD fr, const __grid_constant__ WaveBuffers wb,
+                                                                   uint32_t wave) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in_range = slot < wb.n_slots;
+    uint32_t pid = SLOT_IDLE;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (in_range && !FIRST) { acc = wb.acc[slot]; pid = __float_as_uint(acc.w); }
+    bool live = FIRST ? in_range : (in_range && pid != SLOT_IDLE);
+
+    RngState rng{};
+    RayD ray{};
+    f3 thr = mk3(1.f, 1.f, 1.f);
+    uint32_t sample = 0, depth = 0;
+    bool need_pixel = FIRST && live;      // slot has no pixel yet
+    bool need_primary = false;
+    bool emit = false;
+
+    if (!FIRST && live) {
+        const float4 h = wb.hit[slot];
+        const float4 o = wb.ray_o[slot], d = wb.ray_d[slot], t4 = wb.thr[slot];
+        const uint4 ra = wb.rng_a[slot];
+        const uint2 rb = wb.rng_b[slot];
+        rng.d = ra.x; rng.v0 = ra.y; rng.v1 = ra.z; rng.v2 = ra.w; rng.v3 = rb.x; rng.v4 = rb.y;
+        ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z);
+        thr = mk3(t4.x, t4.y, t4.z);
+        const uint32_t sd = __float_as_uint(t4.w);
+        sample = sd >> 16; depth = sd & 0xFFFFu;
+        HitD hit;
+        hit.t = h.x; hit.tc = h.x; hit.u = h.y; hit.v = h.z; hit.leaf = (int) __float_as_uint(h.w); hit.inst = wb.hit_inst[slot];
+        if (fr.aov_t && sample == 0u && depth == 0u) {       // primary hit of the pixel's first sample
+            uint32_t lx, ly;
+            pixel_coords(pid, wb.tiles_x, lx, ly);
+            const uint32_t lp = ly * cam.width + lx;
+            const bool has = hit.inst >= 0;
+            fr.aov_t[lp] = has ? hit.t : RT_INF;
+            fr.aov_inst[lp] = has ? hit.inst : -1;
+            fr.aov_prim[lp] = has ? (int) ((ref_type(hit.leaf) << 28) | (WIDE ? sc.leaf_prims8[ref_pos(hit.leaf)] : sc.leaf_prims[ref_pos(hit.leaf)])) : -1;
+        }
+        const bool alive = shade_scatter<WIDE>(sc, cam, ray, hit, thr, rng);
+        depth++;
+        if (alive && depth < cam.depth) {
+            emit = true;
+        } else {
+            // path over: rayColor returns the throughput (Q6); next sample or next pixel
+            acc.x += thr.x; acc.y += thr.y; acc.z += thr.z;
+            sample++;
+            if (sample == cam.sqrtSamples * cam.sqrtSamples) {
+                uint32_t lx, ly;
+                pixel_coords(pid, wb.tiles_x, lx, ly);
+                const uint32_t lp = ly * cam.width + lx;
+                const float w = cam.rcpSqrtSamples * cam.rcpSqrtSamples;
+                const float r = acc.x * w, g = acc.y * w, b = acc.z * w;
+                fr.radiance[3 * (size_t) lp + 0] = r;
+                fr.radiance[3 * (size_t) lp + 1] = g;
+                fr.radiance[3 * (size_t) lp + 2] = b;
+                const size_t op = fr.rgba8_is_full_frame ? (size_t) global_row(fr, ly) * cam.width + lx : (size_t) lp;
+                reinterpret_cast<uchar4 *>(fr.rgba8)[op] = make_uchar4(to_byte(r), to_byte(g), to_byte(b), 255);
+                need_pixel = true;
+            } else {
+                need_primary = true;
+            }
+        }
+    }
+
+    // slots that finished a pixel (or have none yet) take the next unstarted pixel; ids outside the image
+    // (edge tiles) are skipped
+    for (;;) {
+        const uint32_t any = __ballot_sync(0xffffffffu, need_pixel);
+        if (any == 0u) break;
+        const uint32_t cand = warp_append(wb.next_pixel, need_pixel);
+        if (need_pixel) {
+            if (cand >= wb.n_pixels) {
+                pid = SLOT_IDLE; live = false; need_pixel = false;
+                wb.acc[slot] = make_float4(0.f, 0.f, 0.f, __uint_as_float(SLOT_IDLE));
+            } else {
+                uint32_t lx, ly;
+                pixel_coords(cand, wb.tiles_x, lx, ly);
+                if (lx < cam.width && ly < fr.local_rows && global_row(fr, ly) < cam.height) {
+                    pid = cand; need_pixel = false; need_primary = true;
+                    const RngState r0 = fr.rng[ly * cam.width + lx];
+                    rng = r0;
+                    acc = make_float4(0.f, 0.f, 0.f, __uint_as_float(pid));
+                    sample = 0;
+                }
+            }
+        }
+    }
+
+    if (live && need_primary) {
+        uint32_t lx, ly;
+        pixel_coords(pid, wb.tiles_x, lx, ly);
+        const uint32_t si = sample / cam.sqrtSamples, sj = sample % cam.sqrtSamples;
+        ray = primary_ray(cam, lx, global_row(fr, ly), si, sj, rng);
+        thr = mk3(1.f, 1.f, 1.f);
+        depth = 0;
+        emit = true;
+        wb.acc[slot] = acc;
+    }
+    if (live && emit) {
+        wb.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, 0.f);
+        wb.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
+        wb.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float((sample << 16) | depth));
+        wb.rng_a[slot] = make_uint4(rng.d, rng.v0, rng.v1, rng.v2);
+        wb.rng_b[slot] = make_uint2(rng.v3, rng.v4);
+    }
+    const uint32_t qi = warp_append(wb.counts + wave, live && emit);
+    if (live && emit) wb.queue[qi] = slot;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// TRACE, binary LBVH.  Persistent warps; per lane one ray in flight.  Each outer iteration:
+//   1. refill: lanes without a ray take the next queue entries (one atomic per warp) when enough of them are idle;
+//   2. node phase: lanes standing on an inner node step down the tree; the phase ends when fewer than NODE_MIN
+//      lanes still have an inner node (the others are parked on a leaf / instance / finished);
+//   3. leaf phase: parked lanes do their primitive test, instance entry or instance exit together.
+// This keeps the expensive reference-exact primitive tests (three IEEE divisions each) from running at one or two
+// active lanes per issue, which is what made the one-thread-per-pixel kernel spend 80 % of its issue slots idle
+// (profiles/r01a: 6.35 of 32 threads active per instruction).
+constexpr int TRACE_THREADS = 128;
+
+template<bool COUNT>
+__global__ void __launch_bounds__(TRACE_THREADS, 4) wave_trace2_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ WaveBuffers wb,
+                                                                       uint32_t wave, int refill_min, int node_min, unsigned long long *stats_out) {
+    const uint32_t n_rays = wb.counts[wave];
+    uint32_t *cursor = wb.cursors + wave;
+    int stack[RT_STACK_SIZE];
+    int sp = 0;
+    uint32_t slot = SLOT_IDLE;
+    bool exhausted = false;
+    int cur = 0, inst = -1;
+    RayD ray{}, wray{};
+    RaySlabs slabs{};
+    HitD hit{};
+    uint32_t overflow = 0;
+    TravStats stats{0, 0, 0};
+
+    for (;;) {
+        // ---- 1. refill ------------------------------------------------------------------------------------------
+        const uint32_t idle = __ballot_sync(0xffffffffu, slot == SLOT_IDLE);
+        if (idle != 0u && !exhausted && (__popc(idle) >= refill_min || idle == 0xffffffffu)) {
+            const uint32_t leader = __ffs(idle) - 1u;
+            uint32_t base = 0;
+            if (lane_id() == leader) base = atomicAdd(cursor, (uint32_t) __popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (slot == SLOT_IDLE) {
+                const uint32_t k = base + (uint32_t) __popc(idle & ((1u << lane_id()) - 1u));
+                if (k < n_rays) {
+                    slot = __ldg(&wb.queue[k]);
+                    const float4 o = wb.ray_o[slot], d = wb.ray_d[slot];
+                    wray.o = mk3(o.x, o.y, o.z); wray.d = mk3(d.x, d.y, d.z);
+                    ray = wray;
+                    slabs = make_slabs(ray);
+                    hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.f; hit.v = 0.f; hit.inst = -1; hit.leaf = 0;
+                    sp = 0; inst = -1; cur = sc.tlas_root_ref;
+                }
+            }
+            if (base + (uint32_t) __popc(idle) >= n_rays) exhausted = true;
+        }
+        if (__ballot_sync(0xffffffffu, slot != SLOT_IDLE) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        // ---- 2. node phase ----------------------------------------------------------------------------------------
+        for (;;) {
+            const bool on_node = slot != SLOT_IDLE && cur >= 0;
+            if (on_node) {
+                const BvhNode2 n = load_node2(inst < 0 ? sc.tlas_nodes : sc.blas_nodes, cur);
+                if (COUNT) stats.nodes++;
+                float tn0, tf0, tn1, tf1;
+                node2_test(n, slabs, RT_TMIN, hit.tc, tn0, tf0, tn1, tf1);
+                const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+                if (h0 && h1) {
+                    const bool swap = tn1 < tn0;
+                    if (sp < RT_STACK_SIZE) stack[sp++] = swap ? n.refs.x : n.refs.y; else overflow = 1u;
+                    cur = swap ? n.refs.y : n.refs.x;
+                } else if (h0) cur = n.refs.x;
+                else if (h1) cur = n.refs.y;
+                else if (sp > 0) cur = stack[--sp];
+                else cur = RT_REF_NONE;                                  // traversal finished
+            }
+            const uint32_t still = __ballot_sync(0xffffffffu, slot != SLOT_IDLE && cur >= 0);
+            if (__popc(still) < node_min) break;
+        }
+        // ---- 3. leaf phase ----------------------------------------------------------------------------------------
+        if (slot != SLOT_IDLE && cur < 0 && cur != RT_REF_NONE) {
+            if (cur == RT_REF_SENTINEL) {
+                inst = -1;
+                ray = wray;
+                slabs = make_slabs(ray);
+            } else if (inst < 0) {
+                inst = (int) ref_pos(cur);
+                if (COUNT) stats.insts++;
+                float inv[12];
+                int root;
+                load_instance_inv(sc, inst, inv, root);
+                ray.o = xf_point(inv, wray.o);
+                ray.d = xf_vector(inv, wray.d);
+                slabs = make_slabs(ray);
+                if (sp < RT_STACK_SIZE) stack[sp++] = RT_REF_SENTINEL; else overflow = 1u;
+                cur = root;
+                goto parked;                                             // root may be a node or a leaf: next iteration
+            } else {
+                if (COUNT) stats.prims++;
+                leaf_test(sc, cur, ray, RT_TMIN, inst, hit);
+            }
+            cur = sp > 0 ? stack[--sp] : RT_REF_NONE;
+        }
+parked:
+        if (slot != SLOT_IDLE && cur == RT_REF_NONE) {
+            wb.hit[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float((uint32_t) hit.leaf));
+            wb.hit_inst[slot] = hit.inst;
+            slot = SLOT_IDLE;
+        }
+    }
+    if (overflow) atomicOr(reinterpret_cast<unsigned int *>(stats_out + 1), 1u);
+    if (COUNT) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            stats.nodes += __shfl_xor_sync(0xffffffffu, stats.nodes, off);
+            stats.prims += __shfl_xor_sync(0xffffffffu, stats.prims, off);
+            stats.insts += __shfl_xor_sync(0xffffffffu, stats.insts, off);
+        }
+        if (lane_id() == 0) {
+            atomicAdd(stats_out + 2, (unsigned long long) stats.nodes);
+            atomicAdd(stats_out + 3, (unsigned long long) stats.prims);
+            atomicAdd(stats_out + 4, (unsigned long long) stats.insts);
+        }
+    }
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+void WaveRenderer::reserve(uint32_t n_slots) {
+    ray_o_.reserve(n_slots); ray_d_.reserve(n_slots); hit_.reserve(n_slots); thr_.reserve(n_slots); acc_.reserve(n_slots);
+    hit_inst_.reserve(n_slots); rng_a_.reserve(n_slots); rng_b_.reserve(n_slots); queue_.reserve(n_slots);
+}
+
+void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count, WaveStats &stats) {
+    constexpr int BATCH = 32;
+    const uint32_t tiles_x = (cam.width + 7u) / 8u, tiles_y = (fr.local_rows + 3u) / 4u;
+    const uint32_t n_pixels = tiles_x * tiles_y * 32u;
+    uint32_t n_slots = slots_override ? slots_override : (1u << 20);
+    if (n_slots > n_pixels) n_slots = n_pixels;
+    n_slots = (n_slots + 31u) & ~31u;
+    reserve(n_slots);
+    counters_.reserve(2 * BATCH + 4);
+    h_counts_.reserve(BATCH);
+
+    WaveBuffers wb{};
+    wb.ray_o = ray_o_.get(); wb.ray_d = ray_d_.get(); wb.hit = hit_.get(); wb.hit_inst = hit_inst_.get();
+    wb.thr = thr_.get(); wb.acc = acc_.get(); wb.rng_a = rng_a_.get(); wb.rng_b = rng_b_.get();
+    wb.queue = queue_.get();
+    wb.counts = counters_.get(); wb.cursors = counters_.get() + BATCH; wb.next_pixel = counters_.get() + 2 * BATCH;
+    wb.n_slots = n_slots; wb.n_pixels = n_pixels; wb.tiles_x = tiles_x;
+
+    if (trace_blocks_per_sm_[0] == 0) {
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_blocks_per_sm_[0], wave_trace2_kernel<false>, TRACE_THREADS, 0));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_blocks_per_sm_[1], wave_trace2_kernel<true>, TRACE_THREADS, 0));
+    }
+    const bool count = fr.count_traversal != 0;
+    const int trace_blocks = sm_count * std::max(1, trace_blocks_per_sm_[count ? 1 : 0]);
+    const unsigned shade_blocks = div_up(n_slots, SHADE_THREADS);
+    const bool wide = mode == 1;
+
+    CUDA_CHECK(cudaMemsetAsync(wb.next_pixel, 0, sizeof(uint32_t), stream));
+    stats = WaveStats{};
+    bool first = true;
+    for (;;) {
+        CUDA_CHECK(cudaMemsetAsync(counters_.get(), 0, 2 * BATCH * sizeof(uint32_t), stream));
+        for (int w = 0; w < BATCH; w++) {
+            if (first) {
+                if (wide) wave_shade_kernel<true, true><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
+                else wave_shade_kernel<true, false><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
+                first = false;
+            } else {
+                if (wide) wave_shade_kernel<false, true><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
+                else wave_shade_kernel<false, false><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
+            }
+            if (count) wave_trace2_kernel<true><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+            else wave_trace2_kernel<false><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+            stats.launches += 2;
+        }
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaMemcpyAsync(h_counts_.get(), wb.counts, BATCH * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+        CUDA_CHECK(cudaStreamSynchronize(stream));
+        bool done = false;
+        for (int w = 0; w < BATCH; w++) {
+            const uint32_t c = h_counts_.get()[w];
+            stats.rays += c;
+            if (c == 0u) { done = true; break; }
+            stats.waves++;
+        }
+        if (done) break;
+    }
+}

@@ -1,0 +1,129 @@
+// kernels_wide.cu — collapse of the binary LBVH into the compressed 8-wide BVH (BvhNode8), on the device.
+//
+// One persistent launch.  Work item i = wide node i; the thread that encodes node i allocates consecutive node
+// slots for its inner children and consecutive leaf-order positions for its leaf primitives (two atomic
+// counters) and publishes the children's binary roots into queue[child_base ..].  Threads own the items
+// tid, tid + T, tid + 2T, ... and poll queue[i] until the producer (always an item with a smaller index, so a
+// resident or finished thread) has written it.  Termination: finished == allocated.
+// The node contents are a pure function of the binary tree (rt_wide_core.h); only the memory layout depends on
+// the order of the atomics, and the parity tests compare the trees canonically against the serial twin.
+#include "build.h"
+
+namespace {
+
+constexpr int CT = 128;
+constexpr int QUEUE_EMPTY = (int) 0x80808080u;     // cudaMemsetAsync(0x80) pattern; never a node index or ~position
+
+__device__ __forceinline__ int find_segment_w(const uint32_t *__restrict__ seg_offset, int n_segs, uint32_t j) {
+    int lo = 0, hi = n_segs - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(&seg_offset[mid]) <= j) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(256) collapse_init_kernel(const uint32_t *__restrict__ seg_offset, const int *__restrict__ seg_root, int n_segs,
+                                                            int *queue, uint32_t *counters) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s == 0) { counters[0] = (uint32_t) n_segs; counters[1] = 0u; counters[2] = 0u; counters[3] = 0u; }
+    if (s >= n_segs) return;
+    const uint32_t first = seg_offset[s], cnt = seg_offset[s + 1] - first;
+    queue[s] = cnt == 1u ? ~(int) first : seg_root[s];
+}
+
+__global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int leaf_max, int capacity, int *queue, uint32_t *counters,
+                                                      BvhNode8 *__restrict__ nodes8, uint32_t *__restrict__ leaf_pos8) {
+    volatile int *vq = queue;
+    volatile uint32_t *vc = counters;
+    const int stride = gridDim.x * blockDim.x;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    for (;;) {
+        if (i < capacity) {
+            const int root = vq[i];
+            if (root != QUEUE_EMPTY) {
+                WideChildren w;
+                wide_expand(view, root, leaf_max, w);
+                const int k = wide_inner_count(w), m = wide_prim_count(w);
+                const uint32_t child_base = k ? atomicAdd(&counters[0], (uint32_t) k) : 0u;
+                const uint32_t prim_base = m ? atomicAdd(&counters[1], (uint32_t) m) : 0u;
+                BvhNode8 node;
+                int child_in_slot[8];
+                wide_encode(w, child_base, prim_base, node, child_in_slot);
+                nodes8[i] = node;
+                uint32_t j = 0, off = 0;
+                for (int sl = 0; sl < 8; sl++) {
+                    const int c = child_in_slot[sl];
+                    if (c < 0) continue;
+                    if (w.ref[c] >= 0) {
+                        vq[child_base + j] = w.ref[c];
+                        j++;
+                    } else {
+                        for (int q = 0; q < w.count[c]; q++) leaf_pos8[prim_base + off + q] = (uint32_t) (w.first[c] + q);
+                        off += (uint32_t) w.count[c];
+                    }
+                }
+                __threadfence();
+                atomicAdd(&counters[2], 1u);
+                i += stride;
+                continue;
+            }
+        }
+        const uint32_t fin = vc[2];
+        __threadfence();
+        const uint32_t alloc = vc[0];
+        if (fin == alloc) break;
+    }
+}
+
+// leaf-order records of the wide BVH: original primitive index (TLAS: instance index) and, for triangles, the
+// 48-byte intersection record (e1/e2 as the reference's constructor, include/Geometry/Triangle.cuh:29-30)
+__global__ void __launch_bounds__(256) emit_leaves8_kernel(GeometryD geo, const uint32_t *__restrict__ leaf_pos8, const uint32_t *__restrict__ vals,
+                                                           const uint32_t *__restrict__ seg_offset, const uint32_t *__restrict__ seg_type,
+                                                           const uint32_t *__restrict__ seg_first, int n_segs, int n, int leaf_mode,
+                                                           uint32_t *__restrict__ leaf_prims8, TriIsect *__restrict__ leaf_tris8) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    const uint32_t pos = leaf_pos8[q];
+    const uint32_t v = vals[pos];
+    if (leaf_mode == 1) { leaf_prims8[q] = v; return; }
+    const int seg = n_segs > 1 ? find_segment_w(seg_offset, n_segs, pos) : 0;
+    const uint32_t prim = __ldg(&seg_first[seg]) + (v - __ldg(&seg_offset[seg]));
+    leaf_prims8[q] = prim;
+    if (__ldg(&seg_type[seg]) == 2u) {
+        const float *s = geo.tri_verts + (size_t) prim * 9;
+        const f3 v0 = mk3(__ldg(s), __ldg(s + 1), __ldg(s + 2));
+        const f3 v1 = mk3(__ldg(s + 3), __ldg(s + 4), __ldg(s + 5));
+        const f3 v2 = mk3(__ldg(s + 6), __ldg(s + 7), __ldg(s + 8));
+        const f3 e1 = v1 - v0, e2 = v2 - v0;
+        TriIsect t;
+        t.v0_id = make_float4(v0.x, v0.y, v0.z, __uint_as_float(prim));
+        t.e1 = make_float4(e1.x, e1.y, e1.z, 0.0f);
+        t.e2 = make_float4(e2.x, e2.y, e2.z, 0.0f);
+        leaf_tris8[q] = t;
+    }
+}
+
+} // namespace
+
+void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count) {
+    if (collapse_blocks_per_sm_ == 0) {
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&collapse_blocks_per_sm_, collapse_kernel, CT, 0));
+        if (collapse_blocks_per_sm_ < 1) collapse_blocks_per_sm_ = 1;
+    }
+    const int capacity = n + n_segs;
+    CUDA_CHECK(cudaMemsetAsync(queue_.get(), 0x80, (size_t) capacity * sizeof(int), stream));
+    collapse_init_kernel<<<div_up(n_segs, 256), 256, 0, stream>>>(seg_offset_.get(), seg_root_.get(), n_segs, queue_.get(), wide_counters_.get());
+    const BinaryTreeView view{left_.get(), right_.get(), range_.get(), node_lo_.get(), node_hi_.get(), prim_lo_.get(), prim_hi_.get(), vals_};
+    // every thread of the grid must be resident (the items poll on one another)
+    const int max_blocks = sm_count * collapse_blocks_per_sm_;
+    const int want_blocks = (int) div_up((size_t) capacity, CT);
+    const int blocks = want_blocks < max_blocks ? want_blocks : max_blocks;
+    const int leaf_max = leaf_mode == 1 ? 1 : RT_WIDE_LEAF_MAX;
+    collapse_kernel<<<blocks, CT, 0, stream>>>(view, leaf_max, capacity, queue_.get(), wide_counters_.get(), nodes8_.get(), leaf_pos8_.get());
+    const GeometryD none{nullptr, nullptr, nullptr};
+    emit_leaves8_kernel<<<div_up(n, 256), 256, 0, stream>>>(geo ? *geo : none, leaf_pos8_.get(), vals_, seg_offset_.get(), seg_type_.get(),
+                                                           seg_first_.get(), n_segs, n, leaf_mode, leaf_prims8_.get(), leaf_tris8_.get());
+    launches += 3;
+    CUDA_CHECK(cudaGetLastError());
+}

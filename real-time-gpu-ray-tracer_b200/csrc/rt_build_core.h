@@ -141,6 +141,7 @@ struct InstanceXformIn {
     float trig[6];          // cos x, sin x, cos y, sin y, cos z, sin z
     float box_lo[3], box_hi[3], centroid[3];
     int root_ref, blas;
+    int root8, prim_type;
 };
 RT_HD void mat4_mul(const float a[4][4], const float b[4][4], float r[4][4]) {
     for (int i = 0; i < 4; i++)
@@ -197,7 +198,7 @@ RT_HD void instance_update(const InstanceXformIn &in, InstanceD &out, Aabb &wbox
     mat4_mul(TR, S, M);
     if (!mat4_inverse(M, Minv)) for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) Minv[i][j] = M[i][j];
     for (int i = 0; i < 3; i++) for (int j = 0; j < 4; j++) { out.fwd[4 * i + j] = M[i][j]; out.inv[4 * i + j] = Minv[i][j]; }
-    out.root_ref = in.root_ref; out.blas = in.blas; out._p0 = 0; out._p1 = 0;
+    out.root_ref = in.root_ref; out.blas = in.blas; out.root8 = in.root8; out.prim_type = in.prim_type;
     // 8-corner world box; the point transform includes the reference's 4th-row terms only through rows 1..3
     f3 lo = mk3(RT_INF, RT_INF, RT_INF), hi = mk3(-RT_INF, -RT_INF, -RT_INF);
     for (int i = 0; i < 2; i++) for (int j = 0; j < 2; j++) for (int k = 0; k < 2; k++) {

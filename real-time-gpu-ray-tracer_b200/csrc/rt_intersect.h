@@ -43,7 +43,7 @@ RT_HD bool sphere_hit_t(const f3 &c, float r, const RayD &ray, float tlo, float 
 
 // ---- reference slab test (reference src/AS/BoundingBox.cu:34-72, Q2): only used as the bug-compatible
 //      filter of parallelograms (Q10); BVH culling uses the fast conservative test in rt_trace_core.h -----
-RT_HD bool ref_box_hit(const f3 &lo, const f3 &hi, const RayD &ray, float curlo, float curhi) {
+RT_HD bool ref_box_hit(const f3 &lo, const f3 &hi, const RayD &ray, float curlo, float curhi, float &t_enter) {
     for (int axis = 0; axis < 3; axis++) {
         const float blo = comp3(lo, axis), bhi = comp3(hi, axis);
         const float q = comp3(ray.o, axis), d = comp3(ray.d, axis);
@@ -62,16 +62,23 @@ RT_HD bool ref_box_hit(const f3 &lo, const f3 &hi, const RayD &ray, float curlo,
         }
         if (curlo >= curhi) return false;
     }
+    t_enter = curlo;
     return true;
 }
 
 // ---- parallelogram (reference src/Geometry/Parallelogram.cu:4-35) -----------------------------------
-RT_HD bool quad_hit_t(const QuadD &p, const RayD &ray, float tlo, float thi, float &t) {
+// thi is the caller's current acceptance bound; on a hit, tbound is the bound to continue with.
+RT_HD bool quad_hit_t(const QuadD &p, const RayD &ray, float tlo, float thi, float &t, float &tbound) {
     const f3 n = mk3(p.n_flag.x, p.n_flag.y, p.n_flag.z);
+    float t_enter = -RT_INF;
     if (p.n_flag.w != 0.0f) {
-        // bug-compatible mode: the reference only reaches the primitive when the ray passes the slab
-        // test of Parallelogram::constructBoundingBox (src/Geometry/Parallelogram.cu:48-50) over [tlo, thi]
-        if (!ref_box_hit(mk3(p.rb_lo.x, p.rb_lo.y, p.rb_lo.z), mk3(p.rb_hi.x, p.rb_hi.y, p.rb_hi.z), ray, tlo, thi)) return false;
+        // bug-compatible mode (Q10): the reference only reaches the primitive when the ray passes the slab test of
+        // Parallelogram::constructBoundingBox (src/Geometry/Parallelogram.cu:48-50) over [tlo, best-so-far], and it
+        // visits boxes near-first (src/AS/TLAS.cu:186-197).  A hit X found BEFORE the wrong box is entered
+        // (t_X < t_enter) therefore culls the parallelogram even when the parallelogram's own hit is nearer.
+        // To make that independent of OUR traversal order, a parallelogram hit keeps the acceptance bound at
+        // max(t, t_enter): a later candidate inside (t, t_enter] replaces it, exactly as if it had been found first.
+        if (!ref_box_hit(mk3(p.rb_lo.x, p.rb_lo.y, p.rb_lo.z), mk3(p.rb_hi.x, p.rb_hi.y, p.rb_hi.z), ray, tlo, thi, t_enter)) return false;
     }
     const float nDotD = dot3(n, ray.d);
     if (near_zero(nDotD)) return false;
@@ -86,5 +93,7 @@ RT_HD bool quad_hit_t(const QuadD &p, const RayD &ray, float tlo, float thi, flo
     if (near_zero(denom)) return false;
     const float alpha = dot3(cross3(pv, v), normal) / denom;
     const float beta = dot3(cross3(u, pv), normal) / denom;
-    return in_range(alpha, 0.0f, 1.0f) && in_range(beta, 0.0f, 1.0f);
+    if (!(in_range(alpha, 0.0f, 1.0f) && in_range(beta, 0.0f, 1.0f))) return false;
+    tbound = t_enter > t ? t_enter : t;
+    return true;
 }

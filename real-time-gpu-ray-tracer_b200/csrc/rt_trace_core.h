@@ -8,6 +8,7 @@
 
 struct HitD {
     float t, u, v;
+    float tc;       // culling / acceptance bound: == t, except after a bug-compatible parallelogram hit (rt_intersect.h quad_hit_t)
     int inst;       // instance index, -1 = miss
     int leaf;       // leaf ref of the winning primitive (type + leaf-order position)
 };
@@ -67,20 +68,20 @@ RT_HD void leaf_test(const SceneD &sc, int ref, const RayD &lray, float tmin, in
         const float4 a = sc.leaf_tris[pos].v0_id, b = sc.leaf_tris[pos].e1, c = sc.leaf_tris[pos].e2;
 #endif
         float t, u, v;
-        if (tri_hit_t(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), lray, tmin, best.t, t, u, v)) {
-            best.t = t; best.u = u; best.v = v; best.inst = inst; best.leaf = ref;
+        if (tri_hit_t(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), lray, tmin, best.tc, t, u, v)) {
+            best.t = t; best.tc = t; best.u = u; best.v = v; best.inst = inst; best.leaf = ref;
         }
     } else if (type == 0u) {
         const SphereD s = sc.spheres[sc.leaf_prims[pos]];
         float t;
-        if (sphere_hit_t(mk3(s.c_r.x, s.c_r.y, s.c_r.z), s.c_r.w, lray, tmin, best.t, t)) {
-            best.t = t; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = ref;
+        if (sphere_hit_t(mk3(s.c_r.x, s.c_r.y, s.c_r.z), s.c_r.w, lray, tmin, best.tc, t)) {
+            best.t = t; best.tc = t; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = ref;
         }
     } else {
         const QuadD q = sc.quads[sc.leaf_prims[pos]];
-        float t;
-        if (quad_hit_t(q, lray, tmin, best.t, t)) {
-            best.t = t; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = ref;
+        float t, tc;
+        if (quad_hit_t(q, lray, tmin, best.tc, t, tc)) {
+            best.t = t; best.tc = tc; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = ref;
         }
     }
 }
@@ -111,7 +112,7 @@ RT_HD void load_instance_inv(const SceneD &sc, int inst, float *inv, int &root) 
 // (reference src/AS/TLAS.cu:131-201, src/AS/Instance.cu:19-50, src/AS/BLAS.cu:119-206) on our own BVH.
 template<bool COUNT>
 RT_HD void trace_closest(const SceneD &sc, const RayD &wray, float tmin, HitD &hit, uint32_t &overflow, TravStats &stats) {
-    hit.t = RT_INF; hit.u = 0.0f; hit.v = 0.0f; hit.inst = -1; hit.leaf = 0;
+    hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.0f; hit.v = 0.0f; hit.inst = -1; hit.leaf = 0;
     int stack[RT_STACK_SIZE];
     int sp = 0;
     int cur = sc.tlas_root_ref;
@@ -123,7 +124,7 @@ RT_HD void trace_closest(const SceneD &sc, const RayD &wray, float tmin, HitD &h
             const BvhNode2 n = load_node2(inst < 0 ? sc.tlas_nodes : sc.blas_nodes, cur);
             if (COUNT) stats.nodes++;
             float tn0, tf0, tn1, tf1;
-            node2_test(n, slabs, tmin, hit.t, tn0, tf0, tn1, tf1);
+            node2_test(n, slabs, tmin, hit.tc, tn0, tf0, tn1, tf1);
             const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
             if (h0 && h1) {
                 const bool swap = tn1 < tn0;
@@ -183,6 +184,7 @@ RT_HD f3 ld3(const float4 &a) { return mk3(a.x, a.y, a.z); }
 // Hit record + scatter: Prim::hit's record fields (reference src/Geometry/*.cu), Instance::hit's back-transform
 // (src/AS/Instance.cu:41-45), Rough/Metal::scatter (include/Material/*.cuh) and rayColor's bookkeeping
 // (src/Global/Kernel.cu:76-98).  Returns false when the path ends; `throughput` is rayColor's `result`.
+template<bool WIDE>
 RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const HitD &hit, f3 &throughput, RngState &rng) {
     if (hit.inst < 0) {
         throughput.x *= cam.background.x; throughput.y *= cam.background.y; throughput.z *= cam.background.z;
@@ -191,7 +193,7 @@ RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const 
     const InstanceD &ins = sc.instances[hit.inst];
     const RayD lray = to_local(ins, ray);
     const uint32_t type = ref_type(hit.leaf), pos = ref_pos(hit.leaf);
-    const uint32_t prim = sc.leaf_prims[pos];
+    const uint32_t prim = WIDE ? sc.leaf_prims8[pos] : sc.leaf_prims[pos];
     const f3 lp = ray_at(lray, hit.t);
     f3 ln;
     uint32_t mt, mi;
@@ -243,33 +245,3 @@ RT_HD uint8_t to_byte(float c) {
     return (uint8_t) (256.0f * g);
 }
 
-struct PixelOut { f3 radiance; uint32_t rays; float aov_t; int aov_inst, aov_prim; TravStats stats; };
-
-// One pixel of the reference's `render` kernel (src/Global/Kernel.cu:116-143): all samples, all bounces.
-template<bool COUNT>
-RT_HD PixelOut render_pixel(const SceneD &sc, const CameraD &cam, uint32_t x, uint32_t y, RngState rng, uint32_t &overflow) {
-    PixelOut out;
-    out.stats.nodes = 0; out.stats.prims = 0; out.stats.insts = 0;
-    out.radiance = mk3(0.0f, 0.0f, 0.0f);
-    out.rays = 0; out.aov_t = RT_INF; out.aov_inst = -1; out.aov_prim = -1;
-    for (uint32_t si = 0; si < cam.sqrtSamples; si++) {
-        for (uint32_t sj = 0; sj < cam.sqrtSamples; sj++) {
-            RayD ray = primary_ray(cam, x, y, si, sj, rng);
-            f3 thr = mk3(1.0f, 1.0f, 1.0f);
-            for (uint32_t depth = 0; depth < cam.depth; depth++) {
-                HitD hit;
-                trace_closest<COUNT>(sc, ray, RT_TMIN, hit, overflow, out.stats);
-                out.rays++;
-                if (si == 0 && sj == 0 && depth == 0 && hit.inst >= 0) {
-                    out.aov_t = hit.t; out.aov_inst = hit.inst;
-                    out.aov_prim = (int) ((ref_type(hit.leaf) << 28) | sc.leaf_prims[ref_pos(hit.leaf)]);
-                }
-                if (!shade_scatter(sc, cam, ray, hit, thr, rng)) break;
-            }
-            out.radiance = out.radiance + thr;
-        }
-    }
-    const float w = cam.rcpSqrtSamples * cam.rcpSqrtSamples;
-    out.radiance = out.radiance * w;
-    return out;
-}

@@ -26,6 +26,25 @@ struct alignas(16) BvhNode2 {
     int4 refs;    // ref0, ref1, -, -
 };
 
+// ---- compressed 8-wide node (80 B, five 16-byte loads) ------------------------------------------------
+// Layout after Ylitie, Karras, Laine 2017 ("Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide
+// BVHs"): child boxes are 8-bit offsets on a per-node power-of-two grid anchored at the node's lower corner;
+// children sit in octant-ordered slots so that traversal order is a XOR of the slot with the ray octant.
+//   n0 : p.x p.y p.z | bytes {ex, ey, ez, imask}   (e* = biased float exponents of the grid step, imask bit s = slot s is an inner node)
+//   n1 : child_base | prim_base | meta[0..3] | meta[4..7]
+//        meta: 0 = empty; inner = 0b001_11sss (sss = slot); leaf = unary(prim count 1..3) << 5 | offset from prim_base (0..23)
+//   n2 : qlo.x[0..3] qlo.x[4..7] qlo.y[0..3] qlo.y[4..7]
+//   n3 : qlo.z[0..3] qlo.z[4..7] qhi.x[0..3] qhi.x[4..7]
+//   n4 : qhi.y[0..3] qhi.y[4..7] qhi.z[0..3] qhi.z[4..7]
+// Inner children of a node are consecutive nodes from child_base in slot order; its leaf primitives are consecutive
+// leaf-order records from prim_base (TLAS: positions in the leaf->instance table).
+struct alignas(16) BvhNode8 {
+    float4 n0;
+    uint4 n1, n2, n3, n4;
+};
+#define RT_WIDE_LEAF_MAX 3      /* primitives per leaf child (3 unary bits)            */
+#define RT_WIDE_STACK 24        /* entries (8 B each) of the per-thread traversal stack */
+
 // ---- primitives -----------------------------------------------------------------------------------
 // Triangle intersection record in LEAF ORDER (Morton-sorted), 48 B: v0|primIndex, e1, e2
 // (e1, e2 precomputed at commit exactly as the reference's constructor, include/Geometry/Triangle.cuh:29-30,44-45)
@@ -58,7 +77,8 @@ struct alignas(16) InstanceD {
     float fwd[12];  // rows 1..3 of transformMatrix  (local -> world)
     int root_ref;   // BLAS root (inner node index or leaf ref)
     int blas;
-    int _p0, _p1;
+    int root8;      // BLAS root in the wide node pool
+    int prim_type;  // rt_primitive_type of the BLAS (a BLAS holds one primitive type)
 };
 
 // ---- camera (the derived fields of the reference's Camera, include/Global/RendererImpl.cuh:32-61) -----
@@ -86,6 +106,12 @@ struct SceneD {
     const float4 *dielectrics;       // albedo.xyz, ior (extension)
     int tlas_root_ref;
     int _pad;
+    // wide (BVH8) acceleration structure: the one the render kernels traverse
+    const BvhNode8 *tlas_nodes8;     // root = node 0
+    const BvhNode8 *blas_nodes8;     // roots = InstanceD::root8
+    const uint32_t *tlas_leaf_inst;  // TLAS leaf order -> instance index
+    const TriIsect *leaf_tris8;      // wide leaf order
+    const uint32_t *leaf_prims8;     // wide leaf order: original primitive index (all types)
 };
 
 // XORWOW state (cuRAND curandStateXORWOW_t without the Box-Muller fields): 24 B per pixel
@@ -104,4 +130,5 @@ struct FrameD {
     // tile sharding: local row r -> global row
     uint32_t shard_rank, shard_world, tile_rows, local_rows;
     uint32_t rgba8_is_full_frame;   // 1: rgba8 indexed by GLOBAL pixel (peer store), 0: by local pixel
+    uint32_t traverse_bvh2;         // 1: traverse the binary LBVH nodes (comparison mode) instead of the wide BVH
 };

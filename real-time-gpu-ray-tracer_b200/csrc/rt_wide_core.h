@@ -1,0 +1,213 @@
+// rt_wide_core.h — compressed 8-wide BVH: collapse of the binary LBVH into BvhNode8 records (build side) and the
+// stack-based closest-hit traversal over them (render side).  Pure per-element / per-ray functions, __host__
+// __device__, so the CUDA kernels and the g++ twin in tests/emul run the identical definition.
+//
+// Replaces the reference's binary BLAS/TLAS node arrays (include/AS/BLAS.cuh:20-34, include/AS/TLAS.cuh:24-39:
+// 40-byte nodes, each box tested twice) and BLAS::hit / TLAS::hit (src/AS/BLAS.cu:119-206, src/AS/TLAS.cu:131-201).
+#pragma once
+
+#include "rt_build_core.h"
+
+// ---- small bit helpers ---------------------------------------------------------------------------------------
+RT_HD int rt_popc(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __popc(x);
+#else
+    return __builtin_popcount(x);
+#endif
+}
+RT_HD int rt_bfind(uint32_t x) {   // index of the highest set bit, x != 0
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz((int) x);
+#else
+    return 31 - __builtin_clz(x);
+#endif
+}
+RT_HD uint32_t rt_byte(uint32_t v, int i) { return (v >> (8 * i)) & 0xFFu; }
+
+// ---- collapse: children of one wide node --------------------------------------------------------------------
+// ref >= 0 : binary inner node that becomes a wide node of its own
+// ref <  0 : leaf child holding the Morton-order positions [first, first + count)
+struct WideChildren {
+    int n;
+    int ref[8];
+    int first[8], count[8];
+    Aabb box[8];
+};
+
+struct BinaryTreeView {
+    const int *left, *right;            // Karras children (>= 0 inner, < 0 leaf ~position)
+    const int2 *range;                  // per inner node: first/last Morton position
+    const float4 *node_lo, *node_hi;    // per inner node box
+    const float4 *prim_lo, *prim_hi;    // per build primitive box (padded)
+    const uint32_t *vals;               // Morton position -> build primitive
+};
+
+RT_HD float aabb_half_area(const Aabb &b) {
+    const float dx = b.hi.x - b.lo.x, dy = b.hi.y - b.lo.y, dz = b.hi.z - b.lo.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+RT_HD Aabb view_box(const float4 *lo, const float4 *hi, int i) {
+    const float4 a = lo[i], b = hi[i];
+    Aabb r;
+    r.lo = mk3(a.x, a.y, a.z);
+    r.hi = mk3(b.x, b.y, b.z);
+    return r;
+}
+RT_HD void wide_set_child(const BinaryTreeView &t, int child, int leaf_max, WideChildren &w, int k) {
+    if (child >= 0) {
+        const int2 rg = t.range[child];
+        const int cnt = rg.y - rg.x + 1;
+        w.box[k] = view_box(t.node_lo, t.node_hi, child);
+        w.first[k] = rg.x;
+        w.count[k] = cnt;
+        w.ref[k] = cnt <= leaf_max ? -1 : child;      // small subtrees become one leaf child
+    } else {
+        const int pos = ~child;
+        w.box[k] = view_box(t.prim_lo, t.prim_hi, (int) t.vals[pos]);
+        w.first[k] = pos;
+        w.count[k] = 1;
+        w.ref[k] = -1;
+    }
+}
+// Greedy top-down collapse: start from the two children of `root`, repeatedly open the inner child with the
+// largest surface area until eight children exist or nothing can be opened.  root < 0: single-leaf node.
+RT_HD void wide_expand(const BinaryTreeView &t, int root, int leaf_max, WideChildren &w) {
+    if (root < 0) {
+        w.n = 1;
+        wide_set_child(t, root, leaf_max, w, 0);
+        return;
+    }
+    const int2 rr = t.range[root];
+    if (rr.y - rr.x + 1 <= leaf_max) {               // whole BLAS fits one leaf child
+        w.n = 1;
+        wide_set_child(t, root, leaf_max, w, 0);
+        return;
+    }
+    w.n = 2;
+    wide_set_child(t, t.left[root], leaf_max, w, 0);
+    wide_set_child(t, t.right[root], leaf_max, w, 1);
+    while (w.n < 8) {
+        int best = -1;
+        float best_area = -1.0f;
+        for (int k = 0; k < w.n; k++) {
+            if (w.ref[k] < 0) continue;
+            const float a = aabb_half_area(w.box[k]);
+            if (a > best_area) { best_area = a; best = k; }
+        }
+        if (best < 0) break;
+        const int node = w.ref[best];
+        wide_set_child(t, t.left[node], leaf_max, w, best);
+        wide_set_child(t, t.right[node], leaf_max, w, w.n);
+        w.n++;
+    }
+}
+
+// ---- octant-ordered slot assignment --------------------------------------------------------------------------
+// Slot s (bit 2 = +x, bit 1 = +y, bit 0 = +z) should hold the child lying furthest towards that corner of the
+// node, so that for a ray of octant `oct` visiting slots in descending (s ^ (7 - oct)) order is front-to-back.
+// Greedy assignment on cost(child, slot) = dot(child centre - node centre, corner direction of the slot).
+RT_HD void wide_assign_slots(const WideChildren &w, const Aabb &node, int *slot_of /* [8] child -> slot */) {
+    const f3 nc = mk3(0.5f * (node.lo.x + node.hi.x), 0.5f * (node.lo.y + node.hi.y), 0.5f * (node.lo.z + node.hi.z));
+    float cost[8][8];
+    for (int c = 0; c < w.n; c++) {
+        const f3 d = mk3(0.5f * (w.box[c].lo.x + w.box[c].hi.x) - nc.x, 0.5f * (w.box[c].lo.y + w.box[c].hi.y) - nc.y,
+                         0.5f * (w.box[c].lo.z + w.box[c].hi.z) - nc.z);
+        for (int s = 0; s < 8; s++)
+            cost[c][s] = ((s & 4) ? d.x : -d.x) + ((s & 2) ? d.y : -d.y) + ((s & 1) ? d.z : -d.z);
+    }
+    uint32_t child_free = (1u << w.n) - 1u, slot_free = 0xFFu;
+    for (int c = 0; c < 8; c++) slot_of[c] = -1;
+    for (int round = 0; round < w.n; round++) {
+        int bc = -1, bs = -1;
+        float best = -RT_INF;
+        for (int c = 0; c < w.n; c++) {
+            if (!(child_free & (1u << c))) continue;
+            for (int s = 0; s < 8; s++) {
+                if (!(slot_free & (1u << s))) continue;
+                if (cost[c][s] > best) { best = cost[c][s]; bc = c; bs = s; }
+            }
+        }
+        slot_of[bc] = bs;
+        child_free &= ~(1u << bc);
+        slot_free &= ~(1u << bs);
+    }
+}
+
+// ---- quantisation grid ---------------------------------------------------------------------------------------
+// Biased exponent byte e with step = 2^(e-127) such that extent / step <= 253 (one spare unit at each end).
+RT_HD uint32_t wide_grid_exponent(float extent) {
+    if (!(extent > 0.0f)) return 27u;                       // degenerate axis: every q is 0, any finite step works
+    const float f = extent / 253.0f;
+    uint32_t e = (f2u(f) >> 23) & 0xFFu;
+    if (f2u(f) & 0x7FFFFFu) e++;                            // round the step up to a power of two
+    if (e < 1u) e = 1u;
+    if (e > 254u) e = 254u;
+    return e;
+}
+RT_HD float wide_grid_step(uint32_t e) { return u2f(e << 23); }
+RT_HD uint32_t wide_quant_lo(float v, float p, float step) {
+    float q = floorf((v - p) / step);
+    if (q < 0.0f) q = 0.0f;
+    if (q > 255.0f) q = 255.0f;
+    uint32_t qi = (uint32_t) q;
+    while (qi > 0u && p + (float) qi * step > v) qi--;      // decoded plane never inside the box
+    return qi;
+}
+RT_HD uint32_t wide_quant_hi(float v, float p, float step) {
+    float q = ceilf((v - p) / step);
+    if (q < 0.0f) q = 0.0f;
+    if (q > 255.0f) q = 255.0f;
+    uint32_t qi = (uint32_t) q;
+    while (qi < 255u && p + (float) qi * step < v) qi++;
+    return qi;
+}
+
+// ---- encode one wide node ------------------------------------------------------------------------------------
+// child_base: index of the first inner child (inner children are numbered in slot order from it),
+// prim_base : leaf-order position of the node's first leaf primitive (leaf children in slot order).
+// Outputs the node, and for each slot the child placed there (child_in_slot[s], -1 = empty) so the caller can
+// enqueue inner children / write leaf records in the same order.
+RT_HD void wide_encode(const WideChildren &w, uint32_t child_base, uint32_t prim_base, BvhNode8 &out, int *child_in_slot /* [8] */) {
+    Aabb node = w.box[0];
+    for (int c = 1; c < w.n; c++) node = aabb_union(node, w.box[c]);
+    int slot_of[8];
+    wide_assign_slots(w, node, slot_of);
+    for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
+    for (int c = 0; c < w.n; c++) child_in_slot[slot_of[c]] = c;
+
+    const uint32_t ex = wide_grid_exponent(node.hi.x - node.lo.x), ey = wide_grid_exponent(node.hi.y - node.lo.y),
+                   ez = wide_grid_exponent(node.hi.z - node.lo.z);
+    const float sx = wide_grid_step(ex), sy = wide_grid_step(ey), sz = wide_grid_step(ez);
+    uint32_t imask = 0, meta[2] = {0, 0}, q[6][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};
+    uint32_t prim_off = 0;
+    for (int s = 0; s < 8; s++) {
+        const int c = child_in_slot[s];
+        if (c < 0) continue;
+        uint32_t m;
+        if (w.ref[c] >= 0) {
+            imask |= 1u << s;
+            m = (1u << 5) | (24u + (uint32_t) s);
+        } else {
+            const uint32_t unary = (1u << w.count[c]) - 1u;   // 1 -> 001, 2 -> 011, 3 -> 111
+            m = (unary << 5) | prim_off;
+            prim_off += (uint32_t) w.count[c];
+        }
+        const int h = s >> 2, sh = 8 * (s & 3);
+        meta[h] |= m << sh;
+        const Aabb &b = w.box[c];
+        q[0][h] |= wide_quant_lo(b.lo.x, node.lo.x, sx) << sh;
+        q[1][h] |= wide_quant_lo(b.lo.y, node.lo.y, sy) << sh;
+        q[2][h] |= wide_quant_lo(b.lo.z, node.lo.z, sz) << sh;
+        q[3][h] |= wide_quant_hi(b.hi.x, node.lo.x, sx) << sh;
+        q[4][h] |= wide_quant_hi(b.hi.y, node.lo.y, sy) << sh;
+        q[5][h] |= wide_quant_hi(b.hi.z, node.lo.z, sz) << sh;
+    }
+    out.n0 = make_float4(node.lo.x, node.lo.y, node.lo.z, u2f(ex | (ey << 8) | (ez << 16) | (imask << 24)));
+    out.n1 = make_uint4(child_base, prim_base, meta[0], meta[1]);
+    out.n2 = make_uint4(q[0][0], q[0][1], q[1][0], q[1][1]);
+    out.n3 = make_uint4(q[2][0], q[2][1], q[3][0], q[3][1]);
+    out.n4 = make_uint4(q[4][0], q[4][1], q[5][0], q[5][1]);
+}
+RT_HD int wide_inner_count(const WideChildren &w) { int k = 0; for (int c = 0; c < w.n; c++) k += w.ref[c] >= 0; return k; }
+RT_HD int wide_prim_count(const WideChildren &w) { int k = 0; for (int c = 0; c < w.n; c++) if (w.ref[c] < 0) k += w.count[c]; return k; }

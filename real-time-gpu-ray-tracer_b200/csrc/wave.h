@@ -1,0 +1,56 @@
+// wave.h — host side of the wavefront path tracer (kernels_wave.cu): slot-streamed path state, ray queue, and
+// the wave loop.  Replaces the reference's one-thread-per-pixel megakernel `render` (src/Global/Kernel.cu:105-147).
+#pragma once
+
+#include "device_util.h"
+#include "rt_types.h"
+
+#include <cstdint>
+#include <vector>
+
+// Device-resident state of the paths in flight.  A SLOT carries one pixel at a time through all of its samples
+// and bounces (the reference's per-pixel XORWOW stream is consumed sequentially, so a pixel is the unit of
+// sequential work); when the pixel is finished the slot takes the next unstarted pixel.
+struct WaveBuffers {
+    float4 *ray_o;        // origin.xyz
+    float4 *ray_d;        // direction.xyz (not normalised after a Rough scatter, like the reference)
+    float4 *hit;          // t, u, v, bits(leaf ref)
+    int *hit_inst;        // instance index, -1 = miss
+    float4 *thr;          // path throughput.xyz, w = bits(sample index << 8 | depth)
+    float4 *acc;          // radiance sum of the finished samples.xyz, w = bits(pixel id in tile-major order), 0xFFFFFFFF = idle slot
+    uint4 *rng_a;         // XORWOW d, v0, v1, v2
+    uint2 *rng_b;         // XORWOW v3, v4
+    uint32_t *queue;      // slots with a ray to trace this wave
+    uint32_t *counts;     // [w] rays queued for wave w of the current batch
+    uint32_t *cursors;    // [w] fetch cursor of the trace kernel for wave w
+    uint32_t *next_pixel; // next unstarted pixel (tile-major id)
+    uint32_t n_slots;
+    uint32_t n_pixels;    // tile-major ids in [0, n_pixels): tiles_x * tiles_y * 32
+    uint32_t tiles_x;
+};
+
+struct WaveStats {
+    uint64_t rays = 0;
+    uint32_t waves = 0;
+    uint32_t launches = 0;
+};
+
+class WaveRenderer {
+public:
+    // renders one frame of this context's shard into fr; returns after the last wave has been enqueued AND counted
+    // (the wave loop reads a 4-byte counter back every `batch` waves to learn when all paths have ended)
+    void render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count, WaveStats &stats);
+    uint32_t slots_override = 0;   // 0 = default
+    int mode = 0;                  // 0: binary LBVH traversal, 1: compressed 8-wide
+    int refill_min = 8;            // lanes of a warp that must be idle before the warp pulls new rays
+    int node_min = 16;             // the node phase of a warp ends when fewer lanes than this stand on an inner node
+private:
+    void reserve(uint32_t n_slots);
+    DeviceBuffer<float4> ray_o_, ray_d_, hit_, thr_, acc_;
+    DeviceBuffer<int> hit_inst_;
+    DeviceBuffer<uint4> rng_a_;
+    DeviceBuffer<uint2> rng_b_;
+    DeviceBuffer<uint32_t> queue_, counters_;
+    PinnedBuffer<uint32_t> h_counts_;
+    int trace_blocks_per_sm_[4] = {0, 0, 0, 0};
+};

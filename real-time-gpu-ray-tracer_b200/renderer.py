@@ -125,6 +125,14 @@ class Renderer:
                                           abi.ptr(parent), abi.ptr(bounds)))
         return dict(keys=keys, prim_ids=ids, left=left, right=right, parent=parent, bounds=bounds)
 
+    def readWideBVH(self, which: int = 0):
+        nn, npr = C.c_size_t(), C.c_size_t()
+        self._check(self.lib.rt_read_wide_bvh(self.ctx, which, C.byref(nn), C.byref(npr), None, None))
+        nodes = np.zeros((nn.value, 20), np.uint32)
+        prims = np.zeros(npr.value, np.uint32)
+        self._check(self.lib.rt_read_wide_bvh(self.ctx, which, C.byref(nn), C.byref(npr), abi.ptr(nodes), abi.ptr(prims)))
+        return nodes, prims
+
     # -- Renderer::cleanup -----------------------------------------------------------------------
     def cleanup(self):
         if self.ctx:

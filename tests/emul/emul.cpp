@@ -21,7 +21,7 @@
 #include <vector>
 
 #include "../../real-time-gpu-ray-tracer_b200/csrc/host_scene.h"
-#include "../../real-time-gpu-ray-tracer_b200/csrc/rt_trace_core.h"
+#include "../../real-time-gpu-ray-tracer_b200/csrc/rt_pixel.h"
 #include "../../oracle/oracle_api.h"
 
 namespace {
@@ -32,9 +32,13 @@ struct Lbvh {
     std::vector<uint64_t> keys;
     std::vector<uint32_t> vals;
     std::vector<int> left, right, parent, leaf_parent;
+    std::vector<int2> range;
     std::vector<Aabb> node_box;
     std::vector<BvhNode2> nodes;
     std::vector<int> seg_root;
+    // wide (BVH8) collapse of this tree: nodes, and wide leaf order -> Morton position
+    std::vector<BvhNode8> nodes8;
+    std::vector<uint32_t> leaf_pos8;
 };
 
 int find_segment(const std::vector<uint32_t> &off, uint32_t j) {
@@ -57,9 +61,10 @@ void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vec
     b.seg_root.assign(n_segs, 0);
     const int m = n > 1 ? n - 1 : 0;
     b.left.assign(m, 0); b.right.assign(m, 0); b.parent.assign(m, -1); b.leaf_parent.assign(n, -1);
-    b.node_box.resize(m); b.nodes.resize(m);
+    b.node_box.resize(m); b.nodes.resize(m); b.range.resize(m);
     for (int i = 0; i < m; i++) {
         const KarrasNode k = karras_node(b.keys.data(), n, i);
+        b.range[i] = make_int2(k.first, k.last);
         b.left[i] = k.left; b.right[i] = k.right;
         if (k.left >= 0) b.parent[k.left] = i; else b.leaf_parent[~k.left] = i;
         if (k.right >= 0) b.parent[k.right] = i; else b.leaf_parent[~k.right] = i;
@@ -105,11 +110,48 @@ void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vec
     }
 }
 
+// serial twin of the device collapse (kernels_wide.cu): queue entries are processed in index order and
+// allocations are sequential, so the layout is the canonical one the GPU layout is compared against
+void collapse_wide(Lbvh &b, const std::vector<uint32_t> &seg_offset, int leaf_max) {
+    const int n = b.n, n_segs = (int) seg_offset.size() - 1;
+    std::vector<float4> nlo(b.node_box.size()), nhi(b.node_box.size()), plo(n), phi(n);
+    for (size_t i = 0; i < b.node_box.size(); i++) {
+        nlo[i] = make_float4(b.node_box[i].lo.x, b.node_box[i].lo.y, b.node_box[i].lo.z, 0.f);
+        nhi[i] = make_float4(b.node_box[i].hi.x, b.node_box[i].hi.y, b.node_box[i].hi.z, 0.f);
+    }
+    for (int i = 0; i < n; i++) {
+        plo[i] = make_float4(b.prim_box[i].lo.x, b.prim_box[i].lo.y, b.prim_box[i].lo.z, 0.f);
+        phi[i] = make_float4(b.prim_box[i].hi.x, b.prim_box[i].hi.y, b.prim_box[i].hi.z, 0.f);
+    }
+    const BinaryTreeView view{b.left.data(), b.right.data(), b.range.data(), nlo.data(), nhi.data(), plo.data(), phi.data(), b.vals.data()};
+    std::vector<int> queue;
+    for (int s = 0; s < n_segs; s++)
+        queue.push_back(seg_offset[s + 1] - seg_offset[s] == 1u ? ~(int) seg_offset[s] : b.seg_root[s]);
+    b.nodes8.clear();
+    b.leaf_pos8.clear();
+    for (size_t i = 0; i < queue.size(); i++) {
+        WideChildren w;
+        wide_expand(view, queue[i], leaf_max, w);
+        const uint32_t child_base = (uint32_t) queue.size(), prim_base = (uint32_t) b.leaf_pos8.size();
+        BvhNode8 node;
+        int child_in_slot[8];
+        wide_encode(w, child_base, prim_base, node, child_in_slot);
+        for (int sl = 0; sl < 8; sl++) {
+            const int c = child_in_slot[sl];
+            if (c < 0) continue;
+            if (w.ref[c] >= 0) queue.push_back(w.ref[c]);
+            else for (int k = 0; k < w.count[c]; k++) b.leaf_pos8.push_back((uint32_t) (w.first[c] + k));
+        }
+        b.nodes8.push_back(node);
+    }
+}
+
 struct Emul {
     HostScene hs;
     Lbvh blas, tlas;
-    std::vector<TriIsect> leaf_tris;
-    std::vector<uint32_t> leaf_prims;
+    std::vector<TriIsect> leaf_tris, leaf_tris8;
+    std::vector<uint32_t> leaf_prims, leaf_prims8, tlas_leaf_inst;
+    bool wide = true;
     std::vector<InstanceD> instances;
     std::vector<Aabb> wbox;
     std::vector<f3> wcentroid;
@@ -178,10 +220,16 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
         }
     }
 
+    collapse_wide(b, hs.seg_offset, RT_WIDE_LEAF_MAX);
+    e->leaf_prims8.resize(n);
+    e->leaf_tris8.resize(n);
+    for (int q = 0; q < n; q++) { e->leaf_prims8[q] = e->leaf_prims[b.leaf_pos8[q]]; e->leaf_tris8[q] = e->leaf_tris[b.leaf_pos8[q]]; }
+
     // ---- instances + TLAS (twin of update_instances_and_tlas)
     const int ni = (int) hs.inst_desc.size();
     std::vector<InstanceXformIn> xin(ni);
     hs.fill_xform_in(xin.data(), b.seg_root);
+    for (int i = 0; i < ni; i++) xin[i].root8 = xin[i].blas;      // wide root of BLAS s is wide node s
     e->instances.resize(ni); e->wbox.resize(ni); e->wcentroid.resize(ni);
     Lbvh &t = e->tlas;
     t.n = ni;
@@ -198,6 +246,9 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     for (int i = 0; i < ni; i++) t.keys[i] = morton_code(t.prim_box[i], scene, tbits);
     const std::vector<uint32_t> toff{0u, (uint32_t) ni}, ttype{0u};
     build_tree(t, toff, ttype, 1);
+    collapse_wide(t, toff, 1);
+    e->tlas_leaf_inst.resize(ni);
+    for (int q = 0; q < ni; q++) e->tlas_leaf_inst[q] = t.vals[t.leaf_pos8[q]];
 
     SceneD &sc = e->sc;
     sc.tlas_nodes = t.nodes.data(); sc.blas_nodes = b.nodes.data(); sc.instances = e->instances.data();
@@ -205,6 +256,9 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     sc.spheres = hs.sphere_rec.data(); sc.quads = hs.quad_rec.data();
     sc.roughs = hs.roughs.data(); sc.metals = hs.metals.data(); sc.dielectrics = hs.dielectrics.data();
     sc.tlas_root_ref = ni > 1 ? 0 : make_leaf_ref(0u, 0u);
+    sc.tlas_nodes8 = t.nodes8.data(); sc.blas_nodes8 = b.nodes8.data(); sc.tlas_leaf_inst = e->tlas_leaf_inst.data();
+    sc.leaf_tris8 = e->leaf_tris8.data(); sc.leaf_prims8 = e->leaf_prims8.data();
+    e->wide = !(flags & 0x80000000u);     // test-only switch: traverse the binary LBVH instead of the wide BVH
     return e;
 }
 
@@ -225,7 +279,9 @@ uint32_t emul_render(void *h, uint64_t seed, int y0, int y1, int threads, uint8_
             curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &st);
             RngState r{st.d, st.v[0], st.v[1], st.v[2], st.v[3], st.v[4]};
             uint32_t overflow = 0;
-            const PixelOut o = render_pixel<false>(e.sc, cam, x, (uint32_t) y, r, overflow);
+            uint2 stack[RT_WIDE_STACK];
+            const PixelOut o = e.wide ? render_pixel<false, true>(e.sc, cam, x, (uint32_t) y, r, overflow, stack, 1)
+                                      : render_pixel<false, false>(e.sc, cam, x, (uint32_t) y, r, overflow, stack, 1);
             if (overflow) ovf = 1;
             segs += o.rays;
             const size_t p = (size_t) y * cam.width + x;
@@ -273,6 +329,17 @@ void emul_lbvh(void *h, int which, size_t *n_prims, uint64_t *keys, uint32_t *va
         bounds[6 * i] = b.node_box[i].lo.x; bounds[6 * i + 1] = b.node_box[i].lo.y; bounds[6 * i + 2] = b.node_box[i].lo.z;
         bounds[6 * i + 3] = b.node_box[i].hi.x; bounds[6 * i + 4] = b.node_box[i].hi.y; bounds[6 * i + 5] = b.node_box[i].hi.z;
     }
+}
+
+// wide BVH of the BLAS batch (which = 0) or the TLAS (which = 1); same layout as rt_read_wide_bvh
+void emul_wide(void *h, int which, size_t *n_nodes, size_t *n_leaf_prims, void *nodes, uint32_t *leaf_prims) {
+    Emul &e = *(Emul *) h;
+    const Lbvh &b = which == 0 ? e.blas : e.tlas;
+    const std::vector<uint32_t> &lp = which == 0 ? e.leaf_prims8 : e.tlas_leaf_inst;
+    if (n_nodes) *n_nodes = b.nodes8.size();
+    if (n_leaf_prims) *n_leaf_prims = lp.size();
+    if (nodes) memcpy(nodes, b.nodes8.data(), b.nodes8.size() * sizeof(BvhNode8));
+    if (leaf_prims) memcpy(leaf_prims, lp.data(), lp.size() * 4);
 }
 
 } // extern "C"

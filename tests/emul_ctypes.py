@@ -33,6 +33,7 @@ def load():
     lib.emul_instances.argtypes = [vp, vp]
     lib.emul_camera.argtypes = [vp, vp]
     lib.emul_lbvh.argtypes = [vp, i32, C.POINTER(sz), vp, vp, vp, vp, vp, vp]
+    lib.emul_wide.argtypes = [vp, i32, C.POINTER(sz), C.POINTER(sz), vp, vp]
     return lib
 
 
@@ -79,6 +80,17 @@ class Emul:
         bounds = np.zeros((m, 6), np.float32)
         self.lib.emul_lbvh(self.h, which, C.byref(nn), abi.ptr(keys), abi.ptr(vals), abi.ptr(left), abi.ptr(right), abi.ptr(parent), abi.ptr(bounds))
         return dict(keys=keys, prim_ids=vals, left=left, right=right, parent=parent, bounds=bounds)
+
+    def wide(self, which=0):
+        nn, npr = C.c_size_t(), C.c_size_t()
+        self.lib.emul_wide(self.h, which, C.byref(nn), C.byref(npr), None, None)
+        nodes = np.zeros((nn.value, 20), np.uint32)
+        prims = np.zeros(npr.value, np.uint32)
+        self.lib.emul_wide(self.h, which, C.byref(nn), C.byref(npr), abi.ptr(nodes), abi.ptr(prims))
+        return nodes, prims
+
+    def n_blas(self):
+        return len({(int(i["type"]), int(i["first_prim"]), max(1, int(i["prim_count"]))) for i in self.sc.instances})
 
     def close(self):
         if self.h:

@@ -23,7 +23,7 @@ def gpu_frame(pkg, sc, flags=0, seed=SEED):
                    t=r.readFramebuffer(pkg.abi.BUF_PRIMARY_T).reshape(H, W).copy(),
                    inst=r.readFramebuffer(pkg.abi.BUF_PRIMARY_INSTANCE).reshape(H, W).copy(),
                    prim=r.readFramebuffer(pkg.abi.BUF_PRIMARY_PRIM).reshape(H, W).copy(),
-                   lbvh=r.readLBVH(0), tlas=r.readLBVH(1))
+                   lbvh=r.readLBVH(0), tlas=r.readLBVH(1), wide=r.readWideBVH(0), wide_tlas=r.readWideBVH(1))
     finally:
         r.cleanup()
     return res
@@ -67,6 +67,28 @@ def test_device_lbvh_equals_cpu_twin(pkg, idx):
         twin = e.lbvh(which)
         for name in ("keys", "prim_ids", "left", "right", "parent", "bounds"):
             assert np.array_equal(g[key][name], twin[name]), f"{sc.name}: {key}.{name} differs from the CPU twin"
+
+
+@pytest.mark.parametrize("idx", range(5))
+def test_device_wide_bvh_equals_cpu_twin(pkg, idx):
+    """The compressed 8-wide BVH built on the device equals the serial twin's node for node (memory placement aside)."""
+    import emul_ctypes as ec
+    sc = parity_scenes(pkg.scenes)[idx]
+    g = gpu_frame(pkg, sc)
+    e = ec.Emul(sc)
+    canon = pkg.abi.canonical_wide_bvh
+    assert canon(*g["wide"], range(e.n_blas())) == canon(*e.wide(0), range(e.n_blas())), sc.name
+    assert canon(*g["wide_tlas"], [0]) == canon(*e.wide(1), [0]), sc.name
+    assert sorted(g["wide"][1].tolist()) == sorted(e.wide(0)[1].tolist())
+
+
+@pytest.mark.parametrize("idx", range(5))
+@pytest.mark.parametrize("mode", ["bvh2", "megakernel", "megakernel+bvh2"])
+def test_comparison_modes(pkg, port, idx, mode):
+    """The comparison modes (binary LBVH traversal, one-thread-per-pixel kernel) give the same frame as the default path."""
+    flags = (pkg.abi.FLAG_TRAVERSE_BVH2 if "bvh2" in mode else 0) | (pkg.abi.FLAG_MEGAKERNEL if "megakernel" in mode else 0)
+    sc = parity_scenes(pkg.scenes)[idx]
+    check_against_oracle(gpu_frame(pkg, sc, flags=flags), port.scene(sc, 99), sc)
 
 
 def test_device_equals_cpu_emulation_bitwise(pkg):

@@ -189,7 +189,7 @@ def run_ours(args):
     pkg, sc, cfg = workload(args)
     abi = pkg.abi
 
-    base_flags = abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0
+    base_flags = (abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0) | (abi.FLAG_MEGAKERNEL if args.megakernel else 0)
     r = pkg.Renderer(device=local, flags=base_flags)
     t0 = time.perf_counter()
     st = r.commitScene(sc)
@@ -351,6 +351,7 @@ def main():
     ap.add_argument("--nz", type=int, default=500)
     ap.add_argument("--tile-rows", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--megakernel", action="store_true", help="comparison mode: one thread per pixel (the reference's kernel structure)")
     ap.add_argument("--bvh2", action="store_true", help="comparison mode: traverse the binary LBVH instead of the wide BVH")
     args = ap.parse_args()
     if args.impl == "reference":

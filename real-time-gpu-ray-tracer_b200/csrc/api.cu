@@ -140,6 +140,7 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     if (const char *e = getenv("RTB200_SLOTS")) c->wave.slots_override = (uint32_t) strtoul(e, nullptr, 0);
     if (const char *e = getenv("RTB200_REFILL_MIN")) c->wave.refill_min = atoi(e);
     if (const char *e = getenv("RTB200_NODE_MIN")) c->wave.node_min = atoi(e);
+    if (const char *e = getenv("RTB200_TRACE_BLOCKS_PER_SM")) c->wave.blocks_per_sm_override = atoi(e);
     *out = c;
     return RT_OK;
 }
@@ -327,7 +328,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     if (mega) {
         launch_render(sc, ctx->hs.cam, fr, s);
     } else {
-        ctx->wave.mode = 0;   // TODO wide trace kernel
+        ctx->wave.mode = fr.traverse_bvh2 ? 0 : 1;
         ctx->wave.render(sc, ctx->hs.cam, fr, s, ctx->sm_count, ws);
     }
     CUDA_CHECK(cudaEventRecord(ctx->ev[3], s));

@@ -272,6 +272,148 @@ parked:
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// TRACE, compressed 8-wide BVH (the default).  Same persistent-warp / lane-refill scheme; every lane runs the
+// per-ray state machine of trace_closest8 (rt_wide_trace.h) step for step, so a ray sees exactly the node loads
+// and primitive tests, in exactly the order, of the serial definition — the warp only decides WHEN a lane may
+// take its next step, so that lanes take the expensive steps together:
+//   NODE  : pop the nearest pending child of the node group, fetch its 80-byte node, test the 8 child boxes
+//   LEAF  : one primitive test (BLAS) or one instance entry (TLAS) of the primitive group
+//   cheap : stack pop / instance exit / ray finished (done by whoever needs it before every vote)
+// Traversal stacks (24 x 8 B per lane) live in shared memory, interleaved by lane (no bank conflicts).
+constexpr uint32_t NG_INNER = 0x00FFFFFFu;      // node group has pending inner hits iff .y > NG_INNER
+
+template<bool COUNT>
+__global__ void __launch_bounds__(TRACE_THREADS, 4) wave_trace8_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ WaveBuffers wb,
+                                                                       uint32_t wave, int refill_min, int node_min, unsigned long long *stats_out) {
+    __shared__ uint2 stack_mem[RT_WIDE_STACK * TRACE_THREADS];
+    uint2 *const stk = stack_mem + threadIdx.x;               // entry k at stk[k * TRACE_THREADS]
+    const uint32_t n_rays = wb.counts[wave];
+    uint32_t *cursor = wb.cursors + wave;
+    uint32_t slot = SLOT_IDLE;
+    bool exhausted = false;
+    WideRay r{};
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
+    int sp = 0, inst = -1, inst_sp = 0, prim_type = 0;
+    HitD hit{};
+    uint32_t overflow = 0;
+    TravStats stats{0, 0, 0};
+
+    for (;;) {
+        // ---- refill -------------------------------------------------------------------------------------------------
+        const uint32_t idle = __ballot_sync(0xffffffffu, slot == SLOT_IDLE);
+        if (idle != 0u && !exhausted && (__popc(idle) >= refill_min || idle == 0xffffffffu)) {
+            const uint32_t leader = __ffs(idle) - 1u;
+            uint32_t base = 0;
+            if (lane_id() == leader) base = atomicAdd(cursor, (uint32_t) __popc(idle));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (slot == SLOT_IDLE) {
+                const uint32_t k = base + (uint32_t) __popc(idle & ((1u << lane_id()) - 1u));
+                if (k < n_rays) {
+                    slot = __ldg(&wb.queue[k]);
+                    const float4 o = wb.ray_o[slot], d = wb.ray_d[slot];
+                    r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);
+                    wide_setup_ray(r);
+                    hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.f; hit.v = 0.f; hit.inst = -1; hit.leaf = 0;
+                    sp = 0; inst = -1; inst_sp = 0;
+                    ng = make_uint2(0u, 0x80000000u);           // TLAS root: one pending inner hit at relative index 0
+                    tg = make_uint2(0u, 0u);
+                }
+            }
+            if (base + (uint32_t) __popc(idle) >= n_rays) exhausted = true;
+        }
+        if (__ballot_sync(0xffffffffu, slot != SLOT_IDLE) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        // ---- node phase ---------------------------------------------------------------------------------------------
+        for (;;) {
+            // cheap transitions: nothing pending in registers -> leave instance / finish / pop
+            if (slot != SLOT_IDLE && tg.y == 0u && ng.y <= NG_INNER) {
+                if (inst >= 0 && sp == inst_sp) {                // BLAS exhausted: back to world space
+                    inst = -1;
+                    const float4 o = wb.ray_o[slot], d = wb.ray_d[slot];
+                    r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);
+                    wide_setup_ray(r);
+                }
+                if (sp == 0) {
+                    wb.hit[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float((uint32_t) hit.leaf));
+                    wb.hit_inst[slot] = hit.inst;
+                    slot = SLOT_IDLE;
+                    ng = make_uint2(0u, 0u);
+                } else {
+                    sp--;
+                    const uint2 e = stk[sp * TRACE_THREADS];
+                    if (e.y > NG_INNER) ng = e; else { tg = e; ng = make_uint2(0u, 0u); }
+                }
+            }
+            const bool on_node = slot != SLOT_IDLE && tg.y == 0u && ng.y > NG_INNER;
+            const uint32_t node_lanes = __ballot_sync(0xffffffffu, on_node);
+            const uint32_t leaf_lanes = __ballot_sync(0xffffffffu, slot != SLOT_IDLE && tg.y != 0u);
+            if (node_lanes == 0u || (__popc(node_lanes) < node_min && leaf_lanes != 0u)) break;
+            if (on_node) {
+                const uint32_t hits_imask = ng.y;
+                const int bit = rt_bfind(hits_imask);
+                const uint32_t base = ng.x;
+                ng.y &= ~(1u << bit);
+                if (ng.y > NG_INNER) {
+                    if (sp < RT_WIDE_STACK) { stk[sp * TRACE_THREADS] = ng; sp++; } else overflow = 1u;
+                }
+                const uint32_t sl = ((uint32_t) bit - 24u) ^ (r.oct_inv4 & 0xFFu);
+                const uint32_t rel = (uint32_t) __popc(hits_imask & ~(0xFFFFFFFFu << sl));
+                const BvhNode8 n = load_node8(inst < 0 ? sc.tlas_nodes8 : sc.blas_nodes8, base + rel);
+                if (COUNT) stats.nodes++;
+                const uint32_t hm = node8_intersect(n, r, RT_TMIN, hit.tc);
+                ng.x = n.n1.x;
+                ng.y = hm & 0xFF000000u;
+                if (ng.y) ng.y |= __float_as_uint(n.n0.w) >> 24;
+                tg.x = n.n1.y;
+                tg.y = hm & 0x00FFFFFFu;
+            }
+        }
+        // ---- leaf phase: one primitive test or one instance entry per lane -------------------------------------------
+        if (slot != SLOT_IDLE && tg.y != 0u) {
+            const int idx = rt_bfind(tg.y);
+            tg.y &= ~(1u << idx);
+            if (inst >= 0) {
+                if (COUNT) stats.prims++;
+                leaf_test8(sc, (uint32_t) prim_type, tg.x + (uint32_t) idx, r.ray, RT_TMIN, inst, hit);
+            } else {
+                // TLAS leaf: enter one instance, keep the rest of the group and the node group for later
+                if (tg.y) { if (sp < RT_WIDE_STACK) { stk[sp * TRACE_THREADS] = tg; sp++; } else overflow = 1u; }
+                if (ng.y > NG_INNER) { if (sp < RT_WIDE_STACK) { stk[sp * TRACE_THREADS] = ng; sp++; } else overflow = 1u; }
+                inst = (int) __ldg(&sc.tlas_leaf_inst[tg.x + (uint32_t) idx]);
+                if (COUNT) stats.insts++;
+                float inv[12];
+                int root8;
+                load_instance_wide(sc, inst, inv, root8, prim_type);
+                const f3 wo = r.ray.o, wd = r.ray.d;
+                r.ray.o = xf_point(inv, wo);                     // Instance::hit: origin as point, direction as vector,
+                r.ray.d = xf_vector(inv, wd);                    // not re-normalised (reference src/AS/Instance.cu:26-28)
+                wide_setup_ray(r);
+                inst_sp = sp;
+                ng = make_uint2((uint32_t) root8, 0x80000000u);
+                tg = make_uint2(0u, 0u);
+            }
+        }
+    }
+    if (overflow) atomicOr(reinterpret_cast<unsigned int *>(stats_out + 1), 1u);
+    if (COUNT) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            stats.nodes += __shfl_xor_sync(0xffffffffu, stats.nodes, off);
+            stats.prims += __shfl_xor_sync(0xffffffffu, stats.prims, off);
+            stats.insts += __shfl_xor_sync(0xffffffffu, stats.insts, off);
+        }
+        if (lane_id() == 0) {
+            atomicAdd(stats_out + 2, (unsigned long long) stats.nodes);
+            atomicAdd(stats_out + 3, (unsigned long long) stats.prims);
+            atomicAdd(stats_out + 4, (unsigned long long) stats.insts);
+        }
+    }
+}
+
 } // namespace
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -301,11 +443,14 @@ void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr
     if (trace_blocks_per_sm_[0] == 0) {
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_blocks_per_sm_[0], wave_trace2_kernel<false>, TRACE_THREADS, 0));
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_blocks_per_sm_[1], wave_trace2_kernel<true>, TRACE_THREADS, 0));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_blocks_per_sm_[2], wave_trace8_kernel<false>, TRACE_THREADS, 0));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_blocks_per_sm_[3], wave_trace8_kernel<true>, TRACE_THREADS, 0));
     }
     const bool count = fr.count_traversal != 0;
-    const int trace_blocks = sm_count * std::max(1, trace_blocks_per_sm_[count ? 1 : 0]);
-    const unsigned shade_blocks = div_up(n_slots, SHADE_THREADS);
     const bool wide = mode == 1;
+    int trace_blocks = sm_count * std::max(1, trace_blocks_per_sm_[(wide ? 2 : 0) + (count ? 1 : 0)]);
+    if (blocks_per_sm_override > 0) trace_blocks = sm_count * std::min(blocks_per_sm_override, trace_blocks / sm_count);
+    const unsigned shade_blocks = div_up(n_slots, SHADE_THREADS);
 
     CUDA_CHECK(cudaMemsetAsync(wb.next_pixel, 0, sizeof(uint32_t), stream));
     stats = WaveStats{};
@@ -321,8 +466,13 @@ void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr
                 if (wide) wave_shade_kernel<false, true><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
                 else wave_shade_kernel<false, false><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
             }
-            if (count) wave_trace2_kernel<true><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
-            else wave_trace2_kernel<false><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+            if (wide) {
+                if (count) wave_trace8_kernel<true><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+                else wave_trace8_kernel<false><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+            } else {
+                if (count) wave_trace2_kernel<true><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+                else wave_trace2_kernel<false><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+            }
             stats.launches += 2;
         }
         CUDA_CHECK(cudaGetLastError());

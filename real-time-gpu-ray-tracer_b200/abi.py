@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "librtb200.so")
+# RTB200_LIB selects another in-tree build of the same sources (tuning variants made by csrc/Makefile VARIANT=...)
+LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(PKG_DIR, "librtb200.so")
 
 # enums (values identical to the reference: include/Basic/BasicTypes.cuh:9-16)
 SPHERE, PARALLELOGRAM, TRIANGLE = 0, 1, 2

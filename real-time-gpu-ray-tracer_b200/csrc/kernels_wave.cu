@@ -283,9 +283,16 @@ parked:
 //   cheap : stack pop / instance exit / ray finished (done by whoever needs it before every vote)
 // Traversal stacks (24 x 8 B per lane) live in shared memory, interleaved by lane (no bank conflicts).
 constexpr uint32_t NG_INNER = 0x00FFFFFFu;      // node group has pending inner hits iff .y > NG_INNER
+#ifndef RT_TRACE8_MIN_BLOCKS
+#define RT_TRACE8_MIN_BLOCKS 8
+#endif
+#ifndef RT_PREFETCH
+#define RT_PREFETCH 0
+#endif
+__device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
 template<bool COUNT>
-__global__ void __launch_bounds__(TRACE_THREADS, 4) wave_trace8_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ WaveBuffers wb,
+__global__ void __launch_bounds__(TRACE_THREADS, RT_TRACE8_MIN_BLOCKS) wave_trace8_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ WaveBuffers wb,
                                                                        uint32_t wave, int refill_min, int node_min, unsigned long long *stats_out) {
     __shared__ uint2 stack_mem[RT_WIDE_STACK * TRACE_THREADS];
     uint2 *const stk = stack_mem + threadIdx.x;               // entry k at stk[k * TRACE_THREADS]
@@ -331,7 +338,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 4) wave_trace8_kernel(const __g
         for (;;) {
             // cheap transitions: nothing pending in registers -> leave instance / finish / pop
             if (slot != SLOT_IDLE && tg.y == 0u && ng.y <= NG_INNER) {
-                if (inst >= 0 && sp == inst_sp) {                // BLAS exhausted: back to world space
+                if (inst >= 0 && sp == inst_sp && sp != 0) {     // BLAS exhausted, TLAS work left: back to world space
                     inst = -1;
                     const float4 o = wb.ray_o[slot], d = wb.ray_d[slot];
                     r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);
@@ -370,6 +377,17 @@ __global__ void __launch_bounds__(TRACE_THREADS, 4) wave_trace8_kernel(const __g
                 if (ng.y) ng.y |= __float_as_uint(n.n0.w) >> 24;
                 tg.x = n.n1.y;
                 tg.y = hm & 0x00FFFFFFu;
+#if RT_PREFETCH
+                // the next record this lane will need is known now: start its trip through L2 while the lane waits for its phase
+                if (tg.y) {
+                    if (inst >= 0 && prim_type == 2) prefetch_l1(sc.leaf_tris8 + (tg.x + (uint32_t) rt_bfind(tg.y)));
+                } else if (ng.y) {
+                    const uint32_t sl2 = ((uint32_t) rt_bfind(ng.y) - 24u) ^ (r.oct_inv4 & 0xFFu);
+                    const BvhNode8 *nx = (inst < 0 ? sc.tlas_nodes8 : sc.blas_nodes8) + (ng.x + (uint32_t) __popc(ng.y & ~(0xFFFFFFFFu << sl2)));
+                    prefetch_l1(nx);
+                    prefetch_l1(reinterpret_cast<const char *>(nx) + 64);
+                }
+#endif
             }
         }
         // ---- leaf phase: one primitive test or one instance entry per lane -------------------------------------------

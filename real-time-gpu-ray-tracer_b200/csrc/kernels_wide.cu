@@ -9,6 +9,8 @@
 // the order of the atomics, and the parity tests compare the trees canonically against the serial twin.
 #include "build.h"
 
+#include <cstdlib>
+
 namespace {
 
 constexpr int CT = 128;
@@ -119,7 +121,8 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     const int max_blocks = sm_count * collapse_blocks_per_sm_;
     const int want_blocks = (int) div_up((size_t) capacity, CT);
     const int blocks = want_blocks < max_blocks ? want_blocks : max_blocks;
-    const int leaf_max = leaf_mode == 1 ? 1 : RT_WIDE_LEAF_MAX;
+    static const int leaf_max_env = getenv("RTB200_LEAF_MAX") ? atoi(getenv("RTB200_LEAF_MAX")) : 0;   // tuning experiments only
+    const int leaf_max = leaf_mode == 1 ? 1 : (leaf_max_env >= 1 && leaf_max_env <= 3 ? leaf_max_env : RT_WIDE_LEAF_MAX);
     collapse_kernel<<<blocks, CT, 0, stream>>>(view, leaf_max, capacity, queue_.get(), wide_counters_.get(), nodes8_.get(), leaf_pos8_.get());
     const GeometryD none{nullptr, nullptr, nullptr};
     emit_leaves8_kernel<<<div_up(n, 256), 256, 0, stream>>>(geo ? *geo : none, leaf_pos8_.get(), vals_, seg_offset_.get(), seg_type_.get(),

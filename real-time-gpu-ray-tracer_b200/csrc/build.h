@@ -35,7 +35,9 @@ public:
     void build_blas(const GeometryD &geo, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type,
                     const std::vector<uint32_t> &seg_first, int morton_bits, cudaStream_t stream, int sm_count);
     // ---- TLAS: one segment over instance world boxes already written to prim_lo()/prim_hi() and bounds() --
+    void prepare_blas(const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type);   // allocations only
     void prepare_tlas(int n_instances);
+    bool emit_bvh2 = false;                  // also emit the 64-byte binary nodes + their leaf-order records (RT_FLAG_TRAVERSE_BVH2)
     void build_tlas(int n_instances, int morton_bits, cudaStream_t stream, int sm_count);
 
     // results (device): the compressed 8-wide BVH the render kernels traverse (root of segment s = node s) ...

@@ -66,7 +66,12 @@ __global__ void __launch_bounds__(BT) prim_bounds_kernel(GeometryD geo, const ui
         prim_lo[j] = make_float4(box.lo.x, box.lo.y, box.lo.z, 0.0f);
         prim_hi[j] = make_float4(box.hi.x, box.hi.y, box.hi.z, 0.0f);
     }
-    const int seg0 = __shfl_sync(0xffffffffu, seg, 0);
+    // reduce per warp, then per block when the whole block lies in one segment (the common case: one atomic set per
+    // 256 primitives — per-warp atomics on the same six words serialised in L2 and dominated this kernel)
+    __shared__ float sh_box[BT / 32][6];
+    __shared__ int sh_seg[BT / 32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int seg0 = __shfl_sync(0xffffffffu, seg, 0);
     const bool uniform = __all_sync(0xffffffffu, seg == seg0 || !valid) && seg0 >= 0;
     if (uniform) {
 #pragma unroll
@@ -78,9 +83,37 @@ __global__ void __launch_bounds__(BT) prim_bounds_kernel(GeometryD geo, const ui
             box.hi.y = fmaxf(box.hi.y, __shfl_xor_sync(0xffffffffu, box.hi.y, off));
             box.hi.z = fmaxf(box.hi.z, __shfl_xor_sync(0xffffffffu, box.hi.z, off));
         }
-        if ((threadIdx.x & 31) == 0) atomic_bounds(bounds + 6 * seg0, box);
     } else if (valid) {
         atomic_bounds(bounds + 6 * seg, box);
+    }
+    if (lane == 0) {
+        sh_seg[warp] = uniform ? seg0 : -2;          // -2: this warp already did its own atomics; -1: warp past the end
+        sh_box[warp][0] = box.lo.x; sh_box[warp][1] = box.lo.y; sh_box[warp][2] = box.lo.z;
+        sh_box[warp][3] = box.hi.x; sh_box[warp][4] = box.hi.y; sh_box[warp][5] = box.hi.z;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const int s = lane < BT / 32 ? sh_seg[lane] : -1;
+        const int sfirst = __shfl_sync(0xffffffffu, s, 0);
+        const bool block_uniform = __all_sync(0xffffffffu, s == sfirst || s == -1) && sfirst >= 0;
+        if (block_uniform) {
+            if (lane == 0) {
+                Aabb b;
+                b.lo = mk3(sh_box[0][0], sh_box[0][1], sh_box[0][2]);
+                b.hi = mk3(sh_box[0][3], sh_box[0][4], sh_box[0][5]);
+                for (int w = 1; w < BT / 32; w++) {
+                    if (sh_seg[w] < 0) continue;
+                    b.lo = mk3(fminf(b.lo.x, sh_box[w][0]), fminf(b.lo.y, sh_box[w][1]), fminf(b.lo.z, sh_box[w][2]));
+                    b.hi = mk3(fmaxf(b.hi.x, sh_box[w][3]), fmaxf(b.hi.y, sh_box[w][4]), fmaxf(b.hi.z, sh_box[w][5]));
+                }
+                atomic_bounds(bounds + 6 * sfirst, b);
+            }
+        } else if (lane < BT / 32 && s >= 0) {
+            Aabb b;
+            b.lo = mk3(sh_box[lane][0], sh_box[lane][1], sh_box[lane][2]);
+            b.hi = mk3(sh_box[lane][3], sh_box[lane][4], sh_box[lane][5]);
+            atomic_bounds(bounds + 6 * s, b);
+        }
     }
 }
 
@@ -147,8 +180,9 @@ __global__ void __launch_bounds__(BT) refit_kernel(const float4 *__restrict__ pr
         float4 llo, lhi, rlo, rhi;
         if (l >= 0) { llo = __ldcg(&node_lo[l]); lhi = __ldcg(&node_hi[l]); } else { const uint32_t p = vals[~l]; llo = prim_lo[p]; lhi = prim_hi[p]; }
         if (r >= 0) { rlo = __ldcg(&node_lo[r]); rhi = __ldcg(&node_hi[r]); } else { const uint32_t p = vals[~r]; rlo = prim_lo[p]; rhi = prim_hi[p]; }
-        __stcg(&node_lo[cur], make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), 0.0f));
-        __stcg(&node_hi[cur], make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), 0.0f));
+        // .w carries the node's Karras children so the wide collapse gets box + children in one pair of loads
+        __stcg(&node_lo[cur], make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), __int_as_float(l)));
+        __stcg(&node_hi[cur], make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), __int_as_float(r)));
         cur = parent[cur];
     }
 }
@@ -272,14 +306,17 @@ void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const
                                                            leaf_parent_.get(), seg_root_.get(), range_.get());
         refit_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(), parent_.get(),
                                                       leaf_parent_.get(), n, flags_.get(), node_lo_.get(), node_hi_.get());
-        emit_nodes_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(),
-                                                               node_lo_.get(), node_hi_.get(), seg_offset_.get(), seg_type_.get(), n_segs, n, leaf_mode,
-                                                               nodes_.get());
-        launches += 3;
+        launches += 2;
+        if (emit_bvh2) {
+            emit_nodes_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(),
+                                                                   node_lo_.get(), node_hi_.get(), seg_offset_.get(), seg_type_.get(), n_segs, n, leaf_mode,
+                                                                   nodes_.get());
+            launches++;
+        }
     }
     single_prim_roots_kernel<<<div_up(n_segs, BT), BT, 0, stream>>>(seg_offset_.get(), seg_type_.get(), n_segs, leaf_mode, vals_, seg_root_.get());
     launches++;
-    if (leaf_mode == 0) {
+    if (leaf_mode == 0 && emit_bvh2) {
         emit_leaves_kernel<<<div_up(n, BT), BT, 0, stream>>>(*geo, vals_, seg_offset_.get(), seg_type_.get(), seg_first_.get(), n_segs, n,
                                                             leaf_prims_.get(), leaf_tris_.get());
         launches++;
@@ -293,9 +330,7 @@ void LbvhBuilder::build_blas(const GeometryD &geo, const std::vector<uint32_t> &
     const int n_segs = (int) seg_type.size();
     const int n = (int) seg_offset.back();
     n_ = n; n_segs_ = n_segs; launches = 0;
-    bool tris = false;
-    for (uint32_t t: seg_type) tris |= (t == 2u);
-    reserve(n, n_segs, tris);
+    prepare_blas(seg_offset, seg_type);
     seg_offset_.upload(seg_offset.data(), seg_offset.size(), stream);
     seg_type_.upload(seg_type.data(), seg_type.size(), stream);
     seg_first_.upload(seg_first.data(), seg_first.size(), stream);
@@ -312,6 +347,12 @@ void LbvhBuilder::build_blas(const GeometryD &geo, const std::vector<uint32_t> &
     seg_root_host.resize(n_segs);
     CUDA_CHECK(cudaMemcpyAsync(seg_root_host.data(), seg_root_.get(), n_segs * sizeof(int), cudaMemcpyDeviceToHost, stream));
     CUDA_CHECK(cudaStreamSynchronize(stream));
+}
+
+void LbvhBuilder::prepare_blas(const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type) {
+    bool tris = false;
+    for (uint32_t t: seg_type) tris |= (t == 2u);
+    reserve((int) seg_offset.back(), (int) seg_type.size(), tris);
 }
 
 void LbvhBuilder::prepare_tlas(int n_instances) {

@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
     volatile uint32_t *vc = counters;
     const int stride = gridDim.x * blockDim.x;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t backoff = 32u;
     for (;;) {
         if (i < capacity) {
             const int root = vq[i];
@@ -68,6 +69,7 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
                 __threadfence();
                 atomicAdd(&counters[2], 1u);
                 i += stride;
+                backoff = 32u;
                 continue;
             }
         }
@@ -75,6 +77,8 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
         __threadfence();
         const uint32_t alloc = vc[0];
         if (fin == alloc) break;
+        __nanosleep(backoff);                      // waiting lanes must not starve the producers of L2 bandwidth
+        if (backoff < 512u) backoff <<= 1;
     }
 }
 
@@ -116,9 +120,10 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     const int capacity = n + n_segs;
     CUDA_CHECK(cudaMemsetAsync(queue_.get(), 0x80, (size_t) capacity * sizeof(int), stream));
     collapse_init_kernel<<<div_up(n_segs, 256), 256, 0, stream>>>(seg_offset_.get(), seg_root_.get(), n_segs, queue_.get(), wide_counters_.get());
-    const BinaryTreeView view{left_.get(), right_.get(), range_.get(), node_lo_.get(), node_hi_.get(), prim_lo_.get(), prim_hi_.get(), vals_};
+    const BinaryTreeView view{range_.get(), node_lo_.get(), node_hi_.get(), prim_lo_.get(), prim_hi_.get(), vals_};
     // every thread of the grid must be resident (the items poll on one another)
-    const int max_blocks = sm_count * collapse_blocks_per_sm_;
+    static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 4;   // tuning
+    const int max_blocks = sm_count * std::min(collapse_blocks_per_sm_, std::max(1, collapse_bps_env));
     const int want_blocks = (int) div_up((size_t) capacity, CT);
     const int blocks = want_blocks < max_blocks ? want_blocks : max_blocks;
     static const int leaf_max_env = getenv("RTB200_LEAF_MAX") ? atoi(getenv("RTB200_LEAF_MAX")) : 0;   // tuning experiments only

@@ -32,13 +32,16 @@ struct WideChildren {
     int n;
     int ref[8];
     int first[8], count[8];
+    int kl[8], kr[8];                   // Karras children of ref[k] (valid when ref[k] >= 0)
     Aabb box[8];
 };
 
+// The binary tree as the refit leaves it: node_lo[i].w / node_hi[i].w carry the bits of the Karras children of
+// node i (>= 0 inner, < 0 leaf ~position), so ONE pair of 16-byte loads gives a node's box and its children and
+// opening a node is a single memory round trip.
 struct BinaryTreeView {
-    const int *left, *right;            // Karras children (>= 0 inner, < 0 leaf ~position)
     const int2 *range;                  // per inner node: first/last Morton position
-    const float4 *node_lo, *node_hi;    // per inner node box
+    const float4 *node_lo, *node_hi;    // per inner node box (+ children in .w)
     const float4 *prim_lo, *prim_hi;    // per build primitive box (padded)
     const uint32_t *vals;               // Morton position -> build primitive
 };
@@ -56,18 +59,27 @@ RT_HD Aabb view_box(const float4 *lo, const float4 *hi, int i) {
 }
 RT_HD void wide_set_child(const BinaryTreeView &t, int child, int leaf_max, WideChildren &w, int k) {
     if (child >= 0) {
-        const int2 rg = t.range[child];
-        const int cnt = rg.y - rg.x + 1;
-        w.box[k] = view_box(t.node_lo, t.node_hi, child);
-        w.first[k] = rg.x;
+        const float4 a = t.node_lo[child], b = t.node_hi[child];
+        w.box[k].lo = mk3(a.x, a.y, a.z);
+        w.box[k].hi = mk3(b.x, b.y, b.z);
+        w.kl[k] = (int) f2u(a.w);
+        w.kr[k] = (int) f2u(b.w);
+        int first = 0, cnt = leaf_max + 1;
+        if (leaf_max > 1) {                                  // small subtrees become one leaf child
+            const int2 rg = t.range[child];
+            first = rg.x;
+            cnt = rg.y - rg.x + 1;
+        }
+        w.first[k] = first;
         w.count[k] = cnt;
-        w.ref[k] = cnt <= leaf_max ? -1 : child;      // small subtrees become one leaf child
+        w.ref[k] = cnt <= leaf_max ? -1 : child;
     } else {
         const int pos = ~child;
         w.box[k] = view_box(t.prim_lo, t.prim_hi, (int) t.vals[pos]);
         w.first[k] = pos;
         w.count[k] = 1;
         w.ref[k] = -1;
+        w.kl[k] = 0; w.kr[k] = 0;
     }
 }
 // Greedy top-down collapse: start from the two children of `root`, repeatedly open the inner child with the
@@ -78,15 +90,17 @@ RT_HD void wide_expand(const BinaryTreeView &t, int root, int leaf_max, WideChil
         wide_set_child(t, root, leaf_max, w, 0);
         return;
     }
-    const int2 rr = t.range[root];
-    if (rr.y - rr.x + 1 <= leaf_max) {               // whole BLAS fits one leaf child
+    wide_set_child(t, root, leaf_max, w, 0);
+    if (w.ref[0] < 0) {                               // whole BLAS fits one leaf child
         w.n = 1;
-        wide_set_child(t, root, leaf_max, w, 0);
         return;
     }
-    w.n = 2;
-    wide_set_child(t, t.left[root], leaf_max, w, 0);
-    wide_set_child(t, t.right[root], leaf_max, w, 1);
+    {
+        const int l = w.kl[0], r = w.kr[0];
+        w.n = 2;
+        wide_set_child(t, l, leaf_max, w, 0);
+        wide_set_child(t, r, leaf_max, w, 1);
+    }
     while (w.n < 8) {
         int best = -1;
         float best_area = -1.0f;
@@ -96,9 +110,9 @@ RT_HD void wide_expand(const BinaryTreeView &t, int root, int leaf_max, WideChil
             if (a > best_area) { best_area = a; best = k; }
         }
         if (best < 0) break;
-        const int node = w.ref[best];
-        wide_set_child(t, t.left[node], leaf_max, w, best);
-        wide_set_child(t, t.right[node], leaf_max, w, w.n);
+        const int l = w.kl[best], r = w.kr[best];
+        wide_set_child(t, l, leaf_max, w, best);
+        wide_set_child(t, r, leaf_max, w, w.n);
         w.n++;
     }
 }
@@ -106,27 +120,37 @@ RT_HD void wide_expand(const BinaryTreeView &t, int root, int leaf_max, WideChil
 // ---- octant-ordered slot assignment --------------------------------------------------------------------------
 // Slot s (bit 2 = +x, bit 1 = +y, bit 0 = +z) should hold the child lying furthest towards that corner of the
 // node, so that for a ray of octant `oct` visiting slots in descending (s ^ (7 - oct)) order is front-to-back.
-// Greedy assignment on cost(child, slot) = dot(child centre - node centre, corner direction of the slot).
+// cost(child, slot) = dot(child centre - node centre, corner direction of the slot).
 RT_HD void wide_assign_slots(const WideChildren &w, const Aabb &node, int *slot_of /* [8] child -> slot */) {
+    // Children in descending order of the best cost they can reach (|dx| + |dy| + |dz|, ties: lower index first);
+    // each takes the free slot with its highest cost (ties: lower slot).  O(8 * 8) — the assignment sits on the
+    // collapse's dependency chain (a node's children cannot start before it is done), so it has to be short.
     const f3 nc = mk3(0.5f * (node.lo.x + node.hi.x), 0.5f * (node.lo.y + node.hi.y), 0.5f * (node.lo.z + node.hi.z));
-    float cost[8][8];
-    for (int c = 0; c < w.n; c++) {
-        const f3 d = mk3(0.5f * (w.box[c].lo.x + w.box[c].hi.x) - nc.x, 0.5f * (w.box[c].lo.y + w.box[c].hi.y) - nc.y,
-                         0.5f * (w.box[c].lo.z + w.box[c].hi.z) - nc.z);
-        for (int s = 0; s < 8; s++)
-            cost[c][s] = ((s & 4) ? d.x : -d.x) + ((s & 2) ? d.y : -d.y) + ((s & 1) ? d.z : -d.z);
+    f3 d[8];
+    float prio[8];
+    for (int c = 0; c < 8; c++) {
+        slot_of[c] = -1;
+        if (c < w.n) {
+            d[c] = mk3(0.5f * (w.box[c].lo.x + w.box[c].hi.x) - nc.x, 0.5f * (w.box[c].lo.y + w.box[c].hi.y) - nc.y,
+                       0.5f * (w.box[c].lo.z + w.box[c].hi.z) - nc.z);
+            prio[c] = (fabsf(d[c].x) + fabsf(d[c].y)) + fabsf(d[c].z);
+        } else {
+            d[c] = mk3(0.0f, 0.0f, 0.0f);
+            prio[c] = -1.0f;
+        }
     }
     uint32_t child_free = (1u << w.n) - 1u, slot_free = 0xFFu;
-    for (int c = 0; c < 8; c++) slot_of[c] = -1;
     for (int round = 0; round < w.n; round++) {
-        int bc = -1, bs = -1;
+        int bc = -1;
+        float bp = -2.0f;
+        for (int c = 0; c < 8; c++)
+            if ((child_free & (1u << c)) && prio[c] > bp) { bp = prio[c]; bc = c; }
+        int bs = -1;
         float best = -RT_INF;
-        for (int c = 0; c < w.n; c++) {
-            if (!(child_free & (1u << c))) continue;
-            for (int s = 0; s < 8; s++) {
-                if (!(slot_free & (1u << s))) continue;
-                if (cost[c][s] > best) { best = cost[c][s]; bc = c; bs = s; }
-            }
+        for (int s = 0; s < 8; s++) {
+            if (!(slot_free & (1u << s))) continue;
+            const float cost = (((s & 4) ? d[bc].x : -d[bc].x) + ((s & 2) ? d[bc].y : -d[bc].y)) + ((s & 1) ? d[bc].z : -d[bc].z);
+            if (cost > best) { best = cost; bs = s; }
         }
         slot_of[bc] = bs;
         child_free &= ~(1u << bc);
@@ -142,20 +166,22 @@ RT_HD uint32_t wide_grid_exponent(float extent) {
     uint32_t e = (f2u(f) >> 23) & 0xFFu;
     if (f2u(f) & 0x7FFFFFu) e++;                            // round the step up to a power of two
     if (e < 1u) e = 1u;
-    if (e > 254u) e = 254u;
+    if (e > 253u) e = 253u;
     return e;
 }
 RT_HD float wide_grid_step(uint32_t e) { return u2f(e << 23); }
-RT_HD uint32_t wide_quant_lo(float v, float p, float step) {
-    float q = floorf((v - p) / step);
+// step is a power of two, so scaling by its reciprocal `inv` is exact (no division on the collapse's critical path)
+RT_HD float wide_grid_inv_step(uint32_t e) { return u2f((254u - e) << 23); }
+RT_HD uint32_t wide_quant_lo(float v, float p, float step, float inv) {
+    float q = floorf((v - p) * inv);
     if (q < 0.0f) q = 0.0f;
     if (q > 255.0f) q = 255.0f;
     uint32_t qi = (uint32_t) q;
     while (qi > 0u && p + (float) qi * step > v) qi--;      // decoded plane never inside the box
     return qi;
 }
-RT_HD uint32_t wide_quant_hi(float v, float p, float step) {
-    float q = ceilf((v - p) / step);
+RT_HD uint32_t wide_quant_hi(float v, float p, float step, float inv) {
+    float q = ceilf((v - p) * inv);
     if (q < 0.0f) q = 0.0f;
     if (q > 255.0f) q = 255.0f;
     uint32_t qi = (uint32_t) q;
@@ -179,6 +205,7 @@ RT_HD void wide_encode(const WideChildren &w, uint32_t child_base, uint32_t prim
     const uint32_t ex = wide_grid_exponent(node.hi.x - node.lo.x), ey = wide_grid_exponent(node.hi.y - node.lo.y),
                    ez = wide_grid_exponent(node.hi.z - node.lo.z);
     const float sx = wide_grid_step(ex), sy = wide_grid_step(ey), sz = wide_grid_step(ez);
+    const float ix = wide_grid_inv_step(ex), iy = wide_grid_inv_step(ey), iz = wide_grid_inv_step(ez);
     uint32_t imask = 0, meta[2] = {0, 0}, q[6][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};
     uint32_t prim_off = 0;
     for (int s = 0; s < 8; s++) {
@@ -196,12 +223,12 @@ RT_HD void wide_encode(const WideChildren &w, uint32_t child_base, uint32_t prim
         const int h = s >> 2, sh = 8 * (s & 3);
         meta[h] |= m << sh;
         const Aabb &b = w.box[c];
-        q[0][h] |= wide_quant_lo(b.lo.x, node.lo.x, sx) << sh;
-        q[1][h] |= wide_quant_lo(b.lo.y, node.lo.y, sy) << sh;
-        q[2][h] |= wide_quant_lo(b.lo.z, node.lo.z, sz) << sh;
-        q[3][h] |= wide_quant_hi(b.hi.x, node.lo.x, sx) << sh;
-        q[4][h] |= wide_quant_hi(b.hi.y, node.lo.y, sy) << sh;
-        q[5][h] |= wide_quant_hi(b.hi.z, node.lo.z, sz) << sh;
+        q[0][h] |= wide_quant_lo(b.lo.x, node.lo.x, sx, ix) << sh;
+        q[1][h] |= wide_quant_lo(b.lo.y, node.lo.y, sy, iy) << sh;
+        q[2][h] |= wide_quant_lo(b.lo.z, node.lo.z, sz, iz) << sh;
+        q[3][h] |= wide_quant_hi(b.hi.x, node.lo.x, sx, ix) << sh;
+        q[4][h] |= wide_quant_hi(b.hi.y, node.lo.y, sy, iy) << sh;
+        q[5][h] |= wide_quant_hi(b.hi.z, node.lo.z, sz, iz) << sh;
     }
     out.n0 = make_float4(node.lo.x, node.lo.y, node.lo.z, u2f(ex | (ey << 8) | (ez << 16) | (imask << 24)));
     out.n1 = make_uint4(child_base, prim_base, meta[0], meta[1]);

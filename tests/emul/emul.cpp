@@ -116,14 +116,14 @@ void collapse_wide(Lbvh &b, const std::vector<uint32_t> &seg_offset, int leaf_ma
     const int n = b.n, n_segs = (int) seg_offset.size() - 1;
     std::vector<float4> nlo(b.node_box.size()), nhi(b.node_box.size()), plo(n), phi(n);
     for (size_t i = 0; i < b.node_box.size(); i++) {
-        nlo[i] = make_float4(b.node_box[i].lo.x, b.node_box[i].lo.y, b.node_box[i].lo.z, 0.f);
-        nhi[i] = make_float4(b.node_box[i].hi.x, b.node_box[i].hi.y, b.node_box[i].hi.z, 0.f);
+        nlo[i] = make_float4(b.node_box[i].lo.x, b.node_box[i].lo.y, b.node_box[i].lo.z, u2f((uint32_t) b.left[i]));
+        nhi[i] = make_float4(b.node_box[i].hi.x, b.node_box[i].hi.y, b.node_box[i].hi.z, u2f((uint32_t) b.right[i]));
     }
     for (int i = 0; i < n; i++) {
         plo[i] = make_float4(b.prim_box[i].lo.x, b.prim_box[i].lo.y, b.prim_box[i].lo.z, 0.f);
         phi[i] = make_float4(b.prim_box[i].hi.x, b.prim_box[i].hi.y, b.prim_box[i].hi.z, 0.f);
     }
-    const BinaryTreeView view{b.left.data(), b.right.data(), b.range.data(), nlo.data(), nhi.data(), plo.data(), phi.data(), b.vals.data()};
+    const BinaryTreeView view{b.range.data(), nlo.data(), nhi.data(), plo.data(), phi.data(), b.vals.data()};
     std::vector<int> queue;
     for (int s = 0; s < n_segs; s++)
         queue.push_back(seg_offset[s + 1] - seg_offset[s] == 1u ? ~(int) seg_offset[s] : b.seg_root[s]);

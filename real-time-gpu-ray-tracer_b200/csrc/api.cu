@@ -8,6 +8,7 @@
 #include "vtk_reader.h"
 #include "wave.h"
 
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <map>
@@ -53,8 +54,14 @@ struct rt_ctx {
     DeviceBuffer<unsigned long long> d_counters;   // [0] rays, [1] overflow flag (low word)
     PinnedBuffer<unsigned long long> h_counters;
 
-    // VTK series
+    // VTK series: the user's own triangles / instances are kept so that every frame can be recomposed as
+    // [VTK triangles | user triangles], [user instances | VTK instances] (reference src/Global/Renderer.cu:17,106-116)
     std::unique_ptr<VtkSeries> vtk;
+    std::vector<rt_triangle> user_tris;
+    std::vector<rt_instance_desc> user_inst;
+    bool composing = false;
+    size_t n_user_inst = 0;
+    float vtk_parse_ms = 0.0f;
 };
 
 namespace {
@@ -163,6 +170,7 @@ int rt_commit_geometry(rt_ctx *ctx, const rt_sphere *spheres, size_t sphere_coun
     RT_API_BEGIN(ctx)
     const std::string e = ctx->hs.commit_geometry(spheres, sphere_count, parallelograms, parallelogram_count, triangles, triangle_count);
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    if (!ctx->composing) ctx->user_tris.assign(triangles, triangles + triangle_count);
     ctx->built = false;
     ctx->d_spheres.upload(ctx->hs.sphere_rec.data(), ctx->hs.sphere_rec.size(), ctx->stream);
     ctx->d_quads.upload(ctx->hs.quad_rec.data(), ctx->hs.quad_rec.size(), ctx->stream);
@@ -199,9 +207,13 @@ int rt_configure_instances(rt_ctx *ctx, const rt_instance_desc *instances, size_
     if (!ctx->geometry_committed) return fail(ctx, RT_ERR_STATE, "rt_configure_instances: commit geometry first");
     const std::string e = ctx->hs.configure_instances(instances, instance_count, initial_xforms);
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
-    ctx->update_cb = update;
-    ctx->update_user = user;
-    if (update) update(ctx->hs.xforms.data(), instance_count, 0, user);   // reference src/Global/Renderer.cu:111
+    if (!ctx->composing) {
+        ctx->user_inst.assign(instances, instances + instance_count);
+        ctx->n_user_inst = instance_count;
+        ctx->update_cb = update;
+        ctx->update_user = user;
+        if (update) update(ctx->hs.xforms.data(), instance_count, 0, user);   // reference src/Global/Renderer.cu:111
+    }
     ctx->instances_configured = true;
     ctx->built = false;
     RT_API_END(ctx)
@@ -209,7 +221,7 @@ int rt_configure_instances(rt_ctx *ctx, const rt_instance_desc *instances, size_
 
 int rt_set_instance_xforms(rt_ctx *ctx, const rt_instance_xform *xforms, size_t instance_count) {
     RT_API_BEGIN(ctx)
-    if (!xforms || instance_count != ctx->hs.xforms.size()) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_instance_xforms: count mismatch");
+    if (!xforms || (instance_count != ctx->hs.xforms.size() && instance_count != ctx->n_user_inst)) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_instance_xforms: count mismatch");
     std::copy(xforms, xforms + instance_count, ctx->hs.xforms.begin());
     RT_API_END(ctx)
 }
@@ -283,7 +295,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     RT_API_BEGIN(ctx)
     if (!ctx->built || !ctx->camera_set || !ctx->materials_committed) return fail(ctx, RT_ERR_STATE, "rt_render_frame: scene not built / camera or materials missing");
     cudaStream_t s = ctx->stream;
-    if (ctx->update_cb) ctx->update_cb(ctx->hs.xforms.data(), ctx->hs.xforms.size(), (size_t) frame_index, ctx->update_user);
+    if (ctx->update_cb) ctx->update_cb(ctx->hs.xforms.data(), ctx->n_user_inst, (size_t) frame_index, ctx->update_user);
     CUDA_CHECK(cudaEventRecord(ctx->ev[0], s));
     update_instances_and_tlas(ctx);
     CUDA_CHECK(cudaEventRecord(ctx->ev[1], s));
@@ -476,8 +488,35 @@ int rt_load_vtk_series(rt_ctx *ctx, const char *series_path, size_t *frame_count
 
 int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
     RT_API_BEGIN(ctx)
-    (void) frame;
-    return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: not implemented yet");
+    if (!ctx->vtk) return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: load a series first");
+    if (!ctx->geometry_committed || !ctx->instances_configured) return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: commit geometry and instances first");
+    if (frame >= ctx->vtk->files.size()) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_vtk_frame: frame out of range");
+    const auto t0 = std::chrono::steady_clock::now();
+    VtkFrame vf;
+    std::string err;
+    if (!vf.read(ctx->vtk->dir + ctx->vtk->files[frame].first, err)) return fail(ctx, RT_ERR_IO, err);
+    std::vector<rt_triangle> tris;
+    std::vector<rt_instance_desc> inst;
+    std::vector<rt_instance_xform> xf;
+    vtk_convert(vf, tris, inst, xf);
+    ctx->vtk_parse_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    // compose: VTK triangles at the head of the triangle array, user TRIANGLE instances shifted by their count,
+    // VTK instances after the user's (reference src/Global/Renderer.cu:17,106-108,114-116)
+    const size_t n_vtk_tris = tris.size();
+    tris.insert(tris.end(), ctx->user_tris.begin(), ctx->user_tris.end());
+    std::vector<rt_instance_desc> all_inst(ctx->user_inst);
+    for (rt_instance_desc &d: all_inst) if (d.type == RT_TRIANGLE) d.first_prim += n_vtk_tris;
+    all_inst.insert(all_inst.end(), inst.begin(), inst.end());
+    std::vector<rt_instance_xform> all_xf(ctx->hs.xforms.begin(), ctx->hs.xforms.begin() + ctx->n_user_inst);
+    all_xf.insert(all_xf.end(), xf.begin(), xf.end());
+    const std::vector<rt_sphere> spheres(ctx->hs.spheres);
+    const std::vector<rt_parallelogram> quads(ctx->hs.quads);
+    ctx->composing = true;
+    int rc = rt_commit_geometry(ctx, spheres.data(), spheres.size(), quads.data(), quads.size(), tris.data(), tris.size());
+    if (rc == RT_OK) rc = rt_configure_instances(ctx, all_inst.data(), all_inst.size(), all_xf.data(), nullptr, nullptr);
+    if (rc == RT_OK) rc = rt_build_acceleration_structure(ctx);
+    ctx->composing = false;
+    if (rc != RT_OK) return rc;
     RT_API_END(ctx)
 }
 

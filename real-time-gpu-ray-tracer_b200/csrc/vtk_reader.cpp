@@ -1,6 +1,10 @@
 #include "vtk_reader.h"
 
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <sstream>
 
@@ -33,4 +37,152 @@ bool VtkSeries::load(const std::string &series_path, std::string &err) {
     dir = slash == std::string::npos ? std::string() : series_path.substr(0, slash + 1);
     if (files.empty()) { err = "series file lists no frames"; return false; }
     return true;
+}
+
+// ---- legacy VTK 2.0 BINARY POLYDATA (big-endian), layout in SURVEY.md Appendix B --------------------------------
+// Does the job of vtkPolyDataReader in VTKReader::readVTKFile (reference src/Global/VTKReader.cu:16-57): header check,
+// POINTS, TRIANGLE_STRIPS, and the presence of the cell arrays "id" and "vel" the reference insists on (:52-57).
+namespace {
+uint32_t be32(const unsigned char *p) { return ((uint32_t) p[0] << 24) | ((uint32_t) p[1] << 16) | ((uint32_t) p[2] << 8) | p[3]; }
+uint64_t be64(const unsigned char *p) { return ((uint64_t) be32(p) << 32) | be32(p + 4); }
+// next text line starting at pos (skipping blank lines); returns false at EOF
+bool next_line(const std::string &s, size_t &pos, std::string &line) {
+    while (pos < s.size()) {
+        const size_t e = s.find('\n', pos);
+        const size_t end = e == std::string::npos ? s.size() : e;
+        line = s.substr(pos, end - pos);
+        pos = end + 1;
+        while (!line.empty() && (line.back() == ' ' || line.back() == '\r')) line.pop_back();
+        if (!line.empty()) return true;
+    }
+    return false;
+}
+}
+
+bool VtkFrame::read(const std::string &path, std::string &err) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f.is_open()) { err = "cannot open vtk file " + path; return false; }
+    std::stringstream ss;
+    ss << f.rdbuf();
+    const std::string s = ss.str();
+    size_t pos = 0;
+    std::string line;
+    if (!next_line(s, pos, line) || line.find("# vtk DataFile Version") == std::string::npos) { err = "illegal vtk file header in " + path; return false; }
+    next_line(s, pos, line);                                       // title
+    if (!next_line(s, pos, line) || line.find("BINARY") == std::string::npos) { err = "only BINARY legacy vtk files are supported: " + path; return false; }
+    if (!next_line(s, pos, line) || line.find("POLYDATA") == std::string::npos) { err = "DATASET POLYDATA expected in " + path; return false; }
+    points.clear();
+    strips.clear();
+    bool have_points = false, have_strips = false;
+    while (next_line(s, pos, line)) {
+        std::istringstream ls(line);
+        std::string key;
+        ls >> key;
+        if (key == "POINTS") {
+            size_t n = 0;
+            std::string type;
+            ls >> n >> type;
+            const size_t w = type == "double" ? 8 : (type == "float" ? 4 : 0);
+            if (!w || pos + n * 3 * w > s.size()) { err = "bad POINTS section in " + path; return false; }
+            points.resize(n * 3);
+            const unsigned char *p = reinterpret_cast<const unsigned char *>(s.data()) + pos;
+            for (size_t i = 0; i < n * 3; i++) {
+                if (w == 8) { const uint64_t u = be64(p + 8 * i); double d; memcpy(&d, &u, 8); points[i] = d; }
+                else { const uint32_t u = be32(p + 4 * i); float d; memcpy(&d, &u, 4); points[i] = d; }
+            }
+            pos += n * 3 * w;
+            have_points = true;
+        } else if (key == "TRIANGLE_STRIPS") {
+            size_t cells = 0, size = 0;
+            ls >> cells >> size;
+            if (pos + size * 4 > s.size()) { err = "bad TRIANGLE_STRIPS section in " + path; return false; }
+            const unsigned char *p = reinterpret_cast<const unsigned char *>(s.data()) + pos;
+            size_t k = 0;
+            strips.resize(cells);
+            for (size_t c = 0; c < cells; c++) {
+                if (k >= size) { err = "truncated TRIANGLE_STRIPS in " + path; return false; }
+                const size_t len = be32(p + 4 * k++);
+                if (k + len > size) { err = "truncated TRIANGLE_STRIPS cell in " + path; return false; }
+                strips[c].resize(len);
+                for (size_t j = 0; j < len; j++) {
+                    const uint32_t id = be32(p + 4 * k++);
+                    if ((size_t) id * 3 + 2 >= points.size()) { err = "point id out of range in " + path; return false; }
+                    strips[c][j] = (int) id;
+                }
+            }
+            pos += size * 4;
+            have_strips = true;
+            break;                                                  // the rest is cell data
+        } else if (key == "VERTICES" || key == "LINES" || key == "POLYGONS") {
+            err = "found illegal cell type " + key + " (only vtkTriangleStrip cells are accepted, VTKReader.cu:81-85)";
+            return false;
+        }
+    }
+    if (!have_points || points.empty() || !have_strips) { err = "no points / strips in " + path; return false; }
+    // reference: cell arrays "id" and "vel" must exist (values are not used downstream)
+    if (s.find("SCALARS id ", pos) == std::string::npos || s.find("VECTORS vel ", pos) == std::string::npos) { err = "failed to read cell data (id / vel) in " + path; return false; }
+    return true;
+}
+
+void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vector<rt_instance_desc> &inst,
+                 std::vector<rt_instance_xform> &xforms) {
+    const std::vector<double> &P = frame.points;
+    const size_t n_points = P.size() / 3;
+    std::vector<double> nrm(n_points * 3, 0.0);
+    // ---- point normals (restated, parity unpinned) ----
+    for (const std::vector<int> &strip: frame.strips) {
+        if (strip.size() < 3) continue;
+        std::vector<int> uniq(strip);
+        std::sort(uniq.begin(), uniq.end());
+        uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+        double c[3] = {0, 0, 0};
+        for (int id: uniq) for (int a = 0; a < 3; a++) c[a] += P[3 * id + a];
+        for (int a = 0; a < 3; a++) c[a] /= (double) uniq.size();
+        for (size_t j = 0; j + 2 < strip.size(); j++) {
+            const int i0 = strip[j], i1 = strip[j + 1], i2 = strip[j + 2];
+            if (i0 == i1 || i1 == i2 || i0 == i2) continue;
+            const double *a = &P[3 * i0], *b = &P[3 * i1], *d = &P[3 * i2];
+            const double e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {d[0] - a[0], d[1] - a[1], d[2] - a[2]};
+            double n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+            const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+            if (!(len > 0.0)) continue;
+            double out = 0.0;
+            for (int k = 0; k < 3; k++) { n[k] /= len; out += n[k] * ((a[k] + b[k] + d[k]) / 3.0 - c[k]); }
+            const double sgn = out < 0.0 ? -1.0 : 1.0;
+            for (int id: {i0, i1, i2}) for (int k = 0; k < 3; k++) nrm[3 * id + k] += sgn * n[k];
+        }
+    }
+    for (size_t i = 0; i < n_points; i++) {
+        double *n = &nrm[3 * i];
+        const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        if (len > 0.0) { n[0] /= len; n[1] /= len; n[2] /= len; }
+    }
+    // ---- triangles + instances ----
+    tris.clear();
+    inst.clear();
+    xforms.clear();
+    auto vert = [&](int id) { return rt_vec3{(float) P[3 * id], (float) P[3 * id + 1], (float) P[3 * id + 2]}; };
+    auto norm = [&](int id) { return rt_vec3{(float) nrm[3 * id], (float) nrm[3 * id + 1], (float) nrm[3 * id + 2]}; };
+    for (const std::vector<int> &strip: frame.strips) {
+        if (strip.size() < 3) continue;
+        rt_instance_desc d{};
+        d.type = RT_TRIANGLE;
+        d.has_bounds = 1;
+        d.first_prim = tris.size();
+        d.prim_count = strip.size() - 2;
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300}, c[3] = {0, 0, 0};
+        for (int id: strip)
+            for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], P[3 * id + a]); hi[a] = std::max(hi[a], P[3 * id + a]); c[a] += P[3 * id + a]; }
+        for (int a = 0; a < 3; a++) { d.bounds_min[a] = (float) lo[a]; d.bounds_max[a] = (float) hi[a]; d.centroid[a] = (float) (c[a] / (double) strip.size()); }
+        for (size_t j = 0; j + 2 < strip.size(); j++) {
+            const int i0 = strip[j], i1 = (j & 1) ? strip[j + 2] : strip[j + 1], i2 = (j & 1) ? strip[j + 1] : strip[j + 2];
+            rt_triangle t{};
+            t.v[0] = vert(i0); t.v[1] = vert(i1); t.v[2] = vert(i2);
+            t.n[0] = norm(i0); t.n[1] = norm(i1); t.n[2] = norm(i2);
+            t.material_type = RT_METAL; t.material_index = 0; t.has_normals = 1;
+            tris.push_back(t);
+        }
+        inst.push_back(d);
+        xforms.push_back(rt_instance_xform{{0.0f, 4.0f, 0.0f}, {90.0f, 0.0f, 0.0f}, {3.0f, 3.0f, 3.0f}});
+    }
 }

@@ -13,3 +13,22 @@ struct VtkSeries {
     std::vector<std::pair<std::string, float>> files;  // (name relative to dir, time)
     bool load(const std::string &series_path, std::string &err);
 };
+
+// One legacy-binary POLYDATA frame: points (as stored, float64) and the triangle-strip cells.
+struct VtkFrame {
+    std::vector<double> points;                 // 3 per point
+    std::vector<std::vector<int>> strips;       // point ids of each TRIANGLE_STRIPS cell (= one particle)
+    bool read(const std::string &path, std::string &err);
+};
+
+#include "../../include/rtb200.h"
+
+// VTKReader::convertToRendererData (reference src/Global/VTKReader.cu:167-220): every strip of n points becomes n - 2
+// triangles (odd ones with vertices 2 and 3 swapped, :184-195), all METAL #0 (:198-201), one instance per particle
+// with the cell's bounds and the mean of its strip points (repeats included, float64 sums; :97-128), and the fixed
+// transform shift (0,4,0), rotate (90,0,0), scale 3 (:210-214).  Vertex normals restate vtkPolyDataNormals (point
+// normals, no splitting, consistent + outward orientation; :60-70) — PARITY UNPINNED, VTK itself cannot run here:
+// unit-length sum of the unit normals of the incident non-degenerate triangles, each oriented away from the
+// particle's mean point.
+void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vector<rt_instance_desc> &inst,
+                 std::vector<rt_instance_xform> &xforms);

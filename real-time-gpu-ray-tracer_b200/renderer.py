@@ -133,6 +133,18 @@ class Renderer:
         self._check(self.lib.rt_read_wide_bvh(self.ctx, which, C.byref(nn), C.byref(npr), abi.ptr(nodes), abi.ptr(prims)))
         return nodes, prims
 
+    # -- Renderer::configureVTKFiles (src/Global/Renderer.cu:394-443) + the per-frame particle rebuild -----------
+    def configureVTKFiles(self, series_path: str) -> int:
+        n = C.c_size_t()
+        self._check(self.lib.rt_load_vtk_series(self.ctx, series_path.encode(), C.byref(n)))
+        return n.value
+
+    def setVTKFrame(self, frame: int) -> abi.BuildStats:
+        self._check(self.lib.rt_set_vtk_frame(self.ctx, frame))
+        st = abi.BuildStats()
+        self._check(self.lib.rt_get_build_stats(self.ctx, C.byref(st)))
+        return st
+
     # -- Renderer::cleanup -----------------------------------------------------------------------
     def cleanup(self):
         if self.ctx:

@@ -256,3 +256,125 @@ def c5(n_instances: int = 10000, n_meshes: int = 16, width: int = 1920, height: 
     x["scale"] = rs.uniform(0.5, 2.0, (n_instances, 1)).astype(f32)
     sc.xforms = x
     return sc
+
+
+# ---- config 3: particle_mesh.vtk.series ---------------------------------------------------------------------------
+def read_vtk_frame(path: str):
+    """numpy restatement of the legacy-binary POLYDATA layout: returns (points float64 [N,3],
+    list of strips as int arrays).  Independent of csrc/vtk_reader.cpp so that each checks the other."""
+    raw = open(path, "rb").read()
+    pos = raw.index(b"POINTS")
+    eol = raw.index(b"\n", pos)
+    _, n, typ = raw[pos:eol].split()
+    n = int(n)
+    dt = ">f8" if typ == b"double" else ">f4"
+    pts = np.frombuffer(raw, dt, n * 3, eol + 1).astype(np.float64).reshape(n, 3)
+    pos = raw.index(b"TRIANGLE_STRIPS", eol + 1 + n * 3 * np.dtype(dt).itemsize)
+    eol = raw.index(b"\n", pos)
+    _, cells, size = raw[pos:eol].split()
+    conn = np.frombuffer(raw, ">i4", int(size), eol + 1).astype(np.int64)
+    strips, k = [], 0
+    for _ in range(int(cells)):
+        ln = int(conn[k])
+        strips.append(conn[k + 1:k + 1 + ln])
+        k += 1 + ln
+    return pts, strips
+
+
+def write_vtk_frame(path: str, pts: np.ndarray, strips) -> None:
+    """Writes a frame in the same on-disk layout (used to synthesise larger frames from a committed one)."""
+    p = len(strips)
+    size = sum(len(s) + 1 for s in strips)
+    with open(path, "wb") as f:
+        f.write(b"# vtk DataFile Version 2.0\nGenerated by rtb200 tests\nBINARY \nDATASET POLYDATA\n")
+        f.write(b"POINTS %d double\n" % len(pts))
+        f.write(np.ascontiguousarray(pts, ">f8").tobytes())
+        f.write(b"\nTRIANGLE_STRIPS %d %d\n" % (p, size))
+        for s in strips:
+            f.write(np.concatenate([[len(s)], s]).astype(">i4").tobytes())
+        f.write(b"\nCELL_DATA %d\nSCALARS id int 1\nLOOKUP_TABLE default\n" % p)
+        f.write(np.arange(p).astype(">i4").tobytes())
+        f.write(b"\nVECTORS vel double\n")
+        f.write(np.zeros((p, 3), ">f8").tobytes())
+        f.write(b"\n")
+
+
+def vtk_particles(pts: np.ndarray, strips):
+    """VTKReader::convertToRendererData (reference src/Global/VTKReader.cu:167-220) + the restated point normals
+    (vtkPolyDataNormals stand-in, parity unpinned): triangles, instance descs, transforms."""
+    nrm = np.zeros_like(pts)
+    for s in strips:
+        c = pts[np.unique(s)].mean(axis=0)
+        a, b, d = s[:-2], s[1:-1], s[2:]
+        ok = (a != b) & (b != d) & (a != d)
+        a, b, d = a[ok], b[ok], d[ok]
+        n = np.cross(pts[b] - pts[a], pts[d] - pts[a])
+        ln = np.sqrt((n * n).sum(1))
+        keep = ln > 0
+        a, b, d, n = a[keep], b[keep], d[keep], n[keep] / ln[keep, None]
+        out = (n * ((pts[a] + pts[b] + pts[d]) / 3.0 - c)).sum(1)
+        n = np.where(out[:, None] < 0, -n, n)
+        for ids in (a, b, d):
+            np.add.at(nrm, ids, n)
+    ln = np.sqrt((nrm * nrm).sum(1))
+    nrm = np.where(ln[:, None] > 0, nrm / np.maximum(ln, 1e-300)[:, None], nrm)
+    tris, ins = [], np.zeros(len(strips), abi.instance_desc_dt)
+    first = 0
+    for k, s in enumerate(strips):
+        m = len(s) - 2
+        j = np.arange(m)
+        i0, i1, i2 = s[j], np.where(j & 1, s[j + 2], s[j + 1]), np.where(j & 1, s[j + 1], s[j + 2])
+        t = np.zeros(m, abi.triangle_dt)
+        t["v"] = np.stack([pts[i0], pts[i1], pts[i2]], 1).astype(f32)
+        t["n"] = np.stack([nrm[i0], nrm[i1], nrm[i2]], 1).astype(f32)
+        t["material_type"], t["material_index"], t["has_normals"] = abi.METAL, 0, 1
+        tris.append(t)
+        ins[k]["type"], ins[k]["has_bounds"], ins[k]["first_prim"], ins[k]["prim_count"] = abi.TRIANGLE, 1, first, m
+        ins[k]["bounds_min"], ins[k]["bounds_max"] = pts[s].min(0).astype(f32), pts[s].max(0).astype(f32)
+        ins[k]["centroid"] = (pts[s].sum(0) / float(len(s))).astype(f32)
+        first += m
+    xf = identity_xforms(len(strips))
+    xf["shift"], xf["rotate_deg"], xf["scale"] = (0.0, 4.0, 0.0), (90.0, 0.0, 0.0), 3.0
+    return np.concatenate(tris), ins, xf
+
+
+def c3(vtk_path: str, frame: int = 0, width: int = 1920, height: int = 1080, spp: int = 1, depth: int = 10) -> "Scene":
+    """Config 3, one frame: the reference demo scene (Main.cu:48-106) + the particles of one .vtk file; VTK triangles
+    sit at the head of the triangle array and VTK instances after the user's (Renderer.cu:17,106-116)."""
+    sc = c1a(frame=frame, width=width, height=height, spp=spp, depth=depth)
+    tris, ins, xf = vtk_particles(*read_vtk_frame(vtk_path))
+    user = sc.instances.copy()
+    user["first_prim"] = np.where(user["type"] == abi.TRIANGLE, user["first_prim"] + len(tris), user["first_prim"])
+    sc.triangles = np.concatenate([tris, sc.triangles])
+    sc.instances = np.concatenate([user, ins])
+    sc.xforms = np.concatenate([sc.xforms, xf])
+    sc.name = f"C3-frame{frame}"
+    return sc
+
+
+def synth_vtk_series(src_vtk: str, out_dir: str, particle_counts, seed: int = 3) -> str:
+    """Synthesises a .vtk.series whose frame k holds particle_counts[k] rigid copies of the particles of `src_vtk`
+    (the reference's own data is 1.2 GB and cannot travel to the GPU box; frame 0 of it is committed as a fixture)."""
+    import os
+    pts, strips = read_vtk_frame(src_vtk)
+    rng = np.random.RandomState(seed)
+    os.makedirs(os.path.join(out_dir, "particle_mesh"), exist_ok=True)
+    names = []
+    for k, count in enumerate(particle_counts):
+        P, S, base = [], [], 0
+        for q in range(count):
+            s = strips[q % len(strips)]
+            ids, inv = np.unique(s, return_inverse=True)
+            shift = np.zeros(3) if q < len(strips) else rng.uniform(-1.5, 1.5, 3) * np.array([1.0, 1.0, 0.3])
+            P.append(pts[ids] + shift)
+            S.append(inv + base)
+            base += len(ids)
+        name = f"particle_mesh/particle_{k * 100:015d}.vtk"
+        write_vtk_frame(os.path.join(out_dir, name), np.concatenate(P), S)
+        names.append(name)
+    series = os.path.join(out_dir, "particle_mesh.vtk.series")
+    with open(series, "w") as f:
+        f.write('{\n  "file-series-version": "1.0",\n  "files": [\n')
+        f.write(",\n".join('    {"name": "%s", "time": %e}' % (n, 0.01 * k) for k, n in enumerate(names)))
+        f.write("\n  ]\n}\n")
+    return series

@@ -45,4 +45,8 @@ def parity_scenes(S):
     b.name = "C1a-frame37-defocus"
     return [a, b, S.c1b(width=128, height=72, spp=4, depth=4),
             S.c2(width=160, height=90, spp=4, depth=10, nx=100, nz=50),
-            S.c5(n_instances=200, n_meshes=4, width=96, height=54, spp=1, depth=4, subdiv=1)]
+            S.c5(n_instances=200, n_meshes=4, width=96, height=54, spp=1, depth=4, subdiv=1),
+            S.c3(os.path.join(ROOT, "tests", "golden", "particle_frame0.vtk"), frame=12, width=160, height=90, spp=1, depth=10)]
+
+
+N_PARITY = 6

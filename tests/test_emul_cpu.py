@@ -5,12 +5,12 @@ import numpy as np
 import pytest
 
 import emul_ctypes as ec
-from conftest import parity_scenes
+from conftest import N_PARITY, parity_scenes
 
 SEED = 0x5EED
 
 
-@pytest.mark.parametrize("idx", range(5))
+@pytest.mark.parametrize("idx", range(N_PARITY))
 def test_cores_match_oracle(pkg, port, idx):
     sc = parity_scenes(pkg.scenes)[idx]
     e = ec.Emul(sc)

@@ -137,7 +137,7 @@ def test_vtk_series_frames(pkg, port, tmp_path):
         for k, name in enumerate(["particle_mesh/particle_000000000000000.vtk", "particle_mesh/particle_000000000000100.vtk"]):
             st = r.setVTKFrame(k)
             sc = S.c3(os.path.join(str(tmp_path), name), frame=12, width=160, height=90, spp=1, depth=10)
-            assert st.primitive_count == len(sc.triangles) - 1 + 3           # particles + the user's four single-primitive BLASes (sphere #1 shared)
+            assert st.primitive_count == len(sc.triangles) - 1 + 4           # particle triangles + the four distinct single-primitive BLASes of the demo scene
             out = r.renderFrame(0, SEED)
             g = dict(out=out, radiance=r.readFramebuffer(pkg.abi.BUF_RADIANCE).reshape(90, 160, 3).copy(),
                      rgba8=r.readFramebuffer(pkg.abi.BUF_RGBA8).reshape(90, 160, 4).copy(),

@@ -174,6 +174,31 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------------------
+def reference_cuda_baseline(pkg, args, device):
+    """north_star's first baseline: the reference's OWN CUDA build (unmodified sources compiled for sm_100a by
+    oracle/Makefile `refcuda`, headless surface) on the same scene and camera, timed in the same run.  Bounded: the
+    workload at 16 spp (the reference needs ~18 s for one 64-spp frame); rays of that frame are counted by our
+    renderer on the identical configuration (the reference kernel does not count, its seeds come from clock64())."""
+    import oracle_ctypes as oc
+    if not os.path.exists(oc.REF_CUDA_PATH):
+        return {"unavailable": "oracle/_ref/libref_cuda.so not built (needs /root/reference at build time)"}
+    spp = min(16, args.spp)
+    sc = pkg.scenes.c2(width=args.width, height=args.height, spp=spp, depth=args.depth, nx=args.nx, nz=args.nz)
+    try:
+        ms, host, _ = oc.ref_cuda_bench(sc, 1, 1)
+    except Exception as e:   # noqa: BLE001
+        return {"unavailable": f"{type(e).__name__}: {e}"}
+    r = pkg.Renderer(device=device)
+    r.commitScene(sc)
+    out = r.renderFrame(0, SEED)
+    out = r.renderFrame(1, SEED)
+    r.cleanup()
+    return {"value": out.rays / (ms[0] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": ms[0], "spp": spp, "rays": int(out.rays),
+            "ours_same_config_ms": out.render_ms, "ours_same_config_mrays": out.rays / (out.render_ms * 1e-3) / 1e6,
+            "host_blas_build_ms_1core": host["blas_build_ms"],
+            "what": "reference render kernel (src/Global/Kernel.cu:105-147, 16x16 blocks) + reference host BVH on one B200, CUDA events"}
+
+
 def c3_rebuild(pkg, device):
     """Config 3's per-frame work on its largest frame shape: 500 particles x 1258 strip triangles = 629 000 triangles
     (synthesised from the committed frame-0 fixture in the reference's on-disk layout): parse + upload + rebuild of all
@@ -344,6 +369,9 @@ def run_ours(args):
             cpu = {"value": c_rays / c_s / 1e6, "unit": "Mrays/s", "cores": c_cores, "kind": kind,
                    "sample": f"{nrows} full scan-lines ({W} px x {sc.sample_count} spp, all bounces) spread evenly over the frame, one host thread per line, {c_s:.1f} s",
                    "host_bvh_build_ms_1core": info["blas_build_ms_1core"]}
+        refcuda = None
+        if world == 1 and not args.no_ref_cuda:
+            refcuda = reference_cuda_baseline(pkg, args, local)
         c3 = None
         if world == 1 and not args.no_c3:
             c3 = c3_rebuild(pkg, local)
@@ -361,6 +389,8 @@ def run_ours(args):
                 "gpu_launches": int(launches), "clocks": clocks}
         if c3:
             line["c3_particle_rebuild"] = c3
+        if refcuda:
+            line["reference_cuda"] = refcuda
         if roof:
             line["roofline"] = roof
         if cpu:
@@ -385,6 +415,7 @@ def main():
     ap.add_argument("--nz", type=int, default=500)
     ap.add_argument("--tile-rows", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-build baseline")
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 particle rebuild measurement")
     ap.add_argument("--megakernel", action="store_true", help="comparison mode: one thread per pixel (the reference's kernel structure)")
     ap.add_argument("--bvh2", action="store_true", help="comparison mode: traverse the binary LBVH instead of the wide BVH")

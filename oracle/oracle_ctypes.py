@@ -137,3 +137,28 @@ class OracleSceneHandle:
         out = np.zeros((len(self.sc.instances), 33), np.float32)
         self.o._instances(self.h, abi.ptr(out))
         return out
+
+
+# ---- the reference's own CUDA build (baseline timed beside ours on the GPU box; oracle/ref_cuda_driver.cu) -----------
+REF_CUDA_PATH = os.path.join(HERE, "_ref", "libref_cuda.so")
+
+
+def ref_cuda_bench(sc, warmup: int = 1, frames: int = 2):
+    """Runs the reference's `render` kernel (unmodified sources, nvcc sm_100a) on scene `sc`.
+    Returns (frame_ms list, host build ms dict, rgba8 image of the last frame)."""
+    if not os.path.exists(REF_CUDA_PATH):
+        raise FileNotFoundError(f"{REF_CUDA_PATH} not built (make -C oracle refcuda, needs /root/reference)")
+    lib = C.CDLL(REF_CUDA_PATH)
+    lib.refcuda_bench.argtypes = [C.POINTER(OracleScene), C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.refcuda_bench.restype = C.c_int
+    s = OracleScene(abi.ptr(sc.spheres), len(sc.spheres), abi.ptr(sc.parallelograms), len(sc.parallelograms),
+                    abi.ptr(sc.triangles), len(sc.triangles), abi.ptr(sc.roughs), len(sc.roughs),
+                    abi.ptr(sc.metals), len(sc.metals), abi.ptr(sc.instances), abi.ptr(sc.xforms), len(sc.instances),
+                    sc.window(), sc.camera_input(), 0)
+    ms = np.zeros(frames, np.float32)
+    host = np.zeros(3, np.float64)
+    img = np.zeros((sc.height, sc.width, 4), np.uint8)
+    rc = lib.refcuda_bench(C.byref(s), warmup, frames, abi.ptr(ms), abi.ptr(host), abi.ptr(img))
+    if rc != 0:
+        raise RuntimeError(f"refcuda_bench failed with {rc}")
+    return ms.tolist(), {"blas_build_ms": host[0], "xform_ms": host[1], "tlas_build_ms": host[2]}, img

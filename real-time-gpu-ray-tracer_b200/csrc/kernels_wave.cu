@@ -444,7 +444,10 @@ void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr
     constexpr int BATCH = 32;
     const uint32_t tiles_x = (cam.width + 7u) / 8u, tiles_y = (fr.local_rows + 3u) / 4u;
     const uint32_t n_pixels = tiles_x * tiles_y * 32u;
-    uint32_t n_slots = slots_override ? slots_override : (1u << 20);
+    // default: every pixel of the shard owns a slot for the whole frame (no re-assignment, so the queue order stays
+    // pixel-coherent and the frame takes max-path-length waves; measured +10 % over 2^20 slots at 1080p); capped at
+    // 16 M slots (1.9 GB of path state).  Binning the queue by direction octant was tried and lost 2.5 %.
+    uint32_t n_slots = slots_override ? slots_override : (1u << 24);
     if (n_slots > n_pixels) n_slots = n_pixels;
     n_slots = (n_slots + 31u) & ~31u;
     reserve(n_slots);

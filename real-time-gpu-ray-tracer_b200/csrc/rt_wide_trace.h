@@ -50,11 +50,23 @@ RT_HD uint32_t sign_extend_s8x4(uint32_t v) {
 // Byte j of w as the float 1 + q * 2^-15 (exact): the byte is dropped into mantissa bits 8..15 of 1.0f by ONE byte
 // permute, instead of an int->float conversion (the conversion pipe was the busiest unit of the first wide kernel,
 // profiles/r01c: 48 conversions per node).
-RT_HD float q_to_unit(uint32_t w, int j) {
+RT_HD float q_to_unit(uint32_t w, uint32_t one_bits, int j) {
 #if defined(__CUDA_ARCH__)
-    return __uint_as_float(__byte_perm(w, 0x3F800000u, 0x7604u | ((uint32_t) j << 4)));
+    return __uint_as_float(__byte_perm(w, one_bits, 0x7604u | ((uint32_t) j << 4)));
 #else
-    return u2f(0x3F800000u | (((w >> (8 * j)) & 0xFFu) << 8));
+    return u2f(one_bits | (((w >> (8 * j)) & 0xFFu) << 8));
+#endif
+}
+// 0x3F800000 held in a register the compiler cannot see through: PRMT takes only one immediate, and it must be the
+// selector — with the constant as the immediate every permute needed an extra move for its selector.
+#if defined(__CUDACC__)
+static __constant__ uint32_t c_one_bits = 0x3F800000u;
+#endif
+RT_HD uint32_t opaque_one_bits() {
+#if defined(__CUDA_ARCH__)
+    return c_one_bits;
+#else
+    return 0x3F800000u;
 #endif
 }
 
@@ -78,6 +90,7 @@ RT_HD uint32_t node8_intersect(const BvhNode8 &n, const WideRay &r, float tmin, 
     const float Ez = rt_fma(4.76837158e-7f, fabsf(oz), 2.38418579e-7f * fabsf(Az));
     const float oxl = Ox - Ex, oxh = Ox + Ex, oyl = Oy - Ey, oyh = Oy + Ey, ozl = Oz - Ez, ozh = Oz + Ez;
     const bool nx = r.ray.d.x < 0.0f, ny = r.ray.d.y < 0.0f, nz = r.ray.d.z < 0.0f;
+    const uint32_t one = opaque_one_bits();
     uint32_t hitmask = 0;
 #pragma unroll
     for (int h = 0; h < 2; h++) {
@@ -93,9 +106,9 @@ RT_HD uint32_t node8_intersect(const BvhNode8 &n, const WideRay &r, float tmin, 
         const uint32_t z0 = nz ? qhz : qlz, z1 = nz ? qlz : qhz;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const float tnx = rt_fma(q_to_unit(x0, j), Ax, oxl), tfx = rt_fma(q_to_unit(x1, j), Ax, oxh);
-            const float tny = rt_fma(q_to_unit(y0, j), Ay, oyl), tfy = rt_fma(q_to_unit(y1, j), Ay, oyh);
-            const float tnz = rt_fma(q_to_unit(z0, j), Az, ozl), tfz = rt_fma(q_to_unit(z1, j), Az, ozh);
+            const float tnx = rt_fma(q_to_unit(x0, one, j), Ax, oxl), tfx = rt_fma(q_to_unit(x1, one, j), Ax, oxh);
+            const float tny = rt_fma(q_to_unit(y0, one, j), Ay, oyl), tfy = rt_fma(q_to_unit(y1, one, j), Ay, oyh);
+            const float tnz = rt_fma(q_to_unit(z0, one, j), Az, ozl), tfz = rt_fma(q_to_unit(z1, one, j), Az, ozh);
             const float tn = rt_max(rt_max(tnx, tny), rt_max(tnz, tmin));
             const float tf = rt_min(rt_min(tfx, tfy), rt_min(tfz, tbest));
             if (tn <= tf) hitmask |= rt_byte(child_bits4, j) << rt_byte(bit_index4, j);

@@ -253,6 +253,8 @@ def run_ours(args):
         r.setTileShard(rank, world, tile_rows)
     W, H = sc.width, sc.height
     ptr, nbytes = r.devicePointer(abi.BUF_RGBA8)
+    if distributed:      # every rank's plane is allocated for the largest shard: gather equal-sized buffers
+        nbytes = pkg.sharding.padded_plane_bytes(H, W * 4, world, tile_rows)
     local_plane = torch.as_tensor(DevPtr(ptr, nbytes), device=f"cuda:{local}")
     gathered = [torch.empty_like(local_plane) for _ in range(world)] if (distributed and rank == 0) else None
     host_fb = torch.empty(W * H * 4, dtype=torch.uint8).pin_memory()
@@ -275,7 +277,7 @@ def run_ours(args):
         if read_back and rank == 0:
             if distributed:
                 # tiles of rank q are rows [(k*world+q)*tile_rows ...): de-interleave on the device, one D2H copy
-                full = torch.stack(gathered).view(world, -1, tile_rows, W * 4).permute(1, 0, 2, 3).reshape(-1, W * 4)[:H].contiguous()
+                full = pkg.sharding.assemble(gathered, H, W * 4, world, tile_rows)
                 host_fb.copy_(full.view(-1), non_blocking=True)
                 torch.cuda.synchronize()
             else:

@@ -3,7 +3,7 @@
 The directory name contains hyphens; import it with
 ``importlib.import_module("real-time-gpu-ray-tracer_b200")`` (``__graft_entry__.package()`` does so).
 """
-from . import abi, scenes  # noqa: F401
+from . import abi, scenes, sharding  # noqa: F401
 from .renderer import Renderer, RtError  # noqa: F401
 
-__all__ = ["abi", "scenes", "Renderer", "RtError"]
+__all__ = ["abi", "scenes", "sharding", "Renderer", "RtError"]

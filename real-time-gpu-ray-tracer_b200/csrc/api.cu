@@ -93,7 +93,10 @@ void compute_local_rows(rt_ctx *c) {
 
 void alloc_frame(rt_ctx *c) {
     compute_local_rows(c);
-    const size_t px = (size_t) c->hs.window.width * c->local_rows;
+    // planes are allocated for the LARGEST shard (rank 0's), so equal-sized gathers may read every rank's plane
+    const uint32_t tiles = (c->hs.window.height + c->tile_rows - 1) / c->tile_rows;
+    const uint32_t max_rows = c->shard_world == 1 ? c->hs.window.height : ((tiles + c->shard_world - 1) / c->shard_world) * c->tile_rows;
+    const size_t px = (size_t) c->hs.window.width * max_rows;
     c->d_rgba8.reserve(px * 4 + 4);
     c->d_radiance.reserve(px * 3 + 3);
     c->d_rng.reserve(px + 1);

@@ -1,0 +1,62 @@
+"""`not gpu` test of the N > 1 path: world_size-2 gloo ranks each render their image-tile shard with the CPU twin of
+the device cores (tests/emul), pack it like librtb200 does, gather to rank 0 and de-interleave with the same helper
+bench.py uses; the result must equal the single-rank frame bit for bit (pixel RNG is keyed by the global pixel)."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SEED = 0x5EED
+TILE_ROWS = 8
+
+
+def _rank_main(rank, world, port, height, out_path):
+    for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch
+    import torch.distributed as dist
+    import emul_ctypes as ec
+    pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    sh = pkg.sharding
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    sc = pkg.scenes.c1a(frame=3, width=64, height=height, spp=1, depth=4)
+    e = ec.Emul(sc)
+    W = sc.width
+    plane = np.zeros((sh.local_rows(height, 0, world, TILE_ROWS), W * 4), np.uint8)     # padded to the largest shard
+    full = e.render(SEED)["rgba8"].reshape(height, W * 4)           # the twin renders whole frames; a rank keeps its rows
+    for ly in range(sh.local_rows(height, rank, world, TILE_ROWS)):
+        gy = sh.global_row(ly, rank, world, TILE_ROWS)
+        if gy < height:
+            plane[ly] = full[gy]
+    assert sorted(sum((sh.owned_rows(height, r, world, TILE_ROWS) for r in range(world)), [])) == list(range(height))
+    t = torch.from_numpy(plane.reshape(-1))
+    gathered = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+    dist.gather(t, gathered, dst=0)
+    if rank == 0:
+        frame = sh.assemble(gathered, height, W * 4, world, TILE_ROWS).numpy()
+        np.save(out_path, np.stack([frame, full]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("height", [36, 44])          # 44 rows = 5.5 tiles: ragged last tile, unequal shards
+def test_tile_shards_gather_to_the_single_rank_frame(tmp_path, height):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "frame.npy")
+    port = 29500 + (os.getpid() + height) % 2000
+    mp.spawn(_rank_main, args=(2, port, height, out), nprocs=2, join=True)
+    frame, full = np.load(out)
+    assert np.array_equal(frame, full)
+
+
+def test_shard_arithmetic_matches_the_library_rule():
+    pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    sh = pkg.sharding
+    for H, world, tr in [(1080, 1, 8), (1080, 2, 8), (1080, 8, 8), (2160, 4, 16), (37, 8, 8)]:
+        rows = sum((sh.owned_rows(H, r, world, tr) for r in range(world)), [])
+        assert sorted(rows) == list(range(H))
+        assert sh.padded_plane_bytes(H, 4, world, tr) >= max(sh.local_rows(H, r, world, tr) for r in range(world)) * 4

@@ -238,6 +238,7 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py (our arm) needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries exactly one JSON line
     if distributed:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg, sc, cfg = workload(args)

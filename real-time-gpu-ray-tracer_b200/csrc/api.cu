@@ -151,6 +151,8 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     if (const char *e = getenv("RTB200_REFILL_MIN")) c->wave.refill_min = atoi(e);
     if (const char *e = getenv("RTB200_NODE_MIN")) c->wave.node_min = atoi(e);
     if (const char *e = getenv("RTB200_TRACE_BLOCKS_PER_SM")) c->wave.blocks_per_sm_override = atoi(e);
+    if (const char *e = getenv("RTB200_GROUPS")) c->wave.n_groups = atoi(e);
+    if (const char *e = getenv("RTB200_FINISH_DIVISOR")) c->wave.finish_divisor = atoi(e);
     *out = c;
     return RT_OK;
 }
@@ -353,7 +355,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     CUDA_CHECK(cudaStreamSynchronize(s));
     if (out) {
         memset(out, 0, sizeof(*out));
-        out->rays = mega ? ctx->h_counters.get()[0] : ws.rays;
+        out->rays = ws.rays + ctx->h_counters.get()[0];      // rays of the wave queues (host-counted) + rays counted on the device
         out->waves = ws.waves;
         out->stack_overflow = (uint32_t) ctx->h_counters.get()[1];
         out->node_fetches = ctx->h_counters.get()[2];

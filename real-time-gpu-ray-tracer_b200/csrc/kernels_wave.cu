@@ -11,6 +11,8 @@
 #include "rt_pixel.h"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 namespace {
 
@@ -117,10 +119,12 @@ __global__ void __launch_bounds__(SHADE_THREADS) wave_shade_kernel(const __grid_
                 pid = SLOT_IDLE; live = false; need_pixel = false;
                 wb.acc[slot] = make_float4(0.f, 0.f, 0.f, __uint_as_float(SLOT_IDLE));
             } else {
+                // group-local id -> tile-major id of the shard: the group's k-th tile is tile k * n_groups + group
+                const uint32_t gp = ((((cand >> 5) * wb.n_groups) + wb.group) << 5) | (cand & 31u);
                 uint32_t lx, ly;
-                pixel_coords(cand, wb.tiles_x, lx, ly);
+                pixel_coords(gp, wb.tiles_x, lx, ly);
                 if (lx < cam.width && ly < fr.local_rows && global_row(fr, ly) < cam.height) {
-                    pid = cand; need_pixel = false; need_primary = true;
+                    pid = gp; need_pixel = false; need_primary = true;
                     const RngState r0 = fr.rng[ly * cam.width + lx];
                     rng = r0;
                     acc = make_float4(0.f, 0.f, 0.f, __uint_as_float(pid));
@@ -432,6 +436,92 @@ __global__ void __launch_bounds__(TRACE_THREADS, RT_TRACE8_MIN_BLOCKS) wave_trac
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// FINISH.  The last third of a frame's waves carries well under 1 % of its rays (a few pixels with long paths), but
+// every wave costs a fixed launch + longest-ray latency.  Once a group's active slots fall below a threshold, this
+// kernel takes the slots of its last queue and runs each one to the end of its pixel in ONE thread — shade, trace,
+// shade, ... exactly the per-slot sequence the waves would have run (same RNG stream, same results).
+template<bool COUNT, bool WIDE>
+__global__ void __launch_bounds__(128) wave_finish_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
+                                                          const __grid_constant__ FrameD fr, const __grid_constant__ WaveBuffers wb, uint32_t wave) {
+    __shared__ uint2 stack_mem[WIDE ? RT_WIDE_STACK * 128 : 1];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= wb.counts[wave]) return;
+    const uint32_t slot = wb.queue[i];
+    float4 acc = wb.acc[slot];
+    uint32_t pid = __float_as_uint(acc.w);
+    const float4 h = wb.hit[slot];
+    const float4 o = wb.ray_o[slot], d = wb.ray_d[slot], t4 = wb.thr[slot];
+    const uint4 ra = wb.rng_a[slot];
+    const uint2 rb = wb.rng_b[slot];
+    RngState rng;
+    rng.d = ra.x; rng.v0 = ra.y; rng.v1 = ra.z; rng.v2 = ra.w; rng.v3 = rb.x; rng.v4 = rb.y;
+    RayD ray;
+    ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z);
+    f3 thr = mk3(t4.x, t4.y, t4.z);
+    uint32_t sample = __float_as_uint(t4.w) >> 16, depth = __float_as_uint(t4.w) & 0xFFFFu;
+    HitD hit;
+    hit.t = h.x; hit.tc = h.x; hit.u = h.y; hit.v = h.z; hit.leaf = (int) __float_as_uint(h.w); hit.inst = wb.hit_inst[slot];
+    uint32_t rays = 0, overflow = 0;
+    TravStats stats{0, 0, 0};
+    const uint32_t spp = cam.sqrtSamples * cam.sqrtSamples;
+    for (;;) {
+        uint32_t lx, ly;
+        pixel_coords(pid, wb.tiles_x, lx, ly);
+        if (fr.aov_t && sample == 0u && depth == 0u) {
+            const uint32_t lp = ly * cam.width + lx;
+            const bool has = hit.inst >= 0;
+            fr.aov_t[lp] = has ? hit.t : RT_INF;
+            fr.aov_inst[lp] = has ? hit.inst : -1;
+            fr.aov_prim[lp] = has ? (int) ((ref_type(hit.leaf) << 28) | (WIDE ? sc.leaf_prims8[ref_pos(hit.leaf)] : sc.leaf_prims[ref_pos(hit.leaf)])) : -1;
+        }
+        const bool alive = shade_scatter<WIDE>(sc, cam, ray, hit, thr, rng);
+        depth++;
+        if (!(alive && depth < cam.depth)) {
+            acc.x += thr.x; acc.y += thr.y; acc.z += thr.z;
+            sample++;
+            if (sample == spp) {
+                const uint32_t lp = ly * cam.width + lx;
+                const float w = cam.rcpSqrtSamples * cam.rcpSqrtSamples;
+                const float r = acc.x * w, g = acc.y * w, b = acc.z * w;
+                fr.radiance[3 * (size_t) lp + 0] = r;
+                fr.radiance[3 * (size_t) lp + 1] = g;
+                fr.radiance[3 * (size_t) lp + 2] = b;
+                const size_t op = fr.rgba8_is_full_frame ? (size_t) global_row(fr, ly) * cam.width + lx : (size_t) lp;
+                reinterpret_cast<uchar4 *>(fr.rgba8)[op] = make_uchar4(to_byte(r), to_byte(g), to_byte(b), 255);
+                // next unstarted pixel of the group, if any (only when there are fewer slots than pixels)
+                bool got = false;
+                for (;;) {
+                    const uint32_t cand = atomicAdd(wb.next_pixel, 1u);
+                    if (cand >= wb.n_pixels) break;
+                    const uint32_t gp = ((((cand >> 5) * wb.n_groups) + wb.group) << 5) | (cand & 31u);
+                    pixel_coords(gp, wb.tiles_x, lx, ly);
+                    if (lx < cam.width && ly < fr.local_rows && global_row(fr, ly) < cam.height) { pid = gp; got = true; break; }
+                }
+                if (!got) break;
+                rng = fr.rng[ly * cam.width + lx];
+                acc = make_float4(0.f, 0.f, 0.f, __uint_as_float(pid));
+                sample = 0;
+            }
+            ray = primary_ray(cam, lx, global_row(fr, ly), sample / cam.sqrtSamples, sample % cam.sqrtSamples, rng);
+            thr = mk3(1.f, 1.f, 1.f);
+            depth = 0;
+        }
+        if (WIDE) trace_closest8<COUNT>(sc, ray, RT_TMIN, hit, overflow, stats, stack_mem + threadIdx.x, 128);
+        else trace_closest<COUNT>(sc, ray, RT_TMIN, hit, overflow, stats);
+        rays++;
+    }
+    wb.acc[slot] = make_float4(0.f, 0.f, 0.f, __uint_as_float(SLOT_IDLE));
+    atomicAdd(fr.ray_counter, (unsigned long long) rays);
+    if (overflow) atomicOr(fr.overflow_flag, 1u);
+    if (COUNT) {
+        atomicAdd(fr.ray_counter + 2, (unsigned long long) stats.nodes);
+        atomicAdd(fr.ray_counter + 3, (unsigned long long) stats.prims);
+        atomicAdd(fr.ray_counter + 4, (unsigned long long) stats.insts);
+    }
+}
+
 } // namespace
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -440,26 +530,55 @@ void WaveRenderer::reserve(uint32_t n_slots) {
     hit_inst_.reserve(n_slots); rng_a_.reserve(n_slots); rng_b_.reserve(n_slots); queue_.reserve(n_slots);
 }
 
+WaveRenderer::~WaveRenderer() {
+    for (int g = 0; g < MAX_GROUPS; g++) {
+        if (g_event_[g]) cudaEventDestroy(g_event_[g]);
+        if (g_stream_[g]) cudaStreamDestroy(g_stream_[g]);
+    }
+    if (fork_event_) cudaEventDestroy(fork_event_);
+}
+
+// The slots are split into n_groups groups (8x4-pixel tiles dealt round-robin) whose wave sequences are independent
+// (a wave only orders the rays of ONE slot) and run concurrently, each on its own stream with 1/n_groups of the
+// resident trace warps: while one group's trace kernel drains its last long rays, the other groups keep the SMs
+// busy, and the fixed per-wave latency (launches, queue hand-over, the longest ray) overlaps with useful work —
+// which is what limits a frame once it is sharded over several GPUs and the waves get small.
 void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count, WaveStats &stats) {
     constexpr int BATCH = 32;
+    constexpr int CW = 2 * BATCH + 4;                      // counter words per group
     const uint32_t tiles_x = (cam.width + 7u) / 8u, tiles_y = (fr.local_rows + 3u) / 4u;
-    const uint32_t n_pixels = tiles_x * tiles_y * 32u;
-    // default: every pixel of the shard owns a slot for the whole frame (no re-assignment, so the queue order stays
-    // pixel-coherent and the frame takes max-path-length waves; measured +10 % over 2^20 slots at 1080p); capped at
-    // 16 M slots (1.9 GB of path state).  Binning the queue by direction octant was tried and lost 2.5 %.
-    uint32_t n_slots = slots_override ? slots_override : (1u << 24);
-    if (n_slots > n_pixels) n_slots = n_pixels;
-    n_slots = (n_slots + 31u) & ~31u;
-    reserve(n_slots);
-    counters_.reserve(2 * BATCH + 4);
-    h_counts_.reserve(BATCH);
-
-    WaveBuffers wb{};
-    wb.ray_o = ray_o_.get(); wb.ray_d = ray_d_.get(); wb.hit = hit_.get(); wb.hit_inst = hit_inst_.get();
-    wb.thr = thr_.get(); wb.acc = acc_.get(); wb.rng_a = rng_a_.get(); wb.rng_b = rng_b_.get();
-    wb.queue = queue_.get();
-    wb.counts = counters_.get(); wb.cursors = counters_.get() + BATCH; wb.next_pixel = counters_.get() + 2 * BATCH;
-    wb.n_slots = n_slots; wb.n_pixels = n_pixels; wb.tiles_x = tiles_x;
+    const uint32_t n_tiles = tiles_x * tiles_y;
+    int G = std::max(1, std::min(n_groups, (int) MAX_GROUPS));
+    if (n_tiles < 64u * (uint32_t) G) G = 1;              // tiny frames: one group
+    // every pixel owns a slot for the whole frame (no re-assignment: the queue order stays pixel-coherent and the frame
+    // takes max-path-length waves; +10 % over 2^20 slots at 1080p).  slots_override caps the slots of the whole frame.
+    // (Binning the queue by direction octant was tried and lost 2.5 %.)
+    std::vector<WaveBuffers> wbs(G);
+    std::vector<uint32_t> slot_base(G + 1, 0u);
+    for (int g = 0; g < G; g++) {
+        const uint32_t gt = (n_tiles - (uint32_t) g + (uint32_t) G - 1u) / (uint32_t) G;
+        uint32_t ns = gt * 32u;
+        if (slots_override) ns = std::min(ns, std::max(32u, (slots_override / (uint32_t) G + 31u) & ~31u));
+        wbs[g].n_pixels = gt * 32u;
+        wbs[g].n_slots = ns;
+        slot_base[g + 1] = slot_base[g] + ns;
+    }
+    reserve(slot_base[G]);
+    counters_.reserve((size_t) G * CW);
+    h_counts_.reserve((size_t) G * BATCH);
+    if (!fork_event_) CUDA_CHECK(cudaEventCreateWithFlags(&fork_event_, cudaEventDisableTiming));
+    for (int g = 0; g < G; g++) {
+        if (!g_stream_[g]) CUDA_CHECK(cudaStreamCreateWithFlags(&g_stream_[g], cudaStreamNonBlocking));
+        if (!g_event_[g]) CUDA_CHECK(cudaEventCreateWithFlags(&g_event_[g], cudaEventDisableTiming));
+        WaveBuffers &wb = wbs[g];
+        const uint32_t b = slot_base[g];
+        wb.ray_o = ray_o_.get() + b; wb.ray_d = ray_d_.get() + b; wb.hit = hit_.get() + b; wb.hit_inst = hit_inst_.get() + b;
+        wb.thr = thr_.get() + b; wb.acc = acc_.get() + b; wb.rng_a = rng_a_.get() + b; wb.rng_b = rng_b_.get() + b;
+        wb.queue = queue_.get() + b;
+        uint32_t *c = counters_.get() + (size_t) g * CW;
+        wb.counts = c; wb.cursors = c + BATCH; wb.next_pixel = c + 2 * BATCH;
+        wb.tiles_x = tiles_x; wb.group = (uint32_t) g; wb.n_groups = (uint32_t) G;
+    }
 
     if (trace_blocks_per_sm_[0] == 0) {
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&trace_blocks_per_sm_[0], wave_trace2_kernel<false>, TRACE_THREADS, 0));
@@ -469,43 +588,88 @@ void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr
     }
     const bool count = fr.count_traversal != 0;
     const bool wide = mode == 1;
-    int trace_blocks = sm_count * std::max(1, trace_blocks_per_sm_[(wide ? 2 : 0) + (count ? 1 : 0)]);
-    if (blocks_per_sm_override > 0) trace_blocks = sm_count * std::min(blocks_per_sm_override, trace_blocks / sm_count);
-    const unsigned shade_blocks = div_up(n_slots, SHADE_THREADS);
+    int bps = std::max(1, trace_blocks_per_sm_[(wide ? 2 : 0) + (count ? 1 : 0)]);
+    if (blocks_per_sm_override > 0) bps = std::min(blocks_per_sm_override, bps);
+    // the resident trace warps are shared out among the groups (at least one block per SM each)
+    const int trace_blocks = sm_count * std::max(1, (bps + G - 1) / G);
 
-    CUDA_CHECK(cudaMemsetAsync(wb.next_pixel, 0, sizeof(uint32_t), stream));
     stats = WaveStats{};
-    bool first = true;
-    for (;;) {
-        CUDA_CHECK(cudaMemsetAsync(counters_.get(), 0, 2 * BATCH * sizeof(uint32_t), stream));
+    CUDA_CHECK(cudaMemsetAsync(counters_.get(), 0, (size_t) G * CW * sizeof(uint32_t), stream));
+    CUDA_CHECK(cudaEventRecord(fork_event_, stream));
+    std::vector<char> first(G, 1), pending(G, 0), done(G, 0);
+    std::vector<uint32_t> waves(G, 0u);
+    auto enqueue_batch = [&](int g) {
+        cudaStream_t s = g_stream_[g];
+        const WaveBuffers &wb = wbs[g];
+        const unsigned shade_blocks = div_up(wb.n_slots, SHADE_THREADS);
+        if (first[g]) CUDA_CHECK(cudaStreamWaitEvent(s, fork_event_, 0));
+        else CUDA_CHECK(cudaMemsetAsync(wb.counts, 0, 2 * BATCH * sizeof(uint32_t), s));
         for (int w = 0; w < BATCH; w++) {
-            if (first) {
-                if (wide) wave_shade_kernel<true, true><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
-                else wave_shade_kernel<true, false><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
-                first = false;
+            if (first[g]) {
+                if (wide) wave_shade_kernel<true, true><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
+                else wave_shade_kernel<true, false><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
+                first[g] = 0;
             } else {
-                if (wide) wave_shade_kernel<false, true><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
-                else wave_shade_kernel<false, false><<<shade_blocks, SHADE_THREADS, 0, stream>>>(sc, cam, fr, wb, (uint32_t) w);
+                if (wide) wave_shade_kernel<false, true><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
+                else wave_shade_kernel<false, false><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
             }
             if (wide) {
-                if (count) wave_trace8_kernel<true><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
-                else wave_trace8_kernel<false><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+                if (count) wave_trace8_kernel<true><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+                else wave_trace8_kernel<false><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
             } else {
-                if (count) wave_trace2_kernel<true><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
-                else wave_trace2_kernel<false><<<trace_blocks, TRACE_THREADS, 0, stream>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+                if (count) wave_trace2_kernel<true><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
+                else wave_trace2_kernel<false><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
             }
             stats.launches += 2;
         }
         CUDA_CHECK(cudaGetLastError());
-        CUDA_CHECK(cudaMemcpyAsync(h_counts_.get(), wb.counts, BATCH * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-        CUDA_CHECK(cudaStreamSynchronize(stream));
-        bool done = false;
-        for (int w = 0; w < BATCH; w++) {
-            const uint32_t c = h_counts_.get()[w];
-            stats.rays += c;
-            if (c == 0u) { done = true; break; }
-            stats.waves++;
+        CUDA_CHECK(cudaMemcpyAsync(h_counts_.get() + (size_t) g * BATCH, wb.counts, BATCH * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaEventRecord(g_event_[g], s));
+        pending[g] = 1;
+    };
+    static const bool dump_waves = getenv("RTB200_DUMP_WAVES") != nullptr;     // debugging aid: rays per wave of group 0
+    int n_done = 0;
+    while (n_done < G) {
+        for (int g = 0; g < G; g++) if (!done[g] && !pending[g]) enqueue_batch(g);
+        // take whichever group finishes its batch first, so that no group waits for another one's host round trip
+        int ready = -1;
+        while (ready < 0) {
+            for (int g = 0; g < G && ready < 0; g++) {
+                if (!pending[g]) continue;
+                const cudaError_t q = cudaEventQuery(g_event_[g]);
+                if (q == cudaSuccess) ready = g;
+                else if (q != cudaErrorNotReady) CUDA_CHECK(q);
+            }
         }
-        if (done) break;
+        pending[ready] = 0;
+        const uint32_t *hc = h_counts_.get() + (size_t) ready * BATCH;
+        for (int w = 0; w < BATCH; w++) {
+            stats.rays += hc[w];
+            if (dump_waves && ready == 0) fprintf(stderr, "wave %u rays %u\n", waves[ready], hc[w]);
+            if (hc[w] == 0u) { done[ready] = 1; n_done++; break; }
+            waves[ready]++;
+        }
+        if (!done[ready] && finish_divisor > 0 && hc[BATCH - 1] <= wbs[ready].n_slots / (uint32_t) finish_divisor) {
+            // few slots left: one thread per remaining slot runs it to the end of its pixel (rays counted on the device)
+            const WaveBuffers &wb = wbs[ready];
+            const unsigned blocks = div_up(hc[BATCH - 1], 128);
+            cudaStream_t s = g_stream_[ready];
+            if (wide) {
+                if (count) wave_finish_kernel<true, true><<<blocks, 128, 0, s>>>(sc, cam, fr, wb, (uint32_t) (BATCH - 1));
+                else wave_finish_kernel<false, true><<<blocks, 128, 0, s>>>(sc, cam, fr, wb, (uint32_t) (BATCH - 1));
+            } else {
+                if (count) wave_finish_kernel<true, false><<<blocks, 128, 0, s>>>(sc, cam, fr, wb, (uint32_t) (BATCH - 1));
+                else wave_finish_kernel<false, false><<<blocks, 128, 0, s>>>(sc, cam, fr, wb, (uint32_t) (BATCH - 1));
+            }
+            CUDA_CHECK(cudaGetLastError());
+            CUDA_CHECK(cudaEventRecord(g_event_[ready], s));
+            stats.launches++;
+            done[ready] = 1;
+            n_done++;
+        }
+    }
+    for (int g = 0; g < G; g++) {
+        stats.waves = std::max(stats.waves, waves[g]);
+        CUDA_CHECK(cudaStreamWaitEvent(stream, g_event_[g], 0));    // join: the caller's stream continues after every group
     }
 }

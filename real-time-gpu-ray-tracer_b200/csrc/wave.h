@@ -25,8 +25,9 @@ struct WaveBuffers {
     uint32_t *cursors;    // [w] fetch cursor of the trace kernel for wave w
     uint32_t *next_pixel; // next unstarted pixel (tile-major id)
     uint32_t n_slots;
-    uint32_t n_pixels;    // tile-major ids in [0, n_pixels): tiles_x * tiles_y * 32
+    uint32_t n_pixels;    // group-local tile-major ids in [0, n_pixels): (tiles of this group) * 32
     uint32_t tiles_x;
+    uint32_t group, n_groups;   // slot group: 8x4-pixel tile t of the shard belongs to group t % n_groups
 };
 
 struct WaveStats {
@@ -44,6 +45,8 @@ public:
     int mode = 0;                  // 0: binary LBVH traversal, 1: compressed 8-wide
     int refill_min = 8;            // lanes of a warp that must be idle before the warp pulls new rays
     int node_min = 20;
+    int finish_divisor = 24;       // a group whose last wave had <= n_slots / finish_divisor rays is finished by wave_finish_kernel (0: never)
+    int n_groups = 8;              // slot groups whose wave sequences run concurrently on their own streams
     int blocks_per_sm_override = 0; // > 0: cap the resident trace blocks per SM (tuning)             // the node phase of a warp ends when fewer lanes than this stand on an inner node
 private:
     void reserve(uint32_t n_slots);
@@ -53,5 +56,12 @@ private:
     DeviceBuffer<uint2> rng_b_;
     DeviceBuffer<uint32_t> queue_, counters_;
     PinnedBuffer<uint32_t> h_counts_;
+    static constexpr int MAX_GROUPS = 16;
+    cudaStream_t g_stream_[MAX_GROUPS] = {};
+    cudaEvent_t g_event_[MAX_GROUPS] = {};
+    cudaEvent_t fork_event_ = nullptr;
+public:
+    ~WaveRenderer();
+private:
     int trace_blocks_per_sm_[4] = {0, 0, 0, 0};
 };

@@ -152,6 +152,7 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     if (const char *e = getenv("RTB200_NODE_MIN")) c->wave.node_min = atoi(e);
     if (const char *e = getenv("RTB200_TRACE_BLOCKS_PER_SM")) c->wave.blocks_per_sm_override = atoi(e);
     if (const char *e = getenv("RTB200_GROUPS")) c->wave.n_groups = atoi(e);
+    if (const char *e = getenv("RTB200_GRAPHS")) c->wave.use_graphs = atoi(e) != 0;
     if (const char *e = getenv("RTB200_FINISH_DIVISOR")) c->wave.finish_divisor = atoi(e);
     *out = c;
     return RT_OK;

@@ -11,6 +11,7 @@
 #include "rt_pixel.h"
 
 #include <algorithm>
+#include <cstring>
 #include <cstdio>
 #include <cstdlib>
 
@@ -18,6 +19,7 @@ namespace {
 
 constexpr int SHADE_THREADS = 256;
 constexpr uint32_t SLOT_IDLE = 0xFFFFFFFFu;
+constexpr uint32_t SLOT_FRESH = 0xFEFEFEFEu;     // byte pattern of the frame-start memset: the slot has no pixel yet
 
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
 
@@ -42,7 +44,7 @@ __device__ __forceinline__ uint32_t warp_append(uint32_t *counter, bool want) {
     return base + (uint32_t) __popc(mask & ((1u << lane_id()) - 1u));
 }
 
-template<bool FIRST, bool WIDE>
+template<bool WIDE>
 __global__ void __launch_bounds__(SHADE_THREADS) wave_shade_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
                                                                    const __grid_constant__ FrameD fr, const __grid_constant__ WaveBuffers wb,
                                                                    uint32_t wave) {
@@ -50,18 +52,19 @@ __global__ void __launch_bounds__(SHADE_THREADS) wave_shade_kernel(const __grid_
     const bool in_range = slot < wb.n_slots;
     uint32_t pid = SLOT_IDLE;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (in_range && !FIRST) { acc = wb.acc[slot]; pid = __float_as_uint(acc.w); }
-    bool live = FIRST ? in_range : (in_range && pid != SLOT_IDLE);
+    if (in_range) { acc = wb.acc[slot]; pid = __float_as_uint(acc.w); }
+    const bool fresh = in_range && pid == SLOT_FRESH;
+    bool live = in_range && pid != SLOT_IDLE;
 
     RngState rng{};
     RayD ray{};
     f3 thr = mk3(1.f, 1.f, 1.f);
     uint32_t sample = 0, depth = 0;
-    bool need_pixel = FIRST && live;      // slot has no pixel yet
+    bool need_pixel = fresh;              // slot has no pixel yet
     bool need_primary = false;
     bool emit = false;
 
-    if (!FIRST && live) {
+    if (live && !fresh) {
         const float4 h = wb.hit[slot];
         const float4 o = wb.ray_o[slot], d = wb.ray_d[slot], t4 = wb.thr[slot];
         const uint4 ra = wb.rng_a[slot];
@@ -532,6 +535,7 @@ void WaveRenderer::reserve(uint32_t n_slots) {
 
 WaveRenderer::~WaveRenderer() {
     for (int g = 0; g < MAX_GROUPS; g++) {
+        if (g_exec_[g]) cudaGraphExecDestroy(g_exec_[g]);
         if (g_event_[g]) cudaEventDestroy(g_event_[g]);
         if (g_stream_[g]) cudaStreamDestroy(g_stream_[g]);
     }
@@ -595,24 +599,21 @@ void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr
 
     stats = WaveStats{};
     CUDA_CHECK(cudaMemsetAsync(counters_.get(), 0, (size_t) G * CW * sizeof(uint32_t), stream));
+    CUDA_CHECK(cudaMemsetAsync(acc_.get(), 0xFE, (size_t) slot_base[G] * sizeof(float4), stream));     // SLOT_FRESH in every .w
     CUDA_CHECK(cudaEventRecord(fork_event_, stream));
     std::vector<char> first(G, 1), pending(G, 0), done(G, 0);
     std::vector<uint32_t> waves(G, 0u);
-    auto enqueue_batch = [&](int g) {
-        cudaStream_t s = g_stream_[g];
+    // One batch = [zero the batch's counters] + BATCH x (shade, trace) + [counts -> pinned host].  Every batch of a group
+    // is the same work with the same arguments, so it is captured ONCE into a CUDA graph and replayed: a frame is a few
+    // hundred graph launches instead of several thousand kernel launches (the host launch rate bounded small shards).
+    struct BatchKey { SceneD sc; CameraD cam; FrameD fr; WaveBuffers wb; int trace_blocks, refill_min, node_min, wide, count; uint32_t *h; };
+    auto launch_waves = [&](int g, cudaStream_t s) {
         const WaveBuffers &wb = wbs[g];
         const unsigned shade_blocks = div_up(wb.n_slots, SHADE_THREADS);
-        if (first[g]) CUDA_CHECK(cudaStreamWaitEvent(s, fork_event_, 0));
-        else CUDA_CHECK(cudaMemsetAsync(wb.counts, 0, 2 * BATCH * sizeof(uint32_t), s));
+        CUDA_CHECK(cudaMemsetAsync(wb.counts, 0, 2 * BATCH * sizeof(uint32_t), s));
         for (int w = 0; w < BATCH; w++) {
-            if (first[g]) {
-                if (wide) wave_shade_kernel<true, true><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
-                else wave_shade_kernel<true, false><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
-                first[g] = 0;
-            } else {
-                if (wide) wave_shade_kernel<false, true><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
-                else wave_shade_kernel<false, false><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
-            }
+            if (wide) wave_shade_kernel<true><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
+            else wave_shade_kernel<false><<<shade_blocks, SHADE_THREADS, 0, s>>>(sc, cam, fr, wb, (uint32_t) w);
             if (wide) {
                 if (count) wave_trace8_kernel<true><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
                 else wave_trace8_kernel<false><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
@@ -620,10 +621,34 @@ void WaveRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr
                 if (count) wave_trace2_kernel<true><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
                 else wave_trace2_kernel<false><<<trace_blocks, TRACE_THREADS, 0, s>>>(sc, wb, (uint32_t) w, refill_min, node_min, fr.ray_counter);
             }
-            stats.launches += 2;
         }
-        CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaMemcpyAsync(h_counts_.get() + (size_t) g * BATCH, wb.counts, BATCH * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    };
+    auto enqueue_batch = [&](int g) {
+        cudaStream_t s = g_stream_[g];
+        if (first[g]) {
+            CUDA_CHECK(cudaStreamWaitEvent(s, fork_event_, 0));
+            first[g] = 0;
+            BatchKey key;
+            memset(&key, 0, sizeof(key));
+            key.sc = sc; key.cam = cam; key.fr = fr; key.wb = wbs[g];
+            key.trace_blocks = trace_blocks; key.refill_min = refill_min; key.node_min = node_min; key.wide = wide; key.count = count;
+            key.h = h_counts_.get();
+            if (g_key_[g].size() != sizeof(key) || memcmp(g_key_[g].data(), &key, sizeof(key)) != 0) {
+                if (g_exec_[g]) { cudaGraphExecDestroy(g_exec_[g]); g_exec_[g] = nullptr; }
+                cudaGraph_t graph = nullptr;
+                CUDA_CHECK(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+                launch_waves(g, s);
+                CUDA_CHECK(cudaStreamEndCapture(s, &graph));
+                CUDA_CHECK(cudaGraphInstantiate(&g_exec_[g], graph, 0));
+                cudaGraphDestroy(graph);
+                g_key_[g].assign(reinterpret_cast<const char *>(&key), reinterpret_cast<const char *>(&key) + sizeof(key));
+            }
+        }
+        if (use_graphs) CUDA_CHECK(cudaGraphLaunch(g_exec_[g], s));
+        else launch_waves(g, s);
+        stats.launches += 2 * BATCH;
+        CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaEventRecord(g_event_[g], s));
         pending[g] = 1;
     };

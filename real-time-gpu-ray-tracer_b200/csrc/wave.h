@@ -45,6 +45,7 @@ public:
     int mode = 0;                  // 0: binary LBVH traversal, 1: compressed 8-wide
     int refill_min = 8;            // lanes of a warp that must be idle before the warp pulls new rays
     int node_min = 20;
+    bool use_graphs = true;        // replay each group's wave batch as a CUDA graph
     int finish_divisor = 24;       // a group whose last wave had <= n_slots / finish_divisor rays is finished by wave_finish_kernel (0: never)
     int n_groups = 8;              // slot groups whose wave sequences run concurrently on their own streams
     int blocks_per_sm_override = 0; // > 0: cap the resident trace blocks per SM (tuning)             // the node phase of a warp ends when fewer lanes than this stand on an inner node
@@ -60,6 +61,8 @@ private:
     cudaStream_t g_stream_[MAX_GROUPS] = {};
     cudaEvent_t g_event_[MAX_GROUPS] = {};
     cudaEvent_t fork_event_ = nullptr;
+    cudaGraphExec_t g_exec_[MAX_GROUPS] = {};     // the captured wave batch of each group ...
+    std::vector<char> g_key_[MAX_GROUPS];         // ... and the kernel arguments it was captured with
 public:
     ~WaveRenderer();
 private:

@@ -244,7 +244,7 @@ def run_ours(args):
     pkg, sc, cfg = workload(args)
     abi = pkg.abi
 
-    base_flags = (abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0) | (abi.FLAG_MEGAKERNEL if args.megakernel else 0)
+    base_flags = (abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0) | (abi.FLAG_MEGAKERNEL if args.megakernel else 0) | (abi.FLAG_WAVEFRONT if args.wavefront else 0)
     r = pkg.Renderer(device=local, flags=base_flags)
     t0 = time.perf_counter()
     st = r.commitScene(sc)
@@ -252,6 +252,8 @@ def run_ours(args):
     tile_rows = args.tile_rows
     if distributed:
         r.setTileShard(rank, world, tile_rows)
+    elif args.emulate_shard > 1:        # tuning aid: this GPU renders rank 0's shard of an N-way split (not a bench line)
+        r.setTileShard(0, args.emulate_shard, tile_rows)
     W, H = sc.width, sc.height
     ptr, nbytes = r.devicePointer(abi.BUF_RGBA8)
     if distributed:      # every rank's plane is allocated for the largest shard: gather equal-sized buffers
@@ -417,10 +419,12 @@ def main():
     ap.add_argument("--nx", type=int, default=1000)
     ap.add_argument("--nz", type=int, default=500)
     ap.add_argument("--tile-rows", type=int, default=8)
+    ap.add_argument("--emulate-shard", type=int, default=1, help="tuning aid: render only rank 0's tiles of an N-way split on one GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-build baseline")
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 particle rebuild measurement")
     ap.add_argument("--megakernel", action="store_true", help="comparison mode: one thread per pixel (the reference's kernel structure)")
+    ap.add_argument("--wavefront", action="store_true", help="comparison mode: wave loop (shade + trace launch per bounce) instead of the persistent path kernel")
     ap.add_argument("--bvh2", action="store_true", help="comparison mode: traverse the binary LBVH instead of the wide BVH")
     args = ap.parse_args()
     if args.impl == "reference":

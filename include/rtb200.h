@@ -131,7 +131,10 @@ enum rt_flags {
     RT_FLAG_TRAVERSE_BVH2           = 1u << 4,
     /* Comparison mode: one thread per pixel runs all samples and bounces (the reference's kernel structure,
      * src/Global/Kernel.cu:105-147) instead of the wavefront (shade/generate + persistent trace kernels).          */
-    RT_FLAG_MEGAKERNEL              = 1u << 5
+    RT_FLAG_MEGAKERNEL              = 1u << 5,
+    /* Comparison mode: the wave loop (one shade/generate + one trace launch per bounce of all paths, ray queues in
+     * between) instead of the default single persistent launch that fuses both (kernels_persist.cu).                */
+    RT_FLAG_WAVEFRONT               = 1u << 6
 };
 
 typedef struct rt_frame_out {

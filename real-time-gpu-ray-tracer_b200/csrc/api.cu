@@ -41,6 +41,8 @@ struct rt_ctx {
     PinnedBuffer<InstanceXformIn> h_xform_in;
     LbvhBuilder blas, tlas;
     WaveRenderer wave;
+    PersistRenderer persist;
+    int path_mode = 1;              // 1: persistent path kernel (default), 0: wave loop; RT_FLAG_WAVEFRONT / RTB200_MODE select
     bool geometry_committed = false, materials_committed = false, instances_configured = false, built = false, camera_set = false;
     rt_build_stats build_stats{};
 
@@ -154,6 +156,12 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     if (const char *e = getenv("RTB200_GROUPS")) c->wave.n_groups = atoi(e);
     if (const char *e = getenv("RTB200_GRAPHS")) c->wave.use_graphs = atoi(e) != 0;
     if (const char *e = getenv("RTB200_FINISH_DIVISOR")) c->wave.finish_divisor = atoi(e);
+    c->persist.node_min = c->wave.node_min;
+    c->persist.blocks_per_sm_override = c->wave.blocks_per_sm_override;
+    if (const char *e = getenv("RTB200_SHADE_MIN")) c->persist.shade_min = atoi(e);
+    if (const char *e = getenv("RTB200_TILE_ORDER")) c->persist.tile_order = atoi(e);
+    if (flags & RT_FLAG_WAVEFRONT) c->path_mode = 0;
+    if (const char *e = getenv("RTB200_MODE")) c->path_mode = strcmp(e, "wave") == 0 ? 0 : 1;     // tuning / A-B runs
     *out = c;
     return RT_OK;
 }
@@ -345,8 +353,12 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     CUDA_CHECK(cudaEventRecord(ctx->ev[2], s));
     WaveStats ws{};
     const bool mega = ctx->flags & RT_FLAG_MEGAKERNEL;
+    const bool persist = !mega && ctx->path_mode == 1 && !fr.traverse_bvh2;
     if (mega) {
         launch_render(sc, ctx->hs.cam, fr, s);
+    } else if (persist) {
+        ctx->persist.render(sc, ctx->hs.cam, fr, s, ctx->sm_count);
+        ws.launches = ctx->persist.launches;
     } else {
         ctx->wave.mode = fr.traverse_bvh2 ? 0 : 1;
         ctx->wave.render(sc, ctx->hs.cam, fr, s, ctx->sm_count, ws);

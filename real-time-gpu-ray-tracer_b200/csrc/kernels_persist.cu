@@ -1,0 +1,332 @@
+// kernels_persist.cu — the whole frame in ONE persistent launch: every resident thread carries one pixel at a time
+// through all of its samples and bounces (the reference's per-pixel XORWOW stream is sequential, so a pixel is the
+// unit of sequential work, src/Global/Kernel.cu:107-146) and takes the next unstarted pixel when it is done.
+//
+// A thread runs the same per-ray state machine as the wavefront trace kernel (trace_closest8 of rt_wide_trace.h,
+// step for step) plus one more step, SHADE (hit record, Rough/Metal::scatter, rayColor's bookkeeping, sample
+// accumulation, next primary ray — exactly wave_shade_kernel's per-slot work).  The warp only votes on WHICH step
+// its lanes take next, so that lanes take the expensive steps together:
+//   NODE  : pop the nearest pending child, fetch its 80-byte node, test the 8 child boxes
+//   LEAF  : one primitive test (BLAS) or one instance entry (TLAS)
+//   SHADE : consume the finished ray's hit, start the path's next ray (or the next sample / pixel)
+// Compared with the wave loop there is no ray queue, no per-wave launch and no wave tail: a lane whose ray ends
+// waits only until enough lanes of its own warp want to shade.  The per-pixel results are bit-identical (each pixel
+// still consumes its own stream in the reference's order); only the schedule differs.
+#include "wave.h"
+
+#include "rt_pixel.h"
+#include "wave_device.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+
+namespace {
+
+constexpr int PT = 128;
+constexpr uint32_t NG_INNER = 0x00FFFFFFu;      // node group has pending inner hits iff .y > NG_INNER
+#ifndef RT_PERSIST_MIN_BLOCKS
+#define RT_PERSIST_MIN_BLOCKS 6   /* 80 registers: no spills; measured faster than 8 blocks x 64 registers */
+#endif
+enum : uint32_t { ST_DEAD = 0u, ST_TRACE = 1u, ST_SHADE = 2u, ST_FRESH = 3u };
+template<bool COUNT>
+__global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
+                                                                            const __grid_constant__ FrameD fr, const __grid_constant__ PersistBuffers pb,
+                                                                            int shade_min, int node_min) {
+    __shared__ uint2 stack_mem[RT_WIDE_STACK * PT];
+    uint2 *const stk = stack_mem + threadIdx.x;               // entry k at stk[k * PT]
+    const uint32_t tid = blockIdx.x * PT + threadIdx.x;
+    const uint32_t slot = tid;                                // path-state entry of this lane
+    uint32_t state = ST_FRESH;
+    WideRay r{};
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
+    int sp = 0, inst = -1, inst_sp = 0, prim_type = 0;
+    HitD hit{};
+    uint32_t overflow = 0, rays = 0;
+    TravStats stats{0, 0, 0};
+
+    for (;;) {
+        // ---- cheap transitions: nothing pending in registers -> leave instance / ray finished / pop -----------------
+        if (state == ST_TRACE && tg.y == 0u && ng.y <= NG_INNER) {
+            if (inst >= 0 && sp == inst_sp && sp != 0) {         // BLAS exhausted, TLAS work left: back to world space
+                inst = -1;
+                const float4 o = pb.ray_o[slot], d = pb.ray_d[slot];
+                r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);
+                wide_setup_ray(r);
+            }
+            if (sp == 0) {
+                state = ST_SHADE;
+                ng = make_uint2(0u, 0u);
+            } else {
+                sp--;
+                const uint2 e = stk[sp * PT];
+                if (e.y > NG_INNER) ng = e; else { tg = e; ng = make_uint2(0u, 0u); }
+            }
+        }
+        const bool on_node = state == ST_TRACE && tg.y == 0u && ng.y > NG_INNER;
+        const bool on_leaf = state == ST_TRACE && tg.y != 0u;
+        const uint32_t node_lanes = __ballot_sync(0xffffffffu, on_node);
+        const uint32_t leaf_lanes = __ballot_sync(0xffffffffu, on_leaf);
+        const uint32_t shade_lanes = __ballot_sync(0xffffffffu, state >= ST_SHADE);
+        if ((node_lanes | leaf_lanes | shade_lanes) == 0u) break;            // every lane ran out of pixels
+        const int nn = __popc(node_lanes), ns = __popc(shade_lanes);
+        int phase;                                                           // 0 node, 1 leaf, 2 shade
+        if (nn >= node_min) phase = 0;
+        else if (ns >= shade_min) phase = 2;
+        else if (leaf_lanes) phase = 1;
+        else if (nn) phase = 0;
+        else phase = 2;
+
+        if (phase == 0) {
+            // ---- NODE ---------------------------------------------------------------------------------------------
+            if (on_node) {
+                const uint32_t hits_imask = ng.y;
+                const int bit = rt_bfind(hits_imask);
+                const uint32_t base = ng.x;
+                ng.y &= ~(1u << bit);
+                if (ng.y > NG_INNER) {
+                    if (sp < RT_WIDE_STACK) { stk[sp * PT] = ng; sp++; } else overflow = 1u;
+                }
+                const uint32_t sl = ((uint32_t) bit - 24u) ^ (r.oct_inv4 & 0xFFu);
+                const uint32_t rel = (uint32_t) __popc(hits_imask & ~(0xFFFFFFFFu << sl));
+                const BvhNode8 n = load_node8(inst < 0 ? sc.tlas_nodes8 : sc.blas_nodes8, base + rel);
+                if (COUNT) stats.nodes++;
+                const uint32_t hm = node8_intersect(n, r, RT_TMIN, hit.tc);
+                ng.x = n.n1.x;
+                ng.y = hm & 0xFF000000u;
+                if (ng.y) ng.y |= __float_as_uint(n.n0.w) >> 24;
+                tg.x = n.n1.y;
+                tg.y = hm & 0x00FFFFFFu;
+            }
+        } else if (phase == 1) {
+            // ---- LEAF: one primitive test or one instance entry per lane --------------------------------------------
+            if (on_leaf) {
+                const int idx = rt_bfind(tg.y);
+                tg.y &= ~(1u << idx);
+                if (inst >= 0) {
+                    if (COUNT) stats.prims++;
+                    leaf_test8(sc, (uint32_t) prim_type, tg.x + (uint32_t) idx, r.ray, RT_TMIN, inst, hit);
+                } else {
+                    // TLAS leaf: enter one instance, keep the rest of the group and the node group for later
+                    if (tg.y) { if (sp < RT_WIDE_STACK) { stk[sp * PT] = tg; sp++; } else overflow = 1u; }
+                    if (ng.y > NG_INNER) { if (sp < RT_WIDE_STACK) { stk[sp * PT] = ng; sp++; } else overflow = 1u; }
+                    inst = (int) __ldg(&sc.tlas_leaf_inst[tg.x + (uint32_t) idx]);
+                    if (COUNT) stats.insts++;
+                    float inv[12];
+                    int root8;
+                    load_instance_wide(sc, inst, inv, root8, prim_type);
+                    const f3 wo = r.ray.o, wd = r.ray.d;
+                    r.ray.o = xf_point(inv, wo);                     // Instance::hit: origin as point, direction as vector,
+                    r.ray.d = xf_vector(inv, wd);                    // not re-normalised (reference src/AS/Instance.cu:26-28)
+                    wide_setup_ray(r);
+                    inst_sp = sp;
+                    ng = make_uint2((uint32_t) root8, 0x80000000u);
+                    tg = make_uint2(0u, 0u);
+                }
+            }
+        } else {
+            // ---- SHADE: the per-slot work of wave_shade_kernel, for the lanes whose ray has finished ------------------
+            const bool shading = state >= ST_SHADE;
+            const bool fresh = state == ST_FRESH;
+            uint32_t pid = SLOT_IDLE;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            RngState rng{};
+            RayD ray{};
+            f3 thr = mk3(1.f, 1.f, 1.f);
+            uint32_t sample = 0, depth = 0, pix_rays = 0;
+            bool need_pixel = shading && fresh;
+            bool need_primary = false, emit = false, acc_dirty = false;
+            if (shading && !fresh) {
+                acc = pb.acc[slot];
+                pid = __float_as_uint(acc.w);
+                const float4 o = pb.ray_o[slot], d = pb.ray_d[slot], t4 = pb.thr[slot];
+                const uint4 ra = pb.rng_a[slot];
+                const uint2 rb = pb.rng_b[slot];
+                rng.d = ra.x; rng.v0 = ra.y; rng.v1 = ra.z; rng.v2 = ra.w; rng.v3 = rb.x; rng.v4 = rb.y;
+                ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z);
+                thr = mk3(t4.x, t4.y, t4.z);
+                const uint32_t sd = __float_as_uint(t4.w);
+                sample = sd >> 16; depth = sd & 0xFFFFu;
+                pix_rays = __float_as_uint(o.w);                     // rays of this pixel so far
+                if (fr.aov_t && sample == 0u && depth == 0u) {       // primary hit of the pixel's first sample
+                    uint32_t lx, ly;
+                    pixel_coords(pid, pb.tiles_x, lx, ly);
+                    const uint32_t lp = ly * cam.width + lx;
+                    const bool has = hit.inst >= 0;
+                    fr.aov_t[lp] = has ? hit.t : RT_INF;
+                    fr.aov_inst[lp] = has ? hit.inst : -1;
+                    fr.aov_prim[lp] = has ? (int) ((ref_type(hit.leaf) << 28) | sc.leaf_prims8[ref_pos(hit.leaf)]) : -1;
+                }
+                const bool alive = shade_scatter<true>(sc, cam, ray, hit, thr, rng);
+                depth++;
+                if (alive && depth < cam.depth) {
+                    emit = true;
+                } else {
+                    // path over: rayColor returns the throughput (Q6); next sample or next pixel
+                    acc.x += thr.x; acc.y += thr.y; acc.z += thr.z;
+                    acc_dirty = true;
+                    sample++;
+                    if (sample == cam.sqrtSamples * cam.sqrtSamples) {
+                        uint32_t lx, ly;
+                        pixel_coords(pid, pb.tiles_x, lx, ly);
+                        const uint32_t lp = ly * cam.width + lx;
+                        const float w = cam.rcpSqrtSamples * cam.rcpSqrtSamples;
+                        const float cr = acc.x * w, cg = acc.y * w, cb = acc.z * w;
+                        fr.radiance[3 * (size_t) lp + 0] = cr;
+                        fr.radiance[3 * (size_t) lp + 1] = cg;
+                        fr.radiance[3 * (size_t) lp + 2] = cb;
+                        const size_t op = fr.rgba8_is_full_frame ? (size_t) global_row(fr, ly) * cam.width + lx : (size_t) lp;
+                        reinterpret_cast<uchar4 *>(fr.rgba8)[op] = make_uchar4(to_byte(cr), to_byte(cg), to_byte(cb), 255);
+                        atomicAdd(&pb.tile_cost[pid >> 5], pix_rays);      // next frame hands the dear tiles out first
+                        need_pixel = true;
+                    } else {
+                        need_primary = true;
+                    }
+                }
+            }
+            // lanes that finished a pixel (or have none yet) take the next unstarted pixel; ids outside the image
+            // (edge tiles) are skipped
+            for (;;) {
+                const uint32_t any = __ballot_sync(0xffffffffu, need_pixel);
+                if (any == 0u) break;
+                const uint32_t cand = warp_append(pb.next_pixel, need_pixel);
+                if (need_pixel) {
+                    if (cand >= pb.n_pixels) {
+                        state = ST_DEAD; need_pixel = false;
+                    } else {
+                        const uint32_t tile = __ldg(&pb.tile_order[cand >> 5]);
+                        const uint32_t gp = (tile << 5) | (cand & 31u);
+                        uint32_t lx, ly;
+                        pixel_coords(gp, pb.tiles_x, lx, ly);
+                        if (lx < cam.width && ly < fr.local_rows && global_row(fr, ly) < cam.height) {
+                            pid = gp; need_pixel = false; need_primary = true;
+                            rng = fr.rng[ly * cam.width + lx];
+                            acc = make_float4(0.f, 0.f, 0.f, __uint_as_float(pid));
+                            acc_dirty = true;
+                            sample = 0;
+                            pix_rays = 0;
+                        }
+                    }
+                }
+            }
+            if (shading && state != ST_DEAD) {
+                if (need_primary) {
+                    uint32_t lx, ly;
+                    pixel_coords(pid, pb.tiles_x, lx, ly);
+                    const uint32_t si = sample / cam.sqrtSamples, sj = sample % cam.sqrtSamples;
+                    ray = primary_ray(cam, lx, global_row(fr, ly), si, sj, rng);
+                    thr = mk3(1.f, 1.f, 1.f);
+                    depth = 0;
+                    emit = true;
+                }
+                if (acc_dirty) pb.acc[slot] = acc;
+                // emit is true here: the lane starts its next ray
+                pb.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(pix_rays + 1u));
+                pb.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
+                pb.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float((sample << 16) | depth));
+                pb.rng_a[slot] = make_uint4(rng.d, rng.v0, rng.v1, rng.v2);
+                pb.rng_b[slot] = make_uint2(rng.v3, rng.v4);
+                r.ray = ray;
+                wide_setup_ray(r);
+                hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.f; hit.v = 0.f; hit.inst = -1; hit.leaf = 0;
+                sp = 0; inst = -1; inst_sp = 0;
+                ng = make_uint2(0u, 0x80000000u);           // TLAS root: one pending inner hit at relative index 0
+                tg = make_uint2(0u, 0u);
+                state = ST_TRACE;
+                rays++;
+            }
+            (void) emit;
+        }
+    }
+
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        rays += __shfl_xor_sync(0xffffffffu, rays, off);
+        overflow |= __shfl_xor_sync(0xffffffffu, overflow, off);
+    }
+    if (lane_id() == 0) {
+        if (rays) atomicAdd(fr.ray_counter, (unsigned long long) rays);
+        if (overflow) atomicOr(fr.overflow_flag, 1u);
+    }
+    if (COUNT) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            stats.nodes += __shfl_xor_sync(0xffffffffu, stats.nodes, off);
+            stats.prims += __shfl_xor_sync(0xffffffffu, stats.prims, off);
+            stats.insts += __shfl_xor_sync(0xffffffffu, stats.insts, off);
+        }
+        if (lane_id() == 0) {
+            atomicAdd(fr.ray_counter + 2, (unsigned long long) stats.nodes);
+            atomicAdd(fr.ray_counter + 3, (unsigned long long) stats.prims);
+            atomicAdd(fr.ray_counter + 4, (unsigned long long) stats.insts);
+        }
+    }
+}
+
+// ---- hand-out order of the tiles -------------------------------------------------------------------------------
+// The frame ends when the LAST pixel does, and a pixel is sequential work: handing the dear tiles out first and the
+// cheap ones (sky: one ray per sample) last keeps the end of the frame short (longest-processing-time-first).  The
+// cost of a tile is what it took in the previous frame of this context (rays traced, accumulated by the path kernel);
+// a frame without history is handed out in scan order.  Key = cost class (64 classes over 1..depth rays per sample,
+// dear first); the radix sort is stable, so tiles of one class stay in scan order and the warps in flight keep
+// sharing BVH nodes.
+__global__ void __launch_bounds__(256) tile_keys_kernel(uint32_t *__restrict__ tile_cost, uint32_t n_tiles, uint32_t base, uint32_t span,
+                                                        uint64_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tiles) return;
+    const uint32_t c = tile_cost[t];
+    tile_cost[t] = 0u;                                            // this frame accumulates afresh
+    uint32_t cls = 0u;
+    if (c > base) {
+        const unsigned long long x = (unsigned long long) (c - base) * 64ull / span;
+        cls = x > 63ull ? 63u : (uint32_t) x;
+    }
+    keys[t] = 63u - cls;
+    vals[t] = t;
+}
+
+} // namespace
+
+void PersistRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count) {
+    if (blocks_per_sm_[0] == 0) {
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm_[0], persist8_kernel<false>, PT, 0));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm_[1], persist8_kernel<true>, PT, 0));
+    }
+    const bool count = fr.count_traversal != 0;
+    int bps = std::max(1, blocks_per_sm_[count ? 1 : 0]);
+    if (blocks_per_sm_override > 0) bps = std::min(bps, blocks_per_sm_override);
+    PersistBuffers pb{};
+    pb.tiles_x = (cam.width + 7u) / 8u;
+    pb.n_tiles = pb.tiles_x * ((fr.local_rows + 3u) / 4u);
+    pb.n_pixels = pb.n_tiles * 32u;
+    // no more threads than pixels (a warp = one 8x4 tile at a time)
+    const uint32_t want_blocks = (pb.n_pixels + PT - 1) / PT;
+    const uint32_t blocks = std::min<uint32_t>((uint32_t) (sm_count * bps), std::max(1u, want_blocks));
+    const size_t n_threads = (size_t) blocks * PT;
+    ray_o_.reserve(n_threads); ray_d_.reserve(n_threads); thr_.reserve(n_threads); acc_.reserve(n_threads);
+    rng_a_.reserve(n_threads); rng_b_.reserve(n_threads);
+    counter_.reserve(1);
+    tile_cost_.reserve(pb.n_tiles); keys_a_.reserve(pb.n_tiles); keys_b_.reserve(pb.n_tiles); vals_a_.reserve(pb.n_tiles); vals_b_.reserve(pb.n_tiles);
+    // the history belongs to one frame geometry (resolution, shard, samples): anything else starts afresh
+    const uint64_t sig = ((uint64_t) cam.width << 40) ^ ((uint64_t) fr.local_rows << 24) ^ ((uint64_t) fr.shard_rank << 16) ^ ((uint64_t) fr.shard_world << 8)
+                         ^ ((uint64_t) cam.sqrtSamples << 4) ^ (uint64_t) cam.depth ^ ((uint64_t) fr.tile_rows << 52);
+    if (sig != history_sig_ || tile_order == 0) {
+        CUDA_CHECK(cudaMemsetAsync(tile_cost_.get(), 0, pb.n_tiles * sizeof(uint32_t), stream));
+        history_sig_ = sig;
+    }
+    uint64_t *keys = keys_a_.get(), *keys_alt = keys_b_.get();
+    uint32_t *vals = vals_a_.get(), *vals_alt = vals_b_.get();
+    const uint32_t spp = cam.sqrtSamples * cam.sqrtSamples;
+    const uint32_t base = 32u * spp, span = std::max(1u, base * (std::max(2u, cam.depth) - 1u));
+    tile_keys_kernel<<<div_up(pb.n_tiles, 256), 256, 0, stream>>>(tile_cost_.get(), pb.n_tiles, base, span, keys, vals);
+    uint32_t sort_launches = 0;
+    sorter_.sort(keys, keys_alt, vals, vals_alt, (int) pb.n_tiles, 6, stream, sm_count, sort_launches);
+    launches = 2 + sort_launches;
+    pb.ray_o = ray_o_.get(); pb.ray_d = ray_d_.get(); pb.thr = thr_.get(); pb.acc = acc_.get();
+    pb.rng_a = rng_a_.get(); pb.rng_b = rng_b_.get(); pb.next_pixel = counter_.get();
+    pb.tile_order = vals; pb.tile_cost = tile_cost_.get();
+    CUDA_CHECK(cudaMemsetAsync(counter_.get(), 0, sizeof(uint32_t), stream));
+    if (count) persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+    else persist8_kernel<false><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+    CUDA_CHECK(cudaGetLastError());
+}

@@ -2,6 +2,7 @@
 // the wave loop.  Replaces the reference's one-thread-per-pixel megakernel `render` (src/Global/Kernel.cu:105-147).
 #pragma once
 
+#include "build.h"
 #include "device_util.h"
 #include "rt_types.h"
 
@@ -67,4 +68,40 @@ public:
     ~WaveRenderer();
 private:
     int trace_blocks_per_sm_[4] = {0, 0, 0, 0};
+};
+
+// ---- persistent path kernel (kernels_persist.cu) --------------------------------------------------------------
+// Path state of the resident threads: one entry per THREAD of the persistent grid (thread id = slot), so every
+// access is coalesced and the arrays (104 B x ~115 k threads) stay in L2.
+struct PersistBuffers {
+    float4 *ray_o, *ray_d;   // world ray of the thread's path segment in flight; ray_o.w = bits(rays of the pixel so far)
+    float4 *thr;             // throughput.xyz, w = bits(sample << 16 | depth)
+    float4 *acc;             // radiance sum of the finished samples.xyz, w = bits(pixel id, tile-major)
+    uint4 *rng_a;            // XORWOW d, v0, v1, v2
+    uint2 *rng_b;            // XORWOW v3, v4
+    uint32_t *next_pixel;    // next unstarted pixel (index into the hand-out order)
+    const uint32_t *tile_order;   // k-th 8x4 tile handed out
+    uint32_t *tile_cost;     // rays traced per tile in this frame (orders the next frame)
+    uint32_t n_pixels;       // tiles * 32
+    uint32_t n_tiles, tiles_x;
+};
+
+class PersistRenderer {
+public:
+    // one path-kernel launch per frame (plus the tile ordering); rays are counted on the device (fr.ray_counter[0])
+    void render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count);
+    int node_min = 20;             // the warp takes a node step while at least this many lanes stand on an inner node
+    int shade_min = 8;             // ... and shades finished rays once this many lanes wait for it
+    int blocks_per_sm_override = 0;
+    int tile_order = 1;            // 1: dear tiles first (cost = rays of the previous frame), 0: always scan order
+    uint32_t launches = 0;         // kernels launched by the last render()
+private:
+    DeviceBuffer<float4> ray_o_, ray_d_, thr_, acc_;
+    DeviceBuffer<uint4> rng_a_;
+    DeviceBuffer<uint2> rng_b_;
+    DeviceBuffer<uint32_t> counter_, tile_cost_, vals_a_, vals_b_;
+    DeviceBuffer<uint64_t> keys_a_, keys_b_;
+    RadixSorter sorter_;
+    uint64_t history_sig_ = 0;
+    int blocks_per_sm_[2] = {0, 0};
 };

@@ -83,10 +83,12 @@ def test_device_wide_bvh_equals_cpu_twin(pkg, idx):
 
 
 @pytest.mark.parametrize("idx", range(N_PARITY))
-@pytest.mark.parametrize("mode", ["bvh2", "megakernel", "megakernel+bvh2"])
+@pytest.mark.parametrize("mode", ["bvh2", "megakernel", "megakernel+bvh2", "wavefront", "wavefront+bvh2"])
 def test_comparison_modes(pkg, port, idx, mode):
-    """The comparison modes (binary LBVH traversal, one-thread-per-pixel kernel) give the same frame as the default path."""
-    flags = (pkg.abi.FLAG_TRAVERSE_BVH2 if "bvh2" in mode else 0) | (pkg.abi.FLAG_MEGAKERNEL if "megakernel" in mode else 0)
+    """The comparison modes (binary LBVH traversal, one-thread-per-pixel kernel, wave loop) give the same frame as the
+    default path (persistent path kernel over the wide BVH)."""
+    flags = (pkg.abi.FLAG_TRAVERSE_BVH2 if "bvh2" in mode else 0) | (pkg.abi.FLAG_MEGAKERNEL if "megakernel" in mode else 0) \
+        | (pkg.abi.FLAG_WAVEFRONT if "wavefront" in mode else 0)
     sc = parity_scenes(pkg.scenes)[idx]
     check_against_oracle(gpu_frame(pkg, sc, flags=flags), port.scene(sc, 99), sc)
 

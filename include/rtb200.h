@@ -251,6 +251,12 @@ int rt_read_wide_bvh(rt_ctx *ctx, size_t which, size_t *n_nodes, size_t *n_leaf_
 int rt_load_vtk_series(rt_ctx *ctx, const char *series_path, size_t *frame_count);
 int rt_set_vtk_frame(rt_ctx *ctx, size_t frame);
 
+/* ---- measurement aid (bench.py roofline denominators; no reference counterpart) ----------------------
+ * Streams a device buffer of `bytes` with 128-bit loads from every SM, `repeats` times back to back, and returns
+ * the read bandwidth in GB/s (CUDA events).  bytes well below the L2 size (126 MB) measures the L2 -> SM read
+ * bandwidth that bounds node/triangle fetches of an L2-resident BVH; bytes well above it measures HBM reads.     */
+int rt_probe_read_bandwidth(rt_ctx *ctx, size_t bytes, int repeats, double *gbs);
+
 #ifdef __cplusplus
 }
 #endif

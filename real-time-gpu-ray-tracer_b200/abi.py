@@ -92,6 +92,7 @@ EXPORTS = [
     "rt_build_acceleration_structure", "rt_get_build_stats", "rt_configure_camera",
     "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm",
     "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame",
+    "rt_probe_read_bandwidth",
 ]
 
 _lib = None
@@ -132,6 +133,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_read_wide_bvh.argtypes = [vp, sz, C.POINTER(sz), C.POINTER(sz), vp, vp]
     lib.rt_load_vtk_series.argtypes = [vp, C.c_char_p, C.POINTER(sz)]
     lib.rt_set_vtk_frame.argtypes = [vp, sz]
+    lib.rt_probe_read_bandwidth.argtypes = [vp, sz, i32, C.POINTER(C.c_double)]
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
         if name not in ("rt_last_error", "rt_version", "rt_struct_size"):

@@ -428,6 +428,13 @@ int rt_read_framebuffer(rt_ctx *ctx, int kind, void *host_dst, size_t dst_bytes)
     RT_API_END(ctx)
 }
 
+int rt_probe_read_bandwidth(rt_ctx *ctx, size_t bytes, int repeats, double *gbs) {
+    RT_API_BEGIN(ctx)
+    if (!gbs || bytes < 4096 || repeats < 1) return fail(ctx, RT_ERR_ARGUMENT, "rt_probe_read_bandwidth: bad argument");
+    *gbs = probe_read_bandwidth(bytes, repeats, ctx->sm_count, ctx->stream);
+    RT_API_END(ctx)
+}
+
 int rt_write_ppm(rt_ctx *ctx, const char *path) {
     RT_API_BEGIN(ctx)
     if (!ctx->camera_set || !path) return fail(ctx, RT_ERR_STATE, "rt_write_ppm: no frame");

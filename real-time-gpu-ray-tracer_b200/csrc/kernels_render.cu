@@ -78,7 +78,46 @@ __global__ void __launch_bounds__(128) render_pixels_kernel(const __grid_constan
     }
 }
 
+// measurement aid: every thread streams 128-bit words of the buffer (grid-stride) and folds them into one word
+__global__ void __launch_bounds__(512) probe_read_kernel(const uint4 *__restrict__ buf, size_t n_words, int repeats, uint32_t *sink) {
+    uint32_t acc = 0;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (int r = 0; r < repeats; r++) {
+        for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += 4 * stride) {
+            uint4 a = make_uint4(0, 0, 0, 0), b = a, c = a, d = a;
+            a = __ldcg(buf + i);
+            if (i + stride < n_words) b = __ldcg(buf + i + stride);
+            if (i + 2 * stride < n_words) c = __ldcg(buf + i + 2 * stride);
+            if (i + 3 * stride < n_words) d = __ldcg(buf + i + 3 * stride);
+            acc ^= a.x ^ a.y ^ a.z ^ a.w ^ b.x ^ b.y ^ b.z ^ b.w ^ c.x ^ c.y ^ c.z ^ c.w ^ d.x ^ d.y ^ d.z ^ d.w;
+        }
+    }
+    if (acc == 0x9E3779B9u) *sink = acc;       // never true for the zero-filled buffer; keeps the loads alive
+}
+
 } // namespace
+
+double probe_read_bandwidth(size_t bytes, int repeats, int sm_count, cudaStream_t stream) {
+    DeviceBuffer<uint4> buf;
+    DeviceBuffer<uint32_t> sink;
+    const size_t n_words = bytes / sizeof(uint4);
+    buf.reserve(n_words);
+    sink.reserve(1);
+    CUDA_CHECK(cudaMemsetAsync(buf.get(), 0, n_words * sizeof(uint4), stream));
+    cudaEvent_t e0, e1;
+    CUDA_CHECK(cudaEventCreate(&e0));
+    CUDA_CHECK(cudaEventCreate(&e1));
+    probe_read_kernel<<<sm_count * 4, 512, 0, stream>>>(buf.get(), n_words, 2, sink.get());       // warm-up (fills L2)
+    CUDA_CHECK(cudaEventRecord(e0, stream));
+    probe_read_kernel<<<sm_count * 4, 512, 0, stream>>>(buf.get(), n_words, repeats, sink.get());
+    CUDA_CHECK(cudaEventRecord(e1, stream));
+    CUDA_CHECK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return (double) n_words * sizeof(uint4) * repeats / (ms * 1e-3) / 1e9;
+}
 
 void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &cam, const FrameD &fr, cudaStream_t stream) {
     const size_t n = (size_t) cam.width * fr.local_rows;

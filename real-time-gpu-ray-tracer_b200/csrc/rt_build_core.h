@@ -58,13 +58,22 @@ RT_HD uint64_t expand_bits21(uint64_t v) {
     v = (v | (v << 2)) & 0x1249249249249249ull;
     return v;
 }
+// The grid is CUBIC: every axis is scaled by the largest extent of the segment, so a split always halves a cell along
+// its longest side.  (Scaling each axis by its own extent makes a flat mesh — a height field, a particle shell —
+// spend every third split on its thin axis: children that overlap completely in the other two.)  Along a short axis
+// the top bits are simply equal for all primitives and the Karras hierarchy skips them.
+#ifndef RT_MORTON_PER_AXIS
+#define RT_MORTON_PER_AXIS 0     /* 1: the first version's per-axis scaling, kept for A/B measurements */
+#endif
 RT_HD uint64_t morton_code(const Aabb &prim, const Aabb &scene, int bits) {
     const float scale = (float) (1u << bits);
+    const float ext_max = rt_max(rt_max(scene.hi.x - scene.lo.x, scene.hi.y - scene.lo.y), scene.hi.z - scene.lo.z);
     uint64_t q[3];
     for (int a = 0; a < 3; a++) {
         const float lo = comp3(scene.lo, a), hi = comp3(scene.hi, a);
         const float c = 0.5f * (comp3(prim.lo, a) + comp3(prim.hi, a));
-        const float ext = hi - lo;
+        const float ext = RT_MORTON_PER_AXIS ? hi - lo : ext_max;
+        (void) hi;
         float n = ext > 0.0f ? (c - lo) / ext : 0.0f;
         n = rt_min(rt_max(n * scale, 0.0f), scale - 1.0f);
         q[a] = (uint64_t) n;

@@ -111,6 +111,12 @@ class Renderer:
     def writePPM(self, path: str):
         self._check(self.lib.rt_write_ppm(self.ctx, path.encode()))
 
+    def probeReadBandwidth(self, nbytes: int, repeats: int = 20) -> float:
+        """Measurement aid: GB/s of streaming an `nbytes` device buffer `repeats` times (L2-resident when it fits L2)."""
+        g = C.c_double(0.0)
+        self._check(self.lib.rt_probe_read_bandwidth(self.ctx, nbytes, repeats, C.byref(g)))
+        return g.value
+
     def readLBVH(self, blas_index: int = 0):
         n = C.c_size_t()
         self._check(self.lib.rt_read_lbvh(self.ctx, blas_index, C.byref(n), None, None, None, None, None, None))

@@ -360,12 +360,27 @@ def run_ours(args):
                     traffic = json.load(open(tp)).get("dram_bytes_per_launch")
                 except Exception:
                     traffic = None
-            roof = {"bound": "hbm", "kernel": "render_pixels_kernel (trace+shade)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            kname = ("render_pixels_kernel (one thread per pixel)" if args.megakernel else
+                     "wave_trace kernels + wave_shade (wave loop)" if (args.wavefront or args.bvh2) else
+                     "persist8_kernel (trace + shade, one launch per frame)")
+            # the BVH + triangle records of this workload are L2-resident (ncu: DRAM throughput < 1 %), so the HBM figure
+            # is the contract's formal roofline and the L2 read bandwidth measured here is the one that can bind
+            l2 = None
+            try:
+                l2_gbs = r.probeReadBandwidth(32 << 20, 40)
+                hbm_read_gbs = r.probeReadBandwidth(2 << 30, 2)
+                l2 = {"peak": l2_gbs, "unit": "GB/s", "frac": achieved / l2_gbs, "hbm_read_probe_gbs": hbm_read_gbs,
+                      "how": "rt_probe_read_bandwidth: 128-bit loads from every SM over a 32 MiB (L2-resident) / 2 GiB buffer, CUDA events"}
+            except Exception as e:   # noqa: BLE001
+                l2 = {"unavailable": str(e)}
+            roof = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": alg, "kernel_ms": t_kernel * 1e3,
+                    "algorithmic_bytes_per_launch": alg, "kernel_ms": t_kernel * 1e3, "l2": l2,
                     "per_ray": {"node_fetches": co.node_fetches / co.rays, "prim_fetches": co.prim_fetches / co.rays,
                                 "instance_fetches": co.instance_fetches / co.rays, "bytes": alg / co.rays},
-                    "record_bytes": {"node": node_b, "triangle": prim_b, "instance": inst_b, "pixel_io": io_b}}
+                    "record_bytes": {"node": node_b, "triangle": prim_b, "instance": inst_b, "pixel_io": io_b},
+                    "note": "traffic = DRAM bytes of one launch from the committed ncu --set full capture (profiles/traffic_latest.json); "
+                            "far below the algorithmic bytes because the working set stays in the 126 MB L2"}
         # ---- CPU baseline: the reference's own code on this box's host cores, bounded sample ---------------------
         cpu = None
         if world == 1 and not args.no_cpu_baseline:

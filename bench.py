@@ -36,6 +36,18 @@ METRIC = "Mrays/s (1M-triangle scene, 1920x1080, 64 spp, depth 10)"
 
 def workload(args):
     pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    if args.config == "c4":      # configs[3]: 10M triangles, 3840x2160, 256 spp, image tiles over 2/4/8 GPUs
+        sc = pkg.scenes.c4(**({"spp": args.spp} if args.spp != 64 else {}))
+        cfg = {"workload": f"configs[3]: synthetic {len(sc.triangles)}-triangle height-field, {sc.width}x{sc.height}, {sc.sample_count} spp, depth {sc.ray_trace_depth}, "
+                           f"frame seed 0x5EED", "triangles": int(len(sc.triangles)), "width": sc.width, "height": sc.height, "spp": sc.sample_count,
+               "depth": sc.ray_trace_depth, "l2": "BVH + triangle records (~1 GB) exceed L2"}
+        return pkg, sc, cfg
+    if args.config == "c5":      # configs[4]: TLAS with 10k instanced BLAS meshes, incoherent diffuse bounces
+        sc = pkg.scenes.c5(**({"spp": args.spp} if args.spp != 64 else {}))
+        cfg = {"workload": f"configs[4]: {len(sc.instances)} instances of 16 particle meshes ({len(sc.triangles)} triangles), all rough, {sc.width}x{sc.height}, "
+                           f"{sc.sample_count} spp, depth {sc.ray_trace_depth}, frame seed 0x5EED", "instances": int(len(sc.instances)),
+               "width": sc.width, "height": sc.height, "spp": sc.sample_count, "depth": sc.ray_trace_depth, "l2": "working set L2-resident; rays incoherent"}
+        return pkg, sc, cfg
     sc = pkg.scenes.c2(width=args.width, height=args.height, spp=args.spp, depth=args.depth, nx=args.nx, nz=args.nz)
     cfg = {"workload": f"configs[1]: synthetic {len(sc.triangles)}-triangle height-field, {sc.width}x{sc.height}, {sc.sample_count} spp, "
                        f"depth {sc.ray_trace_depth}, rough+metal, camera (0,6,9)->(0,0,0) fov 60, frame seed 0x5EED, XORWOW per-pixel streams",
@@ -395,7 +407,8 @@ def run_ours(args):
         c3 = None
         if world == 1 and not args.no_c3:
             c3 = c3_rebuild(pkg, local)
-        line = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        metric = METRIC if args.config == "c2" else f"Mrays/s ({cfg['workload'].split(',')[0]})"
+        line = {"metric": metric, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": max_dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": {**cfg, "parallelism": f"image tiles ({tile_rows} rows) x{world}, scene replicated, NCCL gather" if world > 1 else "single GPU"},
                 "rays_per_frame": tot_rays / args.steps, "wall_ms_per_step": max_wall_ms / args.steps,
@@ -427,6 +440,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c2", choices=["c2", "c4", "c5"], help="c2 = the bench line (BASELINE configs[1]); c4 / c5 = the other GPU configs, extra lines")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--spp", type=int, default=64)
@@ -442,6 +456,8 @@ def main():
     ap.add_argument("--wavefront", action="store_true", help="comparison mode: wave loop (shade + trace launch per bounce) instead of the persistent path kernel")
     ap.add_argument("--bvh2", action="store_true", help="comparison mode: traverse the binary LBVH instead of the wide BVH")
     args = ap.parse_args()
+    if args.config != "c2":
+        args.no_ref_cuda = args.no_c3 = args.no_cpu_baseline = True
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -101,7 +101,9 @@ def test_c5_instancing_stress(pkg, port):
     assert len(np.unique(g["inst"][g["inst"] >= 0])) > 1000          # thousands of distinct instances are visible
     o = frame(pkg, sc, flags=pkg.abi.FLAG_MEGAKERNEL)
     assert o["out"].rays == g["out"].rays and np.array_equal(o["radiance"], g["radiance"])
-    check_lines_against_oracle(g, port, sc, [100, 540, 900])
+    # interpenetrating instances meet in epsilon-ties (the hit the reference keeps there depends on ITS traversal order, Q1):
+    # enough lines that the 99.99 % bar is a statistic, not one pixel
+    check_lines_against_oracle(g, port, sc, list(range(13, 1080, 27)))
 
 
 def test_c4_ten_million_triangles(pkg):

@@ -367,7 +367,7 @@ def run_ours(args):
             achieved = alg / t_kernel / 1e9
             traffic = None
             tp = os.path.join(ROOT, "profiles", "traffic_latest.json")
-            if os.path.exists(tp):
+            if os.path.exists(tp) and args.config == "c2":      # the committed capture is of the bench workload
                 try:
                     traffic = json.load(open(tp)).get("dram_bytes_per_launch")
                 except Exception:

@@ -223,6 +223,12 @@ int rt_read_framebuffer(rt_ctx *ctx, int kind, void *host_dst, size_t dst_bytes)
 int rt_framebuffer_device_ptr(rt_ctx *ctx, int kind, void **dev_ptr, size_t *bytes);
 /* Write the RGBA8 plane as a binary PPM (top-down, flipped) — the headless "display".              */
 int rt_write_ppm(rt_ctx *ctx, const char *path);
+/* Dump any plane of this context (rt_buffer_kind) to a file — the headless output stage after the path:
+ *   RT_BUFFER_RGBA8    -> binary PPM "P6" (as rt_write_ppm)
+ *   RT_BUFFER_RADIANCE -> PFM "PF" (float RGB, little-endian, rows bottom-up: the plane's own order)
+ *   RT_BUFFER_PRIMARY_T-> PFM "Pf" (one float per pixel, +inf on miss)
+ *   RT_BUFFER_PRIMARY_INSTANCE / _PRIM -> "RTAOV1 <width> <height> <kind>\n" + int32 little-endian per pixel, bottom-up */
+int rt_write_image(rt_ctx *ctx, int kind, const char *path);
 
 /* ---- multi-GPU image-tile sharding ---------------------------------------------------------
  * This context renders only tile rows t with (t % world) == rank, a tile being `tile_rows` scan-lines.

@@ -90,7 +90,7 @@ EXPORTS = [
     "rt_create", "rt_cleanup", "rt_last_error", "rt_version", "rt_struct_size",
     "rt_commit_geometry", "rt_commit_materials", "rt_commit_dielectrics", "rt_configure_instances",
     "rt_build_acceleration_structure", "rt_get_build_stats", "rt_configure_camera",
-    "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm",
+    "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm", "rt_write_image",
     "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame",
     "rt_probe_read_bandwidth",
 ]
@@ -128,6 +128,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_read_framebuffer.argtypes = [vp, i32, vp, sz]
     lib.rt_framebuffer_device_ptr.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(sz)]
     lib.rt_write_ppm.argtypes = [vp, C.c_char_p]
+    lib.rt_write_image.argtypes = [vp, i32, C.c_char_p]
     lib.rt_set_tile_shard.argtypes = [vp, u32, u32, u32, vp]
     lib.rt_read_lbvh.argtypes = [vp, sz, C.POINTER(sz), vp, vp, vp, vp, vp, vp]
     lib.rt_read_wide_bvh.argtypes = [vp, sz, C.POINTER(sz), C.POINTER(sz), vp, vp]

@@ -455,6 +455,29 @@ int rt_write_ppm(rt_ctx *ctx, const char *path) {
     RT_API_END(ctx)
 }
 
+int rt_write_image(rt_ctx *ctx, int kind, const char *path) {
+    if (kind == RT_BUFFER_RGBA8) return rt_write_ppm(ctx, path);
+    RT_API_BEGIN(ctx)
+    if (!ctx->camera_set || !path) return fail(ctx, RT_ERR_STATE, "rt_write_image: no frame");
+    void *p = nullptr;
+    size_t n = 0;
+    const int rc = plane_info(ctx, kind, &p, &n);
+    if (rc != RT_OK) return rc;
+    std::vector<uint8_t> buf(n);
+    CUDA_CHECK(cudaMemcpyAsync(buf.data(), p, n, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    FILE *f = fopen(path, "wb");
+    if (!f) return fail(ctx, RT_ERR_IO, std::string("cannot open ") + path);
+    const uint32_t W = ctx->hs.window.width, H = ctx->local_rows;
+    if (kind == RT_BUFFER_RADIANCE) fprintf(f, "PF\n%u %u\n-1.0\n", W, H);
+    else if (kind == RT_BUFFER_PRIMARY_T) fprintf(f, "Pf\n%u %u\n-1.0\n", W, H);
+    else fprintf(f, "RTAOV1 %u %u %d\n", W, H, kind);
+    const bool ok = fwrite(buf.data(), 1, n, f) == n;
+    fclose(f);
+    if (!ok) return fail(ctx, RT_ERR_IO, std::string("short write to ") + path);
+    RT_API_END(ctx)
+}
+
 int rt_read_lbvh(rt_ctx *ctx, size_t which, size_t *n_prims, uint64_t *sorted_keys, uint32_t *sorted_prim_ids, int32_t *left, int32_t *right,
                  int32_t *parent, float *node_bounds) {
     RT_API_BEGIN(ctx)

@@ -1,5 +1,9 @@
 #include "vtk_reader.h"
 
+#include <climits>
+#include <cstdint>
+#include <thread>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -124,14 +128,39 @@ bool VtkFrame::read(const std::string &path, std::string &err) {
     return true;
 }
 
+// Runs fn(k) for k in [0, n) on up to 8 host threads (contiguous chunks).
+template<class F>
+static void parallel_for(size_t n, bool parallel, F fn) {
+    const unsigned hw = std::thread::hardware_concurrency();
+    const size_t T = parallel ? std::min<size_t>(std::min<size_t>(hw ? hw : 1u, 8u), n) : 1;
+    if (T <= 1) { for (size_t k = 0; k < n; k++) fn(k); return; }
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < T; t++)
+        th.emplace_back([=]() { for (size_t k = n * t / T; k < n * (t + 1) / T; k++) fn(k); });
+    for (std::thread &x: th) x.join();
+}
+
 void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vector<rt_instance_desc> &inst,
                  std::vector<rt_instance_xform> &xforms) {
     const std::vector<double> &P = frame.points;
-    const size_t n_points = P.size() / 3;
+    const size_t n_points = P.size() / 3, n_strips = frame.strips.size();
     std::vector<double> nrm(n_points * 3, 0.0);
+    // strips that share no point (one particle = its own points, the layout of the series) can be converted concurrently
+    bool disjoint = true;
+    {
+        std::vector<std::pair<int, int>> span(n_strips);
+        for (size_t k = 0; k < n_strips; k++) {
+            int lo = INT32_MAX, hi = -1;
+            for (int id: frame.strips[k]) { lo = std::min(lo, id); hi = std::max(hi, id); }
+            span[k] = {lo, hi};
+        }
+        std::sort(span.begin(), span.end());
+        for (size_t k = 1; k < n_strips && disjoint; k++) disjoint = span[k].first > span[k - 1].second;
+    }
     // ---- point normals (restated, parity unpinned) ----
-    for (const std::vector<int> &strip: frame.strips) {
-        if (strip.size() < 3) continue;
+    parallel_for(n_strips, disjoint, [&](size_t k) {
+        const std::vector<int> &strip = frame.strips[k];
+        if (strip.size() < 3) return;
         std::vector<int> uniq(strip);
         std::sort(uniq.begin(), uniq.end());
         uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
@@ -147,42 +176,49 @@ void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vec
             const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
             if (!(len > 0.0)) continue;
             double out = 0.0;
-            for (int k = 0; k < 3; k++) { n[k] /= len; out += n[k] * ((a[k] + b[k] + d[k]) / 3.0 - c[k]); }
+            for (int q = 0; q < 3; q++) { n[q] /= len; out += n[q] * ((a[q] + b[q] + d[q]) / 3.0 - c[q]); }
             const double sgn = out < 0.0 ? -1.0 : 1.0;
-            for (int id: {i0, i1, i2}) for (int k = 0; k < 3; k++) nrm[3 * id + k] += sgn * n[k];
+            for (int id: {i0, i1, i2}) for (int q = 0; q < 3; q++) nrm[3 * id + q] += sgn * n[q];
         }
-    }
+    });
     for (size_t i = 0; i < n_points; i++) {
         double *n = &nrm[3 * i];
         const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
         if (len > 0.0) { n[0] /= len; n[1] /= len; n[2] /= len; }
     }
-    // ---- triangles + instances ----
-    tris.clear();
-    inst.clear();
-    xforms.clear();
+    // ---- triangles + instances (strips shorter than 3 points give nothing, like the serial loop they replace) ----
+    std::vector<size_t> first(n_strips + 1, 0), slot(n_strips + 1, 0);
+    for (size_t k = 0; k < n_strips; k++) {
+        const size_t m = frame.strips[k].size();
+        first[k + 1] = first[k] + (m >= 3 ? m - 2 : 0);
+        slot[k + 1] = slot[k] + (m >= 3 ? 1 : 0);
+    }
+    tris.resize(first[n_strips]);                 // every element is overwritten below; a caller that keeps the vector pays no page faults
+    inst.assign(slot[n_strips], rt_instance_desc{});
+    xforms.assign(slot[n_strips], rt_instance_xform{{0.0f, 4.0f, 0.0f}, {90.0f, 0.0f, 0.0f}, {3.0f, 3.0f, 3.0f}});
     auto vert = [&](int id) { return rt_vec3{(float) P[3 * id], (float) P[3 * id + 1], (float) P[3 * id + 2]}; };
     auto norm = [&](int id) { return rt_vec3{(float) nrm[3 * id], (float) nrm[3 * id + 1], (float) nrm[3 * id + 2]}; };
-    for (const std::vector<int> &strip: frame.strips) {
-        if (strip.size() < 3) continue;
+    parallel_for(n_strips, true, [&](size_t k) {
+        const std::vector<int> &strip = frame.strips[k];
+        if (strip.size() < 3) return;
         rt_instance_desc d{};
         d.type = RT_TRIANGLE;
         d.has_bounds = 1;
-        d.first_prim = tris.size();
+        d.first_prim = first[k];
         d.prim_count = strip.size() - 2;
         double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300}, c[3] = {0, 0, 0};
         for (int id: strip)
             for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], P[3 * id + a]); hi[a] = std::max(hi[a], P[3 * id + a]); c[a] += P[3 * id + a]; }
         for (int a = 0; a < 3; a++) { d.bounds_min[a] = (float) lo[a]; d.bounds_max[a] = (float) hi[a]; d.centroid[a] = (float) (c[a] / (double) strip.size()); }
+        rt_triangle *out = tris.data() + first[k];
         for (size_t j = 0; j + 2 < strip.size(); j++) {
             const int i0 = strip[j], i1 = (j & 1) ? strip[j + 2] : strip[j + 1], i2 = (j & 1) ? strip[j + 1] : strip[j + 2];
             rt_triangle t{};
             t.v[0] = vert(i0); t.v[1] = vert(i1); t.v[2] = vert(i2);
             t.n[0] = norm(i0); t.n[1] = norm(i1); t.n[2] = norm(i2);
             t.material_type = RT_METAL; t.material_index = 0; t.has_normals = 1;
-            tris.push_back(t);
+            out[j] = t;
         }
-        inst.push_back(d);
-        xforms.push_back(rt_instance_xform{{0.0f, 4.0f, 0.0f}, {90.0f, 0.0f, 0.0f}, {3.0f, 3.0f, 3.0f}});
-    }
+        inst[slot[k]] = d;
+    });
 }

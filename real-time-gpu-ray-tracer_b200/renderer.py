@@ -111,6 +111,10 @@ class Renderer:
     def writePPM(self, path: str):
         self._check(self.lib.rt_write_ppm(self.ctx, path.encode()))
 
+    def writeImage(self, kind: int, path: str):
+        """Headless output stage: PPM (RGBA8), PFM (radiance, primary t) or raw int32 AOV dump of a plane."""
+        self._check(self.lib.rt_write_image(self.ctx, kind, path.encode()))
+
     def probeReadBandwidth(self, nbytes: int, repeats: int = 20) -> float:
         """Measurement aid: GB/s of streaming an `nbytes` device buffer `repeats` times (L2-resident when it fits L2)."""
         g = C.c_double(0.0)

@@ -154,3 +154,33 @@ def test_vtk_series_frames(pkg, port, tmp_path):
         rr = pkg.Renderer(device=0)
         rr.configureVTKFiles(str(tmp_path / "missing.series"))
     assert e.value.code == -1
+
+
+def test_output_writers(pkg, tmp_path):
+    """rt_write_image: PPM / PFM / AOV dumps hold exactly the planes rt_read_framebuffer returns."""
+    sc = parity_scenes(pkg.scenes)[0]
+    r = pkg.Renderer(device=0, flags=pkg.abi.FLAG_RECORD_PRIMARY_AOV)
+    try:
+        r.commitScene(sc)
+        r.renderFrame(0, SEED)
+        H, W = sc.height, sc.width
+        for kind, name in [(pkg.abi.BUF_RGBA8, "f.ppm"), (pkg.abi.BUF_RADIANCE, "f.pfm"), (pkg.abi.BUF_PRIMARY_T, "t.pfm"), (pkg.abi.BUF_PRIMARY_PRIM, "p.aov")]:
+            r.writeImage(kind, str(tmp_path / name))
+        rad = r.readFramebuffer(pkg.abi.BUF_RADIANCE).reshape(H, W, 3)
+        raw = (tmp_path / "f.pfm").read_bytes()
+        hdr = f"PF\n{W} {H}\n-1.0\n".encode()
+        assert raw.startswith(hdr) and np.array_equal(np.frombuffer(raw[len(hdr):], np.float32).reshape(H, W, 3), rad)
+        rgba = r.readFramebuffer(pkg.abi.BUF_RGBA8).reshape(H, W, 4)
+        raw = (tmp_path / "f.ppm").read_bytes()
+        hdr = f"P6\n{W} {H}\n255\n".encode()
+        assert raw.startswith(hdr) and np.array_equal(np.frombuffer(raw[len(hdr):], np.uint8).reshape(H, W, 3), rgba[::-1, :, :3])
+        prim = r.readFramebuffer(pkg.abi.BUF_PRIMARY_PRIM).reshape(H, W)
+        raw = (tmp_path / "p.aov").read_bytes()
+        hdr = f"RTAOV1 {W} {H} {pkg.abi.BUF_PRIMARY_PRIM}\n".encode()
+        assert raw.startswith(hdr) and np.array_equal(np.frombuffer(raw[len(hdr):], np.int32).reshape(H, W), prim)
+        t = r.readFramebuffer(pkg.abi.BUF_PRIMARY_T).reshape(H, W)
+        raw = (tmp_path / "t.pfm").read_bytes()
+        hdr = f"Pf\n{W} {H}\n-1.0\n".encode()
+        assert raw.startswith(hdr) and np.array_equal(np.frombuffer(raw[len(hdr):], np.float32).reshape(H, W), t)
+    finally:
+        r.cleanup()

@@ -219,25 +219,31 @@ def c3_rebuild(pkg, device):
     S = pkg.scenes
     fixture = os.path.join(ROOT, "tests", "golden", "particle_frame0.vtk")
     with tempfile.TemporaryDirectory() as tmp:
-        series = S.synth_vtk_series(fixture, tmp, [500, 500, 500])
+        series = S.synth_vtk_series(fixture, tmp, [500] * 6)
         r = pkg.Renderer(device=device)
         r.commitScene(S.c1a(frame=0, width=1920, height=1080, spp=1, depth=10))
         r.configureVTKFiles(series)
-        blas, tlas, wall, frame_ms, rays = [], [], [], [], 0
-        for k in range(3):
+        blas, tlas, wall, frame_ms, loop_ms, rays = [], [], [], [], [], 0
+        r.prefetchVTKFrame(0)
+        for k in range(6):
             t0 = time.perf_counter()
-            st = r.setVTKFrame(k)
+            st = r.setVTKFrame(k)            # takes the frame read ahead by the host thread; commit + upload + rebuild
             wall.append(1e3 * (time.perf_counter() - t0))
+            if k + 1 < 6:
+                r.prefetchVTKFrame(k + 1)    # the next frame is parsed while this one renders
             blas.append(st.blas_ms)
             tlas.append(st.tlas_ms)
             out = r.renderFrame(k, SEED)
             frame_ms.append(out.render_ms)
+            loop_ms.append(1e3 * (time.perf_counter() - t0))
             rays = out.rays
         r.cleanup()
     return {"triangles": int(st.primitive_count), "blas_count": int(st.blas_count), "lbvh_rebuild_ms": min(blas[1:]), "tlas_ms": min(tlas[1:]),
             "build_kernel_launches": int(st.kernel_launches), "achieved_gbs": 280 * st.primitive_count / min(blas[1:]) / 1e6,
-            "parse_upload_rebuild_wall_ms": min(wall[1:]), "render_ms_1080p_1spp": min(frame_ms[1:]), "rays": int(rays),
-            "what": "rt_set_vtk_frame on a 500-particle frame; lbvh_rebuild_ms = CUDA events, triangles resident -> wide BVH ready"}
+            "commit_upload_rebuild_wall_ms": min(wall[1:]), "render_ms_1080p_1spp": min(frame_ms[1:]), "rays": int(rays),
+            "animation_loop_wall_ms_per_frame": statistics.median(loop_ms[2:]),
+            "what": "rt_set_vtk_frame on 500-particle frames with rt_prefetch_vtk_frame reading the next one ahead; lbvh_rebuild_ms = CUDA events, "
+                    "triangles resident -> wide BVH ready; animation_loop = set frame + rebuild + render 1080p, host wall per frame"}
 
 
 def run_ours(args):

@@ -256,6 +256,10 @@ int rt_read_wide_bvh(rt_ctx *ctx, size_t which, size_t *n_nodes, size_t *n_leaf_
  *      src/Global/Renderer.cu:394-443; VTKReader src/Global/VTKReader.cu:16-220) ------------------ */
 int rt_load_vtk_series(rt_ctx *ctx, const char *series_path, size_t *frame_count);
 int rt_set_vtk_frame(rt_ctx *ctx, size_t frame);
+/* Frame-loop overlap (the loop body of Renderer::startRender, src/Global/Renderer.cu:232-338, keeps host preparation of
+ * the next frame beside the GPU's current one): start reading + converting series frame `frame` on a host thread and
+ * return at once; the next rt_set_vtk_frame(frame) takes the result instead of parsing.  One read-ahead at a time.  */
+int rt_prefetch_vtk_frame(rt_ctx *ctx, size_t frame);
 
 /* ---- measurement aid (bench.py roofline denominators; no reference counterpart) ----------------------
  * Streams a device buffer of `bytes` with 128-bit loads from every SM, `repeats` times back to back, and returns

@@ -91,7 +91,7 @@ EXPORTS = [
     "rt_commit_geometry", "rt_commit_materials", "rt_commit_dielectrics", "rt_configure_instances",
     "rt_build_acceleration_structure", "rt_get_build_stats", "rt_configure_camera",
     "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm", "rt_write_image",
-    "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame",
+    "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame", "rt_prefetch_vtk_frame",
     "rt_probe_read_bandwidth",
 ]
 
@@ -134,6 +134,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_read_wide_bvh.argtypes = [vp, sz, C.POINTER(sz), C.POINTER(sz), vp, vp]
     lib.rt_load_vtk_series.argtypes = [vp, C.c_char_p, C.POINTER(sz)]
     lib.rt_set_vtk_frame.argtypes = [vp, sz]
+    lib.rt_prefetch_vtk_frame.argtypes = [vp, sz]
     lib.rt_probe_read_bandwidth.argtypes = [vp, sz, i32, C.POINTER(C.c_double)]
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported

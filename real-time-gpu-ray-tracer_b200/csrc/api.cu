@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstring>
 #include <map>
+#include <thread>
 #include <memory>
 #include <string>
 #include <tuple>
@@ -59,6 +60,30 @@ struct rt_ctx {
     // VTK series: the user's own triangles / instances are kept so that every frame can be recomposed as
     // [VTK triangles | user triangles], [user instances | VTK instances] (reference src/Global/Renderer.cu:17,106-116)
     std::unique_ptr<VtkSeries> vtk;
+    // one parsed + converted series frame.  Two of them: the one being committed and the one a host thread reads ahead
+    // (rt_prefetch_vtk_frame) while the GPU renders; the vectors keep their capacity from frame to frame.
+    struct VtkStage {
+        VtkFrame vf;
+        std::vector<rt_triangle> tris;
+        std::vector<rt_instance_desc> inst;
+        std::vector<rt_instance_xform> xf;
+        size_t frame = (size_t) -1;
+        bool ok = false;
+        std::string err;
+        float parse_ms = 0.0f;
+        std::thread worker;
+        void load(const VtkSeries &series, size_t f) {
+            const auto t0 = std::chrono::steady_clock::now();
+            frame = f;
+            err.clear();
+            ok = vf.read(series.dir + series.files[f].first, err);
+            if (ok) vtk_convert(vf, tris, inst, xf);
+            parse_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        }
+        void join() { if (worker.joinable()) worker.join(); }
+    };
+    VtkStage vtk_stage[2];
+    int vtk_ahead = -1;             // stage a read-ahead is running on / has finished in (-1: none)
     std::vector<rt_triangle> user_tris;
     std::vector<rt_instance_desc> user_inst;
     bool composing = false;
@@ -169,6 +194,7 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
 int rt_cleanup(rt_ctx *ctx) {
     if (!ctx) return RT_ERR_ARGUMENT;
     cudaSetDevice(ctx->device);
+    for (auto &st: ctx->vtk_stage) st.join();
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); }
     for (auto &e: ctx->ev) if (e) cudaEventDestroy(e);
     cudaStream_t s = ctx->stream;
@@ -539,15 +565,21 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
     if (!ctx->vtk) return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: load a series first");
     if (!ctx->geometry_committed || !ctx->instances_configured) return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: commit geometry and instances first");
     if (frame >= ctx->vtk->files.size()) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_vtk_frame: frame out of range");
-    const auto t0 = std::chrono::steady_clock::now();
-    VtkFrame vf;
-    std::string err;
-    if (!vf.read(ctx->vtk->dir + ctx->vtk->files[frame].first, err)) return fail(ctx, RT_ERR_IO, err);
-    std::vector<rt_triangle> tris;
-    std::vector<rt_instance_desc> inst;
-    std::vector<rt_instance_xform> xf;
-    vtk_convert(vf, tris, inst, xf);
-    ctx->vtk_parse_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    // the frame may have been read ahead by rt_prefetch_vtk_frame; otherwise read it now
+    int cur = -1;
+    if (ctx->vtk_ahead >= 0) {
+        ctx->vtk_stage[ctx->vtk_ahead].join();
+        if (ctx->vtk_stage[ctx->vtk_ahead].frame == frame) cur = ctx->vtk_ahead;
+        ctx->vtk_ahead = -1;
+    }
+    if (cur < 0) { cur = 0; ctx->vtk_stage[0].load(*ctx->vtk, frame); }
+    rt_ctx::VtkStage &st = ctx->vtk_stage[cur];
+    if (!st.ok) return fail(ctx, RT_ERR_IO, st.err);
+    ctx->vtk_parse_ms = st.parse_ms;
+    std::vector<rt_triangle> &tris = st.tris;
+    const std::vector<rt_instance_desc> &inst = st.inst;
+    const std::vector<rt_instance_xform> &xf = st.xf;
+    st.frame = (size_t) -1;                                     // consumed (tris gets the user's triangles appended below)
     // compose: VTK triangles at the head of the triangle array, user TRIANGLE instances shifted by their count,
     // VTK instances after the user's (reference src/Global/Renderer.cu:17,106-108,114-116)
     const size_t n_vtk_tris = tris.size();
@@ -565,6 +597,19 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
     if (rc == RT_OK) rc = rt_build_acceleration_structure(ctx);
     ctx->composing = false;
     if (rc != RT_OK) return rc;
+    RT_API_END(ctx)
+}
+
+int rt_prefetch_vtk_frame(rt_ctx *ctx, size_t frame) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->vtk) return fail(ctx, RT_ERR_STATE, "rt_prefetch_vtk_frame: load a series first");
+    if (frame >= ctx->vtk->files.size()) return fail(ctx, RT_ERR_ARGUMENT, "rt_prefetch_vtk_frame: frame out of range");
+    if (ctx->vtk_ahead >= 0) ctx->vtk_stage[ctx->vtk_ahead].join();       // one read-ahead at a time
+    // stage 0 is the one rt_set_vtk_frame reads into when nothing was prefetched; read ahead into stage 1
+    rt_ctx::VtkStage *st = &ctx->vtk_stage[1];
+    const VtkSeries *series = ctx->vtk.get();
+    st->worker = std::thread([st, series, frame]() { st->load(*series, frame); });
+    ctx->vtk_ahead = 1;
     RT_API_END(ctx)
 }
 

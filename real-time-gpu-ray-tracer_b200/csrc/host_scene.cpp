@@ -1,4 +1,5 @@
 #include "host_scene.h"
+#include "host_parallel.h"
 
 #include <algorithm>
 #include <cmath>
@@ -76,7 +77,7 @@ std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_p
     }
     tri_verts.resize(nt * 9);
     tri_shade.resize(nt);
-    for (size_t i = 0; i < nt; i++) {
+    parallel_for(nt, true, [&](size_t i) {
         // Triangle constructors (reference include/Geometry/Triangle.cuh:26-46)
         const rt_triangle &g = t[i];
         float *v = &tri_verts[i * 9];
@@ -90,7 +91,7 @@ std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_p
         tri_shade[i].n0_mt = make_float4(n0.x, n0.y, n0.z, u2f(g.material_type));
         tri_shade[i].n1_mi = make_float4(n1.x, n1.y, n1.z, u2f(g.material_index));
         tri_shade[i].n2 = make_float4(n2.x, n2.y, n2.z, 0.0f);
-    }
+    }, 65536);
     return "";
 }
 

@@ -1,4 +1,5 @@
 #include "vtk_reader.h"
+#include "host_parallel.h"
 
 #include <climits>
 #include <cstdint>
@@ -126,18 +127,6 @@ bool VtkFrame::read(const std::string &path, std::string &err) {
     // reference: cell arrays "id" and "vel" must exist (values are not used downstream)
     if (s.find("SCALARS id ", pos) == std::string::npos || s.find("VECTORS vel ", pos) == std::string::npos) { err = "failed to read cell data (id / vel) in " + path; return false; }
     return true;
-}
-
-// Runs fn(k) for k in [0, n) on up to 8 host threads (contiguous chunks).
-template<class F>
-static void parallel_for(size_t n, bool parallel, F fn) {
-    const unsigned hw = std::thread::hardware_concurrency();
-    const size_t T = parallel ? std::min<size_t>(std::min<size_t>(hw ? hw : 1u, 8u), n) : 1;
-    if (T <= 1) { for (size_t k = 0; k < n; k++) fn(k); return; }
-    std::vector<std::thread> th;
-    for (size_t t = 0; t < T; t++)
-        th.emplace_back([=]() { for (size_t k = n * t / T; k < n * (t + 1) / T; k++) fn(k); });
-    for (std::thread &x: th) x.join();
 }
 
 void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vector<rt_instance_desc> &inst,

@@ -155,6 +155,10 @@ class Renderer:
         self._check(self.lib.rt_get_build_stats(self.ctx, C.byref(st)))
         return st
 
+    def prefetchVTKFrame(self, frame: int):
+        """Read + convert a series frame on a host thread while the GPU renders; the next setVTKFrame(frame) picks it up."""
+        self._check(self.lib.rt_prefetch_vtk_frame(self.ctx, frame))
+
     # -- Renderer::cleanup -----------------------------------------------------------------------
     def cleanup(self):
         if self.ctx:

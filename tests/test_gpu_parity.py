@@ -137,6 +137,8 @@ def test_vtk_series_frames(pkg, port, tmp_path):
         r.commitScene(base)
         assert r.configureVTKFiles(series) == 2
         for k, name in enumerate(["particle_mesh/particle_000000000000000.vtk", "particle_mesh/particle_000000000000100.vtk"]):
+            if k == 1:
+                r.prefetchVTKFrame(1)       # read ahead on a host thread: setVTKFrame(1) must take that result
             st = r.setVTKFrame(k)
             sc = S.c3(os.path.join(str(tmp_path), name), frame=12, width=160, height=90, spp=1, depth=10)
             assert st.primitive_count == len(sc.triangles) - 1 + 4           # particle triangles + the four distinct single-primitive BLASes of the demo scene

@@ -262,7 +262,7 @@ def run_ours(args):
     pkg, sc, cfg = workload(args)
     abi = pkg.abi
 
-    base_flags = (abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0) | (abi.FLAG_MEGAKERNEL if args.megakernel else 0) | (abi.FLAG_WAVEFRONT if args.wavefront else 0)
+    base_flags = (abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0) | (abi.FLAG_MEGAKERNEL if args.megakernel else 0) | (abi.FLAG_WAVEFRONT if args.wavefront else 0) | (abi.FLAG_SAH_REFINE if args.sah else 0)
     r = pkg.Renderer(device=local, flags=base_flags)
     t0 = time.perf_counter()
     st = r.commitScene(sc)
@@ -460,6 +460,7 @@ def main():
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 particle rebuild measurement")
     ap.add_argument("--megakernel", action="store_true", help="comparison mode: one thread per pixel (the reference's kernel structure)")
     ap.add_argument("--wavefront", action="store_true", help="comparison mode: wave loop (shade + trace launch per bounce) instead of the persistent path kernel")
+    ap.add_argument("--sah", action="store_true", help="optional SAH refinement of the LBVH (tree rotations in the refit)")
     ap.add_argument("--bvh2", action="store_true", help="comparison mode: traverse the binary LBVH instead of the wide BVH")
     args = ap.parse_args()
     if args.config != "c2":

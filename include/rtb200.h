@@ -134,7 +134,10 @@ enum rt_flags {
     RT_FLAG_MEGAKERNEL              = 1u << 5,
     /* Comparison mode: the wave loop (one shade/generate + one trace launch per bounce of all paths, ray queues in
      * between) instead of the default single persistent launch that fuses both (kernels_persist.cu).                */
-    RT_FLAG_WAVEFRONT               = 1u << 6
+    RT_FLAG_WAVEFRONT               = 1u << 6,
+    /* Optional SAH refinement of the LBVH: one tree rotation per node, applied bottom-up inside the refit (measured:
+     * -1.5 % node visits on config 2, +0.3 ms build per 629 k triangles — off by default).                          */
+    RT_FLAG_SAH_REFINE              = 1u << 7
 };
 
 typedef struct rt_frame_out {

@@ -26,6 +26,7 @@ FLAG_COUNT_TRAVERSAL = 1 << 3
 FLAG_TRAVERSE_BVH2 = 1 << 4
 FLAG_MEGAKERNEL = 1 << 5
 FLAG_WAVEFRONT = 1 << 6
+FLAG_SAH_REFINE = 1 << 7
 
 BUF_RGBA8, BUF_RADIANCE, BUF_PRIMARY_T, BUF_PRIMARY_INSTANCE, BUF_PRIMARY_PRIM = range(5)
 

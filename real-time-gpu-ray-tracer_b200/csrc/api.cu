@@ -276,6 +276,8 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     const GeometryD geo{ctx->d_tri_verts.get(), ctx->d_spheres.get(), ctx->d_quads.get()};
     const size_t n_prims = hs.seg_offset.back();
     ctx->blas.emit_bvh2 = ctx->tlas.emit_bvh2 = (ctx->flags & (RT_FLAG_TRAVERSE_BVH2 | RT_FLAG_KEEP_LBVH)) != 0;
+    // rotated subtrees no longer cover one contiguous Morton range, which multi-primitive leaves (a tuning experiment) rely on
+    ctx->blas.sah_rotations = ctx->tlas.sah_rotations = (ctx->flags & RT_FLAG_SAH_REFINE) && !getenv("RTB200_LEAF_MAX");
     ctx->blas.prepare_blas(hs.seg_offset, hs.seg_type);          // allocations stay outside the timed build
     ctx->d_instances.reserve(n_inst);
     ctx->d_xform_in.reserve(n_inst);

@@ -37,6 +37,7 @@ public:
     // ---- TLAS: one segment over instance world boxes already written to prim_lo()/prim_hi() and bounds() --
     void prepare_blas(const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type);   // allocations only
     void prepare_tlas(int n_instances);
+    bool sah_rotations = false;              // optional SAH refinement (RT_FLAG_SAH_REFINE): one tree rotation per node inside the refit (rt_build_core.h best_rotation)
     bool emit_bvh2 = false;                  // also emit the 64-byte binary nodes + their leaf-order records (RT_FLAG_TRAVERSE_BVH2)
     void build_tlas(int n_instances, int morton_bits, cudaStream_t stream, int sm_count);
 

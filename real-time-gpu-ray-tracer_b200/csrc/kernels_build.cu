@@ -165,7 +165,33 @@ __global__ void __launch_bounds__(BT) single_prim_roots_kernel(const uint32_t *_
     }
 }
 
-// K4: bottom-up refit; the second child to arrive at a node computes its box
+// K4: bottom-up refit; the second child to arrive at a node computes its box.  refit_rotate_kernel (RT_FLAG_SAH_REFINE)
+// first tries one SAH tree rotation at the node (best_rotation, rt_build_core.h).  The arriving thread is the only one active in
+// the node's subtree (everything below is finished, nothing above has started), so rewriting the node's children and
+// one child's record is race-free.  Nodes that span several segments (the junk above the BLAS roots) never rotate.
+struct RefitChild { Aabb box; int kl, kr; };
+__device__ __forceinline__ RefitChild refit_load(int c, const float4 *prim_lo, const float4 *prim_hi, const uint32_t *vals,
+                                                 const float4 *node_lo, const float4 *node_hi) {
+    RefitChild r;
+    float4 lo, hi;
+    if (c >= 0) { lo = __ldcg(&node_lo[c]); hi = __ldcg(&node_hi[c]); r.kl = __float_as_int(lo.w); r.kr = __float_as_int(hi.w); }
+    else { const uint32_t p = vals[~c]; lo = prim_lo[p]; hi = prim_hi[p]; r.kl = 0; r.kr = 0; }
+    r.box.lo = mk3(lo.x, lo.y, lo.z);
+    r.box.hi = mk3(hi.x, hi.y, hi.z);
+    return r;
+}
+__device__ __forceinline__ void refit_store(int node, const Aabb &b, int l, int r, float4 *node_lo, float4 *node_hi, int *left, int *right) {
+    // .w carries the node's children so the wide collapse gets box + children in one pair of loads
+    __stcg(&node_lo[node], make_float4(b.lo.x, b.lo.y, b.lo.z, __int_as_float(l)));
+    __stcg(&node_hi[node], make_float4(b.hi.x, b.hi.y, b.hi.z, __int_as_float(r)));
+    left[node] = l;
+    right[node] = r;
+}
+__device__ __forceinline__ void refit_set_parent(int child, int p, int *parent, int *leaf_parent) {
+    if (child >= 0) parent[child] = p; else leaf_parent[~child] = p;
+}
+
+// The plain refit (the default): no rotation, children as Karras made them.
 __global__ void __launch_bounds__(BT) refit_kernel(const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi, const uint32_t *__restrict__ vals,
                                                    const int *__restrict__ left, const int *__restrict__ right, const int *__restrict__ parent,
                                                    const int *__restrict__ leaf_parent, int n, int *flags, float4 *node_lo, float4 *node_hi) {
@@ -184,6 +210,55 @@ __global__ void __launch_bounds__(BT) refit_kernel(const float4 *__restrict__ pr
         __stcg(&node_lo[cur], make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), __int_as_float(l)));
         __stcg(&node_hi[cur], make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), __int_as_float(r)));
         cur = parent[cur];
+    }
+}
+
+__global__ void __launch_bounds__(BT) refit_rotate_kernel(const float4 *__restrict__ prim_lo, const float4 *__restrict__ prim_hi, const uint32_t *__restrict__ vals,
+                                                   int *left, int *right, int *parent, int *leaf_parent, int n, int *flags,
+                                                   float4 *node_lo, float4 *node_hi, const int2 *__restrict__ range,
+                                                   const uint32_t *__restrict__ seg_offset, int n_segs, int rotate) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    int cur = leaf_parent[pos];
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(&flags[cur], 1) == 0) return;
+        __threadfence();
+        int l = __ldcg(&left[cur]), r = __ldcg(&right[cur]);
+        RefitChild L = refit_load(l, prim_lo, prim_hi, vals, node_lo, node_hi);
+        RefitChild R = refit_load(r, prim_lo, prim_hi, vals, node_lo, node_hi);
+        const int up = __ldcg(&parent[cur]);
+        bool may = rotate != 0 && (l >= 0 || r >= 0);
+        if (may && n_segs > 1) {
+            const int2 rg = range[cur];
+            may = find_segment(seg_offset, n_segs, (uint32_t) rg.x) == find_segment(seg_offset, n_segs, (uint32_t) rg.y);
+        }
+        if (may) {
+            RefitChild LL{}, LR{}, RL{}, RR{};
+            if (l >= 0) { LL = refit_load(L.kl, prim_lo, prim_hi, vals, node_lo, node_hi); LR = refit_load(L.kr, prim_lo, prim_hi, vals, node_lo, node_hi); }
+            if (r >= 0) { RL = refit_load(R.kl, prim_lo, prim_hi, vals, node_lo, node_hi); RR = refit_load(R.kr, prim_lo, prim_hi, vals, node_lo, node_hi); }
+            Aabb nb;
+            const int rot = best_rotation(L.box, R.box, l >= 0, LL.box, LR.box, r >= 0, RL.box, RR.box, nb);
+            if (rot == 1) {            // R <-> LL : L = (R, LR), N = (L, LL)
+                refit_store(l, nb, r, L.kr, node_lo, node_hi, left, right);
+                refit_set_parent(r, l, parent, leaf_parent); refit_set_parent(L.kl, cur, parent, leaf_parent);
+                r = L.kl; L.box = nb; R.box = LL.box;
+            } else if (rot == 2) {     // R <-> LR : L = (LL, R), N = (L, LR)
+                refit_store(l, nb, L.kl, r, node_lo, node_hi, left, right);
+                refit_set_parent(r, l, parent, leaf_parent); refit_set_parent(L.kr, cur, parent, leaf_parent);
+                r = L.kr; L.box = nb; R.box = LR.box;
+            } else if (rot == 3) {     // L <-> RL : R = (L, RR), N = (RL, R)
+                refit_store(r, nb, l, R.kr, node_lo, node_hi, left, right);
+                refit_set_parent(l, r, parent, leaf_parent); refit_set_parent(R.kl, cur, parent, leaf_parent);
+                l = R.kl; R.box = nb; L.box = RL.box;
+            } else if (rot == 4) {     // L <-> RR : R = (RL, L), N = (RR, R)
+                refit_store(r, nb, R.kl, l, node_lo, node_hi, left, right);
+                refit_set_parent(l, r, parent, leaf_parent); refit_set_parent(R.kr, cur, parent, leaf_parent);
+                l = R.kr; R.box = nb; L.box = RR.box;
+            }
+        }
+        refit_store(cur, aabb_union(L.box, R.box), l, r, node_lo, node_hi, left, right);
+        cur = up;
     }
 }
 
@@ -304,8 +379,13 @@ void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const
         CUDA_CHECK(cudaMemsetAsync(flags_.get(), 0, (size_t) (n - 1) * sizeof(int), stream));
         karras_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(keys_, n, seg_offset_.get(), n_segs, left_.get(), right_.get(), parent_.get(),
                                                            leaf_parent_.get(), seg_root_.get(), range_.get());
-        refit_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(), parent_.get(),
-                                                      leaf_parent_.get(), n, flags_.get(), node_lo_.get(), node_hi_.get());
+        if (sah_rotations)
+            refit_rotate_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(), parent_.get(),
+                                                                 leaf_parent_.get(), n, flags_.get(), node_lo_.get(), node_hi_.get(), range_.get(),
+                                                                 seg_offset_.get(), n_segs, 1);
+        else
+            refit_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(), parent_.get(),
+                                                          leaf_parent_.get(), n, flags_.get(), node_lo_.get(), node_hi_.get());
         launches += 2;
         if (emit_bvh2) {
             emit_nodes_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(),

@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
             f3 thr = mk3(1.f, 1.f, 1.f);
             uint32_t sample = 0, depth = 0, pix_rays = 0;
             bool need_pixel = shading && fresh;
-            bool need_primary = false, emit = false, acc_dirty = false;
+            bool need_primary = false, acc_dirty = false;
             if (shading && !fresh) {
                 acc = pb.acc[slot];
                 pid = __float_as_uint(acc.w);
@@ -159,9 +159,7 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 }
                 const bool alive = shade_scatter<true>(sc, cam, ray, hit, thr, rng);
                 depth++;
-                if (alive && depth < cam.depth) {
-                    emit = true;
-                } else {
+                if (!(alive && depth < cam.depth)) {
                     // path over: rayColor returns the throughput (Q6); next sample or next pixel
                     acc.x += thr.x; acc.y += thr.y; acc.z += thr.z;
                     acc_dirty = true;
@@ -217,10 +215,9 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                     ray = primary_ray(cam, lx, global_row(fr, ly), si, sj, rng);
                     thr = mk3(1.f, 1.f, 1.f);
                     depth = 0;
-                    emit = true;
                 }
                 if (acc_dirty) pb.acc[slot] = acc;
-                // emit is true here: the lane starts its next ray
+                // every lane that is still alive here starts a ray: the path's next segment or a new primary ray
                 pb.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(pix_rays + 1u));
                 pb.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
                 pb.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float((sample << 16) | depth));
@@ -235,7 +232,6 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 state = ST_TRACE;
                 rays++;
             }
-            (void) emit;
         }
     }
 

@@ -14,6 +14,39 @@ RT_HD Aabb aabb_union(const Aabb &a, const Aabb &b) {
     r.hi = mk3(rt_max(a.hi.x, b.hi.x), rt_max(a.hi.y, b.hi.y), rt_max(a.hi.z, b.hi.z));
     return r;
 }
+RT_HD float aabb_half_area(const Aabb &b) {
+    const float dx = b.hi.x - b.lo.x, dy = b.hi.y - b.lo.y, dz = b.hi.z - b.lo.z;
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// ---- SAH refinement of the binary LBVH: one tree rotation per node, applied bottom-up inside the refit ---------
+// (Kensler 2008 / Kopta et al. 2012.)  At node N = (L, R) with finished subtrees, a grandchild may trade places with
+// its uncle: N = ((LL, LR), R) -> ((R, LR), LL) etc.  N's box and leaf set stay, only the box of the inner child
+// changes, and with it the surface-area cost of the tree.  The rotation with the largest area reduction is taken
+// (first candidate wins ties).  The decision depends only on N's subtree, which is final when the refit reaches N,
+// so the result is the same for any bottom-up order — the atomic GPU refit and the serial twin agree bit for bit.
+// Returns 0: none, 1: R <-> LL, 2: R <-> LR, 3: L <-> RL, 4: L <-> RR; new_inner = the changed child's new box.
+RT_HD int best_rotation(const Aabb &L, const Aabb &R, bool l_inner, const Aabb &LL, const Aabb &LR,
+                        bool r_inner, const Aabb &RL, const Aabb &RR, Aabb &new_inner) {
+    int best = 0;
+    float gain = 0.0f;
+    if (l_inner) {
+        const float cur = aabb_half_area(L);
+        const Aabb a = aabb_union(R, LR), b = aabb_union(R, LL);
+        const float ga = cur - aabb_half_area(a), gb = cur - aabb_half_area(b);
+        if (ga > gain) { gain = ga; best = 1; new_inner = a; }
+        if (gb > gain) { gain = gb; best = 2; new_inner = b; }
+    }
+    if (r_inner) {
+        const float cur = aabb_half_area(R);
+        const Aabb a = aabb_union(L, RR), b = aabb_union(L, RL);
+        const float ga = cur - aabb_half_area(a), gb = cur - aabb_half_area(b);
+        if (ga > gain) { gain = ga; best = 3; new_inner = a; }
+        if (gb > gain) { gain = gb; best = 4; new_inner = b; }
+    }
+    return best;
+}
+
 // Conservative padding so that the fma-based slab test can never cull a true hit on the box surface.
 // The reference pads only degenerate axes by 1e-6 (ensureVolume, include/AS/BoundingBox.cuh:24-28).
 RT_HD Aabb aabb_pad(const Aabb &a) {

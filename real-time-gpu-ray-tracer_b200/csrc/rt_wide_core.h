@@ -46,10 +46,6 @@ struct BinaryTreeView {
     const uint32_t *vals;               // Morton position -> build primitive
 };
 
-RT_HD float aabb_half_area(const Aabb &b) {
-    const float dx = b.hi.x - b.lo.x, dy = b.hi.y - b.lo.y, dz = b.hi.z - b.lo.z;
-    return dx * dy + dy * dz + dz * dx;
-}
 RT_HD Aabb view_box(const float4 *lo, const float4 *hi, int i) {
     const float4 a = lo[i], b = hi[i];
     Aabb r;

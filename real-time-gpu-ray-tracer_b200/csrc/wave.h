@@ -45,11 +45,11 @@ public:
     uint32_t slots_override = 0;   // 0 = default
     int mode = 0;                  // 0: binary LBVH traversal, 1: compressed 8-wide
     int refill_min = 8;            // lanes of a warp that must be idle before the warp pulls new rays
-    int node_min = 20;
+    int node_min = 20;             // the node phase of a warp ends when fewer lanes than this stand on an inner node
     bool use_graphs = true;        // replay each group's wave batch as a CUDA graph
     int finish_divisor = 24;       // a group whose last wave had <= n_slots / finish_divisor rays is finished by wave_finish_kernel (0: never)
     int n_groups = 8;              // slot groups whose wave sequences run concurrently on their own streams
-    int blocks_per_sm_override = 0; // > 0: cap the resident trace blocks per SM (tuning)             // the node phase of a warp ends when fewer lanes than this stand on an inner node
+    int blocks_per_sm_override = 0; // > 0: cap the resident trace blocks per SM (tuning)
 private:
     void reserve(uint32_t n_slots);
     DeviceBuffer<float4> ray_o_, ray_d_, hit_, thr_, acc_;

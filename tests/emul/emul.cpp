@@ -48,7 +48,7 @@ int find_segment(const std::vector<uint32_t> &off, uint32_t j) {
 }
 
 // serial twin of LbvhBuilder::run_tree
-void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type, int leaf_mode) {
+void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type, int leaf_mode, bool rotate) {
     const int n = b.n;
     const int n_segs = (int) seg_type.size();
     std::vector<uint32_t> order(n);
@@ -84,7 +84,23 @@ void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vec
             const int l = b.left[i], r = b.right[i];
             const bool lready = l < 0 || done[l], rready = r < 0 || done[r];
             if (lready && rready) {
-                b.node_box[i] = aabb_union(child_box(l), child_box(r));
+                // SAH rotation at node i (same decision function as the device refit, kernels_build.cu refit_kernel)
+                int L = l, R = r;
+                bool may = rotate && (L >= 0 || R >= 0);
+                if (may) may = find_segment(seg_offset, (uint32_t) b.range[i].x) == find_segment(seg_offset, (uint32_t) b.range[i].y);
+                if (may) {
+                    Aabb z{}, nb{};
+                    const Aabb LL = L >= 0 ? child_box(b.left[L]) : z, LR = L >= 0 ? child_box(b.right[L]) : z;
+                    const Aabb RL = R >= 0 ? child_box(b.left[R]) : z, RR = R >= 0 ? child_box(b.right[R]) : z;
+                    const int rot = best_rotation(child_box(L), child_box(R), L >= 0, LL, LR, R >= 0, RL, RR, nb);
+                    auto set_parent = [&](int c, int p) { if (c >= 0) b.parent[c] = p; else b.leaf_parent[~c] = p; };
+                    if (rot == 1) { const int ll = b.left[L]; b.left[L] = R; b.node_box[L] = nb; set_parent(R, L); set_parent(ll, i); R = ll; }
+                    else if (rot == 2) { const int lr = b.right[L]; b.right[L] = R; b.node_box[L] = nb; set_parent(R, L); set_parent(lr, i); R = lr; }
+                    else if (rot == 3) { const int rl = b.left[R]; b.left[R] = L; b.node_box[R] = nb; set_parent(L, R); set_parent(rl, i); L = rl; }
+                    else if (rot == 4) { const int rr = b.right[R]; b.right[R] = L; b.node_box[R] = nb; set_parent(L, R); set_parent(rr, i); L = rr; }
+                    b.left[i] = L; b.right[i] = R;
+                }
+                b.node_box[i] = aabb_union(child_box(L), child_box(R));
                 done[i] = 1;
                 st.pop_back();
             } else {
@@ -204,7 +220,7 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
         const int seg = find_segment(hs.seg_offset, (uint32_t) j);
         b.keys[j] = ((uint64_t) seg << (3 * bits)) | morton_code(b.prim_box[j], seg_bounds[seg], bits);
     }
-    build_tree(b, hs.seg_offset, hs.seg_type, 0);
+    build_tree(b, hs.seg_offset, hs.seg_type, 0, (hs.flags & RT_FLAG_SAH_REFINE) != 0);
     e->leaf_prims.resize(n);
     e->leaf_tris.resize(n);
     for (int pos = 0; pos < n; pos++) {
@@ -245,7 +261,7 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     t.keys.resize(ni);
     for (int i = 0; i < ni; i++) t.keys[i] = morton_code(t.prim_box[i], scene, tbits);
     const std::vector<uint32_t> toff{0u, (uint32_t) ni}, ttype{0u};
-    build_tree(t, toff, ttype, 1);
+    build_tree(t, toff, ttype, 1, (hs.flags & RT_FLAG_SAH_REFINE) != 0);
     collapse_wide(t, toff, 1);
     e->tlas_leaf_inst.resize(ni);
     for (int q = 0; q < ni; q++) e->tlas_leaf_inst[q] = t.vals[t.leaf_pos8[q]];

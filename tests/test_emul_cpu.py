@@ -28,10 +28,11 @@ def test_cores_match_oracle(pkg, port, idx):
     assert np.array_equal(cam_e[keep], cam_o[keep])
 
 
+@pytest.mark.parametrize("flags", [0, 1 << 7])     # plain Karras LBVH / RT_FLAG_SAH_REFINE (tree rotations in the refit)
 @pytest.mark.parametrize("idx", [0, 2, 3, 4])
-def test_lbvh_invariants(pkg, idx):
+def test_lbvh_invariants(pkg, idx, flags):
     sc = parity_scenes(pkg.scenes)[idx]
-    e = ec.Emul(sc)
+    e = ec.Emul(sc, flags)
     for which in (0, 1):
         b = e.lbvh(which)
         n = len(b["keys"])

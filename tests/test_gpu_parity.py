@@ -186,3 +186,22 @@ def test_output_writers(pkg, tmp_path):
         assert raw.startswith(hdr) and np.array_equal(np.frombuffer(raw[len(hdr):], np.float32).reshape(H, W), t)
     finally:
         r.cleanup()
+
+
+@pytest.mark.parametrize("idx", [0, 3, 4, 5])
+def test_sah_refinement(pkg, port, idx):
+    """RT_FLAG_SAH_REFINE: the rotated tree is the one the serial twin makes (binary and wide), and the frame still
+    matches the oracle (the closest hit does not depend on the topology)."""
+    import emul_ctypes as ec
+    sc = parity_scenes(pkg.scenes)[idx]
+    g = gpu_frame(pkg, sc, flags=pkg.abi.FLAG_SAH_REFINE | pkg.abi.FLAG_KEEP_LBVH)
+    e = ec.Emul(sc, pkg.abi.FLAG_SAH_REFINE)
+    for which, key in ((0, "lbvh"), (1, "tlas")):
+        twin = e.lbvh(which)
+        for name in ("keys", "prim_ids", "left", "right", "parent", "bounds"):
+            assert np.array_equal(g[key][name], twin[name]), f"{sc.name}: {key}.{name} differs from the CPU twin"
+    plain = ec.Emul(sc).lbvh(0)
+    if len(plain["left"]) > 64:
+        assert not np.array_equal(plain["left"], g["lbvh"]["left"]), "no rotation was applied"
+    assert sorted(g["wide"][1].tolist()) == sorted(e.wide(0)[1].tolist())
+    check_against_oracle(g, port.scene(sc, 5), sc)

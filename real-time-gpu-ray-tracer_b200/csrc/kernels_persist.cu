@@ -28,6 +28,14 @@ constexpr uint32_t NG_INNER = 0x00FFFFFFu;      // node group has pending inner 
 #ifndef RT_PERSIST_MIN_BLOCKS
 #define RT_PERSIST_MIN_BLOCKS 6   /* 80 registers: no spills; measured faster than 8 blocks x 64 registers */
 #endif
+// Shared-memory staging of the top BVH levels (north_star): the first RT_STAGE_TOP_NODES records of the BLAS node pool
+// (the collapse allocates breadth-first, so these are the roots and the levels right below them) are copied into
+// shared memory by every CTA and node steps read them from there.  Measured on C2 (profiles/r01h_stage_top_nodes.txt):
+// no gain — those records are the ones that already hit in L1 (L1 hit rate 49 % of all sectors) — so it is compiled
+// out by default (0); the variant build is `make VARIANT=stage EXTRA=-DRT_STAGE_TOP_NODES=96`.
+#ifndef RT_STAGE_TOP_NODES
+#define RT_STAGE_TOP_NODES 0
+#endif
 enum : uint32_t { ST_DEAD = 0u, ST_TRACE = 1u, ST_SHADE = 2u, ST_FRESH = 3u };
 template<bool COUNT>
 __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
@@ -35,6 +43,12 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                                                                             int shade_min, int node_min) {
     __shared__ uint2 stack_mem[RT_WIDE_STACK * PT];
     uint2 *const stk = stack_mem + threadIdx.x;               // entry k at stk[k * PT]
+#if RT_STAGE_TOP_NODES > 0
+    __shared__ uint4 top_nodes[RT_STAGE_TOP_NODES * 5];
+    const uint32_t n_top = min((uint32_t) RT_STAGE_TOP_NODES, pb.n_blas_nodes);
+    for (uint32_t i = threadIdx.x; i < n_top * 5u; i += PT) top_nodes[i] = __ldg(reinterpret_cast<const uint4 *>(sc.blas_nodes8) + i);
+    __syncthreads();
+#endif
     const uint32_t tid = blockIdx.x * PT + threadIdx.x;
     const uint32_t slot = tid;                                // path-state entry of this lane
     uint32_t state = ST_FRESH;
@@ -89,7 +103,19 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 }
                 const uint32_t sl = ((uint32_t) bit - 24u) ^ (r.oct_inv4 & 0xFFu);
                 const uint32_t rel = (uint32_t) __popc(hits_imask & ~(0xFFFFFFFFu << sl));
+#if RT_STAGE_TOP_NODES > 0
+                BvhNode8 n;
+                if (inst >= 0 && base + rel < n_top) {
+                    const uint4 *q = top_nodes + (base + rel) * 5u;
+                    const uint4 a = q[0];
+                    n.n0 = make_float4(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z), __uint_as_float(a.w));
+                    n.n1 = q[1]; n.n2 = q[2]; n.n3 = q[3]; n.n4 = q[4];
+                } else {
+                    n = load_node8(inst < 0 ? sc.tlas_nodes8 : sc.blas_nodes8, base + rel);
+                }
+#else
                 const BvhNode8 n = load_node8(inst < 0 ? sc.tlas_nodes8 : sc.blas_nodes8, base + rel);
+#endif
                 if (COUNT) stats.nodes++;
                 const uint32_t hm = node8_intersect(n, r, RT_TMIN, hit.tc);
                 ng.x = n.n1.x;
@@ -321,6 +347,7 @@ void PersistRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD 
     pb.ray_o = ray_o_.get(); pb.ray_d = ray_d_.get(); pb.thr = thr_.get(); pb.acc = acc_.get();
     pb.rng_a = rng_a_.get(); pb.rng_b = rng_b_.get(); pb.next_pixel = counter_.get();
     pb.tile_order = vals; pb.tile_cost = tile_cost_.get();
+    pb.n_blas_nodes = n_blas_nodes;
     CUDA_CHECK(cudaMemsetAsync(counter_.get(), 0, sizeof(uint32_t), stream));
     if (count) persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
     else persist8_kernel<false><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);

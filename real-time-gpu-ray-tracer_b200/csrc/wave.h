@@ -84,6 +84,7 @@ struct PersistBuffers {
     uint32_t *tile_cost;     // rays traced per tile in this frame (orders the next frame)
     uint32_t n_pixels;       // tiles * 32
     uint32_t n_tiles, tiles_x;
+    uint32_t n_blas_nodes;   // records in the BLAS node pool (bounds the shared-memory staging variant)
 };
 
 class PersistRenderer {
@@ -95,6 +96,7 @@ public:
     int blocks_per_sm_override = 0;
     int tile_order = 1;            // 1: dear tiles first (cost = rays of the previous frame), 0: always scan order
     uint32_t launches = 0;         // kernels launched by the last render()
+    uint32_t n_blas_nodes = 0;     // set by the caller: size of the BLAS wide-node pool
 private:
     DeviceBuffer<float4> ray_o_, ray_d_, thr_, acc_;
     DeviceBuffer<uint4> rng_a_;

@@ -137,7 +137,7 @@ void update_instances_and_tlas(rt_ctx *c) {
     c->hs.fill_xform_in(c->h_xform_in.get(), c->blas.seg_root_host);
     CUDA_CHECK(cudaMemcpyAsync(c->d_xform_in.get(), c->h_xform_in.get(), (size_t) n * sizeof(InstanceXformIn), cudaMemcpyHostToDevice, c->stream));
     launch_instance_update(c->d_xform_in.get(), n, c->d_instances.get(), c->tlas.prim_lo(), c->tlas.prim_hi(), c->d_wcentroid.get(),
-                           c->tlas.bounds(), c->stream);
+                           c->tlas.bounds(), c->d_tri_verts.get(), c->stream);
     c->tlas.build_tlas(n, morton_bits_for((size_t) n), c->stream, c->sm_count);
 }
 
@@ -413,7 +413,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
         CUDA_CHECK(cudaEventElapsedTime(&out->tlas_ms, ctx->ev[0], ctx->ev[1]));
         CUDA_CHECK(cudaEventElapsedTime(&out->rng_ms, ctx->ev[1], ctx->ev[2]));
         CUDA_CHECK(cudaEventElapsedTime(&out->trace_ms, ctx->ev[2], ctx->ev[3]));
-        out->kernel_launches = ctx->tlas.launches + 2 /*instance update*/ + 1 /*rng*/ + (mega ? 1 : ws.launches);
+        out->kernel_launches = ctx->tlas.launches + 3 /*instance update: bounds init, matrices, world boxes*/ + 1 /*rng*/ + (mega ? 1 : ws.launches);
     }
     RT_API_END(ctx)
 }

@@ -97,4 +97,4 @@ private:
 // per-frame instance update (device restatement of Instance::updateTransformArguments); writes InstanceD
 // records plus the TLAS builder's prim boxes and scene bounds.
 void launch_instance_update(const InstanceXformIn *in, int n, InstanceD *out, float4 *wlo, float4 *whi, float4 *wcentroid,
-                            uint32_t *bounds, cudaStream_t stream);
+                            uint32_t *bounds, const float *tri_verts, cudaStream_t stream);

@@ -252,6 +252,10 @@ void HostScene::fill_xform_in(InstanceXformIn *out, const std::vector<int> &seg_
         o.blas = inst_blas[i];
         o.root8 = inst_blas[i];                 // the wide root of BLAS s is wide node s (kernels_wide.cu)
         o.prim_type = (int) inst_desc[i].type;
+        const bool rotated = o.trig[1] != 0.0f || o.trig[3] != 0.0f || o.trig[5] != 0.0f;      // unrotated: the 8-corner box is exact
+        const bool tight = inst_desc[i].type == RT_TRIANGLE && rotated && inst_desc[i].prim_count >= 2 && inst_desc[i].prim_count <= RT_TIGHT_BOUNDS_MAX_TRIS;
+        o.tri_first = tight ? (int) inst_desc[i].first_prim : 0;
+        o.tri_count = tight ? (int) inst_desc[i].prim_count : 0;
     }
 }
 

@@ -327,8 +327,7 @@ __global__ void __launch_bounds__(BT) emit_leaves_kernel(GeometryD geo, const ui
 }
 
 __global__ void __launch_bounds__(BT) instance_update_kernel(const InstanceXformIn *__restrict__ in, int n, InstanceD *__restrict__ out,
-                                                             float4 *__restrict__ wlo, float4 *__restrict__ whi, float4 *__restrict__ wcentroid,
-                                                             uint32_t *bounds) {
+                                                             float4 *__restrict__ wlo, float4 *__restrict__ whi, float4 *__restrict__ wcentroid) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     InstanceD o;
@@ -336,20 +335,55 @@ __global__ void __launch_bounds__(BT) instance_update_kernel(const InstanceXform
     f3 c;
     instance_update(in[i], o, box, c);
     out[i] = o;
-    // the TLAS culls with a padded copy of the reference's transformedBoundingBox
-    const Aabb padded = aabb_pad(box);
-    wlo[i] = make_float4(padded.lo.x, padded.lo.y, padded.lo.z, 0.0f);
-    whi[i] = make_float4(padded.hi.x, padded.hi.y, padded.hi.z, 0.0f);
+    wlo[i] = make_float4(box.lo.x, box.lo.y, box.lo.z, 0.0f);      // the reference's transformedBoundingBox; finished below
+    whi[i] = make_float4(box.hi.x, box.hi.y, box.hi.z, 0.0f);
     wcentroid[i] = make_float4(c.x, c.y, c.z, 0.0f);
-    atomic_bounds(bounds, padded);
+}
+
+// One warp per instance: tighten the world box from the transformed vertices where asked (instance_tight_box), pad it
+// for the TLAS and fold it into the scene bounds.
+__global__ void __launch_bounds__(BT) instance_bounds_kernel(const InstanceXformIn *__restrict__ in, int n, const InstanceD *__restrict__ inst,
+                                                             const float *__restrict__ tri_verts, float4 *__restrict__ wlo, float4 *__restrict__ whi,
+                                                             uint32_t *bounds) {
+    const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const int cnt = in[i].tri_count;
+    const float4 a = wlo[i], b = whi[i];
+    Aabb box;
+    box.lo = mk3(a.x, a.y, a.z);
+    box.hi = mk3(b.x, b.y, b.z);
+    if (cnt > 0) {
+        float fwd[12];
+#pragma unroll
+        for (int k = 0; k < 12; k++) fwd[k] = inst[i].fwd[k];
+        Aabb v;
+        v.lo = mk3(RT_INF, RT_INF, RT_INF);
+        v.hi = mk3(-RT_INF, -RT_INF, -RT_INF);
+        const float *p = tri_verts + (size_t) in[i].tri_first * 9;
+        for (int k = lane; k < cnt * 3; k += 32) aabb_grow(v, xf_point(fwd, mk3(__ldg(p + 3 * k), __ldg(p + 3 * k + 1), __ldg(p + 3 * k + 2))));
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            v.lo.x = fminf(v.lo.x, __shfl_xor_sync(0xffffffffu, v.lo.x, off)); v.lo.y = fminf(v.lo.y, __shfl_xor_sync(0xffffffffu, v.lo.y, off));
+            v.lo.z = fminf(v.lo.z, __shfl_xor_sync(0xffffffffu, v.lo.z, off)); v.hi.x = fmaxf(v.hi.x, __shfl_xor_sync(0xffffffffu, v.hi.x, off));
+            v.hi.y = fmaxf(v.hi.y, __shfl_xor_sync(0xffffffffu, v.hi.y, off)); v.hi.z = fmaxf(v.hi.z, __shfl_xor_sync(0xffffffffu, v.hi.z, off));
+        }
+        box = instance_tight_box(box, v);
+    }
+    if (lane == 0) {
+        const Aabb padded = aabb_pad(box);
+        wlo[i] = make_float4(padded.lo.x, padded.lo.y, padded.lo.z, 0.0f);
+        whi[i] = make_float4(padded.hi.x, padded.hi.y, padded.hi.z, 0.0f);
+        atomic_bounds(bounds, padded);
+    }
 }
 
 } // namespace
 
 void launch_instance_update(const InstanceXformIn *in, int n, InstanceD *out, float4 *wlo, float4 *whi, float4 *wcentroid,
-                            uint32_t *bounds, cudaStream_t stream) {
+                            uint32_t *bounds, const float *tri_verts, cudaStream_t stream) {
     init_bounds_kernel<<<1, BT, 0, stream>>>(bounds, 1);
-    instance_update_kernel<<<div_up(n, 64), 64, 0, stream>>>(in, n, out, wlo, whi, wcentroid, bounds);
+    instance_update_kernel<<<div_up(n, 64), 64, 0, stream>>>(in, n, out, wlo, whi, wcentroid);
+    instance_bounds_kernel<<<div_up((size_t) n * 32, BT), BT, 0, stream>>>(in, n, out, tri_verts, wlo, whi, bounds);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -184,7 +184,9 @@ struct InstanceXformIn {
     float box_lo[3], box_hi[3], centroid[3];
     int root_ref, blas;
     int root8, prim_type;
+    int tri_first, tri_count;   // triangle BLAS whose world box is tightened from its vertices (tri_count = 0: keep the 8-corner box)
 };
+#define RT_TIGHT_BOUNDS_MAX_TRIS 4096   /* larger meshes keep the 8-corner box (one warp walks the vertices every frame) */
 RT_HD void mat4_mul(const float a[4][4], const float b[4][4], float r[4][4]) {
     for (int i = 0; i < 4; i++)
         for (int j = 0; j < 4; j++) {
@@ -254,4 +256,18 @@ RT_HD void instance_update(const InstanceXformIn &in, InstanceD &out, Aabb &wbox
     ensure_volume(lo.x, hi.x); ensure_volume(lo.y, hi.y); ensure_volume(lo.z, hi.z);
     wbox.lo = lo; wbox.hi = hi;
     wcentroid = xf_point(out.fwd, mk3(in.centroid[0], in.centroid[1], in.centroid[2]));
+}
+// The 8-corner box of a ROTATED mesh is loose (a unit sphere's grows to side 2*sqrt(3): 3x the surface, so 3x the rays
+// that enter the instance for nothing).  For small triangle BLASes the TLAS therefore culls with the exact world box
+// of the transformed vertices, clipped to the 8-corner box; min/max are exact, so the walking order does not matter.
+RT_HD void aabb_grow(Aabb &b, const f3 &p) {
+    b.lo = mk3(rt_min(b.lo.x, p.x), rt_min(b.lo.y, p.y), rt_min(b.lo.z, p.z));
+    b.hi = mk3(rt_max(b.hi.x, p.x), rt_max(b.hi.y, p.y), rt_max(b.hi.z, p.z));
+}
+RT_HD Aabb instance_tight_box(const Aabb &corner_box, const Aabb &vertex_box) {
+    Aabb r;
+    r.lo = mk3(rt_max(corner_box.lo.x, vertex_box.lo.x), rt_max(corner_box.lo.y, vertex_box.lo.y), rt_max(corner_box.lo.z, vertex_box.lo.z));
+    r.hi = mk3(rt_min(corner_box.hi.x, vertex_box.hi.x), rt_min(corner_box.hi.y, vertex_box.hi.y), rt_min(corner_box.hi.z, vertex_box.hi.z));
+    ensure_volume(r.lo.x, r.hi.x); ensure_volume(r.lo.y, r.hi.y); ensure_volume(r.lo.z, r.hi.z);
+    return r;
 }

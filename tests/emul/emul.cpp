@@ -254,7 +254,15 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     scene.lo = mk3(RT_INF, RT_INF, RT_INF); scene.hi = mk3(-RT_INF, -RT_INF, -RT_INF);
     for (int i = 0; i < ni; i++) {
         instance_update(xin[i], e->instances[i], e->wbox[i], e->wcentroid[i]);
-        t.prim_box[i] = aabb_pad(e->wbox[i]);
+        if (xin[i].tri_count > 0) {          // twin of instance_bounds_kernel: exact world box of the transformed vertices
+            Aabb v;
+            v.lo = mk3(RT_INF, RT_INF, RT_INF); v.hi = mk3(-RT_INF, -RT_INF, -RT_INF);
+            const float *p = hs.tri_verts.data() + (size_t) xin[i].tri_first * 9;
+            for (int k = 0; k < xin[i].tri_count * 3; k++) aabb_grow(v, xf_point(e->instances[i].fwd, mk3(p[3 * k], p[3 * k + 1], p[3 * k + 2])));
+            t.prim_box[i] = aabb_pad(instance_tight_box(e->wbox[i], v));     // e->wbox stays the reference's transformedBoundingBox
+        } else {
+            t.prim_box[i] = aabb_pad(e->wbox[i]);
+        }
         scene = aabb_union(scene, t.prim_box[i]);
     }
     const int tbits = morton_bits_for((size_t) ni);

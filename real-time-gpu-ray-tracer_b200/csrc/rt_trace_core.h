@@ -215,19 +215,25 @@ RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const 
     }
     const f3 wp = xf_point(ins.fwd, lp);
     const f3 wn = unit3(xf_normal(ins.inv, ln));
-    if (mt == 0u) {                                                  // Rough::scatter
-        const float4 m = sc.roughs[mi];
-        f3 dir = wn + rng_space_vector(rng);
+    // Rough::scatter and Metal::scatter (fuzz > 0) both draw ONE random unit vector; it is drawn at a single place so
+    // that the lanes of a warp that shade different materials run the rejection loop together (the stream position
+    // and every value are the same as drawing it inside each branch: nothing else consumes the stream in between).
+    const bool rough = mt == 0u, metal = mt == 1u;
+    float4 m = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (rough) m = sc.roughs[mi]; else if (metal) m = sc.metals[mi];
+    f3 rv = mk3(0.0f, 0.0f, 0.0f);
+    if (rough || (metal && m.w > 0.0f)) rv = rng_space_vector(rng);
+    if (rough) {                                                     // Rough::scatter
+        f3 dir = wn + rv;
         if (feq(len2(dir), RT_EPS * RT_EPS)) dir = wn;
         ray.o = wp; ray.d = dir;                                     // not normalised (Q5)
         throughput.x *= m.x; throughput.y *= m.y; throughput.z *= m.z;
         return true;
     }
-    if (mt == 1u) {                                                  // Metal::scatter
-        const float4 m = sc.metals[mi];
+    if (metal) {                                                     // Metal::scatter
         const f3 v = ray.d;
         f3 refl = unit3(v - wn * (2 * dot3(v, wn)));
-        if (m.w > 0.0f) refl = refl + rng_space_vector(rng) * m.w;
+        if (m.w > 0.0f) refl = refl + rv * m.w;
         ray.o = wp; ray.d = refl;
         if (!(dot3(refl, wn) > 0.0f)) return false;                  // rayColor returns before attenuating (Q6)
         throughput.x *= m.x; throughput.y *= m.y; throughput.z *= m.z;

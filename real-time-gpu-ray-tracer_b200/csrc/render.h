@@ -4,7 +4,10 @@
 #include "device_util.h"
 #include "rt_types.h"
 
-void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &cam, const FrameD &fr, cudaStream_t stream);
+// tables: RNG_TABLE_WORDS device words owned by the context (jump matrices per hex digit, filled on first use)
+constexpr size_t RNG_TABLE_WORDS = 8 * 15 * 800;
+void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &cam, const FrameD &fr, cudaStream_t stream, uint32_t *tables,
+                     bool &tables_ready);
 void launch_render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream);
 // measurement aid: read bandwidth of a buffer of `bytes` streamed `repeats` times (GB/s)
 double probe_read_bandwidth(size_t bytes, int repeats, int sm_count, cudaStream_t stream);

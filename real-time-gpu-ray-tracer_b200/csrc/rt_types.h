@@ -43,7 +43,9 @@ struct alignas(16) BvhNode8 {
     uint4 n1, n2, n3, n4;
 };
 #define RT_WIDE_LEAF_MAX 1      /* primitives per leaf child (format allows 3; 1 measured fastest: the exact triangle test is dearer than a box) */
+#ifndef RT_WIDE_STACK
 #define RT_WIDE_STACK 24        /* entries (8 B each) of the per-thread traversal stack */
+#endif
 
 // ---- primitives -----------------------------------------------------------------------------------
 // Triangle intersection record in LEAF ORDER (Morton-sorted), 48 B: v0|primIndex, e1, e2

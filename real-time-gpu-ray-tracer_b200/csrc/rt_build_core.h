@@ -55,8 +55,18 @@ RT_HD Aabb aabb_pad(const Aabb &a) {
     r.hi = mk3(a.hi.x + (fabsf(a.hi.x) * 4e-7f + 1e-6f), a.hi.y + (fabsf(a.hi.y) * 4e-7f + 1e-6f), a.hi.z + (fabsf(a.hi.z) * 4e-7f + 1e-6f));
     return r;
 }
+// A triangle with v1 == v0 or v2 == v0 has e1 = 0 or e2 = 0 exactly, so Moller-Trumbore's det is exactly 0 for every
+// ray and tri_hit_t rejects it (near_zero): it can never be hit, here or in the reference.  The triangle strips of the
+// particle meshes are 41 % such triangles (they keep their primitive index, so they stay in the BVH); their box is
+// shrunk to the point v0 so that rays stop paying node visits and triangle tests for them.
+// (v1 == v2 gives e1 == e2 and a det that is only NEARLY zero — those keep their full box.)
 RT_HD Aabb tri_aabb(const float *v9) {
     Aabb r;
+    if ((v9[3] == v9[0] && v9[4] == v9[1] && v9[5] == v9[2]) || (v9[6] == v9[0] && v9[7] == v9[1] && v9[8] == v9[2])) {
+        r.lo = mk3(v9[0], v9[1], v9[2]);
+        r.hi = r.lo;
+        return r;
+    }
     r.lo = mk3(rt_min(rt_min(v9[0], v9[3]), v9[6]), rt_min(rt_min(v9[1], v9[4]), v9[7]), rt_min(rt_min(v9[2], v9[5]), v9[8]));
     r.hi = mk3(rt_max(rt_max(v9[0], v9[3]), v9[6]), rt_max(rt_max(v9[1], v9[4]), v9[7]), rt_max(rt_max(v9[2], v9[5]), v9[8]));
     return r;

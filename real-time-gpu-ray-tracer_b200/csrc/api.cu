@@ -41,6 +41,23 @@ struct rt_ctx {
     DeviceBuffer<float4> d_wcentroid;
     PinnedBuffer<InstanceXformIn> h_xform_in;
     LbvhBuilder blas, tlas;
+    // The big per-frame uploads of the animation (triangle vertices and shading records, 52 MB at 629 k triangles) come
+    // from HostScene's vectors; page-locking their storage in place makes the copies DMA at PCIe speed instead of being
+    // staged through the driver's bounce buffer.  The registration follows the vector's allocation.
+    struct PinnedRange {
+        void *p = nullptr;
+        size_t bytes = 0;
+        void release() { if (p) cudaHostUnregister(p); p = nullptr; bytes = 0; }
+        void ensure(void *q, size_t b) {
+            if (q == p && b == bytes) return;
+            release();
+            if (q && b >= (4u << 20)) {
+                if (cudaHostRegister(q, b, cudaHostRegisterDefault) == cudaSuccess) { p = q; bytes = b; } else cudaGetLastError();
+            }
+        }
+        ~PinnedRange() { release(); }
+    };
+    PinnedRange pin_verts, pin_shade;
     DeviceBuffer<uint32_t> d_rng_tables;   // XORWOW sequence-jump matrices per hex digit (kernels_render.cu)
     bool rng_tables_ready = false;
     WaveRenderer wave;
@@ -210,8 +227,15 @@ const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->err.c_str() : "
 int rt_commit_geometry(rt_ctx *ctx, const rt_sphere *spheres, size_t sphere_count, const rt_parallelogram *parallelograms,
                        size_t parallelogram_count, const rt_triangle *triangles, size_t triangle_count) {
     RT_API_BEGIN(ctx)
+    // the vectors are about to grow: their old storage must not stay registered when it is freed
+    if (triangle_count * 9 > ctx->hs.tri_verts.capacity()) ctx->pin_verts.release();
+    if (triangle_count > ctx->hs.tri_shade.capacity()) ctx->pin_shade.release();
     const std::string e = ctx->hs.commit_geometry(spheres, sphere_count, parallelograms, parallelogram_count, triangles, triangle_count);
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    if (ctx->composing) {        // animation frames: the same vectors are refilled every frame
+        ctx->pin_verts.ensure(ctx->hs.tri_verts.data(), ctx->hs.tri_verts.capacity() * sizeof(ctx->hs.tri_verts[0]));
+        ctx->pin_shade.ensure(ctx->hs.tri_shade.data(), ctx->hs.tri_shade.capacity() * sizeof(ctx->hs.tri_shade[0]));
+    }
     if (!ctx->composing) ctx->user_tris.assign(triangles, triangles + triangle_count);
     ctx->built = false;
     ctx->d_spheres.upload(ctx->hs.sphere_rec.data(), ctx->hs.sphere_rec.size(), ctx->stream);

@@ -362,18 +362,18 @@ def run_ours(args):
             peak, peak_src = float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
         except Exception:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        if world == 1:
+        if True:      # at N > 1: rank 0's kernel on its 1/N shard (tiles interleaved, so the whole-frame per-ray counts apply)
             rc = pkg.Renderer(device=local, flags=abi.FLAG_COUNT_TRAVERSAL | base_flags)
             rc.commitScene(sc)
             co = rc.renderFrame(0, SEED)
             rc.cleanup()
             node_b, prim_b, inst_b, io_b = (64 if args.bvh2 else 80), 48, 64, 24 + 16 + 12
-            alg = co.node_fetches * node_b + co.prim_fetches * prim_b + co.instance_fetches * inst_b + W * H * io_b
+            alg = (co.node_fetches * node_b + co.prim_fetches * prim_b + co.instance_fetches * inst_b + W * H * io_b) / world
             t_kernel = statistics.mean(trace_ms) * 1e-3
             achieved = alg / t_kernel / 1e9
             traffic = None
             tp = os.path.join(ROOT, "profiles", "traffic_latest.json")
-            if os.path.exists(tp) and args.config == "c2":      # the committed capture is of the bench workload
+            if os.path.exists(tp) and args.config == "c2" and world == 1:      # the committed capture is of the bench workload
                 try:
                     traffic = json.load(open(tp)).get("dram_bytes_per_launch")
                 except Exception:

@@ -41,6 +41,7 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
     const int stride = gridDim.x * blockDim.x;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t backoff = 32u;
+    bool allocated = false;                        // item i is known to be allocated (so it will be published)
     for (;;) {
         if (i < capacity) {
             const int root = vq[i];
@@ -70,15 +71,25 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
                 atomicAdd(&counters[2], 1u);
                 i += stride;
                 backoff = 32u;
+                allocated = false;
                 continue;
             }
+        }
+        // Not published yet.  An index below the allocation count WILL be published (its parent is running): poll only
+        // the queue.  Only threads whose index is not allocated (yet) look at the termination condition — the two
+        // counters are one hot line that 75 k polling threads used to hammer on every iteration.
+        if (!allocated) allocated = i < capacity && (uint32_t) i < vc[0];       // the count only grows: ask once
+        if (allocated) {
+            __nanosleep(backoff);
+            if (backoff < 256u) backoff <<= 1;
+            continue;
         }
         const uint32_t fin = vc[2];
         __threadfence();
         const uint32_t alloc = vc[0];
         if (fin == alloc) break;
         __nanosleep(backoff);                      // waiting lanes must not starve the producers of L2 bandwidth
-        if (backoff < 512u) backoff <<= 1;
+        if (backoff < 2048u) backoff <<= 1;
     }
 }
 
@@ -122,7 +133,7 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     collapse_init_kernel<<<div_up(n_segs, 256), 256, 0, stream>>>(seg_offset_.get(), seg_root_.get(), n_segs, queue_.get(), wide_counters_.get());
     const BinaryTreeView view{range_.get(), node_lo_.get(), node_hi_.get(), prim_lo_.get(), prim_hi_.get(), vals_};
     // every thread of the grid must be resident (the items poll on one another)
-    static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 4;   // tuning
+    static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 2;   // tuning (measured: 2 beats 3, 4, 8 — fewer pollers)
     const int max_blocks = sm_count * std::min(collapse_blocks_per_sm_, std::max(1, collapse_bps_env));
     const int want_blocks = (int) div_up((size_t) capacity, CT);
     const int blocks = want_blocks < max_blocks ? want_blocks : max_blocks;

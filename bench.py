@@ -246,6 +246,143 @@ def c3_rebuild(pkg, device):
                     "triangles resident -> wide BVH ready; animation_loop = set frame + rebuild + render 1080p, host wall per frame"}
 
 
+def run_c3(args):
+    """configs[2]: the particle_mesh.vtk.series animation, frames sharded i mod N over the ranks.  One
+    step = one pass over the whole animation; every rank reads ahead, commits, rebuilds (all particle BLASes + TLAS)
+    and renders its own frames at 1080p / 1 spp / depth 10 (Main.cu:88-89); nothing is exchanged per frame.
+    `value` is device time (CUDA events: rebuild + render of every frame, one renderer per GPU, frame by frame through
+    rt_set_vtk_frame / rt_render_frame); `e2e` is the host wall clock of the library's own loop (rt_run_vtk_animation)
+    with --renderers-per-gpu R contexts per GPU (frames of the rank dealt round-robin): one context's commit + H2D
+    overlaps the other's render, and every frame lands in pinned host memory."""
+    import tempfile
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    distributed = world > 1
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (our arm) needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    R = max(1, args.renderers_per_gpu)
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("RTB200_HOST_THREADS", str(max(1, min(8, cores // (world * R)))))     # the ranks share the host's cores
+    if distributed:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    abi, S, sh = pkg.abi, pkg.scenes, pkg.sharding
+    F = args.frames
+    counts = S.c3_particle_counts(F)
+    mine = sh.frames_of_rank(F, rank, world)
+    fixture = os.path.join(ROOT, "tests", "golden", "particle_frame0.vtk")
+    W, H = 1920, 1080
+
+    class Lane:
+        """one renderer context with its own copy of the frames it will render"""
+        def __init__(self, tmp, frames, tag):
+            self.frames = frames
+            self.host_fb = torch.empty(W * H * 4, dtype=torch.uint8).pin_memory()
+            series = S.synth_vtk_series(fixture, os.path.join(tmp, tag), [counts[f] for f in frames], frame_ids=frames)
+            d = os.path.join(tmp, tag, "particle_mesh")
+            self.bytes = sum(os.path.getsize(os.path.join(d, n)) for n in os.listdir(d))
+            self.r = pkg.Renderer(device=local)
+            self.r.commitScene(S.c1a(frame=0, width=W, height=H, spp=1, depth=10))
+            assert self.r.configureVTKFiles(series) == len(frames)
+
+        def animation(self, read_back):
+            """this lane's frames once; returns (rays, device ms = rebuild + render, launches, triangles, rebuild ms list)"""
+            r = self.r
+            rays, dev, launches, tris, reb = 0, 0.0, 0, 0, []
+            if self.frames:
+                r.prefetchVTKFrame(0)
+            for j, f in enumerate(self.frames):
+                st = r.setVTKFrame(j)                    # takes the frame read ahead; commit + upload + rebuild
+                if j + 1 < len(self.frames):
+                    r.prefetchVTKFrame(j + 1)            # the next frame is parsed while this one renders
+                out = r.renderFrame(f, SEED)
+                rays += out.rays
+                dev += st.blas_ms + st.tlas_ms + out.render_ms
+                reb.append(st.blas_ms + st.tlas_ms)
+                launches += st.kernel_launches + out.kernel_launches
+                tris += st.primitive_count
+                if read_back:
+                    r.lib.rt_read_framebuffer(r.ctx, abi.BUF_RGBA8, C.c_void_p(self.host_fb.data_ptr()), self.host_fb.numel())
+            return rays, dev, launches, tris, reb
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with tempfile.TemporaryDirectory() as tmp:
+        # ---- value: one renderer per GPU, device time ---------------------------------------------------------------
+        one = Lane(tmp, mine, "v")
+        for _ in range(args.warmup):
+            one.animation(False)
+        sampler = ClockSampler(local)
+        barrier()
+        if rank == 0:
+            sampler.start()
+        rays, dev_ms, launches, tris, rebuilds = 0, 0.0, 0, 0, []
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            n, ms, l, t, reb = one.animation(False)
+            rays += n; dev_ms += ms; launches += l; tris += t; rebuilds += reb
+        barrier()
+        wall_ms = 1e3 * (time.perf_counter() - t0)
+        clocks = sampler.stop() if rank == 0 else None
+        series_bytes = one.bytes
+        # ---- e2e: the library's own frame loop (rt_run_vtk_animation), R renderer contexts per GPU, frames delivered
+        #      to a host sink in pinned memory --------------------------------------------------------------------------
+        delivered = []
+
+        def sink(frame, img, out):
+            delivered.append(frame)
+            return 0
+
+        for _ in range(max(1, args.warmup - 1)):
+            one.r.runVTKAnimation(0, 1, 0, SEED, R, sink)
+        barrier()
+        e_rays = 0
+        delivered.clear()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e_rays += one.r.runVTKAnimation(0, 1, 0, SEED, R, sink).rays
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        assert len(delivered) == len(mine) * args.steps
+        one.r.cleanup()
+    tot = torch.tensor([float(rays), float(e_rays), float(tris), float(launches), float(series_bytes)], dtype=torch.float64, device=f"cuda:{local}")
+    mx = torch.tensor([dev_ms, e2e_s, wall_ms, max(rebuilds) if rebuilds else 0.0], dtype=torch.float64, device=f"cuda:{local}")
+    if distributed:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    tot_rays, tot_e_rays, tot_tris, tot_launches, tot_bytes = tot.tolist()
+    max_dev_ms, max_e2e_s, max_wall_ms, max_rebuild = mx.tolist()
+    if rank == 0:
+        line = {"metric": "Mrays/s (configs[2]: particle_mesh.vtk.series animation, per-frame LBVH rebuild + render, frames sharded over the GPUs)",
+                "value": tot_rays / (max_dev_ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": max_dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"configs[2]: {F}-frame stand-in for files/particle_mesh.vtk.series ({counts[0]}..{counts[-1]} particles x 1258 strip triangles, "
+                                       "the reference's on-disk layout, synthesised from the committed frame-0 fixture) + the 5 Main.cu instances, 1920x1080, 1 spp, depth 10",
+                           "frames": F, "width": W, "height": H, "spp": 1, "depth": 10,
+                           "parallelism": f"frames i mod {world}, scene rebuilt per frame on the owning GPU, no per-frame exchange" if world > 1 else "single GPU",
+                           "l2": "every frame is a new scene (new BVH, new triangle records): nothing is reused between timed iterations"},
+                "frames_per_s": F * args.steps / (max_dev_ms * 1e-3), "wall_ms_per_step": max_wall_ms / args.steps,
+                "wall_frames_per_s_one_renderer": F * args.steps / (max_wall_ms * 1e-3),
+                "triangles_rebuilt_per_step": tot_tris / args.steps, "slowest_rebuild_ms": max_rebuild,
+                "e2e": {"value": tot_e_rays / max_e2e_s / 1e6, "unit": "Mrays/s", "frames_per_s": F * args.steps / max_e2e_s,
+                        "renderers_per_gpu": R, "host_threads_per_renderer": int(os.environ["RTB200_HOST_THREADS"]), "host_cores": cores,
+                        "h2d_bytes_per_step": int(tot_tris / args.steps * 36), "d2h_bytes_per_step": int(F * (W * H * 4 + 64)),
+                        "ms_per_step": 1e3 * max_e2e_s / args.steps, "vtk_bytes_read_per_step": int(tot_bytes),
+                        "what": "rt_run_vtk_animation: per frame disk -> host (read ahead), commit, H2D, rebuild, render, RGBA8 -> pinned host, sink call; host wall clock"},
+                "gpu_launches": int(tot_launches), "clocks": clocks}
+        print(json.dumps(line))
+    if distributed:
+        dist.destroy_process_group()
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -446,7 +583,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="c2", choices=["c2", "c4", "c5"], help="c2 = the bench line (BASELINE configs[1]); c4 / c5 = the other GPU configs, extra lines")
+    ap.add_argument("--config", default="c2", choices=["c2", "c3", "c4", "c5"], help="c2 = the bench line (BASELINE configs[1]); c3 (animation, frames sharded) / c4 / c5 = the other GPU configs, extra lines")
+    ap.add_argument("--frames", type=int, default=64, help="--config c3: frames of the synthesised particle animation")
+    ap.add_argument("--renderers-per-gpu", type=int, default=3, help="--config c3, e2e pass: renderer contexts (host threads) per GPU")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--spp", type=int, default=64)
@@ -467,6 +606,8 @@ def main():
         args.no_ref_cuda = args.no_c3 = args.no_cpu_baseline = True
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == "c3":
+        run_c3(args)
     else:
         run_ours(args)
 

@@ -264,6 +264,29 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame);
  * return at once; the next rt_set_vtk_frame(frame) takes the result instead of parsing.  One read-ahead at a time.  */
 int rt_prefetch_vtk_frame(rt_ctx *ctx, size_t frame);
 
+/* The whole headless frame loop of the animation behind one call (Renderer::startRender's while-loop,
+ * src/Global/Renderer.cu:232-338, with the SDL/GL present replaced by `sink`): renders the series frames
+ * first_frame, first_frame + frame_stride, ... (at most max_frames of them; 0 = to the end of the series) — frame
+ * sharding over GPUs is first_frame = rank, frame_stride = world.  `lanes` renderer contexts (this one plus lanes-1
+ * internal copies of its committed scene, camera and shard, each with its own stream, device buffers and read-ahead
+ * thread) run on `lanes` host threads and take the frames round-robin, so one lane's commit + upload overlaps the
+ * other's render on the same GPU.  Per frame: rt_set_vtk_frame (frame read ahead), rt_render_frame(frame, seed), RGBA8
+ * plane -> pinned host memory, then `sink` (may be NULL) is called — one call at a time, from a lane's thread, frames
+ * NOT in order across lanes; a non-zero return stops the loop (RT_ERR_STATE).  Every frame is the one
+ * rt_set_vtk_frame + rt_render_frame on a single context would produce.                                                   */
+typedef struct rt_animation_stats {
+    uint64_t frames;              /* frames rendered                                                     */
+    uint64_t rays;
+    uint64_t triangles;           /* primitives rebuilt, summed over the frames                          */
+    uint64_t kernel_launches;
+    double   wall_ms;             /* host wall clock of the whole loop                                   */
+    double   device_ms;           /* sum over frames of CUDA-event rebuild + render time (lanes overlap) */
+    double   slowest_rebuild_ms;  /* max over frames of BLAS batch + TLAS rebuild                        */
+} rt_animation_stats;
+typedef int (*rt_frame_sink)(void *user, size_t frame, const void *rgba8, size_t bytes, const rt_frame_out *out);
+int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t frame_stride, size_t max_frames, uint64_t seed, int lanes,
+                         rt_frame_sink sink, void *user, rt_animation_stats *stats);
+
 /* ---- measurement aid (bench.py roofline denominators; no reference counterpart) ----------------------
  * Streams a device buffer of `bytes` with 128-bit loads from every SM, `repeats` times back to back, and returns
  * the read bandwidth in GB/s (CUDA events).  bytes well below the L2 size (126 MB) measures the L2 -> SM read

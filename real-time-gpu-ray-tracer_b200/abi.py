@@ -76,6 +76,12 @@ class BuildStats(C.Structure):
                 ("kernel_launches", C.c_uint32), ("_pad", C.c_uint32)]
 
 
+class AnimationStats(C.Structure):
+    _fields_ = [("frames", C.c_uint64), ("rays", C.c_uint64), ("triangles", C.c_uint64), ("kernel_launches", C.c_uint64),
+                ("wall_ms", C.c_double), ("device_ms", C.c_double), ("slowest_rebuild_ms", C.c_double)]
+
+
+FRAME_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(FrameOut))
 UPDATE_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p)
 
 _STRUCT_SIZES = {
@@ -83,7 +89,7 @@ _STRUCT_SIZES = {
     "rt_rough": rough_dt.itemsize, "rt_metal": metal_dt.itemsize, "rt_dielectric": dielectric_dt.itemsize,
     "rt_instance_desc": instance_desc_dt.itemsize, "rt_instance_xform": instance_xform_dt.itemsize,
     "rt_window": C.sizeof(Window), "rt_camera_input": C.sizeof(CameraInput), "rt_frame_out": C.sizeof(FrameOut),
-    "rt_build_stats": C.sizeof(BuildStats),
+    "rt_build_stats": C.sizeof(BuildStats), "rt_animation_stats": C.sizeof(AnimationStats),
 }
 
 # every symbol include/rtb200.h declares
@@ -93,7 +99,7 @@ EXPORTS = [
     "rt_build_acceleration_structure", "rt_get_build_stats", "rt_configure_camera",
     "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm", "rt_write_image",
     "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame", "rt_prefetch_vtk_frame",
-    "rt_probe_read_bandwidth",
+    "rt_probe_read_bandwidth", "rt_run_vtk_animation",
 ]
 
 _lib = None
@@ -136,6 +142,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_load_vtk_series.argtypes = [vp, C.c_char_p, C.POINTER(sz)]
     lib.rt_set_vtk_frame.argtypes = [vp, sz]
     lib.rt_prefetch_vtk_frame.argtypes = [vp, sz]
+    lib.rt_run_vtk_animation.argtypes = [vp, sz, sz, sz, u64, i32, FRAME_SINK, vp, C.POINTER(AnimationStats)]
     lib.rt_probe_read_bandwidth.argtypes = [vp, sz, i32, C.POINTER(C.c_double)]
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported

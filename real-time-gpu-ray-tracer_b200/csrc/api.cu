@@ -8,8 +8,12 @@
 #include "vtk_reader.h"
 #include "wave.h"
 
+#include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
+#include <functional>
+#include <mutex>
 #include <cstring>
 #include <map>
 #include <thread>
@@ -78,7 +82,7 @@ struct rt_ctx {
 
     // VTK series: the user's own triangles / instances are kept so that every frame can be recomposed as
     // [VTK triangles | user triangles], [user instances | VTK instances] (reference src/Global/Renderer.cu:17,106-116)
-    std::unique_ptr<VtkSeries> vtk;
+    std::shared_ptr<const VtkSeries> vtk;    // shared with the lanes of rt_run_vtk_animation
     // one parsed + converted series frame.  Two of them: the one being committed and the one a host thread reads ahead
     // (rt_prefetch_vtk_frame) while the GPU renders; the vectors keep their capacity from frame to frame.
     struct VtkStage {
@@ -108,6 +112,10 @@ struct rt_ctx {
     bool composing = false;
     size_t n_user_inst = 0;
     float vtk_parse_ms = 0.0f;
+    // rt_run_vtk_animation: the extra renderer contexts (lanes) and the pinned frame each lane delivers; kept between
+    // calls so that their device buffers, page-locked ranges and jump tables are allocated once
+    std::vector<rt_ctx *> lane_ctx;
+    PinnedBuffer<uint8_t> h_frame;
 };
 
 namespace {
@@ -170,7 +178,7 @@ size_t rt_struct_size(const char *name) {
     if (!name) return 0;
 #define RT_SZ(T) if (strcmp(name, #T) == 0) return sizeof(T);
     RT_SZ(rt_vec3) RT_SZ(rt_sphere) RT_SZ(rt_parallelogram) RT_SZ(rt_triangle) RT_SZ(rt_rough) RT_SZ(rt_metal) RT_SZ(rt_dielectric)
-    RT_SZ(rt_instance_desc) RT_SZ(rt_instance_xform) RT_SZ(rt_window) RT_SZ(rt_camera_input) RT_SZ(rt_frame_out) RT_SZ(rt_build_stats)
+    RT_SZ(rt_instance_desc) RT_SZ(rt_instance_xform) RT_SZ(rt_window) RT_SZ(rt_camera_input) RT_SZ(rt_frame_out) RT_SZ(rt_build_stats) RT_SZ(rt_animation_stats)
 #undef RT_SZ
     return 0;
 }
@@ -213,6 +221,8 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
 int rt_cleanup(rt_ctx *ctx) {
     if (!ctx) return RT_ERR_ARGUMENT;
     cudaSetDevice(ctx->device);
+    for (rt_ctx *l: ctx->lane_ctx) rt_cleanup(l);
+    ctx->lane_ctx.clear();
     for (auto &st: ctx->vtk_stage) st.join();
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); }
     for (auto &e: ctx->ev) if (e) cudaEventDestroy(e);
@@ -582,7 +592,7 @@ int rt_read_wide_bvh(rt_ctx *ctx, size_t which, size_t *n_nodes, size_t *n_leaf_
 int rt_load_vtk_series(rt_ctx *ctx, const char *series_path, size_t *frame_count) {
     RT_API_BEGIN(ctx)
     if (!series_path) return fail(ctx, RT_ERR_ARGUMENT, "rt_load_vtk_series: null path");
-    auto series = std::make_unique<VtkSeries>();
+    auto series = std::make_shared<VtkSeries>();
     std::string err;
     if (!series->load(series_path, err)) return fail(ctx, RT_ERR_IO, err);
     if (frame_count) *frame_count = series->files.size();
@@ -644,3 +654,141 @@ int rt_prefetch_vtk_frame(rt_ctx *ctx, size_t frame) {
 }
 
 } // extern "C"
+
+// ---- the animation loop behind the ABI ---------------------------------------------------------------------------
+namespace {
+
+// a lane follows the caller's context: same committed scene (the triangles arrive with the lane's own
+// rt_set_vtk_frame), camera and shard; own stream, device buffers, read-ahead stages
+int sync_lane(rt_ctx *src, rt_ctx *c) {
+    HostScene &h = c->hs;
+    const HostScene &g = src->hs;
+    h.flags = g.flags;
+    h.spheres = g.spheres; h.quads = g.quads; h.sphere_rec = g.sphere_rec; h.quad_rec = g.quad_rec;
+    h.roughs = g.roughs; h.metals = g.metals; h.dielectrics = g.dielectrics;
+    h.xforms.assign(g.xforms.begin(), g.xforms.begin() + src->n_user_inst);
+    h.window = g.window; h.cam = g.cam;
+    c->user_tris = src->user_tris;
+    c->user_inst = src->user_inst;
+    c->n_user_inst = src->n_user_inst;
+    c->update_cb = src->update_cb;
+    c->update_user = src->update_user;
+    c->vtk = src->vtk;
+    c->path_mode = src->path_mode;
+    c->shard_rank = src->shard_rank; c->shard_world = src->shard_world; c->tile_rows = src->tile_rows; c->peer_rgba8 = nullptr;
+    try {
+        c->d_spheres.upload(h.sphere_rec.data(), h.sphere_rec.size(), c->stream);
+        c->d_quads.upload(h.quad_rec.data(), h.quad_rec.size(), c->stream);
+        c->d_roughs.upload(h.roughs.data(), h.roughs.size(), c->stream);
+        c->d_metals.upload(h.metals.data(), h.metals.size(), c->stream);
+        c->d_dielectrics.upload(h.dielectrics.data(), h.dielectrics.size(), c->stream);
+        CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        c->geometry_committed = src->geometry_committed;
+        c->materials_committed = src->materials_committed;
+        c->instances_configured = src->instances_configured;
+        c->camera_set = src->camera_set;
+        c->built = false;
+        if (c->camera_set) alloc_frame(c);
+    } catch (const std::exception &e) {
+        src->err = e.what();
+        cudaGetLastError();
+        return RT_ERR_CUDA;
+    }
+    return RT_OK;
+}
+
+struct AnimationShared {
+    std::mutex mu;                       // sink calls and the totals
+    rt_animation_stats tot{};
+    std::atomic<int> stop{0};            // first error code / sink stop
+    std::string err;
+    rt_frame_sink sink = nullptr;
+    void *user = nullptr;
+};
+
+void run_lane(rt_ctx *c, const std::vector<size_t> &frames, uint64_t seed, AnimationShared *sh) {
+    if (frames.empty()) return;
+    auto bail = [&](int rc, const std::string &msg) {
+        std::lock_guard<std::mutex> g(sh->mu);
+        int expected = 0;
+        if (sh->stop.compare_exchange_strong(expected, rc)) sh->err = msg;
+    };
+    if (cudaSetDevice(c->device) != cudaSuccess) { bail(RT_ERR_CUDA, "cudaSetDevice failed"); return; }
+    size_t plane = 0;
+    PinnedBuffer<uint8_t> &host = c->h_frame;
+    int rc = rt_prefetch_vtk_frame(c, frames[0]);
+    for (size_t j = 0; rc == RT_OK && j < frames.size() && sh->stop.load() == 0; j++) {
+        rc = rt_set_vtk_frame(c, frames[j]);
+        if (rc != RT_OK) break;
+        if (j + 1 < frames.size()) rc = rt_prefetch_vtk_frame(c, frames[j + 1]);     // parsed while this frame renders
+        if (rc != RT_OK) break;
+        rt_frame_out out{};
+        rc = rt_render_frame(c, frames[j], seed, &out);
+        if (rc != RT_OK) break;
+        plane = (size_t) c->hs.window.width * c->local_rows * 4;
+        try {
+            host.reserve(plane + 4);
+        } catch (const std::exception &e) { c->err = e.what(); rc = RT_ERR_CUDA; break; }
+        rc = rt_read_framebuffer(c, RT_BUFFER_RGBA8, host.get(), plane);
+        if (rc != RT_OK) break;
+        std::lock_guard<std::mutex> g(sh->mu);
+        rt_animation_stats &t = sh->tot;
+        t.frames++;
+        t.rays += out.rays;
+        t.triangles += c->build_stats.primitive_count;
+        t.kernel_launches += c->build_stats.kernel_launches + out.kernel_launches;
+        const double rebuild = (double) c->build_stats.blas_ms + c->build_stats.tlas_ms;
+        t.device_ms += rebuild + out.render_ms;
+        if (rebuild > t.slowest_rebuild_ms) t.slowest_rebuild_ms = rebuild;
+        if (sh->sink && sh->sink(sh->user, frames[j], host.get(), plane, &out) != 0) {
+            int expected = 0;
+            if (sh->stop.compare_exchange_strong(expected, RT_ERR_STATE)) sh->err = "rt_run_vtk_animation: stopped by the frame sink";
+        }
+    }
+    for (auto &st: c->vtk_stage) st.join();       // a read-ahead may still be running after an early stop
+    c->vtk_ahead = -1;
+    if (rc != RT_OK) bail(rc, c->err);
+}
+
+} // namespace
+
+extern "C" int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t frame_stride, size_t max_frames, uint64_t seed, int lanes,
+                                    rt_frame_sink sink, void *user, rt_animation_stats *stats) {
+    RT_API_BEGIN(ctx)
+    if (!ctx->vtk) return fail(ctx, RT_ERR_STATE, "rt_run_vtk_animation: load a series first");
+    if (!ctx->geometry_committed || !ctx->instances_configured || !ctx->camera_set || !ctx->materials_committed)
+        return fail(ctx, RT_ERR_STATE, "rt_run_vtk_animation: commit geometry, materials, instances and camera first");
+    if (frame_stride == 0 || lanes < 1 || lanes > 8) return fail(ctx, RT_ERR_ARGUMENT, "rt_run_vtk_animation: frame_stride >= 1 and 1 <= lanes <= 8");
+    if (ctx->peer_rgba8) return fail(ctx, RT_ERR_STATE, "rt_run_vtk_animation: not with a peer framebuffer");
+    std::vector<size_t> frames;
+    for (size_t f = first_frame; f < ctx->vtk->files.size() && (max_frames == 0 || frames.size() < max_frames); f += frame_stride) frames.push_back(f);
+    const int L = (int) std::max<size_t>(1, std::min<size_t>((size_t) lanes, frames.size()));
+    while ((int) ctx->lane_ctx.size() < L - 1) {
+        rt_ctx *c = nullptr;
+        const int rc = rt_create(&c, ctx->device, ctx->flags);
+        if (rc != RT_OK) return fail(ctx, rc, "rt_run_vtk_animation: could not create a lane context");
+        ctx->lane_ctx.push_back(c);
+    }
+    std::vector<rt_ctx *> lane_ctx(1, ctx);
+    for (int l = 1; l < L; l++) {
+        const int rc = sync_lane(ctx, ctx->lane_ctx[l - 1]);
+        if (rc != RT_OK) return rc;
+        lane_ctx.push_back(ctx->lane_ctx[l - 1]);
+    }
+    std::vector<std::vector<size_t>> lane_frames(L);
+    for (size_t k = 0; k < frames.size(); k++) lane_frames[k % L].push_back(frames[k]);
+    AnimationShared sh;
+    sh.sink = sink;
+    sh.user = user;
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> th;
+    for (int l = 1; l < L; l++) th.emplace_back(run_lane, lane_ctx[l], std::cref(lane_frames[l]), seed, &sh);
+    run_lane(ctx, lane_frames[0], seed, &sh);
+    for (std::thread &t: th) t.join();
+    sh.tot.wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    cudaSetDevice(ctx->device);
+    if (stats) *stats = sh.tot;
+    if (sh.stop.load() != 0) return fail(ctx, sh.stop.load(), sh.err);
+    RT_API_END(ctx)
+}
+

@@ -159,6 +159,28 @@ class Renderer:
         """Read + convert a series frame on a host thread while the GPU renders; the next setVTKFrame(frame) picks it up."""
         self._check(self.lib.rt_prefetch_vtk_frame(self.ctx, frame))
 
+    def runVTKAnimation(self, first_frame: int = 0, frame_stride: int = 1, max_frames: int = 0, seed: int = 0x5EED, lanes: int = 2,
+                        sink=None) -> abi.AnimationStats:
+        """The headless frame loop (Renderer::startRender's loop) in the library: series frames first_frame,
+        first_frame + frame_stride, ... on `lanes` renderer contexts of this GPU.  sink(frame, rgba8 [rows, W, 4] view,
+        FrameOut) is called once per finished frame (frames of different lanes arrive out of order; copy what you keep)."""
+        st = abi.AnimationStats()
+        W = self.width
+
+        def _sink(_user, frame, ptr, nbytes, out):
+            try:
+                buf = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(nbytes,))
+                img = buf.reshape(-1, W, 4) if W else buf
+                return int(sink(int(frame), img, out.contents) or 0)
+            except Exception:                      # an exception must not unwind through the C frames
+                import traceback
+                traceback.print_exc()
+                return 1
+
+        cb = abi.FRAME_SINK(_sink) if sink is not None else abi.FRAME_SINK()
+        self._check(self.lib.rt_run_vtk_animation(self.ctx, first_frame, frame_stride, max_frames, seed, lanes, cb, None, C.byref(st)))
+        return st
+
     # -- Renderer::cleanup -----------------------------------------------------------------------
     def cleanup(self):
         if self.ctx:

@@ -352,15 +352,19 @@ def c3(vtk_path: str, frame: int = 0, width: int = 1920, height: int = 1080, spp
     return sc
 
 
-def synth_vtk_series(src_vtk: str, out_dir: str, particle_counts, seed: int = 3) -> str:
+def synth_vtk_series(src_vtk: str, out_dir: str, particle_counts, seed: int = 3, frame_ids=None) -> str:
     """Synthesises a .vtk.series whose frame k holds particle_counts[k] rigid copies of the particles of `src_vtk`
-    (the reference's own data is 1.2 GB and cannot travel to the GPU box; frame 0 of it is committed as a fixture)."""
+    (the reference's own data is 1.2 GB and cannot travel to the GPU box; frame 0 of it is committed as a fixture).
+    With `frame_ids` (frame sharding: a rank writes only its own frames) entry k is animation frame frame_ids[k]; its
+    content then depends on (seed, frame id) alone, so every rank's copy of a frame is the same file."""
     import os
     pts, strips = read_vtk_frame(src_vtk)
     rng = np.random.RandomState(seed)
     os.makedirs(os.path.join(out_dir, "particle_mesh"), exist_ok=True)
     names = []
     for k, count in enumerate(particle_counts):
+        if frame_ids is not None:
+            rng = np.random.RandomState((seed * 1000003 + int(frame_ids[k])) & 0x7FFFFFFF)
         P, S, base = [], [], 0
         for q in range(count):
             s = strips[q % len(strips)]
@@ -369,12 +373,21 @@ def synth_vtk_series(src_vtk: str, out_dir: str, particle_counts, seed: int = 3)
             P.append(pts[ids] + shift)
             S.append(inv + base)
             base += len(ids)
-        name = f"particle_mesh/particle_{k * 100:015d}.vtk"
+        fid = k if frame_ids is None else int(frame_ids[k])
+        name = f"particle_mesh/particle_{fid * 100:015d}.vtk"
         write_vtk_frame(os.path.join(out_dir, name), np.concatenate(P), S)
         names.append(name)
     series = os.path.join(out_dir, "particle_mesh.vtk.series")
     with open(series, "w") as f:
         f.write('{\n  "file-series-version": "1.0",\n  "files": [\n')
-        f.write(",\n".join('    {"name": "%s", "time": %e}' % (n, 0.01 * k) for k, n in enumerate(names)))
+        f.write(",\n".join('    {"name": "%s", "time": %e}' % (n, 0.01 * (k if frame_ids is None else int(frame_ids[k]))) for k, n in enumerate(names)))
         f.write("\n  ]\n}\n")
     return series
+
+
+def c3_particle_counts(n_frames: int, first: int = 25, last: int = 500):
+    """Particle count of each frame of an n_frames-long stand-in for files/particle_mesh.vtk.series (the reference's
+    401 frames grow from 25 particles at t = 0 to 500 at t = 4.0)."""
+    if n_frames == 1:
+        return [last]
+    return [int(round(first + (last - first) * i / (n_frames - 1))) for i in range(n_frames)]

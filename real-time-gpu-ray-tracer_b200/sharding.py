@@ -1,7 +1,10 @@
 """Image-tile sharding of a frame over N ranks — the host-side arithmetic shared by bench.py and
 the multi-process tests.  Mirrors compute_local_rows / global_row in csrc/api.cu and csrc/kernels_wave.cu:
 tile t (tile_rows scan-lines) belongs to rank t % world; a rank's planes are packed (local tile k = global tile
-k * world + rank) and padded to whole tiles."""
+k * world + rank) and padded to whole tiles.
+
+Frame sharding of the particle animation (config 3): frame i belongs to rank i % world; a rank reads,
+rebuilds and renders its own frames and nothing is exchanged per frame."""
 from __future__ import annotations
 
 import numpy as np
@@ -39,3 +42,16 @@ def assemble(planes, height: int, row_bytes: int, world: int, tile_rows: int):
 def padded_plane_bytes(height: int, row_bytes: int, world: int, tile_rows: int) -> int:
     """Bytes of the largest rank's packed plane (rank 0): gather buffers are padded to this size."""
     return local_rows(height, 0, world, tile_rows) * row_bytes
+
+
+def frames_of_rank(n_frames: int, rank: int, world: int) -> list[int]:
+    """Animation frames rendered by `rank`, in order: frame i -> rank i % world."""
+    return list(range(rank, n_frames, world))
+
+
+def interleave_frames(per_rank, n_frames: int):
+    """Inverse of frames_of_rank: per_rank[q][j] is rank q's j-th result; returns the results in frame order."""
+    world = len(per_rank)
+    out = [per_rank[i % world][i // world] for i in range(n_frames)]
+    assert all(len(per_rank[q]) >= len(frames_of_rank(n_frames, q, world)) for q in range(world))
+    return out

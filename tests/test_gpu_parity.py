@@ -158,6 +158,105 @@ def test_vtk_series_frames(pkg, port, tmp_path):
     assert e.value.code == -1
 
 
+def test_vtk_frame_shards_equal_the_single_loop(pkg, tmp_path):
+    """Config 3's multi-GPU partitioning (frame i -> rank i % world): each rank's renderer reads, rebuilds and renders
+    only its own frames from its own copy of the series; put back in frame order the images are, bit for bit, those
+    of one renderer looping over the whole animation (a frame does not depend on the frames rendered before it)."""
+    import os
+    S, sh = pkg.scenes, pkg.sharding
+    fixture = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "particle_frame0.vtk")
+    counts = [25, 31, 28, 40, 33]
+    F = len(counts)
+
+    def loop(series, frames):
+        r = pkg.Renderer(device=0)
+        imgs, tris = [], []
+        try:
+            r.commitScene(S.c1a(frame=0, width=160, height=90, spp=2, depth=10))
+            assert r.configureVTKFiles(series) == len(frames)
+            r.prefetchVTKFrame(0)
+            for j, f in enumerate(frames):
+                st = r.setVTKFrame(j)
+                if j + 1 < len(frames):
+                    r.prefetchVTKFrame(j + 1)
+                r.renderFrame(f, SEED)
+                imgs.append(r.readFramebuffer(pkg.abi.BUF_RADIANCE).copy())
+                tris.append(int(st.primitive_count))
+        finally:
+            r.cleanup()
+        return imgs, tris
+
+    whole, tris = loop(S.synth_vtk_series(fixture, str(tmp_path / "all"), counts, frame_ids=list(range(F))), list(range(F)))
+    assert len({t for t in tris}) == len(set(counts))            # every frame rebuilt its own particle set
+    for world in (2, 3):
+        per_rank = []
+        for rank in range(world):
+            mine = sh.frames_of_rank(F, rank, world)
+            series = S.synth_vtk_series(fixture, str(tmp_path / f"w{world}r{rank}"), [counts[f] for f in mine], frame_ids=mine)
+            per_rank.append(loop(series, mine)[0])
+        got = sh.interleave_frames(per_rank, F)
+        for f in range(F):
+            assert np.array_equal(got[f], whole[f]), f"world {world}: frame {f} differs"
+    assert not np.array_equal(whole[0], whole[1])
+
+
+def test_animation_loop_in_the_library(pkg, tmp_path):
+    """rt_run_vtk_animation (the headless frame loop behind the ABI, several renderer contexts per GPU): every frame
+    it hands to the sink is the frame rt_set_vtk_frame + rt_render_frame give on one context, bit for bit; frame
+    sharding is first_frame = rank, frame_stride = world."""
+    import os
+    S = pkg.scenes
+    fixture = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "particle_frame0.vtk")
+    counts = [25, 31, 28, 40, 33, 26]
+    F = len(counts)
+    series = S.synth_vtk_series(fixture, str(tmp_path), counts, frame_ids=list(range(F)))
+    base = S.c1a(frame=0, width=160, height=90, spp=2, depth=10)
+    want, rays = [], []
+    r = pkg.Renderer(device=0)
+    try:
+        r.commitScene(base)
+        assert r.configureVTKFiles(series) == F
+        for f in range(F):
+            r.setVTKFrame(f)
+            rays.append(r.renderFrame(f, SEED).rays)
+            want.append(r.readFramebuffer(pkg.abi.BUF_RGBA8).reshape(90, 160, 4).copy())
+    finally:
+        r.cleanup()
+    for lanes, first, stride, limit in [(1, 0, 1, 0), (2, 0, 1, 0), (3, 0, 1, 0), (2, 1, 2, 0), (2, 0, 1, 3), (8, 4, 1, 0)]:
+        frames = list(range(first, F, stride))[: (limit or F)]
+        got = {}
+        r = pkg.Renderer(device=0)
+        try:
+            r.commitScene(base)
+            r.configureVTKFiles(series)
+
+            def sink(frame, img, out):
+                assert frame not in got
+                got[frame] = (img.copy(), out.rays)
+
+            st = r.runVTKAnimation(first, stride, limit, SEED, lanes, sink)
+            assert sorted(got) == frames and st.frames == len(frames)
+            assert st.rays == sum(rays[f] for f in frames) and st.wall_ms > 0 and st.device_ms > 0 and 0 < st.slowest_rebuild_ms < 50
+            for f in frames:
+                assert got[f][1] == rays[f]
+                assert np.array_equal(got[f][0], want[f]), f"lanes={lanes}: frame {f} differs"
+            # the context stays usable after the loop (lane 0 is the caller's context)
+            r.setVTKFrame(0)
+            r.renderFrame(0, SEED)
+            assert np.array_equal(r.readFramebuffer(pkg.abi.BUF_RGBA8).reshape(90, 160, 4), want[0])
+            # a sink that returns non-zero stops the loop
+            seen = []
+            with pytest.raises(pkg.RtError) as e:
+                r.runVTKAnimation(0, 1, 0, SEED, lanes, lambda frame, img, out: seen.append(frame) or 1)
+            assert e.value.code == -3 and 1 <= len(seen) <= lanes
+        finally:
+            r.cleanup()
+    with pytest.raises(pkg.RtError):
+        rr = pkg.Renderer(device=0)
+        rr.commitScene(base)
+        rr.runVTKAnimation()                      # no series loaded
+
+
 def test_output_writers(pkg, tmp_path):
     """rt_write_image: PPM / PFM / AOV dumps hold exactly the planes rt_read_framebuffer returns."""
     sc = parity_scenes(pkg.scenes)[0]

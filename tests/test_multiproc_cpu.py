@@ -60,3 +60,68 @@ def test_shard_arithmetic_matches_the_library_rule():
         rows = sum((sh.owned_rows(H, r, world, tr) for r in range(world)), [])
         assert sorted(rows) == list(range(H))
         assert sh.padded_plane_bytes(H, 4, world, tr) >= max(sh.local_rows(H, r, world, tr) for r in range(world)) * 4
+
+
+def _frame_rank_main(rank, world, port, n_frames, out_path):
+    for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import torch
+    import torch.distributed as dist
+    import emul_ctypes as ec
+    pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    sh = pkg.sharding
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    W, H = 48, 27
+
+    def render(f):          # frame f of the animation: the demo instances move with the frame number (Main.cu:6-42)
+        return ec.Emul(pkg.scenes.c1a(frame=f, width=W, height=H, spp=1, depth=4)).render(SEED)["rgba8"].reshape(-1)
+
+    mine = sh.frames_of_rank(n_frames, rank, world)
+    slots = len(sh.frames_of_rank(n_frames, 0, world))                 # rank 0 owns the most frames: pad to that
+    buf = np.zeros((slots, W * H * 4), np.uint8)
+    for j, f in enumerate(mine):
+        buf[j] = render(f)
+    t = torch.from_numpy(buf.reshape(-1))
+    gathered = [torch.empty_like(t) for _ in range(world)] if rank == 0 else None
+    dist.gather(t, gathered, dst=0)                                     # only the finished images travel, once
+    if rank == 0:
+        per_rank = [g.numpy().reshape(slots, -1) for g in gathered]
+        got = np.stack(sh.interleave_frames(per_rank, n_frames))
+        want = np.stack([render(f) for f in range(n_frames)])
+        np.save(out_path, np.stack([got, want]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_frame_shards_cover_the_animation(tmp_path):
+    """Config 3's partitioning: frame i -> rank i % world, no per-frame exchange; the frames the ranks rendered,
+    put back in order, are the frames of the single-rank loop."""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "frames.npy")
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_frame_rank_main, args=(2, port, 5, out), nprocs=2, join=True)
+    got, want = np.load(out)
+    assert np.array_equal(got, want)
+    assert not np.array_equal(want[0], want[1])        # the frames do differ
+
+
+def test_frame_shard_arithmetic_and_rank_local_series(tmp_path):
+    pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    sh, S = pkg.sharding, pkg.scenes
+    for n, world in [(401, 8), (5, 2), (3, 8), (64, 4)]:
+        owned = [sh.frames_of_rank(n, q, world) for q in range(world)]
+        assert sorted(sum(owned, [])) == list(range(n))
+        assert sh.interleave_frames(owned, n) == list(range(n))
+    counts = S.c3_particle_counts(401)
+    assert counts[0] == 25 and counts[-1] == 500 and all(b >= a for a, b in zip(counts, counts[1:]))
+    # a rank's own series holds byte-identical copies of the frames it owns
+    fixture = os.path.join(ROOT, "tests", "golden", "particle_frame0.vtk")
+    cnt = [26, 27, 30, 28]
+    S.synth_vtk_series(fixture, str(tmp_path / "all"), cnt, frame_ids=list(range(4)))
+    mine = sh.frames_of_rank(4, 1, 2)
+    series = S.synth_vtk_series(fixture, str(tmp_path / "r1"), [cnt[f] for f in mine], frame_ids=mine)
+    assert open(series).read().count('"name"') == 2
+    for f in mine:
+        name = f"particle_mesh/particle_{f * 100:015d}.vtk"
+        assert (tmp_path / "all" / name).read_bytes() == (tmp_path / "r1" / name).read_bytes()

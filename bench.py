@@ -265,9 +265,11 @@ def run_c3(args):
         raise RuntimeError("bench.py (our arm) needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
     os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-    R = max(1, args.renderers_per_gpu)
     cores = os.cpu_count() or 1
+    # a lane keeps two host threads busy (its own + its read-ahead): leave each rank its share of the host's cores
+    R = max(1, args.renderers_per_gpu) if args.renderers_per_gpu > 0 else min(3, max(1, cores // (2 * world)))
     os.environ.setdefault("RTB200_HOST_THREADS", str(max(1, min(8, cores // (world * R)))))     # the ranks share the host's cores
+    os.environ.setdefault("RTB200_BLOCKING_WAIT", "1" if world * R * 4 > cores else "0")        # spin only when cores are plentiful
     if distributed:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
@@ -346,9 +348,13 @@ def run_c3(args):
         barrier()
         e_rays = 0
         delivered.clear()
+        host_ms = {"parse": 0.0, "set_frame": 0.0, "render": 0.0, "readback": 0.0, "sink": 0.0}
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            e_rays += one.r.runVTKAnimation(0, 1, 0, SEED, R, sink).rays
+            a = one.r.runVTKAnimation(0, 1, 0, SEED, R, sink)
+            e_rays += a.rays
+            for k, v in (("parse", a.parse_ms), ("set_frame", a.set_frame_ms), ("render", a.render_wall_ms), ("readback", a.readback_ms), ("sink", a.sink_ms)):
+                host_ms[k] += v / max(1, a.frames) / args.steps
         barrier()
         e2e_s = time.perf_counter() - t0
         assert len(delivered) == len(mine) * args.steps
@@ -376,6 +382,7 @@ def run_c3(args):
                         "renderers_per_gpu": R, "host_threads_per_renderer": int(os.environ["RTB200_HOST_THREADS"]), "host_cores": cores,
                         "h2d_bytes_per_step": int(tot_tris / args.steps * 36), "d2h_bytes_per_step": int(F * (W * H * 4 + 64)),
                         "ms_per_step": 1e3 * max_e2e_s / args.steps, "vtk_bytes_read_per_step": int(tot_bytes),
+                        "rank0_host_ms_per_frame": {k: round(v, 3) for k, v in host_ms.items()},
                         "what": "rt_run_vtk_animation: per frame disk -> host (read ahead), commit, H2D, rebuild, render, RGBA8 -> pinned host, sink call; host wall clock"},
                 "gpu_launches": int(tot_launches), "clocks": clocks}
         print(json.dumps(line))
@@ -585,7 +592,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c2", choices=["c2", "c3", "c4", "c5"], help="c2 = the bench line (BASELINE configs[1]); c3 (animation, frames sharded) / c4 / c5 = the other GPU configs, extra lines")
     ap.add_argument("--frames", type=int, default=64, help="--config c3: frames of the synthesised particle animation")
-    ap.add_argument("--renderers-per-gpu", type=int, default=3, help="--config c3, e2e pass: renderer contexts (host threads) per GPU")
+    ap.add_argument("--renderers-per-gpu", type=int, default=0, help="--config c3, e2e pass: renderer contexts (lanes of rt_run_vtk_animation) per GPU; 0 = min(3, host cores / (2 x ranks))")
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--spp", type=int, default=64)

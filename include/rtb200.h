@@ -282,6 +282,12 @@ typedef struct rt_animation_stats {
     double   wall_ms;             /* host wall clock of the whole loop                                   */
     double   device_ms;           /* sum over frames of CUDA-event rebuild + render time (lanes overlap) */
     double   slowest_rebuild_ms;  /* max over frames of BLAS batch + TLAS rebuild                        */
+    /* where the lanes' host threads spent their time, summed over frames (host wall clock per call) */
+    double   parse_ms;            /* read-ahead threads: file -> triangles (overlaps everything else)    */
+    double   set_frame_ms;        /* rt_set_vtk_frame: wait for the read-ahead, compose, commit, H2D, rebuild */
+    double   render_wall_ms;      /* rt_render_frame                                                     */
+    double   readback_ms;         /* RGBA8 plane -> pinned host                                          */
+    double   sink_ms;             /* inside the caller's sink (incl. waiting for the other lanes' calls) */
 } rt_animation_stats;
 typedef int (*rt_frame_sink)(void *user, size_t frame, const void *rgba8, size_t bytes, const rt_frame_out *out);
 int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t frame_stride, size_t max_frames, uint64_t seed, int lanes,

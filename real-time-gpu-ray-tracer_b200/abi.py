@@ -78,7 +78,9 @@ class BuildStats(C.Structure):
 
 class AnimationStats(C.Structure):
     _fields_ = [("frames", C.c_uint64), ("rays", C.c_uint64), ("triangles", C.c_uint64), ("kernel_launches", C.c_uint64),
-                ("wall_ms", C.c_double), ("device_ms", C.c_double), ("slowest_rebuild_ms", C.c_double)]
+                ("wall_ms", C.c_double), ("device_ms", C.c_double), ("slowest_rebuild_ms", C.c_double),
+                ("parse_ms", C.c_double), ("set_frame_ms", C.c_double), ("render_wall_ms", C.c_double), ("readback_ms", C.c_double),
+                ("sink_ms", C.c_double)]
 
 
 FRAME_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(FrameOut))

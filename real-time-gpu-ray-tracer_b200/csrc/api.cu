@@ -116,6 +116,19 @@ struct rt_ctx {
     // calls so that their device buffers, page-locked ranges and jump tables are allocated once
     std::vector<rt_ctx *> lane_ctx;
     PinnedBuffer<uint8_t> h_frame;
+    // Host waits of the frame path.  cudaStreamSynchronize spins; with several lanes per GPU and several ranks per host the
+    // spinning threads would take the cores the other lanes' parsing and commits need, so inside the animation loop the
+    // wait sleeps on a blocking-sync event instead.
+    cudaEvent_t ev_block = nullptr;
+    bool blocking_wait = false;
+    void wait() {
+        if (blocking_wait && ev_block) {
+            CUDA_CHECK(cudaEventRecord(ev_block, stream));
+            CUDA_CHECK(cudaEventSynchronize(ev_block));
+        } else {
+            CUDA_CHECK(cudaStreamSynchronize(stream));
+        }
+    }
 };
 
 namespace {
@@ -196,6 +209,7 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     try {
         CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
         for (auto &e: c->ev) CUDA_CHECK(cudaEventCreate(&e));
+        CUDA_CHECK(cudaEventCreateWithFlags(&c->ev_block, cudaEventBlockingSync | cudaEventDisableTiming));
         CUDA_CHECK(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, cuda_device));
     } catch (const std::exception &) {
         delete c;
@@ -226,6 +240,7 @@ int rt_cleanup(rt_ctx *ctx) {
     for (auto &st: ctx->vtk_stage) st.join();
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); }
     for (auto &e: ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->ev_block) cudaEventDestroy(ctx->ev_block);
     cudaStream_t s = ctx->stream;
     delete ctx;   // frees device buffers
     if (s) cudaStreamDestroy(s);
@@ -252,7 +267,7 @@ int rt_commit_geometry(rt_ctx *ctx, const rt_sphere *spheres, size_t sphere_coun
     ctx->d_quads.upload(ctx->hs.quad_rec.data(), ctx->hs.quad_rec.size(), ctx->stream);
     ctx->d_tri_verts.upload(ctx->hs.tri_verts.data(), ctx->hs.tri_verts.size(), ctx->stream);
     ctx->d_tri_shade.upload(ctx->hs.tri_shade.data(), ctx->hs.tri_shade.size(), ctx->stream);
-    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    ctx->wait();
     ctx->geometry_committed = true;
     RT_API_END(ctx)
 }
@@ -314,6 +329,7 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     ctx->blas.emit_bvh2 = ctx->tlas.emit_bvh2 = (ctx->flags & (RT_FLAG_TRAVERSE_BVH2 | RT_FLAG_KEEP_LBVH)) != 0;
     // rotated subtrees no longer cover one contiguous Morton range, which multi-primitive leaves (a tuning experiment) rely on
     ctx->blas.sah_rotations = ctx->tlas.sah_rotations = (ctx->flags & RT_FLAG_SAH_REFINE) && !getenv("RTB200_LEAF_MAX");
+    ctx->blas.wait_event = ctx->tlas.wait_event = ctx->blocking_wait ? ctx->ev_block : nullptr;
     ctx->blas.prepare_blas(hs.seg_offset, hs.seg_type);          // allocations stay outside the timed build
     ctx->d_instances.reserve(n_inst);
     ctx->d_xform_in.reserve(n_inst);
@@ -327,7 +343,7 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     // TLAS (also rebuilt every frame)
     update_instances_and_tlas(ctx);
     CUDA_CHECK(cudaEventRecord(ctx->ev[2], ctx->stream));
-    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    ctx->wait();
     rt_build_stats &st = ctx->build_stats;
     CUDA_CHECK(cudaEventElapsedTime(&st.blas_ms, ctx->ev[0], ctx->ev[1]));
     CUDA_CHECK(cudaEventElapsedTime(&st.tlas_ms, ctx->ev[1], ctx->ev[2]));
@@ -431,7 +447,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     }
     CUDA_CHECK(cudaEventRecord(ctx->ev[3], s));
     CUDA_CHECK(cudaMemcpyAsync(ctx->h_counters.get(), ctx->d_counters.get(), 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-    CUDA_CHECK(cudaStreamSynchronize(s));
+    ctx->wait();
     if (out) {
         memset(out, 0, sizeof(*out));
         out->rays = ws.rays + ctx->h_counters.get()[0];      // rays of the wave queues (host-counted) + rays counted on the device
@@ -490,7 +506,7 @@ int rt_read_framebuffer(rt_ctx *ctx, int kind, void *host_dst, size_t dst_bytes)
     if (rc != RT_OK) return rc;
     if (!host_dst || dst_bytes < n) return fail(ctx, RT_ERR_ARGUMENT, "rt_read_framebuffer: destination too small");
     CUDA_CHECK(cudaMemcpyAsync(host_dst, p, n, cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    ctx->wait();
     RT_API_END(ctx)
 }
 
@@ -716,34 +732,45 @@ void run_lane(rt_ctx *c, const std::vector<size_t> &frames, uint64_t seed, Anima
     if (cudaSetDevice(c->device) != cudaSuccess) { bail(RT_ERR_CUDA, "cudaSetDevice failed"); return; }
     size_t plane = 0;
     PinnedBuffer<uint8_t> &host = c->h_frame;
+    using clk = std::chrono::steady_clock;
+    auto ms_since = [](clk::time_point t) { return std::chrono::duration<double, std::milli>(clk::now() - t).count(); };
     int rc = rt_prefetch_vtk_frame(c, frames[0]);
     for (size_t j = 0; rc == RT_OK && j < frames.size() && sh->stop.load() == 0; j++) {
+        clk::time_point t = clk::now();
         rc = rt_set_vtk_frame(c, frames[j]);
         if (rc != RT_OK) break;
+        const double set_ms = ms_since(t), parse_ms = c->vtk_parse_ms;
         if (j + 1 < frames.size()) rc = rt_prefetch_vtk_frame(c, frames[j + 1]);     // parsed while this frame renders
         if (rc != RT_OK) break;
         rt_frame_out out{};
+        t = clk::now();
         rc = rt_render_frame(c, frames[j], seed, &out);
         if (rc != RT_OK) break;
+        const double render_ms = ms_since(t);
         plane = (size_t) c->hs.window.width * c->local_rows * 4;
         try {
             host.reserve(plane + 4);
         } catch (const std::exception &e) { c->err = e.what(); rc = RT_ERR_CUDA; break; }
+        t = clk::now();
         rc = rt_read_framebuffer(c, RT_BUFFER_RGBA8, host.get(), plane);
         if (rc != RT_OK) break;
+        const double read_ms = ms_since(t);
+        t = clk::now();
         std::lock_guard<std::mutex> g(sh->mu);
-        rt_animation_stats &t = sh->tot;
-        t.frames++;
-        t.rays += out.rays;
-        t.triangles += c->build_stats.primitive_count;
-        t.kernel_launches += c->build_stats.kernel_launches + out.kernel_launches;
+        rt_animation_stats &tot = sh->tot;
+        tot.frames++;
+        tot.rays += out.rays;
+        tot.triangles += c->build_stats.primitive_count;
+        tot.kernel_launches += c->build_stats.kernel_launches + out.kernel_launches;
         const double rebuild = (double) c->build_stats.blas_ms + c->build_stats.tlas_ms;
-        t.device_ms += rebuild + out.render_ms;
-        if (rebuild > t.slowest_rebuild_ms) t.slowest_rebuild_ms = rebuild;
+        tot.device_ms += rebuild + out.render_ms;
+        if (rebuild > tot.slowest_rebuild_ms) tot.slowest_rebuild_ms = rebuild;
+        tot.parse_ms += parse_ms; tot.set_frame_ms += set_ms; tot.render_wall_ms += render_ms; tot.readback_ms += read_ms;
         if (sh->sink && sh->sink(sh->user, frames[j], host.get(), plane, &out) != 0) {
             int expected = 0;
             if (sh->stop.compare_exchange_strong(expected, RT_ERR_STATE)) sh->err = "rt_run_vtk_animation: stopped by the frame sink";
         }
+        tot.sink_ms += ms_since(t);
     }
     for (auto &st: c->vtk_stage) st.join();       // a read-ahead may still be running after an early stop
     c->vtk_ahead = -1;
@@ -777,6 +804,11 @@ extern "C" int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t fram
     }
     std::vector<std::vector<size_t>> lane_frames(L);
     for (size_t k = 0; k < frames.size(); k++) lane_frames[k % L].push_back(frames[k]);
+    std::vector<bool> was_blocking;
+    // RTB200_BLOCKING_WAIT=0/1 overrides; default: sleep when several lanes share the host, spin (lower latency) with one
+    const char *bw = getenv("RTB200_BLOCKING_WAIT");
+    const bool block = bw ? atoi(bw) != 0 : L > 1;
+    for (rt_ctx *c: lane_ctx) { was_blocking.push_back(c->blocking_wait); c->blocking_wait = block; }
     AnimationShared sh;
     sh.sink = sink;
     sh.user = user;
@@ -786,6 +818,7 @@ extern "C" int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t fram
     run_lane(ctx, lane_frames[0], seed, &sh);
     for (std::thread &t: th) t.join();
     sh.tot.wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    for (size_t k = 0; k < lane_ctx.size(); k++) lane_ctx[k]->blocking_wait = was_blocking[k];
     cudaSetDevice(ctx->device);
     if (stats) *stats = sh.tot;
     if (sh.stop.load() != 0) return fail(ctx, sh.stop.load(), sh.err);

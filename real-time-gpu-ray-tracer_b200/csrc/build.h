@@ -68,6 +68,7 @@ public:
     const float4 *node_lo() const { return node_lo_.get(); }
     const float4 *node_hi() const { return node_hi_.get(); }
     uint32_t launches = 0;
+    cudaEvent_t wait_event = nullptr;        // blocking-sync event for the host wait in build_blas (nullptr: cudaStreamSynchronize)
     size_t node_bytes() const { return (size_t) (n_ > 1 ? n_ - 1 : 0) * sizeof(BvhNode2); }
 
 private:

@@ -460,7 +460,12 @@ void LbvhBuilder::build_blas(const GeometryD &geo, const std::vector<uint32_t> &
     run_tree(n, n_segs, 3 * morton_bits + seg_bits, 0, &geo, stream, sm_count);
     seg_root_host.resize(n_segs);
     CUDA_CHECK(cudaMemcpyAsync(seg_root_host.data(), seg_root_.get(), n_segs * sizeof(int), cudaMemcpyDeviceToHost, stream));
-    CUDA_CHECK(cudaStreamSynchronize(stream));
+    if (wait_event) {                    // sleep instead of spinning (animation lanes, see rt_ctx::wait in api.cu)
+        CUDA_CHECK(cudaEventRecord(wait_event, stream));
+        CUDA_CHECK(cudaEventSynchronize(wait_event));
+    } else {
+        CUDA_CHECK(cudaStreamSynchronize(stream));
+    }
 }
 
 void LbvhBuilder::prepare_blas(const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type) {

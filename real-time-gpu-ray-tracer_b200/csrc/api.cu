@@ -87,6 +87,8 @@ struct rt_ctx {
     // (rt_prefetch_vtk_frame) while the GPU renders; the vectors keep their capacity from frame to frame.
     struct VtkStage {
         VtkFrame vf;
+        VtkCompact compact;                 // device expansion (default): per-point tables + strip ids instead of `tris`
+        bool expand_on_device = true;
         std::vector<rt_triangle> tris;
         std::vector<rt_instance_desc> inst;
         std::vector<rt_instance_xform> xf;
@@ -100,12 +102,20 @@ struct rt_ctx {
             frame = f;
             err.clear();
             ok = vf.read(series.dir + series.files[f].first, err);
-            if (ok) vtk_convert(vf, tris, inst, xf);
+            if (ok) {
+                if (expand_on_device) vtk_convert_compact(vf, compact, inst, xf);
+                else vtk_convert(vf, tris, inst, xf);
+            }
             parse_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
         }
         void join() { if (worker.joinable()) worker.join(); }
     };
     VtkStage vtk_stage[2];
+    // strips -> triangle records on the device (launch_expand_strips); RTB200_VTK_EXPAND=host keeps the host conversion
+    bool vtk_expand_on_device = true;
+    DeviceBuffer<float> d_vtk_points, d_vtk_normals;
+    DeviceBuffer<int> d_vtk_ids;
+    DeviceBuffer<uint32_t> d_vtk_first_tri, d_vtk_first_id;
     int vtk_ahead = -1;             // stage a read-ahead is running on / has finished in (-1: none)
     std::vector<rt_triangle> user_tris;
     std::vector<rt_instance_desc> user_inst;
@@ -226,6 +236,8 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     c->persist.blocks_per_sm_override = c->wave.blocks_per_sm_override;
     if (const char *e = getenv("RTB200_SHADE_MIN")) c->persist.shade_min = atoi(e);
     if (const char *e = getenv("RTB200_TILE_ORDER")) c->persist.tile_order = atoi(e);
+    if (const char *e = getenv("RTB200_VTK_EXPAND")) c->vtk_expand_on_device = strcmp(e, "host") != 0;
+    for (auto &st: c->vtk_stage) st.expand_on_device = c->vtk_expand_on_device;
     if (flags & RT_FLAG_WAVEFRONT) c->path_mode = 0;
     if (const char *e = getenv("RTB200_MODE")) c->path_mode = strcmp(e, "wave") == 0 ? 0 : 1;     // tuning / A-B runs
     *out = c;
@@ -638,8 +650,9 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
     st.frame = (size_t) -1;                                     // consumed (tris gets the user's triangles appended below)
     // compose: VTK triangles at the head of the triangle array, user TRIANGLE instances shifted by their count,
     // VTK instances after the user's (reference src/Global/Renderer.cu:17,106-108,114-116)
-    const size_t n_vtk_tris = tris.size();
-    tris.insert(tris.end(), ctx->user_tris.begin(), ctx->user_tris.end());
+    const bool on_device = st.expand_on_device;
+    const size_t n_vtk_tris = on_device ? st.compact.n_tris : tris.size();
+    if (!on_device) tris.insert(tris.end(), ctx->user_tris.begin(), ctx->user_tris.end());
     std::vector<rt_instance_desc> all_inst(ctx->user_inst);
     for (rt_instance_desc &d: all_inst) if (d.type == RT_TRIANGLE) d.first_prim += n_vtk_tris;
     all_inst.insert(all_inst.end(), inst.begin(), inst.end());
@@ -648,11 +661,37 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
     const std::vector<rt_sphere> spheres(ctx->hs.spheres);
     const std::vector<rt_parallelogram> quads(ctx->hs.quads);
     ctx->composing = true;
-    int rc = rt_commit_geometry(ctx, spheres.data(), spheres.size(), quads.data(), quads.size(), tris.data(), tris.size());
+    int rc = RT_OK;
+    if (on_device) {
+        // spheres and parallelograms stay as committed; the frame's triangles are expanded from the strips on the device
+        // and the caller's own triangles (converted on the host, a handful) follow them
+        const VtkCompact &vc = st.compact;
+        const size_t n_user = ctx->user_tris.size(), n_all = n_vtk_tris + n_user;
+        const std::string e = ctx->hs.commit_triangle_tail(n_vtk_tris, ctx->user_tris.data(), n_user);
+        if (!e.empty()) { ctx->composing = false; return fail(ctx, RT_ERR_ARGUMENT, e); }
+        cudaStream_t s = ctx->stream;
+        ctx->d_tri_verts.reserve(n_all * 9);
+        ctx->d_tri_shade.reserve(n_all);
+        ctx->d_vtk_points.upload(&vc.points.data()->x, vc.points.size() * 3, s);
+        ctx->d_vtk_normals.upload(&vc.normals.data()->x, vc.normals.size() * 3, s);
+        ctx->d_vtk_ids.upload(vc.ids.data(), vc.ids.size(), s);
+        ctx->d_vtk_first_tri.upload(vc.strip_first_tri.data(), vc.strip_first_tri.size(), s);
+        ctx->d_vtk_first_id.upload(vc.strip_first_id.data(), vc.strip_first_id.size(), s);
+        launch_expand_strips(ctx->d_vtk_points.get(), ctx->d_vtk_normals.get(), ctx->d_vtk_ids.get(), ctx->d_vtk_first_tri.get(), ctx->d_vtk_first_id.get(),
+                             (int) vc.strip_first_id.size(), (uint32_t) n_vtk_tris, RT_METAL, 0u, ctx->d_tri_verts.get(), ctx->d_tri_shade.get(), s);
+        if (n_user) {
+            CUDA_CHECK(cudaMemcpyAsync(ctx->d_tri_verts.get() + n_vtk_tris * 9, ctx->hs.tri_verts.data() + n_vtk_tris * 9, n_user * 9 * sizeof(float), cudaMemcpyHostToDevice, s));
+            CUDA_CHECK(cudaMemcpyAsync(ctx->d_tri_shade.get() + n_vtk_tris, ctx->hs.tri_shade.data() + n_vtk_tris, n_user * sizeof(TriShade), cudaMemcpyHostToDevice, s));
+        }
+        ctx->built = false;          // the build that follows on the same stream is ordered after the expansion
+    } else {
+        rc = rt_commit_geometry(ctx, spheres.data(), spheres.size(), quads.data(), quads.size(), tris.data(), tris.size());
+    }
     if (rc == RT_OK) rc = rt_configure_instances(ctx, all_inst.data(), all_inst.size(), all_xf.data(), nullptr, nullptr);
     if (rc == RT_OK) rc = rt_build_acceleration_structure(ctx);
     ctx->composing = false;
     if (rc != RT_OK) return rc;
+    if (on_device) ctx->build_stats.kernel_launches += 1;       // expand_strips_kernel
     RT_API_END(ctx)
 }
 

@@ -97,5 +97,9 @@ private:
 
 // per-frame instance update (device restatement of Instance::updateTransformArguments); writes InstanceD
 // records plus the TLAS builder's prim boxes and scene bounds.
+// triangle strips of a particle frame -> triangle vertex + shading records (config 3 input stage; kernels_build.cu)
+void launch_expand_strips(const float *points, const float *normals, const int *ids, const uint32_t *strip_first_tri, const uint32_t *strip_first_id,
+                          int n_strips, uint32_t n_tris, uint32_t material_type, uint32_t material_index, float *tri_verts, TriShade *tri_shade,
+                          cudaStream_t stream);
 void launch_instance_update(const InstanceXformIn *in, int n, InstanceD *out, float4 *wlo, float4 *whi, float4 *wcentroid,
                             uint32_t *bounds, const float *tri_verts, cudaStream_t stream);

@@ -77,9 +77,25 @@ std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_p
     }
     tri_verts.resize(nt * 9);
     tri_shade.resize(nt);
-    parallel_for(nt, true, [&](size_t i) {
+    convert_triangles(t, nt, 0);
+    return "";
+}
+
+std::string HostScene::commit_triangle_tail(size_t n_head, const rt_triangle *t, size_t nt) {
+    if (nt && !t) return "commit_triangle_tail: null array with non-zero count";
+    if (n_head + nt > RT_REF_POS_MASK) return "rt_commit_geometry: more than 2^29 primitives of one type";
+    n_tris = n_head + nt;
+    tri_verts.resize(n_tris * 9);
+    tri_shade.resize(n_tris);
+    convert_triangles(t, nt, n_head);
+    return "";
+}
+
+void HostScene::convert_triangles(const rt_triangle *t, size_t nt, size_t at) {
+    parallel_for(nt, true, [&](size_t q) {
         // Triangle constructors (reference include/Geometry/Triangle.cuh:26-46)
-        const rt_triangle &g = t[i];
+        const size_t i = at + q;
+        const rt_triangle &g = t[q];
         float *v = &tri_verts[i * 9];
         for (int k = 0; k < 3; k++) { v[3 * k] = g.v[k].x; v[3 * k + 1] = g.v[k].y; v[3 * k + 2] = g.v[k].z; }
         f3 n0, n1, n2;
@@ -92,7 +108,6 @@ std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_p
         tri_shade[i].n1_mi = make_float4(n1.x, n1.y, n1.z, u2f(g.material_index));
         tri_shade[i].n2 = make_float4(n2.x, n2.y, n2.z, 0.0f);
     }, 65536);
-    return "";
 }
 
 std::string HostScene::commit_materials(const rt_rough *r, size_t nr, const rt_metal *m, size_t nm) {

@@ -38,6 +38,9 @@ struct HostScene {
 
     // each returns an empty string on success, else the error text (-> RT_ERR_ARGUMENT)
     std::string commit_geometry(const rt_sphere *s, size_t ns, const rt_parallelogram *p, size_t np, const rt_triangle *t, size_t nt);
+    // animation frames whose first n_head triangles are produced on the device (strip expansion): only the caller's own
+    // triangles, which follow them, are converted here (tri_verts / tri_shade keep stale values in the head)
+    std::string commit_triangle_tail(size_t n_head, const rt_triangle *t, size_t nt);
     std::string commit_materials(const rt_rough *r, size_t nr, const rt_metal *m, size_t nm);
     std::string commit_dielectrics(const rt_dielectric *d, size_t n);
     std::string configure_instances(const rt_instance_desc *d, size_t n, const rt_instance_xform *x);
@@ -46,6 +49,7 @@ struct HostScene {
     // per frame: transform arguments -> kernel input records (trig evaluated here with the host libm)
     void fill_xform_in(InstanceXformIn *out, const std::vector<int> &seg_root) const;
     size_t prim_bytes() const;
+    void convert_triangles(const rt_triangle *t, size_t nt, size_t at);      // rt_triangle[k] -> tri_verts / tri_shade[at + k]
 };
 
 int morton_bits_for(size_t n);

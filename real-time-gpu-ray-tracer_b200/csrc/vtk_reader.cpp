@@ -1,6 +1,7 @@
 #include "vtk_reader.h"
 #include "host_parallel.h"
 
+#include <chrono>
 #include <climits>
 #include <cstdint>
 #include <thread>
@@ -8,6 +9,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
@@ -48,8 +50,8 @@ bool VtkSeries::load(const std::string &series_path, std::string &err) {
 // Does the job of vtkPolyDataReader in VTKReader::readVTKFile (reference src/Global/VTKReader.cu:16-57): header check,
 // POINTS, TRIANGLE_STRIPS, and the presence of the cell arrays "id" and "vel" the reference insists on (:52-57).
 namespace {
-uint32_t be32(const unsigned char *p) { return ((uint32_t) p[0] << 24) | ((uint32_t) p[1] << 16) | ((uint32_t) p[2] << 8) | p[3]; }
-uint64_t be64(const unsigned char *p) { return ((uint64_t) be32(p) << 32) | be32(p + 4); }
+uint32_t be32(const unsigned char *p) { uint32_t u; memcpy(&u, p, 4); return __builtin_bswap32(u); }
+uint64_t be64(const unsigned char *p) { uint64_t u; memcpy(&u, p, 8); return __builtin_bswap64(u); }
 // next text line starting at pos (skipping blank lines); returns false at EOF
 bool next_line(const std::string &s, size_t &pos, std::string &line) {
     while (pos < s.size()) {
@@ -65,11 +67,19 @@ bool next_line(const std::string &s, size_t &pos, std::string &line) {
 }
 
 bool VtkFrame::read(const std::string &path, std::string &err) {
-    std::ifstream f(path, std::ios::binary);
-    if (!f.is_open()) { err = "cannot open vtk file " + path; return false; }
-    std::stringstream ss;
-    ss << f.rdbuf();
-    const std::string s = ss.str();
+    // one read() of the whole file into a buffer that keeps its capacity from frame to frame
+    std::string &s = file_;
+    {
+        FILE *fp = fopen(path.c_str(), "rb");
+        if (!fp) { err = "cannot open vtk file " + path; return false; }
+        fseek(fp, 0, SEEK_END);
+        const long bytes = ftell(fp);
+        fseek(fp, 0, SEEK_SET);
+        s.resize(bytes > 0 ? (size_t) bytes : 0);
+        const size_t got = s.empty() ? 0 : fread(&s[0], 1, s.size(), fp);
+        fclose(fp);
+        if (got != s.size()) { err = "short read of vtk file " + path; return false; }
+    }
     size_t pos = 0;
     std::string line;
     if (!next_line(s, pos, line) || line.find("# vtk DataFile Version") == std::string::npos) { err = "illegal vtk file header in " + path; return false; }
@@ -109,11 +119,14 @@ bool VtkFrame::read(const std::string &path, std::string &err) {
                 const size_t len = be32(p + 4 * k++);
                 if (k + len > size) { err = "truncated TRIANGLE_STRIPS cell in " + path; return false; }
                 strips[c].resize(len);
+                int *dst = strips[c].data();
+                uint32_t worst = 0;
                 for (size_t j = 0; j < len; j++) {
                     const uint32_t id = be32(p + 4 * k++);
-                    if ((size_t) id * 3 + 2 >= points.size()) { err = "point id out of range in " + path; return false; }
-                    strips[c][j] = (int) id;
+                    worst = id > worst ? id : worst;
+                    dst[j] = (int) id;
                 }
+                if (len && (size_t) worst * 3 + 2 >= points.size()) { err = "point id out of range in " + path; return false; }
             }
             pos += size * 4;
             have_strips = true;
@@ -129,11 +142,12 @@ bool VtkFrame::read(const std::string &path, std::string &err) {
     return true;
 }
 
-void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vector<rt_instance_desc> &inst,
-                 std::vector<rt_instance_xform> &xforms) {
+namespace {
+// point normals of a frame (restated, parity unpinned — see vtk_reader.h), float64, unit length or zero
+void point_normals(const VtkFrame &frame, std::vector<double> &nrm) {
     const std::vector<double> &P = frame.points;
     const size_t n_points = P.size() / 3, n_strips = frame.strips.size();
-    std::vector<double> nrm(n_points * 3, 0.0);
+    nrm.assign(n_points * 3, 0.0);
     // strips that share no point (one particle = its own points, the layout of the series) can be converted concurrently
     bool disjoint = true;
     {
@@ -150,12 +164,19 @@ void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vec
     parallel_for(n_strips, disjoint, [&](size_t k) {
         const std::vector<int> &strip = frame.strips[k];
         if (strip.size() < 3) return;
-        std::vector<int> uniq(strip);
-        std::sort(uniq.begin(), uniq.end());
-        uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+        // centroid of the strip's distinct points, summed in ascending id order
+        int lo = INT32_MAX, hi = -1;
+        for (int id: strip) { lo = std::min(lo, id); hi = std::max(hi, id); }
+        std::vector<unsigned char> seen((size_t) (hi - lo + 1), 0);
+        for (int id: strip) seen[id - lo] = 1;
         double c[3] = {0, 0, 0};
-        for (int id: uniq) for (int a = 0; a < 3; a++) c[a] += P[3 * id + a];
-        for (int a = 0; a < 3; a++) c[a] /= (double) uniq.size();
+        size_t n_uniq = 0;
+        for (int id = lo; id <= hi; id++) {
+            if (!seen[id - lo]) continue;
+            n_uniq++;
+            for (int a = 0; a < 3; a++) c[a] += P[3 * id + a];
+        }
+        for (int a = 0; a < 3; a++) c[a] /= (double) n_uniq;
         for (size_t j = 0; j + 2 < strip.size(); j++) {
             const int i0 = strip[j], i1 = strip[j + 1], i2 = strip[j + 2];
             if (i0 == i1 || i1 == i2 || i0 == i2) continue;
@@ -175,30 +196,97 @@ void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vec
         const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
         if (len > 0.0) { n[0] /= len; n[1] /= len; n[2] /= len; }
     }
-    // ---- triangles + instances (strips shorter than 3 points give nothing, like the serial loop they replace) ----
-    std::vector<size_t> first(n_strips + 1, 0), slot(n_strips + 1, 0);
+}
+
+// per-strip triangle / instance-slot offsets and the instance records (bounds, centroid: VTKReader.cu:97-128)
+void strip_layout(const VtkFrame &frame, std::vector<size_t> &first, std::vector<size_t> &slot) {
+    const size_t n_strips = frame.strips.size();
+    first.assign(n_strips + 1, 0);
+    slot.assign(n_strips + 1, 0);
     for (size_t k = 0; k < n_strips; k++) {
         const size_t m = frame.strips[k].size();
         first[k + 1] = first[k] + (m >= 3 ? m - 2 : 0);
         slot[k + 1] = slot[k] + (m >= 3 ? 1 : 0);
     }
+}
+rt_instance_desc strip_instance(const std::vector<double> &P, const std::vector<int> &strip, size_t first_prim) {
+    rt_instance_desc d{};
+    d.type = RT_TRIANGLE;
+    d.has_bounds = 1;
+    d.first_prim = first_prim;
+    d.prim_count = strip.size() - 2;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300}, c[3] = {0, 0, 0};
+    for (int id: strip)
+        for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], P[3 * id + a]); hi[a] = std::max(hi[a], P[3 * id + a]); c[a] += P[3 * id + a]; }
+    for (int a = 0; a < 3; a++) { d.bounds_min[a] = (float) lo[a]; d.bounds_max[a] = (float) hi[a]; d.centroid[a] = (float) (c[a] / (double) strip.size()); }
+    return d;
+}
+const rt_instance_xform PARTICLE_XFORM{{0.0f, 4.0f, 0.0f}, {90.0f, 0.0f, 0.0f}, {3.0f, 3.0f, 3.0f}};     // VTKReader.cu:210-214
+} // namespace
+
+void vtk_convert_compact(const VtkFrame &frame, VtkCompact &out, std::vector<rt_instance_desc> &inst, std::vector<rt_instance_xform> &xforms) {
+    const std::vector<double> &P = frame.points;
+    const size_t n_points = P.size() / 3, n_strips = frame.strips.size();
+    std::vector<double> nrm;
+#ifdef VTK_PROFILE
+    auto T0 = std::chrono::steady_clock::now();
+#endif
+    point_normals(frame, nrm);
+#ifdef VTK_PROFILE
+    fprintf(stderr, "point_normals %.2f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - T0).count());
+#endif
+    out.points.resize(n_points);
+    out.normals.resize(n_points);
+    for (size_t i = 0; i < n_points; i++) {
+        out.points[i] = rt_vec3{(float) P[3 * i], (float) P[3 * i + 1], (float) P[3 * i + 2]};
+        out.normals[i] = rt_vec3{(float) nrm[3 * i], (float) nrm[3 * i + 1], (float) nrm[3 * i + 2]};
+    }
+    std::vector<size_t> first, slot;
+    strip_layout(frame, first, slot);
+    out.n_tris = first[n_strips];
+    out.strip_first_tri.clear();
+    out.strip_first_id.clear();
+    out.ids.clear();
+    inst.assign(slot[n_strips], rt_instance_desc{});
+    xforms.assign(slot[n_strips], PARTICLE_XFORM);
+    for (size_t k = 0; k < n_strips; k++) {
+        const std::vector<int> &strip = frame.strips[k];
+        if (strip.size() < 3) continue;
+        out.strip_first_tri.push_back((uint32_t) first[k]);
+        out.strip_first_id.push_back((uint32_t) out.ids.size());
+        out.ids.insert(out.ids.end(), strip.begin(), strip.end());
+    }
+    out.strip_first_tri.push_back((uint32_t) out.n_tris);          // sentinel
+    parallel_for(n_strips, true, [&](size_t k) {
+        const std::vector<int> &strip = frame.strips[k];
+        if (strip.size() >= 3) inst[slot[k]] = strip_instance(P, strip, first[k]);
+    });
+}
+
+void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vector<rt_instance_desc> &inst,
+                 std::vector<rt_instance_xform> &xforms) {
+    const std::vector<double> &P = frame.points;
+    const size_t n_points = P.size() / 3, n_strips = frame.strips.size();
+    std::vector<double> nrm;
+    point_normals(frame, nrm);
+    // ---- triangles + instances (strips shorter than 3 points give nothing, like the serial loop they replace) ----
+    std::vector<size_t> first, slot;
+    strip_layout(frame, first, slot);
     tris.resize(first[n_strips]);                 // every element is overwritten below; a caller that keeps the vector pays no page faults
     inst.assign(slot[n_strips], rt_instance_desc{});
-    xforms.assign(slot[n_strips], rt_instance_xform{{0.0f, 4.0f, 0.0f}, {90.0f, 0.0f, 0.0f}, {3.0f, 3.0f, 3.0f}});
-    auto vert = [&](int id) { return rt_vec3{(float) P[3 * id], (float) P[3 * id + 1], (float) P[3 * id + 2]}; };
-    auto norm = [&](int id) { return rt_vec3{(float) nrm[3 * id], (float) nrm[3 * id + 1], (float) nrm[3 * id + 2]}; };
+    xforms.assign(slot[n_strips], PARTICLE_XFORM);
+    // single-precision tables: every point is used by ~30 triangle corners
+    std::vector<rt_vec3> Pf(n_points), Nf(n_points);
+    for (size_t i = 0; i < n_points; i++) {
+        Pf[i] = rt_vec3{(float) P[3 * i], (float) P[3 * i + 1], (float) P[3 * i + 2]};
+        Nf[i] = rt_vec3{(float) nrm[3 * i], (float) nrm[3 * i + 1], (float) nrm[3 * i + 2]};
+    }
+    auto vert = [&](int id) { return Pf[id]; };
+    auto norm = [&](int id) { return Nf[id]; };
     parallel_for(n_strips, true, [&](size_t k) {
         const std::vector<int> &strip = frame.strips[k];
         if (strip.size() < 3) return;
-        rt_instance_desc d{};
-        d.type = RT_TRIANGLE;
-        d.has_bounds = 1;
-        d.first_prim = first[k];
-        d.prim_count = strip.size() - 2;
-        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300}, c[3] = {0, 0, 0};
-        for (int id: strip)
-            for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], P[3 * id + a]); hi[a] = std::max(hi[a], P[3 * id + a]); c[a] += P[3 * id + a]; }
-        for (int a = 0; a < 3; a++) { d.bounds_min[a] = (float) lo[a]; d.bounds_max[a] = (float) hi[a]; d.centroid[a] = (float) (c[a] / (double) strip.size()); }
+        const rt_instance_desc d = strip_instance(P, strip, first[k]);
         rt_triangle *out = tris.data() + first[k];
         for (size_t j = 0; j + 2 < strip.size(); j++) {
             const int i0 = strip[j], i1 = (j & 1) ? strip[j + 2] : strip[j + 1], i2 = (j & 1) ? strip[j + 1] : strip[j + 2];

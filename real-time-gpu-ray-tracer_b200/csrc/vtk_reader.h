@@ -19,6 +19,7 @@ struct VtkFrame {
     std::vector<double> points;                 // 3 per point
     std::vector<std::vector<int>> strips;       // point ids of each TRIANGLE_STRIPS cell (= one particle)
     bool read(const std::string &path, std::string &err);
+    std::string file_;                          // the file's bytes (capacity kept between frames)
 };
 
 #include "../../include/rtb200.h"
@@ -32,3 +33,16 @@ struct VtkFrame {
 // particle's mean point.
 void vtk_convert(const VtkFrame &frame, std::vector<rt_triangle> &tris, std::vector<rt_instance_desc> &inst,
                  std::vector<rt_instance_xform> &xforms);
+
+// The same conversion without writing the triangles out on the host: the per-point tables (single precision, as the
+// triangle records hold them), the strips' point ids back to back and where each strip's triangles start.  The device
+// expands them into triangle records (expand_strips_kernel, kernels_build.cu): 4 MB instead of 53 MB per 500-particle
+// frame cross PCIe, and the host writes none of the 629 k records.
+struct VtkCompact {
+    std::vector<rt_vec3> points, normals;       // per point
+    std::vector<int> ids;                       // strips with >= 3 points, concatenated
+    std::vector<uint32_t> strip_first_tri;      // per kept strip, plus the total as the last entry
+    std::vector<uint32_t> strip_first_id;       // per kept strip: offset of its ids
+    size_t n_tris = 0;
+};
+void vtk_convert_compact(const VtkFrame &frame, VtkCompact &out, std::vector<rt_instance_desc> &inst, std::vector<rt_instance_xform> &xforms);

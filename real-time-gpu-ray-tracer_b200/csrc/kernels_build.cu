@@ -490,11 +490,8 @@ void LbvhBuilder::build_tlas(int n_instances, int morton_bits, cudaStream_t stre
 }
 
 
-// ---- config 3 input stage: triangle strips -> triangle records, on the device ------------------------------------
-// One thread per triangle q of the frame: strip k with strip_first_tri[k] <= q (binary search), j = q - first;
-// corners ids[j], ids[j+1], ids[j+2], the last two swapped for odd j (reference src/Global/VTKReader.cu:184-195);
-// writes the 9 vertex floats and the 48-byte shading record (point normals, METAL #0, VTKReader.cu:198-201) exactly
-// as HostScene::commit_geometry lays them out for the same rt_triangle.
+// ---- config 3 input stage: triangle strips -> triangle records, on the device (one thread per triangle of the frame;
+// the per-triangle work is expand_strip_triangle, rt_build_core.h) ---------------------------------------------------
 namespace {
 __global__ void __launch_bounds__(256) expand_strips_kernel(const float *__restrict__ points, const float *__restrict__ normals, const int *__restrict__ ids,
                                                             const uint32_t *__restrict__ strip_first_tri, const uint32_t *__restrict__ strip_first_id,
@@ -502,28 +499,7 @@ __global__ void __launch_bounds__(256) expand_strips_kernel(const float *__restr
                                                             float *__restrict__ tri_verts, TriShade *__restrict__ tri_shade) {
     const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= n_tris) return;
-    int lo = 0, hi = n_strips - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (__ldg(&strip_first_tri[mid]) <= q) lo = mid; else hi = mid - 1;
-    }
-    const uint32_t j = q - __ldg(&strip_first_tri[lo]);
-    const int *s = ids + __ldg(&strip_first_id[lo]) + j;
-    const int i0 = __ldg(s), a = __ldg(s + 1), b = __ldg(s + 2);
-    const int i1 = (j & 1u) ? b : a, i2 = (j & 1u) ? a : b;
-    float *v = tri_verts + (size_t) q * 9;
-    const int c[3] = {i0, i1, i2};
-    float n[9];
-    for (int k = 0; k < 3; k++)
-        for (int x = 0; x < 3; x++) {
-            v[3 * k + x] = __ldg(&points[3 * (size_t) c[k] + x]);
-            n[3 * k + x] = __ldg(&normals[3 * (size_t) c[k] + x]);
-        }
-    TriShade t;
-    t.n0_mt = make_float4(n[0], n[1], n[2], __uint_as_float(material_type));
-    t.n1_mi = make_float4(n[3], n[4], n[5], __uint_as_float(material_index));
-    t.n2 = make_float4(n[6], n[7], n[8], 0.0f);
-    tri_shade[q] = t;
+    expand_strip_triangle(q, points, normals, ids, strip_first_tri, strip_first_id, n_strips, material_type, material_index, tri_verts, tri_shade);
 }
 } // namespace
 

@@ -281,3 +281,35 @@ RT_HD Aabb instance_tight_box(const Aabb &corner_box, const Aabb &vertex_box) {
     ensure_volume(r.lo.x, r.hi.x); ensure_volume(r.lo.y, r.hi.y); ensure_volume(r.lo.z, r.hi.z);
     return r;
 }
+
+
+// ---- config 3 input stage: triangle q of a particle frame from the strips (kernels_build.cu expand_strips_kernel; the
+// CPU twin runs the same function).  Strip k with strip_first_tri[k] <= q (binary search), j = q - first; corners
+// ids[j], ids[j+1], ids[j+2], the last two swapped for odd j (reference src/Global/VTKReader.cu:184-195); writes the
+// 9 vertex floats and the 48-byte shading record (point normals + material) exactly as HostScene::convert_triangles
+// lays them out for the same rt_triangle.
+RT_HD void expand_strip_triangle(uint32_t q, const float *points, const float *normals, const int *ids, const uint32_t *strip_first_tri,
+                                 const uint32_t *strip_first_id, int n_strips, uint32_t material_type, uint32_t material_index,
+                                 float *tri_verts, TriShade *tri_shade) {
+    int lo = 0, hi = n_strips - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (strip_first_tri[mid] <= q) lo = mid; else hi = mid - 1;
+    }
+    const uint32_t j = q - strip_first_tri[lo];
+    const int *s = ids + strip_first_id[lo] + j;
+    const int i0 = s[0], a = s[1], b = s[2];
+    const int c[3] = {i0, (j & 1u) ? b : a, (j & 1u) ? a : b};
+    float *v = tri_verts + (size_t) q * 9;
+    float n[9];
+    for (int k = 0; k < 3; k++)
+        for (int x = 0; x < 3; x++) {
+            v[3 * k + x] = points[3 * (size_t) c[k] + x];
+            n[3 * k + x] = normals[3 * (size_t) c[k] + x];
+        }
+    TriShade t;
+    t.n0_mt = make_float4(n[0], n[1], n[2], u2f(material_type));
+    t.n1_mi = make_float4(n[3], n[4], n[5], u2f(material_index));
+    t.n2 = make_float4(n[6], n[7], n[8], 0.0f);
+    tri_shade[q] = t;
+}

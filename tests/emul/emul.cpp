@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "../../real-time-gpu-ray-tracer_b200/csrc/host_scene.h"
+#include "../../real-time-gpu-ray-tracer_b200/csrc/vtk_reader.h"
 #include "../../real-time-gpu-ray-tracer_b200/csrc/rt_pixel.h"
 #include "../../oracle/oracle_api.h"
 
@@ -364,6 +365,44 @@ void emul_wide(void *h, int which, size_t *n_nodes, size_t *n_leaf_prims, void *
     if (n_leaf_prims) *n_leaf_prims = lp.size();
     if (nodes) memcpy(nodes, b.nodes8.data(), b.nodes8.size() * sizeof(BvhNode8));
     if (leaf_prims) memcpy(leaf_prims, lp.data(), lp.size() * 4);
+}
+
+// ---- config 3 input stage: the C++ reader + both conversions of one .vtk frame, no GPU -----------------------------
+// mode 0: vtk_convert (rt_triangle array) -> HostScene::commit_geometry (the host path, RTB200_VTK_EXPAND=host)
+// mode 1: vtk_convert_compact + expand_strip_triangle for every triangle (what expand_strips_kernel does on the device)
+// Outputs (any may be NULL): tri_verts [9 per triangle], tri_shade [12 floats per triangle], instance descs, transforms.
+int emul_vtk_frame(const char *path, int mode, uint64_t *n_tris, uint64_t *n_inst, float *tri_verts, float *tri_shade,
+                   rt_instance_desc *inst_out, rt_instance_xform *xf_out) {
+    VtkFrame vf;
+    std::string err;
+    if (!vf.read(path, err)) return -1;
+    std::vector<rt_instance_desc> inst;
+    std::vector<rt_instance_xform> xf;
+    std::vector<float> verts;
+    std::vector<TriShade> shade;
+    if (mode == 0) {
+        std::vector<rt_triangle> tris;
+        vtk_convert(vf, tris, inst, xf);
+        HostScene hs;
+        if (!hs.commit_geometry(nullptr, 0, nullptr, 0, tris.data(), tris.size()).empty()) return -2;
+        verts = hs.tri_verts;
+        shade = hs.tri_shade;
+    } else {
+        VtkCompact vc;
+        vtk_convert_compact(vf, vc, inst, xf);
+        verts.resize(vc.n_tris * 9);
+        shade.resize(vc.n_tris);
+        for (uint32_t q = 0; q < (uint32_t) vc.n_tris; q++)
+            expand_strip_triangle(q, &vc.points.data()->x, &vc.normals.data()->x, vc.ids.data(), vc.strip_first_tri.data(), vc.strip_first_id.data(),
+                                  (int) vc.strip_first_id.size(), RT_METAL, 0u, verts.data(), shade.data());
+    }
+    if (n_tris) *n_tris = shade.size();
+    if (n_inst) *n_inst = inst.size();
+    if (tri_verts) memcpy(tri_verts, verts.data(), verts.size() * sizeof(float));
+    if (tri_shade) memcpy(tri_shade, shade.data(), shade.size() * sizeof(TriShade));
+    if (inst_out) memcpy(inst_out, inst.data(), inst.size() * sizeof(rt_instance_desc));
+    if (xf_out) memcpy(xf_out, xf.data(), xf.size() * sizeof(rt_instance_xform));
+    return 0;
 }
 
 } // extern "C"

@@ -34,7 +34,26 @@ def load():
     lib.emul_camera.argtypes = [vp, vp]
     lib.emul_lbvh.argtypes = [vp, i32, C.POINTER(sz), vp, vp, vp, vp, vp, vp]
     lib.emul_wide.argtypes = [vp, i32, C.POINTER(sz), C.POINTER(sz), vp, vp]
+    lib.emul_vtk_frame.argtypes = [C.c_char_p, i32, C.POINTER(u64), C.POINTER(u64), vp, vp, vp, vp]
     return lib
+
+
+def vtk_frame(path: str, mode: int):
+    """The product's C++ reader + conversion of one .vtk frame on the CPU.  mode 0: host conversion (rt_triangle ->
+    commit), mode 1: compact conversion + the device's per-triangle expansion function.  Returns (tri_verts [n, 9],
+    tri_shade [n, 12] as uint32 bit patterns, instance descs, transforms)."""
+    lib = load()
+    nt, ni = C.c_uint64(), C.c_uint64()
+    rc = lib.emul_vtk_frame(path.encode(), mode, C.byref(nt), C.byref(ni), None, None, None, None)
+    if rc != 0:
+        raise RuntimeError(f"emul_vtk_frame({path}) failed: {rc}")
+    verts = np.zeros((nt.value, 9), np.float32)
+    shade = np.zeros((nt.value, 12), np.uint32)
+    inst = np.zeros(ni.value, abi.instance_desc_dt)
+    xf = np.zeros(ni.value, abi.instance_xform_dt)
+    rc = lib.emul_vtk_frame(path.encode(), mode, None, None, verts.ctypes.data, shade.ctypes.data, inst.ctypes.data, xf.ctypes.data)
+    assert rc == 0
+    return verts, shade, inst, xf
 
 
 class Emul:

@@ -58,3 +58,31 @@ def test_parallelogram_bbox_flag(pkg):
     compat = ec.Emul(sc).render(SEED)
     fixed = ec.Emul(sc, flags=pkg.abi.FLAG_FIX_PARALLELOGRAM_BBOX).render(SEED)
     assert (fixed["inst"] == 0).sum() > (compat["inst"] == 0).sum()
+
+
+def test_vtk_reader_and_strip_expansion(pkg, tmp_path):
+    """Config 3's input stage without a GPU: the product's C++ reader + host conversion, and the compact conversion +
+    the per-triangle expansion function the device runs (expand_strip_triangle, shared header), give bit for bit the
+    triangle records, instance records and transforms of the numpy parse the parity scenes are built from."""
+    import os
+    S = pkg.scenes
+    fixture = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "particle_frame0.vtk")
+    series = S.synth_vtk_series(fixture, str(tmp_path), [25, 37], frame_ids=[0, 5])
+    assert os.path.exists(series)
+    for name in ("particle_000000000000000.vtk", "particle_000000000000500.vtk"):
+        path = os.path.join(str(tmp_path), "particle_mesh", name)
+        tris, ins, xf = S.vtk_particles(*S.read_vtk_frame(path))
+        want_verts = np.ascontiguousarray(tris["v"]).reshape(len(tris), 9)
+        want_normals = np.ascontiguousarray(tris["n"]).reshape(len(tris), 9)
+        got = [ec.vtk_frame(path, mode) for mode in (0, 1)]
+        for verts, shade, inst, xforms in got:
+            assert len(verts) == len(tris) and len(inst) == len(ins)
+            assert np.array_equal(verts.view(np.uint32), want_verts.view(np.uint32))
+            n = np.stack([shade[:, 0:3], shade[:, 4:7], shade[:, 8:11]], axis=1).reshape(len(tris), 9)
+            assert np.array_equal(n, want_normals.view(np.uint32))
+            assert (shade[:, 3] == pkg.abi.METAL).all() and (shade[:, 7] == 0).all() and (shade[:, 11] == 0).all()
+            assert inst.tobytes() == ins.tobytes() and xforms.tobytes() == xf.tobytes()
+        # the degenerate strip triangles (repeated ids) are kept: primitive indices must match the reference's
+        assert (want_verts[:, 0:3] == want_verts[:, 3:6]).all(axis=1).any()
+    with pytest.raises(RuntimeError):
+        ec.vtk_frame(str(tmp_path / "missing.vtk"), 1)

@@ -124,10 +124,13 @@ def test_error_codes(pkg):
     r.cleanup()
 
 
-def test_vtk_series_frames(pkg, port, tmp_path):
+@pytest.mark.parametrize("expand", ["device", "host"])
+def test_vtk_series_frames(pkg, port, tmp_path, monkeypatch, expand):
     """Config 3: rt_load_vtk_series + rt_set_vtk_frame (C++ reader, per-frame rebuild of all particle BLASes + TLAS)
-    gives the same frame as committing the numpy-parsed scene directly, and matches the oracle."""
+    gives the same frame as committing the numpy-parsed scene directly, and matches the oracle — with the strips
+    expanded into triangle records on the device (default) and on the host (RTB200_VTK_EXPAND=host)."""
     import os
+    monkeypatch.setenv("RTB200_VTK_EXPAND", expand)
     S = pkg.scenes
     fixture = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "particle_frame0.vtk")
     series = S.synth_vtk_series(fixture, str(tmp_path), [25, 40])

@@ -479,6 +479,7 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- e2e: same steps through the public API with host buffers: transforms H2D, framebuffer D2H ---------------
+    frame(args.warmup, True)        # untimed: first use of the read-back path (torch's de-interleave kernels, allocator, pinned copy)
     barrier()
     e_rays = 0
     t0 = time.perf_counter()

@@ -273,7 +273,9 @@ int rt_prefetch_vtk_frame(rt_ctx *ctx, size_t frame);
  * other's render on the same GPU.  Per frame: rt_set_vtk_frame (frame read ahead), rt_render_frame(frame, seed), RGBA8
  * plane -> pinned host memory, then `sink` (may be NULL) is called — one call at a time, from a lane's thread, frames
  * NOT in order across lanes; a non-zero return stops the loop (RT_ERR_STATE).  Every frame is the one
- * rt_set_vtk_frame + rt_render_frame on a single context would produce.                                                   */
+ * rt_set_vtk_frame + rt_render_frame on a single context would produce.  An rt_update_cb registered with
+ * rt_configure_instances is called from the lanes' threads (concurrently for different frames).  The lane contexts are
+ * kept until rt_cleanup.                                                                                                  */
 typedef struct rt_animation_stats {
     uint64_t frames;              /* frames rendered                                                     */
     uint64_t rays;

@@ -660,6 +660,7 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
     all_xf.insert(all_xf.end(), xf.begin(), xf.end());
     const std::vector<rt_sphere> spheres(ctx->hs.spheres);
     const std::vector<rt_parallelogram> quads(ctx->hs.quads);
+    struct ComposeGuard { rt_ctx *c; ~ComposeGuard() { c->composing = false; } } compose_guard{ctx};     // also on a thrown CudaError
     ctx->composing = true;
     int rc = RT_OK;
     if (on_device) {

@@ -63,6 +63,37 @@ __global__ void __launch_bounds__(RNG_ROWS) rng_tables_kernel(uint32_t *__restri
     for (int k = 0; k < 5; k++) out[k] = v[k];
 }
 
+// The 5 index bits that differ between the lanes of a warp, as ONE product per lane: LOW[row][word][c] = word of the
+// image of e_row under the jump by c sequences, c = 0..31.  For a fixed (row, word) the 32 values are one 128-byte
+// line, so lanes with c = 0..31 (in any order) load their own matrix with one coalesced transaction per (row, word)
+// — the lane-specific matrices that were a 16-way L1 gather in row-major layout.
+// block c, thread = row r
+__global__ void __launch_bounds__(RNG_ROWS) rng_low_table_kernel(uint32_t *__restrict__ tables) {
+    const int c = blockIdx.x, r = threadIdx.x;
+    uint32_t v[5] = {0, 0, 0, 0, 0};
+    v[r >> 5] = 1u << (r & 31);
+    if (c & 15) xorwow_matvec(tables + (size_t) ((c & 15) - 1) * RNG_MAT_WORDS, v);            // T[0][c & 15]
+    if (c >> 4) xorwow_matvec(tables + (size_t) (15 + 1 - 1) * RNG_MAT_WORDS, v);              // T[1][1]: bit 4
+    uint32_t *low = tables + RNG_HEX_TABLE_WORDS;
+    for (int k = 0; k < 5; k++) low[(size_t) (r * 5 + k) * 32 + c] = v[k];
+}
+
+__device__ __forceinline__ void xorwow_matvec_low(const uint32_t *__restrict__ low, uint32_t c, uint32_t v[5]) {
+    uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
+    const uint32_t *base = low + c;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        const uint32_t w = v[i];
+#pragma unroll 8
+        for (int j = 0; j < 32; j++) {
+            const uint32_t mask = 0u - ((w >> j) & 1u);
+            const uint32_t *row = base + (size_t) (5 * (32 * i + j)) * 32;
+            r0 ^= __ldg(row) & mask; r1 ^= __ldg(row + 32) & mask; r2 ^= __ldg(row + 64) & mask; r3 ^= __ldg(row + 96) & mask; r4 ^= __ldg(row + 128) & mask;
+        }
+    }
+    v[0] = r0; v[1] = r1; v[2] = r2; v[3] = r3; v[4] = r4;
+}
+
 __global__ void __launch_bounds__(256) rng_init_tables_kernel(RngState *__restrict__ states, const uint32_t *__restrict__ tables, unsigned long long seed,
                                                               uint32_t width, uint32_t pitch, uint32_t local_rows, uint32_t rank, uint32_t world,
                                                               uint32_t tile_rows) {
@@ -82,14 +113,17 @@ __global__ void __launch_bounds__(256) rng_init_tables_kernel(RngState *__restri
     // bits that vary across the warp are applied one at a time with the warp-uniform single-bit matrix T[b / 4][1 << b % 4]
     // (every lane computes, lanes whose bit is clear keep their vector), and only the bits all lanes share go through
     // the hex-digit tables.
-    const uint32_t vary = __reduce_or_sync(0xffffffffu, pixelIndex ^ __shfl_sync(0xffffffffu, pixelIndex, 0));
+    // the low 5 bits: one product with the lane's own matrix from the lane-interleaved table (coalesced when the warp's
+    // pixels are consecutive; correct in any case)
+    xorwow_matvec_low(tables + RNG_HEX_TABLE_WORDS, pixelIndex & 31u, v);
+    const uint32_t vary = __reduce_or_sync(0xffffffffu, pixelIndex ^ __shfl_sync(0xffffffffu, pixelIndex, 0)) & ~31u;
     for (uint32_t rest = vary; rest != 0u; rest &= rest - 1u) {
         const int b = __ffs(rest) - 1;
         uint32_t w[5] = {v[0], v[1], v[2], v[3], v[4]};
         xorwow_matvec(tables + (size_t) ((b >> 2) * 15 + (1 << (b & 3)) - 1) * RNG_MAT_WORDS, w);
         if ((pixelIndex >> b) & 1u) { v[0] = w[0]; v[1] = w[1]; v[2] = w[2]; v[3] = w[3]; v[4] = w[4]; }
     }
-    uint32_t p = pixelIndex & ~vary;
+    uint32_t p = pixelIndex & ~(vary | 31u);
     for (int h = 0; p != 0u; h++, p >>= 4) {
         const uint32_t d = p & 15u;
         if (d) xorwow_matvec(tables + (size_t) (h * 15 + (int) d - 1) * RNG_MAT_WORDS, v);
@@ -201,6 +235,7 @@ void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &c
     if (tables && !use_curand) {
         if (!tables_ready) {
             rng_tables_kernel<<<RNG_HEX_DIGITS * 15, RNG_ROWS, 0, stream>>>(tables);
+            rng_low_table_kernel<<<32, RNG_ROWS, 0, stream>>>(tables);
             tables_ready = true;
         }
         rng_init_tables_kernel<<<div_up(n, 256), 256, 0, stream>>>(states, tables, seed, cam.width, cam.pitch, fr.local_rows, fr.shard_rank, fr.shard_world,

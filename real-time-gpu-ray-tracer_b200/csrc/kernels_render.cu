@@ -78,6 +78,22 @@ __global__ void __launch_bounds__(RNG_ROWS) rng_low_table_kernel(uint32_t *__res
     for (int k = 0; k < 5; k++) low[(size_t) (r * 5 + k) * 32 + c] = v[k];
 }
 
+// Byte-digit tables for the index bits every lane of a warp shares: WIDE[0][d] = jump by d << 5 sequences, WIDE[1][d] =
+// jump by d << 13, d = 1..255 (products of the hex tables) — two products cover bits 5..20 (a 1080p frame has 21 index
+// bits) instead of up to five hex-digit products.  block (which, d - 1), thread = row r
+__global__ void __launch_bounds__(RNG_ROWS) rng_wide_tables_kernel(uint32_t *__restrict__ tables) {
+    const int which = blockIdx.x / 255, d = blockIdx.x % 255 + 1, r = threadIdx.x;
+    uint32_t v[5] = {0, 0, 0, 0, 0};
+    v[r >> 5] = 1u << (r & 31);
+    const uint32_t val = (uint32_t) d << (which ? 13 : 5);
+    for (int h = 0; h < RNG_HEX_DIGITS; h++) {
+        const uint32_t dd = (val >> (4 * h)) & 15u;
+        if (dd) xorwow_matvec(tables + (size_t) (h * 15 + (int) dd - 1) * RNG_MAT_WORDS, v);
+    }
+    uint32_t *out = tables + RNG_HEX_TABLE_WORDS + RNG_LOW_TABLE_WORDS + ((size_t) (which * 255 + d - 1) * RNG_ROWS + r) * 5;
+    for (int k = 0; k < 5; k++) out[k] = v[k];
+}
+
 __device__ __forceinline__ void xorwow_matvec_low(const uint32_t *__restrict__ low, uint32_t c, uint32_t v[5]) {
     uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
     const uint32_t *base = low + c;
@@ -124,6 +140,11 @@ __global__ void __launch_bounds__(256) rng_init_tables_kernel(RngState *__restri
         if ((pixelIndex >> b) & 1u) { v[0] = w[0]; v[1] = w[1]; v[2] = w[2]; v[3] = w[3]; v[4] = w[4]; }
     }
     uint32_t p = pixelIndex & ~(vary | 31u);
+    const uint32_t *wide = tables + RNG_HEX_TABLE_WORDS + RNG_LOW_TABLE_WORDS;
+    const uint32_t da = (p >> 5) & 255u, db = (p >> 13) & 255u;
+    if (da) xorwow_matvec(wide + (size_t) (da - 1u) * RNG_MAT_WORDS, v);
+    if (db) xorwow_matvec(wide + (size_t) (255u + db - 1u) * RNG_MAT_WORDS, v);
+    p &= ~0x1FFFFFu;                                   // bits 21 and up (frames beyond 2 M pixels): hex digits
     for (int h = 0; p != 0u; h++, p >>= 4) {
         const uint32_t d = p & 15u;
         if (d) xorwow_matvec(tables + (size_t) (h * 15 + (int) d - 1) * RNG_MAT_WORDS, v);
@@ -236,6 +257,7 @@ void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &c
         if (!tables_ready) {
             rng_tables_kernel<<<RNG_HEX_DIGITS * 15, RNG_ROWS, 0, stream>>>(tables);
             rng_low_table_kernel<<<32, RNG_ROWS, 0, stream>>>(tables);
+            rng_wide_tables_kernel<<<2 * 255, RNG_ROWS, 0, stream>>>(tables);
             tables_ready = true;
         }
         rng_init_tables_kernel<<<div_up(n, 256), 256, 0, stream>>>(states, tables, seed, cam.width, cam.pitch, fr.local_rows, fr.shard_rank, fr.shard_world,

@@ -114,6 +114,25 @@ typedef struct rt_camera_input {
     uint64_t ray_trace_depth;
 } rt_camera_input;
 
+/* ---- scripted camera input (replaces the WASD / mouse controller of the window) -----------------------
+ * SDL_OpenGLWindow::calculateNewPosition (src/Global/SDL_OpenGLWindow.cu:182-256) as a pure function of the
+ * current camera and one step of input: yaw of the view direction about the camera's V, pitch about its U
+ * (Rodrigues rotation, include/Basic/Vec3.cuh:140-160), optional pitch clamp, then W/A/S/D in the horizontal
+ * plane, SPACE / LSHIFT along `up`, diagonal moves normalised.  The caller feeds the result to
+ * rt_configure_camera before the next rt_render_frame (Renderer.cu:247-255 does exactly that every frame).
+ * Restated from the reference (its file needs SDL/GL headers to compile): PARITY UNPINNED.                     */
+enum rt_key { RT_KEY_W = 1, RT_KEY_A = 2, RT_KEY_S = 4, RT_KEY_D = 8, RT_KEY_SPACE = 16, RT_KEY_LSHIFT = 32 };
+typedef struct rt_camera_motion {
+    int32_t  dx, dy;             /* relative mouse motion of this step, pixels                                   */
+    uint32_t keys;               /* RT_KEY_* bits held during this step                                         */
+    float    mouse_sensitivity;  /* radians per pixel (reference: 0.001, Renderer.cu:224-225)                    */
+    float    pitch_limit;        /* radians; the reference passes PI / radians(80) = 2.25 (SDL_OpenGLWindow.cuh:66),
+                                    which asin() never exceeds — pass that for identical behaviour             */
+    float    move_speed;         /* world units per step (reference start value 2 * 0.05)                        */
+} rt_camera_motion;
+/* next = current with center/target moved; *moved (may be NULL) = 1 if anything changed.  Host arithmetic only. */
+int rt_camera_step(const rt_camera_input *current, const rt_camera_motion *motion, rt_camera_input *next, int *moved);
+
 /* ---- options ----------------------------------------------------------------------------- */
 enum rt_flags {
     RT_FLAG_NONE                    = 0,

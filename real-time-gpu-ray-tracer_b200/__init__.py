@@ -4,6 +4,6 @@ The directory name contains hyphens; import it with
 ``importlib.import_module("real-time-gpu-ray-tracer_b200")`` (``__graft_entry__.package()`` does so).
 """
 from . import abi, scenes, sharding  # noqa: F401
-from .renderer import Renderer, RtError  # noqa: F401
+from .renderer import Renderer, RtError, cameraStep  # noqa: F401
 
-__all__ = ["abi", "scenes", "sharding", "Renderer", "RtError"]
+__all__ = ["abi", "scenes", "sharding", "Renderer", "RtError", "cameraStep"]

@@ -64,6 +64,15 @@ class CameraInput(C.Structure):
                 ("sample_count", C.c_uint64), ("ray_trace_depth", C.c_uint64)]
 
 
+class CameraMotion(C.Structure):
+    """One step of scripted input for rt_camera_step (the reference's WASD / mouse controller)."""
+    _fields_ = [("dx", C.c_int32), ("dy", C.c_int32), ("keys", C.c_uint32), ("mouse_sensitivity", C.c_float),
+                ("pitch_limit", C.c_float), ("move_speed", C.c_float)]
+
+
+KEY_W, KEY_A, KEY_S, KEY_D, KEY_SPACE, KEY_LSHIFT = 1, 2, 4, 8, 16, 32
+
+
 class FrameOut(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("primary_rays", C.c_uint64), ("render_ms", C.c_float), ("tlas_ms", C.c_float),
                 ("rng_ms", C.c_float), ("trace_ms", C.c_float), ("kernel_launches", C.c_uint32), ("stack_overflow", C.c_uint32),
@@ -92,6 +101,7 @@ _STRUCT_SIZES = {
     "rt_instance_desc": instance_desc_dt.itemsize, "rt_instance_xform": instance_xform_dt.itemsize,
     "rt_window": C.sizeof(Window), "rt_camera_input": C.sizeof(CameraInput), "rt_frame_out": C.sizeof(FrameOut),
     "rt_build_stats": C.sizeof(BuildStats), "rt_animation_stats": C.sizeof(AnimationStats),
+    "rt_camera_motion": C.sizeof(CameraMotion),
 }
 
 # every symbol include/rtb200.h declares
@@ -101,7 +111,7 @@ EXPORTS = [
     "rt_build_acceleration_structure", "rt_get_build_stats", "rt_configure_camera",
     "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm", "rt_write_image",
     "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame", "rt_prefetch_vtk_frame",
-    "rt_probe_read_bandwidth", "rt_run_vtk_animation",
+    "rt_probe_read_bandwidth", "rt_run_vtk_animation", "rt_camera_step",
 ]
 
 _lib = None
@@ -145,6 +155,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_set_vtk_frame.argtypes = [vp, sz]
     lib.rt_prefetch_vtk_frame.argtypes = [vp, sz]
     lib.rt_run_vtk_animation.argtypes = [vp, sz, sz, sz, u64, i32, FRAME_SINK, vp, C.POINTER(AnimationStats)]
+    lib.rt_camera_step.argtypes = [C.POINTER(CameraInput), C.POINTER(CameraMotion), C.POINTER(CameraInput), C.POINTER(C.c_int)]
     lib.rt_probe_read_bandwidth.argtypes = [vp, sz, i32, C.POINTER(C.c_double)]
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported

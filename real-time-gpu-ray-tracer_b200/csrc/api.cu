@@ -201,7 +201,7 @@ size_t rt_struct_size(const char *name) {
     if (!name) return 0;
 #define RT_SZ(T) if (strcmp(name, #T) == 0) return sizeof(T);
     RT_SZ(rt_vec3) RT_SZ(rt_sphere) RT_SZ(rt_parallelogram) RT_SZ(rt_triangle) RT_SZ(rt_rough) RT_SZ(rt_metal) RT_SZ(rt_dielectric)
-    RT_SZ(rt_instance_desc) RT_SZ(rt_instance_xform) RT_SZ(rt_window) RT_SZ(rt_camera_input) RT_SZ(rt_frame_out) RT_SZ(rt_build_stats) RT_SZ(rt_animation_stats)
+    RT_SZ(rt_instance_desc) RT_SZ(rt_instance_xform) RT_SZ(rt_window) RT_SZ(rt_camera_input) RT_SZ(rt_frame_out) RT_SZ(rt_build_stats) RT_SZ(rt_animation_stats) RT_SZ(rt_camera_motion)
 #undef RT_SZ
     return 0;
 }
@@ -387,6 +387,13 @@ int rt_configure_camera(rt_ctx *ctx, const rt_window *window, const rt_camera_in
     alloc_frame(ctx);
     ctx->camera_set = true;
     RT_API_END(ctx)
+}
+
+int rt_camera_step(const rt_camera_input *current, const rt_camera_motion *motion, rt_camera_input *next, int *moved) {
+    if (!current || !motion || !next) return RT_ERR_ARGUMENT;
+    const bool m = camera_step(*current, *motion, *next);
+    if (moved) *moved = m ? 1 : 0;
+    return RT_OK;
 }
 
 int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_rows, void *peer_rgba8) {

@@ -282,3 +282,64 @@ size_t HostScene::prim_bytes() const {
     }
     return b;
 }
+
+
+// ---- scripted camera input ------------------------------------------------------------------------------------------
+namespace {
+// Vec3::rotate (reference include/Basic/Vec3.cuh:140-160): Rodrigues, axis normalised first
+f3 rotate_about(const f3 &v, const f3 &axis, float angle) {
+    const f3 k = unit3(axis);
+    const float c = std::cos(angle), s = std::sin(angle);
+    const f3 part1 = v * c;
+    const f3 part2 = cross3(k, v) * s;
+    const f3 part3 = (k * dot3(k, v)) * (1.0f - c);
+    return (part1 + part2) + part3;
+}
+}
+
+bool camera_step(const rt_camera_input &cur, const rt_camera_motion &m, rt_camera_input &next) {
+    next = cur;
+    const f3 center = V(cur.center), target = V(cur.target), up = V(cur.up);
+    // camera frame as RendererImpl::calculateCameraProperties builds it (src/Global/RenderPin.cu:83-85)
+    const f3 camW = unit3(target - center);
+    const f3 camU = unit3(cross3(camW, up));
+    const f3 camV = unit3(cross3(camU, camW));
+    f3 new_center = center, new_target = target;
+    bool moved = false;
+    if (m.dx != 0 || m.dy != 0) {                              // mouse: only the look-at point changes (:193-236)
+        moved = true;
+        const f3 view = target - center;
+        f3 W = unit3(camW);
+        const f3 U = unit3(camU), Vv = unit3(camV);
+        const float yaw = -static_cast<float>(m.dx) * m.mouse_sensitivity;
+        W = rotate_about(W, Vv, yaw);
+        const float pitch = -static_cast<float>(m.dy) * m.mouse_sensitivity;
+        W = rotate_about(W, U, pitch);
+        float new_pitch = std::asin(W.y);
+        bool fix = false;
+        if (new_pitch > m.pitch_limit) { new_pitch = m.pitch_limit; fix = true; }
+        else if (new_pitch < -m.pitch_limit) { new_pitch = -m.pitch_limit; fix = true; }
+        if (fix) {
+            const f3 horizontal = unit3(mk3(W.x, 0.0f, W.z));
+            W = horizontal * std::cos(new_pitch) + mk3(0.0f, std::sin(new_pitch), 0.0f);
+        }
+        new_target = center + W * std::sqrt(len2(view));
+    }
+    f3 dir = mk3(0.0f, 0.0f, 0.0f);                            // keys: always in the horizontal plane (:238-254)
+    const f3 forward = unit3(mk3(camW.x, 0.0f, camW.z));
+    if (m.keys & RT_KEY_W) dir = dir + forward;
+    if (m.keys & RT_KEY_S) dir = dir - forward;
+    if (m.keys & RT_KEY_D) dir = dir + camU;
+    if (m.keys & RT_KEY_A) dir = dir - camU;
+    if (m.keys & RT_KEY_SPACE) dir = dir + up;
+    if (m.keys & RT_KEY_LSHIFT) dir = dir - up;
+    if (len2(dir) > 0.0f) {
+        moved = true;
+        const f3 t = unit3(dir) * m.move_speed;
+        new_center = new_center + t;
+        new_target = new_target + t;
+    }
+    next.center = rt_vec3{new_center.x, new_center.y, new_center.z};
+    next.target = rt_vec3{new_target.x, new_target.y, new_target.z};
+    return moved;
+}

@@ -16,6 +16,19 @@ class RtError(RuntimeError):
         self.code = code
 
 
+def cameraStep(camera: abi.CameraInput, dx: int = 0, dy: int = 0, keys: int = 0, mouse_sensitivity: float = 0.001,
+               pitch_limit: float = float(np.float32(np.pi) / np.float32(np.deg2rad(np.float32(80.0)))), move_speed: float = 0.1):
+    """One step of the reference's camera controller (SDL_OpenGLWindow::calculateNewPosition) as scripted input:
+    returns (next CameraInput, moved).  Defaults are the reference's (Renderer.cu:224-225)."""
+    lib = abi.load_library()
+    nxt, moved = abi.CameraInput(), C.c_int(0)
+    m = abi.CameraMotion(dx, dy, keys, mouse_sensitivity, pitch_limit, move_speed)
+    rc = lib.rt_camera_step(C.byref(camera), C.byref(m), C.byref(nxt), C.byref(moved))
+    if rc != 0:
+        raise RtError(rc, "rt_camera_step failed")
+    return nxt, bool(moved.value)
+
+
 class Renderer:
     def __init__(self, device: int = 0, flags: int = 0):
         self.lib = abi.load_library()

@@ -260,6 +260,37 @@ def test_animation_loop_in_the_library(pkg, tmp_path):
         rr.runVTKAnimation()                      # no series loaded
 
 
+def test_scripted_camera_path(pkg):
+    """Frame loop with scripted camera input (rt_camera_step -> rt_configure_camera between frames, what
+    Renderer.cu:247-255 does with the WASD / mouse state): every frame of the walk equals the frame of a fresh renderer
+    given that camera, and the walk does change the image."""
+    sc = parity_scenes(pkg.scenes)[0]
+    cam = sc.camera_input()
+    r = pkg.Renderer(device=0)
+    try:
+        r.commitScene(sc)
+        r.renderFrame(0, SEED)
+        prev = r.readFramebuffer(pkg.abi.BUF_RGBA8).copy()
+        for step, (dx, dy, keys) in enumerate([(60, -15, pkg.abi.KEY_W), (0, 0, pkg.abi.KEY_D | pkg.abi.KEY_SPACE), (-120, 30, 0)]):
+            cam, moved = pkg.cameraStep(cam, dx, dy, keys, move_speed=0.4)
+            assert moved
+            r.configureCamera(sc.window(), cam)
+            r.renderFrame(step + 1, SEED)
+            img = r.readFramebuffer(pkg.abi.BUF_RGBA8).copy()
+            assert not np.array_equal(img, prev)
+            fresh = pkg.Renderer(device=0)
+            try:
+                fresh.commitScene(sc)
+                fresh.configureCamera(sc.window(), cam)
+                fresh.renderFrame(step + 1, SEED)
+                assert np.array_equal(fresh.readFramebuffer(pkg.abi.BUF_RGBA8), img)
+            finally:
+                fresh.cleanup()
+            prev = img
+    finally:
+        r.cleanup()
+
+
 def test_output_writers(pkg, tmp_path):
     """rt_write_image: PPM / PFM / AOV dumps hold exactly the planes rt_read_framebuffer returns."""
     sc = parity_scenes(pkg.scenes)[0]

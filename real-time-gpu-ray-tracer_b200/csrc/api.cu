@@ -188,7 +188,7 @@ void update_instances_and_tlas(rt_ctx *c) {
     CUDA_CHECK(cudaMemcpyAsync(c->d_xform_in.get(), c->h_xform_in.get(), (size_t) n * sizeof(InstanceXformIn), cudaMemcpyHostToDevice, c->stream));
     launch_instance_update(c->d_xform_in.get(), n, c->d_instances.get(), c->tlas.prim_lo(), c->tlas.prim_hi(), c->d_wcentroid.get(),
                            c->tlas.bounds(), c->d_tri_verts.get(), c->stream);
-    c->tlas.build_tlas(n, morton_bits_for((size_t) n), c->stream, c->sm_count);
+    c->tlas.build_tlas(n, tlas_morton_bits((size_t) n), c->stream, c->sm_count);
 }
 
 } // namespace

@@ -44,6 +44,11 @@ int morton_bits_for(size_t n) {
     return 16;
 }
 
+int tlas_morton_bits(size_t n_instances) {
+    // instances are few and differ wildly in size: never fewer than 10 bits per axis (one more sort pass on ~1e3 keys)
+    return std::max(10, morton_bits_for(n_instances));
+}
+
 std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_parallelogram *p, size_t np, const rt_triangle *t, size_t nt) {
     if ((ns && !s) || (np && !p) || (nt && !t)) return "rt_commit_geometry: null array with non-zero count";
     if (nt > RT_REF_POS_MASK || ns > RT_REF_POS_MASK || np > RT_REF_POS_MASK) return "rt_commit_geometry: more than 2^29 primitives of one type";

@@ -53,5 +53,6 @@ struct HostScene {
 };
 
 int morton_bits_for(size_t n);
+int tlas_morton_bits(size_t n_instances);
 // SDL_OpenGLWindow::calculateNewPosition restated (reference src/Global/SDL_OpenGLWindow.cu:182-256); true if the camera moved
 bool camera_step(const rt_camera_input &cur, const rt_camera_motion &m, rt_camera_input &next);

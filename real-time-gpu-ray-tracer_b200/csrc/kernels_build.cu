@@ -373,7 +373,7 @@ __global__ void __launch_bounds__(BT) instance_bounds_kernel(const InstanceXform
         const Aabb padded = aabb_pad(box);
         wlo[i] = make_float4(padded.lo.x, padded.lo.y, padded.lo.z, 0.0f);
         whi[i] = make_float4(padded.hi.x, padded.hi.y, padded.hi.z, 0.0f);
-        atomic_bounds(bounds, padded);
+        atomic_bounds(bounds, aabb_centre_box(padded));      // the TLAS grid spans the instance centres (rt_build_core.h)
     }
 }
 

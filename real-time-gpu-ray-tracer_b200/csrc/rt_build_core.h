@@ -108,6 +108,16 @@ RT_HD uint64_t expand_bits21(uint64_t v) {
 #ifndef RT_MORTON_PER_AXIS
 #define RT_MORTON_PER_AXIS 0     /* 1: the first version's per-axis scaling, kept for A/B measurements */
 #endif
+// The box centre morton_code quantises, as a degenerate box.  The TLAS takes its Morton grid from the union of the
+// instances' CENTRES, not of their boxes: one huge instance (the demo scene's r = 1000 sky sphere around particles a
+// few units across) would otherwise put every other instance into the same few cells and leave their order — and
+// the TLAS topology — to the index tie-break.
+RT_HD Aabb aabb_centre_box(const Aabb &b) {
+    Aabb c;
+    c.lo = mk3(0.5f * (b.lo.x + b.hi.x), 0.5f * (b.lo.y + b.hi.y), 0.5f * (b.lo.z + b.hi.z));
+    c.hi = c.lo;
+    return c;
+}
 RT_HD uint64_t morton_code(const Aabb &prim, const Aabb &scene, int bits) {
     const float scale = (float) (1u << bits);
     const float ext_max = rt_max(rt_max(scene.hi.x - scene.lo.x, scene.hi.y - scene.lo.y), scene.hi.z - scene.lo.z);

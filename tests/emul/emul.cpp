@@ -264,9 +264,9 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
         } else {
             t.prim_box[i] = aabb_pad(e->wbox[i]);
         }
-        scene = aabb_union(scene, t.prim_box[i]);
+        scene = aabb_union(scene, aabb_centre_box(t.prim_box[i]));        // the grid spans the instance centres
     }
-    const int tbits = morton_bits_for((size_t) ni);
+    const int tbits = tlas_morton_bits((size_t) ni);
     t.keys.resize(ni);
     for (int i = 0; i < ni; i++) t.keys[i] = morton_code(t.prim_box[i], scene, tbits);
     const std::vector<uint32_t> toff{0u, (uint32_t) ni}, ttype{0u};

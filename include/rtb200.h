@@ -243,10 +243,11 @@ int rt_set_instance_xforms(rt_ctx *ctx, const rt_instance_xform *xforms, size_t 
 int rt_read_framebuffer(rt_ctx *ctx, int kind, void *host_dst, size_t dst_bytes);
 /* Device pointer of a plane (for NCCL / peer access by the caller); size in bytes via *bytes.      */
 int rt_framebuffer_device_ptr(rt_ctx *ctx, int kind, void **dev_ptr, size_t *bytes);
-/* Write the RGBA8 plane as a binary PPM (top-down, flipped) — the headless "display".              */
+/* Write the RGBA8 plane as a binary PPM (top-down, flipped) — the headless "display"; a path ending in ".png" gets
+ * an 8-bit RGBA PNG instead (top-down, uncompressed deflate: no zlib dependency).                    */
 int rt_write_ppm(rt_ctx *ctx, const char *path);
 /* Dump any plane of this context (rt_buffer_kind) to a file — the headless output stage after the path:
- *   RT_BUFFER_RGBA8    -> binary PPM "P6" (as rt_write_ppm)
+ *   RT_BUFFER_RGBA8    -> binary PPM "P6", or PNG when the path ends in ".png" (as rt_write_ppm)
  *   RT_BUFFER_RADIANCE -> PFM "PF" (float RGB, little-endian, rows bottom-up: the plane's own order)
  *   RT_BUFFER_PRIMARY_T-> PFM "Pf" (one float per pixel, +inf on miss)
  *   RT_BUFFER_PRIMARY_INSTANCE / _PRIM -> "RTAOV1 <width> <height> <kind>\n" + int32 little-endian per pixel, bottom-up */

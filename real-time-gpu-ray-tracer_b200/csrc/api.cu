@@ -4,6 +4,7 @@
 
 #include "build.h"
 #include "host_scene.h"
+#include "image_io.h"
 #include "render.h"
 #include "vtk_reader.h"
 #include "wave.h"
@@ -545,6 +546,15 @@ int rt_write_ppm(rt_ctx *ctx, const char *path) {
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     FILE *f = fopen(path, "wb");
     if (!f) return fail(ctx, RT_ERR_IO, std::string("cannot open ") + path);
+    const size_t len = strlen(path);
+    if (len >= 4 && strcmp(path + len - 4, ".png") == 0) {           // "*.png": 8-bit RGBA PNG, top-down (image_io.h)
+        std::vector<uint8_t> png;
+        png_encode_rgba8(img.data(), W, H, true, png);
+        const bool ok = fwrite(png.data(), 1, png.size(), f) == png.size();
+        fclose(f);
+        if (!ok) return fail(ctx, RT_ERR_IO, std::string("short write to ") + path);
+        return RT_OK;
+    }
     fprintf(f, "P6\n%u %u\n255\n", W, H);
     std::vector<uint8_t> row((size_t) W * 3);
     for (uint32_t y = 0; y < H; y++) {   // row 0 of the framebuffer is the bottom scan-line: flip

@@ -22,6 +22,7 @@
 
 #include "../../real-time-gpu-ray-tracer_b200/csrc/host_scene.h"
 #include "../../real-time-gpu-ray-tracer_b200/csrc/vtk_reader.h"
+#include "../../real-time-gpu-ray-tracer_b200/csrc/image_io.h"
 #include "../../real-time-gpu-ray-tracer_b200/csrc/rt_pixel.h"
 #include "../../oracle/oracle_api.h"
 
@@ -403,6 +404,15 @@ int emul_vtk_frame(const char *path, int mode, uint64_t *n_tris, uint64_t *n_ins
     if (inst_out) memcpy(inst_out, inst.data(), inst.size() * sizeof(rt_instance_desc));
     if (xf_out) memcpy(xf_out, xf.data(), xf.size() * sizeof(rt_instance_xform));
     return 0;
+}
+
+// ---- output stage: the product's PNG encoder (csrc/image_io.h), no GPU ---------------------------------------------
+// returns the file size; writes at most `cap` bytes to `out`
+uint64_t emul_png_encode(const uint8_t *rgba, uint32_t w, uint32_t h, int bottom_up, uint8_t *out, uint64_t cap) {
+    std::vector<uint8_t> png;
+    png_encode_rgba8(rgba, w, h, bottom_up != 0, png);
+    if (out) memcpy(out, png.data(), std::min<uint64_t>(cap, png.size()));
+    return png.size();
 }
 
 } // extern "C"

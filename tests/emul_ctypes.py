@@ -35,7 +35,44 @@ def load():
     lib.emul_lbvh.argtypes = [vp, i32, C.POINTER(sz), vp, vp, vp, vp, vp, vp]
     lib.emul_wide.argtypes = [vp, i32, C.POINTER(sz), C.POINTER(sz), vp, vp]
     lib.emul_vtk_frame.argtypes = [C.c_char_p, i32, C.POINTER(u64), C.POINTER(u64), vp, vp, vp, vp]
+    lib.emul_png_encode.argtypes = [vp, C.c_uint32, C.c_uint32, i32, vp, u64]
+    lib.emul_png_encode.restype = u64
     return lib
+
+
+def png_encode(rgba: np.ndarray, bottom_up: bool = True) -> bytes:
+    """The product's PNG encoder (csrc/image_io.h) on an [H, W, 4] uint8 array."""
+    lib = load()
+    rgba = np.ascontiguousarray(rgba, np.uint8)
+    h, w = rgba.shape[:2]
+    n = lib.emul_png_encode(rgba.ctypes.data, w, h, int(bottom_up), None, 0)
+    out = np.zeros(n, np.uint8)
+    lib.emul_png_encode(rgba.ctypes.data, w, h, int(bottom_up), out.ctypes.data, n)
+    return out.tobytes()
+
+
+def png_decode(data: bytes) -> np.ndarray:
+    """Minimal PNG reader for the tests (8-bit RGBA, filter 0 only — what png_encode_rgba8 writes): checks the
+    signature, every chunk CRC and the zlib stream; returns [H, W, 4] top-down."""
+    import struct
+    import zlib
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h = 8, b"", 0, 0
+    while pos < len(data):
+        n, typ = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        (crc,) = struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])
+        assert zlib.crc32(typ + body) == crc, f"bad CRC in {typ}"
+        if typ == b"IHDR":
+            w, h, depth, colour, comp, flt, lace = struct.unpack(">IIBBBBB", body)
+            assert (depth, colour, comp, flt, lace) == (8, 6, 0, 0, 0)
+        elif typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    assert typ == b"IEND"
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, w * 4 + 1)
+    assert (raw[:, 0] == 0).all()
+    return raw[:, 1:].reshape(h, w, 4).copy()
 
 
 def vtk_frame(path: str, mode: int):

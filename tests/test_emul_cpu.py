@@ -86,3 +86,15 @@ def test_vtk_reader_and_strip_expansion(pkg, tmp_path):
         assert (want_verts[:, 0:3] == want_verts[:, 3:6]).all(axis=1).any()
     with pytest.raises(RuntimeError):
         ec.vtk_frame(str(tmp_path / "missing.vtk"), 1)
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (5, 7), (90, 160), (270, 480)])       # 270x480: several stored deflate blocks
+def test_png_encoder(shape):
+    """Output stage: the product's dependency-free PNG encoder round-trips through zlib (signature, chunk CRCs,
+    Adler-32, stored blocks), rows flipped top-down like the PPM writer."""
+    h, w = shape
+    img = np.random.RandomState(h * 1000 + w).randint(0, 256, (h, w, 4)).astype(np.uint8)
+    png = ec.png_encode(img, bottom_up=True)
+    assert np.array_equal(ec.png_decode(png), img[::-1])
+    assert np.array_equal(ec.png_decode(ec.png_encode(img, bottom_up=False)), img)
+    assert len(png) > h * (w * 4 + 1)            # stored, not compressed

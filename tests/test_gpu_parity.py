@@ -309,6 +309,9 @@ def test_output_writers(pkg, tmp_path):
         raw = (tmp_path / "f.ppm").read_bytes()
         hdr = f"P6\n{W} {H}\n255\n".encode()
         assert raw.startswith(hdr) and np.array_equal(np.frombuffer(raw[len(hdr):], np.uint8).reshape(H, W, 3), rgba[::-1, :, :3])
+        import emul_ctypes as ec
+        r.writeImage(pkg.abi.BUF_RGBA8, str(tmp_path / "f.png"))              # ".png": 8-bit RGBA PNG, top-down
+        assert np.array_equal(ec.png_decode((tmp_path / "f.png").read_bytes()), rgba[::-1])
         prim = r.readFramebuffer(pkg.abi.BUF_PRIMARY_PRIM).reshape(H, W)
         raw = (tmp_path / "p.aov").read_bytes()
         hdr = f"RTAOV1 {W} {H} {pkg.abi.BUF_PRIMARY_PRIM}\n".encode()

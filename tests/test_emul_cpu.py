@@ -98,3 +98,44 @@ def test_png_encoder(shape):
     assert np.array_equal(ec.png_decode(png), img[::-1])
     assert np.array_equal(ec.png_decode(ec.png_encode(img, bottom_up=False)), img)
     assert len(png) > h * (w * 4 + 1)            # stored, not compressed
+
+
+@pytest.mark.parametrize("shared_points", [False, True])
+def test_vtk_ragged_strips(pkg, tmp_path, shared_points):
+    """Edge cases of the input stage: strips of unequal length, strips too short to hold a triangle (skipped, like the
+    reference's loop), repeated ids, and strips that share points (the normals then accumulate serially).  The host
+    conversion and the compact conversion + device expansion function agree bit for bit; vertices, triangle order
+    (odd triangles swapped) and instance records agree with the numpy parse."""
+    S = pkg.scenes
+    rng = np.random.RandomState(5 + int(shared_points))
+    lengths = [3, 4, 7, 2, 1, 10, 5, 3]
+    pts = rng.uniform(-1.0, 1.0, (40, 3))
+    strips, base = [], 0
+    for n in lengths:
+        if shared_points:
+            ids = rng.randint(0, len(pts), n)
+        else:
+            ids = base + rng.randint(0, 5, n)          # repeats inside a strip: degenerate triangles
+            base += 5
+        strips.append(ids.astype(np.int64))
+    path = str(tmp_path / "ragged.vtk")
+    S.write_vtk_frame(path, pts, strips)
+    host = ec.vtk_frame(path, 0)
+    dev = ec.vtk_frame(path, 1)
+    for a, b in zip(host, dev):
+        assert a.tobytes() == b.tobytes()
+    verts, shade, inst, xf = dev
+    kept = [s for s in strips if len(s) >= 3]
+    assert len(inst) == len(kept) and len(verts) == sum(len(s) - 2 for s in kept)
+    q = 0
+    for k, s in enumerate(kept):
+        assert inst[k]["first_prim"] == q and inst[k]["prim_count"] == len(s) - 2 and inst[k]["type"] == pkg.abi.TRIANGLE
+        assert np.array_equal(inst[k]["bounds_min"], pts[s].min(0).astype(np.float32))
+        assert np.array_equal(inst[k]["bounds_max"], pts[s].max(0).astype(np.float32))
+        for j in range(len(s) - 2):
+            i0, i1, i2 = s[j], (s[j + 2] if j & 1 else s[j + 1]), (s[j + 1] if j & 1 else s[j + 2])
+            assert np.array_equal(verts[q], pts[[i0, i1, i2]].astype(np.float32).reshape(9))
+            q += 1
+    n = np.stack([shade[:, 0:3], shade[:, 4:7], shade[:, 8:11]], 1).view(np.float32)
+    ln = np.sqrt((n.astype(np.float64) ** 2).sum(-1))
+    assert (np.abs(ln - 1.0) < 1e-5).__or__(ln == 0.0).all()          # unit point normals, or none (only degenerate triangles)

@@ -137,3 +137,15 @@ def test_camera_step_scripted_input(pkg):
         free, _ = pkg.cameraStep(cam, dy=dy)
         w = vec(free.target) - vec(free.center)
         assert abs(abs(np.arcsin(w[1] / np.linalg.norm(w))) - 1.2) < 1e-3
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/rtb200.h is the drop-in boundary: it must compile as C99 (what a cgo / JNI / ctypes-side binding sees)
+    and as C++, with no torch or CUDA types in it."""
+    import subprocess
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "include/rtb200.h"\nint main(void) { rt_camera_motion m; rt_animation_stats s; rt_frame_out o; (void) m; (void) s; (void) o; return 0; }\n')
+    subprocess.check_call(["gcc", "-I", ROOT, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", str(src)])
+    subprocess.check_call(["g++", "-I", ROOT, "-std=c++17", "-Wall", "-Werror", "-fsyntax-only", "-x", "c++", str(src)])
+    text = open(os.path.join(ROOT, "include", "rtb200.h")).read()
+    assert "torch" not in text and "cuda_runtime" not in text

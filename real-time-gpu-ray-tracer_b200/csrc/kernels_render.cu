@@ -35,9 +35,12 @@ __global__ void __launch_bounds__(256) rng_init_kernel(RngState *__restrict__ st
 // HEX digit (T[h][d] = M[2h]^(d & 3) * M[2h+1]^(d >> 2), 8 x 15 matrices, 384 KB), so a pixel needs one branch-free
 // product per non-zero hex digit (~5).  Powers of one matrix commute, so the result is the same state bit for bit —
 // the parity tests against the oracle (host curand_init) cover it; RTB200_RNG_INIT=curand selects the kernel above.
-constexpr int RNG_HEX_DIGITS = 8, RNG_ROWS = 160, RNG_MAT_WORDS = 800;
+constexpr int RNG_HEX_DIGITS = 8, RNG_ROWS = 160, RNG_ROW_WORDS = 8, RNG_MAT_WORDS = RNG_ROWS * RNG_ROW_WORDS;
 
-__device__ __forceinline__ void xorwow_matvec(const uint32_t *__restrict__ m, uint32_t v[5]) {
+// v <- M v over GF(2); row r of M = image of basis vector e_r, 5 words.  STRIDE 5: cuRAND's own precalc matrices;
+// STRIDE 8: the tables built here, rows padded to 32 bytes so that a row is one 128-bit load + one word.
+template<int STRIDE>
+__device__ __forceinline__ void xorwow_matvec_s(const uint32_t *__restrict__ m, uint32_t v[5]) {
     uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
 #pragma unroll
     for (int i = 0; i < 5; i++) {
@@ -45,22 +48,28 @@ __device__ __forceinline__ void xorwow_matvec(const uint32_t *__restrict__ m, ui
 #pragma unroll 8
         for (int j = 0; j < 32; j++) {
             const uint32_t mask = 0u - ((w >> j) & 1u);
-            const uint32_t *row = m + 5 * (32 * i + j);
-            r0 ^= __ldg(row) & mask; r1 ^= __ldg(row + 1) & mask; r2 ^= __ldg(row + 2) & mask; r3 ^= __ldg(row + 3) & mask; r4 ^= __ldg(row + 4) & mask;
+            const uint32_t *row = m + STRIDE * (32 * i + j);
+            if (STRIDE == 8) {
+                const uint4 a = __ldg(reinterpret_cast<const uint4 *>(row));
+                r0 ^= a.x & mask; r1 ^= a.y & mask; r2 ^= a.z & mask; r3 ^= a.w & mask; r4 ^= __ldg(row + 4) & mask;
+            } else {
+                r0 ^= __ldg(row) & mask; r1 ^= __ldg(row + 1) & mask; r2 ^= __ldg(row + 2) & mask; r3 ^= __ldg(row + 3) & mask; r4 ^= __ldg(row + 4) & mask;
+            }
         }
     }
     v[0] = r0; v[1] = r1; v[2] = r2; v[3] = r3; v[4] = r4;
 }
+__device__ __forceinline__ void xorwow_matvec(const uint32_t *__restrict__ m, uint32_t v[5]) { xorwow_matvec_s<RNG_ROW_WORDS>(m, v); }
 
 // block (h, d - 1), thread = row r: row r of T[h][d] = image of basis vector e_r under M[2h]^(d & 3) M[2h+1]^(d >> 2)
 __global__ void __launch_bounds__(RNG_ROWS) rng_tables_kernel(uint32_t *__restrict__ tables) {
     const int h = blockIdx.x / 15, d = blockIdx.x % 15 + 1, r = threadIdx.x;
     uint32_t v[5] = {0, 0, 0, 0, 0};
     v[r >> 5] = 1u << (r & 31);
-    for (int t = 0; t < (d & 3); t++) xorwow_matvec(precalc_xorwow_matrix[2 * h], v);
-    for (int t = 0; t < (d >> 2); t++) xorwow_matvec(precalc_xorwow_matrix[2 * h + 1], v);
-    uint32_t *out = tables + ((size_t) (h * 15 + d - 1) * RNG_ROWS + r) * 5;
-    for (int k = 0; k < 5; k++) out[k] = v[k];
+    for (int t = 0; t < (d & 3); t++) xorwow_matvec_s<5>(precalc_xorwow_matrix[2 * h], v);
+    for (int t = 0; t < (d >> 2); t++) xorwow_matvec_s<5>(precalc_xorwow_matrix[2 * h + 1], v);
+    uint32_t *out = tables + ((size_t) (h * 15 + d - 1) * RNG_ROWS + r) * RNG_ROW_WORDS;
+    for (int k = 0; k < RNG_ROW_WORDS; k++) out[k] = k < 5 ? v[k] : 0u;
 }
 
 // The 5 index bits that differ between the lanes of a warp, as ONE product per lane: LOW[row][word][c] = word of the
@@ -90,8 +99,8 @@ __global__ void __launch_bounds__(RNG_ROWS) rng_wide_tables_kernel(uint32_t *__r
         const uint32_t dd = (val >> (4 * h)) & 15u;
         if (dd) xorwow_matvec(tables + (size_t) (h * 15 + (int) dd - 1) * RNG_MAT_WORDS, v);
     }
-    uint32_t *out = tables + RNG_HEX_TABLE_WORDS + RNG_LOW_TABLE_WORDS + ((size_t) (which * 255 + d - 1) * RNG_ROWS + r) * 5;
-    for (int k = 0; k < 5; k++) out[k] = v[k];
+    uint32_t *out = tables + RNG_HEX_TABLE_WORDS + RNG_LOW_TABLE_WORDS + ((size_t) (which * 255 + d - 1) * RNG_ROWS + r) * RNG_ROW_WORDS;
+    for (int k = 0; k < RNG_ROW_WORDS; k++) out[k] = k < 5 ? v[k] : 0u;
 }
 
 __device__ __forceinline__ void xorwow_matvec_low(const uint32_t *__restrict__ low, uint32_t c, uint32_t v[5]) {

@@ -121,3 +121,26 @@ def test_c4_ten_million_triangles(pkg):
     o = frame(pkg, sc, flags=pkg.abi.FLAG_WAVEFRONT)
     assert o["out"].rays == g["out"].rays and np.array_equal(o["radiance"], g["radiance"])
     print(f"C4: build {g['stats'].blas_ms:.2f} ms for 10M triangles, {len(nodes)} wide nodes, frame {g['out'].render_ms:.1f} ms, {g['out'].rays} rays")
+
+
+def test_pixel_indices_beyond_2_21(pkg, port):
+    """Frames of more than 2 M pixels (config 4 is 8.3 M) take extra jump-table products for the top bits of the pixel
+    index in the per-pixel RNG initialisation.  A 32 x 140 000 frame of the enclosed demo scene (every path scatters, so
+    every pixel consumes its stream) puts the scene's rows just above index 2^21; the sampled scan-lines must equal the
+    oracle's bit for bit (profiles/tools/check_high_pixel_index.py is the same check as a script)."""
+    sc = pkg.scenes.c1a(frame=0, width=32, height=140000, spp=1, depth=4)
+    lines = [65535, 65536, 69900, 69990, 70000, 70040]            # pixel index = 32 * y + x: 2^21 starts at y = 65536
+    h = port.scene(sc, 7)
+    want = {y: h.render(SEED, y, y + 1, rgba8=False)[1][y] for y in lines}
+    h.close()
+    r = pkg.Renderer(device=0)
+    try:
+        r.commitScene(sc)
+        out = r.renderFrame(0, SEED)
+        rad = r.readFramebuffer(pkg.abi.BUF_RADIANCE).reshape(sc.height, sc.width, 3)
+    finally:
+        r.cleanup()
+    assert out.stack_overflow == 0
+    assert len({float(want[y].sum()) for y in lines}) > 3           # the lines do differ: the streams are being consumed
+    for y in lines:
+        assert np.array_equal(rad[y], want[y]), f"scan-line {y} (pixel indices from {32 * y}) differs from the oracle"

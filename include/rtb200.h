@@ -250,6 +250,8 @@ int rt_write_ppm(rt_ctx *ctx, const char *path);
  *   RT_BUFFER_RGBA8    -> binary PPM "P6", or PNG when the path ends in ".png" (as rt_write_ppm)
  *   RT_BUFFER_RADIANCE -> PFM "PF" (float RGB, little-endian, rows bottom-up: the plane's own order)
  *   RT_BUFFER_PRIMARY_T-> PFM "Pf" (one float per pixel, +inf on miss)
+ *   either of the two with a path ending in ".exr" -> uncompressed 32-bit float OpenEXR scan-line file, rows top-down
+ *                         (channels R, G, B / Z)
  *   RT_BUFFER_PRIMARY_INSTANCE / _PRIM -> "RTAOV1 <width> <height> <kind>\n" + int32 little-endian per pixel, bottom-up */
 int rt_write_image(rt_ctx *ctx, int kind, const char *path);
 

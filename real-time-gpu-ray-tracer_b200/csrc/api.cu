@@ -580,6 +580,16 @@ int rt_write_image(rt_ctx *ctx, int kind, const char *path) {
     FILE *f = fopen(path, "wb");
     if (!f) return fail(ctx, RT_ERR_IO, std::string("cannot open ") + path);
     const uint32_t W = ctx->hs.window.width, H = ctx->local_rows;
+    const size_t len = strlen(path);
+    if (len >= 4 && strcmp(path + len - 4, ".exr") == 0 && (kind == RT_BUFFER_RADIANCE || kind == RT_BUFFER_PRIMARY_T)) {
+        // "*.exr": uncompressed 32-bit float OpenEXR, top-down (image_io.h); radiance -> R, G, B; primary t -> Z
+        std::vector<uint8_t> exr;
+        exr_encode_float(reinterpret_cast<const float *>(buf.data()), W, H, kind == RT_BUFFER_RADIANCE ? 3 : 1, true, exr);
+        const bool ok_exr = fwrite(exr.data(), 1, exr.size(), f) == exr.size();
+        fclose(f);
+        if (!ok_exr) return fail(ctx, RT_ERR_IO, std::string("short write to ") + path);
+        return RT_OK;
+    }
     if (kind == RT_BUFFER_RADIANCE) fprintf(f, "PF\n%u %u\n-1.0\n", W, H);
     else if (kind == RT_BUFFER_PRIMARY_T) fprintf(f, "Pf\n%u %u\n-1.0\n", W, H);
     else fprintf(f, "RTAOV1 %u %u %d\n", W, H, kind);

@@ -73,3 +73,64 @@ inline void png_encode_rgba8(const uint8_t *rgba, uint32_t W, uint32_t H, bool b
     chunk(out, "IDAT", z);
     chunk(out, "IEND", std::vector<uint8_t>());
 }
+
+
+// ---- OpenEXR, uncompressed scan-line file, 32-bit float channels ---------------------------------------------------
+// planes: n_channels interleaved floats per pixel (3: radiance RGB -> channels B, G, R; 1: depth -> channel Z), H rows of
+// W pixels, row 0 = bottom scan-line when bottom_up.  EXR stores channels in alphabetical order, one block per
+// scan-line (y, byte count, then each channel's W values), top-down (lineOrder INCREASING_Y), after a table of block
+// offsets.  Everything little-endian.
+namespace exr_detail {
+inline void put(std::vector<uint8_t> &o, const void *p, size_t n) { const uint8_t *b = (const uint8_t *) p; o.insert(o.end(), b, b + n); }
+inline void i32(std::vector<uint8_t> &o, int32_t v) { put(o, &v, 4); }
+inline void f32(std::vector<uint8_t> &o, float v) { put(o, &v, 4); }
+inline void str(std::vector<uint8_t> &o, const char *s) { while (*s) o.push_back((uint8_t) *s++); o.push_back(0); }
+inline void attr(std::vector<uint8_t> &o, const char *name, const char *type, const std::vector<uint8_t> &value) {
+    str(o, name); str(o, type); i32(o, (int32_t) value.size()); o.insert(o.end(), value.begin(), value.end());
+}
+} // namespace exr_detail
+
+inline void exr_encode_float(const float *plane, uint32_t W, uint32_t H, int n_channels, bool bottom_up, std::vector<uint8_t> &out) {
+    using namespace exr_detail;
+    out.clear();
+    i32(out, 20000630);                       // magic
+    i32(out, 2);                              // version 2, single-part scan-line
+    // channel c of the file <- component src[c] of the plane (alphabetical channel names)
+    const char *names3[3] = {"B", "G", "R"};
+    const int src3[3] = {2, 1, 0};
+    const char *names1[1] = {"Z"};
+    const int src1[1] = {0};
+    const char **names = n_channels == 3 ? names3 : names1;
+    const int *src = n_channels == 3 ? src3 : src1;
+    std::vector<uint8_t> v;
+    for (int c = 0; c < n_channels; c++) { str(v, names[c]); i32(v, 2 /*FLOAT*/); v.push_back(0); v.push_back(0); v.push_back(0); v.push_back(0); i32(v, 1); i32(v, 1); }
+    v.push_back(0);
+    attr(out, "channels", "chlist", v);
+    v.assign(1, 0);
+    attr(out, "compression", "compression", v);                 // NO_COMPRESSION
+    v.clear(); i32(v, 0); i32(v, 0); i32(v, (int32_t) W - 1); i32(v, (int32_t) H - 1);
+    attr(out, "dataWindow", "box2i", v);
+    attr(out, "displayWindow", "box2i", v);
+    v.assign(1, 0);
+    attr(out, "lineOrder", "lineOrder", v);                     // INCREASING_Y
+    v.clear(); f32(v, 1.0f);
+    attr(out, "pixelAspectRatio", "float", v);
+    v.clear(); f32(v, 0.0f); f32(v, 0.0f);
+    attr(out, "screenWindowCenter", "v2f", v);
+    v.clear(); f32(v, 1.0f);
+    attr(out, "screenWindowWidth", "float", v);
+    out.push_back(0);                         // end of header
+    const size_t line_bytes = (size_t) W * 4 * n_channels, block = 8 + line_bytes;
+    const uint64_t first = out.size() + (uint64_t) H * 8;
+    for (uint32_t y = 0; y < H; y++) { const uint64_t off = first + (uint64_t) y * block; put(out, &off, 8); }
+    std::vector<float> row(W);
+    for (uint32_t y = 0; y < H; y++) {
+        const float *line = plane + (size_t) (bottom_up ? H - 1 - y : y) * W * n_channels;
+        i32(out, (int32_t) y);
+        i32(out, (int32_t) line_bytes);
+        for (int c = 0; c < n_channels; c++) {
+            for (uint32_t x = 0; x < W; x++) row[x] = line[(size_t) x * n_channels + src[c]];
+            put(out, row.data(), (size_t) W * 4);
+        }
+    }
+}

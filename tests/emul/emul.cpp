@@ -415,4 +415,11 @@ uint64_t emul_png_encode(const uint8_t *rgba, uint32_t w, uint32_t h, int bottom
     return png.size();
 }
 
+uint64_t emul_exr_encode(const float *plane, uint32_t w, uint32_t h, int n_channels, int bottom_up, uint8_t *out, uint64_t cap) {
+    std::vector<uint8_t> exr;
+    exr_encode_float(plane, w, h, n_channels, bottom_up != 0, exr);
+    if (out) memcpy(out, exr.data(), std::min<uint64_t>(cap, exr.size()));
+    return exr.size();
+}
+
 } // extern "C"

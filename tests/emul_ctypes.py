@@ -37,7 +37,65 @@ def load():
     lib.emul_vtk_frame.argtypes = [C.c_char_p, i32, C.POINTER(u64), C.POINTER(u64), vp, vp, vp, vp]
     lib.emul_png_encode.argtypes = [vp, C.c_uint32, C.c_uint32, i32, vp, u64]
     lib.emul_png_encode.restype = u64
+    lib.emul_exr_encode.argtypes = [vp, C.c_uint32, C.c_uint32, i32, i32, vp, u64]
+    lib.emul_exr_encode.restype = u64
     return lib
+
+
+def exr_encode(plane: np.ndarray, bottom_up: bool = True) -> bytes:
+    """The product's EXR encoder (csrc/image_io.h) on an [H, W, 3] or [H, W] float32 array."""
+    lib = load()
+    plane = np.ascontiguousarray(plane, np.float32)
+    h, w = plane.shape[:2]
+    nc = 3 if plane.ndim == 3 else 1
+    n = lib.emul_exr_encode(plane.ctypes.data, w, h, nc, int(bottom_up), None, 0)
+    out = np.zeros(n, np.uint8)
+    lib.emul_exr_encode(plane.ctypes.data, w, h, nc, int(bottom_up), out.ctypes.data, n)
+    return out.tobytes()
+
+
+def exr_decode(data: bytes):
+    """Minimal OpenEXR reader for the tests (single-part, uncompressed, FLOAT channels): returns (attributes, {channel
+    name: [H, W] float32 array, top-down})."""
+    import struct
+    magic, version = struct.unpack_from("<ii", data, 0)
+    assert magic == 20000630 and version == 2
+    pos, attrs = 8, {}
+
+    def cstr(p):
+        e = data.index(b"\0", p)
+        return data[p:e].decode(), e + 1
+
+    while data[pos] != 0:
+        name, pos = cstr(pos)
+        typ, pos = cstr(pos)
+        (size,) = struct.unpack_from("<i", data, pos)
+        attrs[name] = (typ, data[pos + 4:pos + 4 + size])
+        pos += 4 + size
+    pos += 1
+    assert attrs["compression"] == ("compression", b"\0") and attrs["lineOrder"] == ("lineOrder", b"\0")
+    xmin, ymin, xmax, ymax = struct.unpack("<4i", attrs["dataWindow"][1])
+    w, h = xmax - xmin + 1, ymax - ymin + 1
+    chans, p, body = [], 0, attrs["channels"][1]
+    while body[p] != 0:
+        e = body.index(b"\0", p)
+        nm = body[p:e].decode()
+        ptype, _plinear, xs, ys = struct.unpack_from("<iIii", body, e + 1)
+        assert ptype == 2 and xs == 1 and ys == 1
+        chans.append(nm)
+        p = e + 1 + 16
+    assert chans == sorted(chans)
+    offsets = struct.unpack_from(f"<{h}Q", data, pos)
+    out = {c: np.zeros((h, w), np.float32) for c in chans}
+    for y in range(h):
+        yy, nbytes = struct.unpack_from("<ii", data, offsets[y])
+        assert yy == ymin + y and nbytes == w * 4 * len(chans)
+        q = offsets[y] + 8
+        for c in chans:
+            out[c][y] = np.frombuffer(data, "<f4", w, q)
+            q += w * 4
+    assert offsets[-1] + 8 + w * 4 * len(chans) == len(data)
+    return attrs, out
 
 
 def png_encode(rgba: np.ndarray, bottom_up: bool = True) -> bytes:

@@ -1,6 +1,8 @@
 """`not gpu` tests of the product's host logic and of its __host__ __device__ cores compiled by g++
 (tests/emul): the same traversal / intersection / shading / LBVH functions the CUDA kernels call must reproduce the
 oracle, so kernel bugs are separated from algorithm bugs before GPU time is spent."""
+import os
+
 import numpy as np
 import pytest
 
@@ -139,3 +141,41 @@ def test_vtk_ragged_strips(pkg, tmp_path, shared_points):
     n = np.stack([shade[:, 0:3], shade[:, 4:7], shade[:, 8:11]], 1).view(np.float32)
     ln = np.sqrt((n.astype(np.float64) ** 2).sum(-1))
     assert (np.abs(ln - 1.0) < 1e-5).__or__(ln == 0.0).all()          # unit point normals, or none (only degenerate triangles)
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (7, 5), (90, 160)])
+def test_exr_encoder(shape):
+    """Output stage: uncompressed 32-bit float OpenEXR (radiance -> R, G, B; primary t -> Z incl. +inf on a miss), rows
+    flipped top-down; parsed back with an independent reader (header attributes, offset table, scan-line blocks)."""
+    h, w = shape
+    rs = np.random.RandomState(h * 100 + w)
+    rad = rs.uniform(0.0, 4.0, (h, w, 3)).astype(np.float32)
+    attrs, ch = ec.exr_decode(ec.exr_encode(rad, bottom_up=True))
+    assert sorted(ch) == ["B", "G", "R"] and attrs["channels"][0] == "chlist" and attrs["dataWindow"] == attrs["displayWindow"]
+    for k, name in enumerate("RGB"):
+        assert np.array_equal(ch[name], rad[::-1, :, k])
+    t = rs.uniform(0.001, 100.0, (h, w)).astype(np.float32)
+    t[0, 0] = np.inf
+    _, ch = ec.exr_decode(ec.exr_encode(t, bottom_up=False))
+    assert list(ch) == ["Z"] and np.array_equal(ch["Z"], t)
+
+
+def test_image_files_open_in_independent_readers(tmp_path):
+    """The PNG opens in Pillow and the EXR in OpenCV's OpenEXR reader with exactly the written values (skipped where
+    those libraries are missing — the round-trip tests above do not depend on them)."""
+    import io
+    import subprocess
+    import sys
+    rs = np.random.RandomState(3)
+    img = rs.randint(0, 256, (37, 53, 4)).astype(np.uint8)
+    Image = pytest.importorskip("PIL.Image")
+    assert np.array_equal(np.array(Image.open(io.BytesIO(ec.png_encode(img, bottom_up=True)))), img[::-1])
+    pytest.importorskip("cv2")
+    rad = rs.uniform(0.0, 4.0, (37, 53, 3)).astype(np.float32)
+    (tmp_path / "t.exr").write_bytes(ec.exr_encode(rad, bottom_up=True))
+    np.save(tmp_path / "want.npy", rad[::-1])
+    code = ("import cv2, numpy as np, sys; a = cv2.imread(sys.argv[1], cv2.IMREAD_UNCHANGED); "
+            "sys.exit(0 if a is not None and np.array_equal(a[..., ::-1], np.load(sys.argv[2])) else 3)")
+    env = dict(os.environ, OPENCV_IO_ENABLE_OPENEXR="1")
+    rc = subprocess.run([sys.executable, "-c", code, str(tmp_path / "t.exr"), str(tmp_path / "want.npy")], env=env).returncode
+    assert rc == 0

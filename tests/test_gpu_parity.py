@@ -312,6 +312,9 @@ def test_output_writers(pkg, tmp_path):
         import emul_ctypes as ec
         r.writeImage(pkg.abi.BUF_RGBA8, str(tmp_path / "f.png"))              # ".png": 8-bit RGBA PNG, top-down
         assert np.array_equal(ec.png_decode((tmp_path / "f.png").read_bytes()), rgba[::-1])
+        r.writeImage(pkg.abi.BUF_RADIANCE, str(tmp_path / "f.exr"))            # ".exr": uncompressed float OpenEXR, top-down
+        _, ch = ec.exr_decode((tmp_path / "f.exr").read_bytes())
+        assert all(np.array_equal(ch[c], rad[::-1, :, k]) for k, c in enumerate("RGB"))
         prim = r.readFramebuffer(pkg.abi.BUF_PRIMARY_PRIM).reshape(H, W)
         raw = (tmp_path / "p.aov").read_bytes()
         hdr = f"RTAOV1 {W} {H} {pkg.abi.BUF_PRIMARY_PRIM}\n".encode()

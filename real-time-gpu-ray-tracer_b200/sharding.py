@@ -31,7 +31,9 @@ def owned_rows(height: int, rank: int, world: int, tile_rows: int) -> list[int]:
 def assemble(planes, height: int, row_bytes: int, world: int, tile_rows: int):
     """De-interleaves the gathered packed planes (one 1-D uint8 tensor/array per rank, padded to equal length) into
     the full frame [height, row_bytes].  Works on torch tensors (device or host) and numpy arrays alike."""
-    if hasattr(planes[0], "numpy") or hasattr(planes[0], "device"):
+    if world == 1:                                               # a single rank's plane is the frame itself (not padded to whole tiles)
+        return planes[0][:height * row_bytes].reshape(height, row_bytes)
+    if type(planes[0]).__module__.split(".")[0] == "torch":      # (numpy 2 arrays have .device too)
         import torch
         stack = torch.stack(list(planes))
         return stack.view(world, -1, tile_rows, row_bytes).permute(1, 0, 2, 3).reshape(-1, row_bytes)[:height].contiguous()

@@ -125,3 +125,40 @@ def test_frame_shard_arithmetic_and_rank_local_series(tmp_path):
     for f in mine:
         name = f"particle_mesh/particle_{f * 100:015d}.vtk"
         assert (tmp_path / "all" / name).read_bytes() == (tmp_path / "r1" / name).read_bytes()
+
+
+def test_sharding_properties_hypothesis():
+    """Property tests of the two partitions (image tiles by row, animation frames): every unit is owned exactly once,
+    the packed planes de-interleave back to the frame for ragged heights / more ranks than tiles, and the frame
+    interleave inverts frames_of_rank."""
+    hyp = pytest.importorskip("hypothesis")
+    st = pytest.importorskip("hypothesis.strategies")
+    pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
+    sh = pkg.sharding
+
+    @hyp.settings(max_examples=150, deadline=None)
+    @hyp.given(st.integers(1, 300), st.integers(1, 9), st.sampled_from([1, 2, 4, 8, 16, 32]), st.integers(1, 5))
+    def tiles(height, world, tile_rows, row_bytes):
+        owned = [sh.owned_rows(height, r, world, tile_rows) for r in range(world)]
+        assert sorted(sum(owned, [])) == list(range(height))
+        frame = np.arange(height * row_bytes, dtype=np.int64).reshape(height, row_bytes) % 251
+        pad = sh.padded_plane_bytes(height, row_bytes, world, tile_rows)
+        planes = []
+        for r in range(world):
+            plane = np.zeros(pad, np.uint8)
+            rows = owned[r]
+            plane[:len(rows) * row_bytes] = frame[rows].astype(np.uint8).reshape(-1)
+            assert sh.local_rows(height, r, world, tile_rows) * row_bytes <= pad
+            planes.append(plane)
+        assert np.array_equal(sh.assemble(planes, height, row_bytes, world, tile_rows), frame.astype(np.uint8))
+
+    @hyp.settings(max_examples=150, deadline=None)
+    @hyp.given(st.integers(0, 500), st.integers(1, 16))
+    def frames(n, world):
+        per_rank = [sh.frames_of_rank(n, r, world) for r in range(world)]
+        assert sorted(sum(per_rank, [])) == list(range(n))
+        assert max(len(p) for p in per_rank) - min(len(p) for p in per_rank) <= 1
+        assert sh.interleave_frames(per_rank, n) == list(range(n))
+
+    tiles()
+    frames()

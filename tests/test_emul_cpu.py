@@ -179,3 +179,35 @@ def test_image_files_open_in_independent_readers(tmp_path):
     env = dict(os.environ, OPENCV_IO_ENABLE_OPENEXR="1")
     rc = subprocess.run([sys.executable, "-c", code, str(tmp_path / "t.exr"), str(tmp_path / "want.npy")], env=env).returncode
     assert rc == 0
+
+
+def test_vtk_conversions_agree_on_random_strips(pkg, tmp_path):
+    """Property test of the input stage: for random strip sets (empty strips, strips too short for a triangle, repeated
+    ids, shared points) the host conversion and the compact conversion + device expansion function agree bit for bit,
+    and the triangle count / vertex order follow the strip rule."""
+    hyp = pytest.importorskip("hypothesis")
+    st = pytest.importorskip("hypothesis.strategies")
+    S = pkg.scenes
+    path = str(tmp_path / "h.vtk")
+
+    @hyp.settings(max_examples=60, deadline=None)
+    @hyp.given(st.lists(st.lists(st.integers(0, 11), min_size=0, max_size=12), min_size=1, max_size=6), st.integers(0, 2 ** 31 - 1))
+    def check(strips, seed):
+        pts = np.random.RandomState(seed).uniform(-2.0, 2.0, (12, 3))
+        strips = [np.asarray(s, np.int64) for s in strips]
+        S.write_vtk_frame(path, pts, strips)
+        host, dev = ec.vtk_frame(path, 0), ec.vtk_frame(path, 1)
+        for a, b in zip(host, dev):
+            assert a.tobytes() == b.tobytes()
+        verts, shade, inst, xf = dev
+        kept = [s for s in strips if len(s) >= 3]
+        assert len(inst) == len(kept) == len(xf) and len(verts) == len(shade) == sum(len(s) - 2 for s in kept)
+        q = 0
+        for s in kept:
+            for j in range(len(s) - 2):
+                i0, i1, i2 = s[j], (s[j + 2] if j & 1 else s[j + 1]), (s[j + 1] if j & 1 else s[j + 2])
+                assert np.array_equal(verts[q], pts[[i0, i1, i2]].astype(np.float32).reshape(9))
+                q += 1
+        assert np.isfinite(shade[:, [0, 1, 2, 4, 5, 6, 8, 9, 10]].view(np.float32)).all()
+
+    check()

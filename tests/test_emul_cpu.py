@@ -211,3 +211,50 @@ def test_vtk_conversions_agree_on_random_strips(pkg, tmp_path):
         assert np.isfinite(shade[:, [0, 1, 2, 4, 5, 6, 8, 9, 10]].view(np.float32)).all()
 
     check()
+
+
+def test_lbvh_on_degenerate_meshes_hypothesis(pkg):
+    """Property test of the build cores (Morton keys, Karras hierarchy, refit, wide collapse — the functions the CUDA
+    kernels run, here through the serial twin) on meshes made to break them: duplicate triangles, zero-area triangles,
+    all centroids equal (every Morton key identical: the hierarchy is decided by the position tie-break alone), flat
+    meshes.  The tree must stay a tree: every primitive in exactly one leaf, every node under one parent, parent boxes
+    containing child boxes, the wide BVH's leaf order a permutation; and a frame still renders without stack overflow."""
+    hyp = pytest.importorskip("hypothesis")
+    st = pytest.importorskip("hypothesis.strategies")
+    S, abi = pkg.scenes, pkg.abi
+    coord = st.sampled_from([0.0, 0.0, 1.0, 2.0, 0.5])
+    tri = st.tuples(*[coord] * 9)
+
+    @hyp.settings(max_examples=40, deadline=None)
+    @hyp.given(st.lists(tri, min_size=1, max_size=48), st.booleans(), st.sampled_from([0, 1 << 7]))
+    def check(tris, duplicate, flags):
+        if duplicate:
+            tris = tris + tris
+        t = np.zeros(len(tris), abi.triangle_dt)
+        t["v"] = np.asarray(tris, np.float32).reshape(-1, 3, 3)
+        t["material_type"], t["material_index"], t["has_normals"] = abi.ROUGH, 0, 0
+        sc = S._mesh_scene(t, "degenerate", 16, 9, 1, 3, (0.7, 0.8, 5.0), (0.7, 0.8, 0.0), 60.0)
+        e = ec.Emul(sc, flags)
+        try:
+            b = e.lbvh(0)
+            n = len(b["keys"])
+            assert n == len(t) and sorted(b["prim_ids"].tolist()) == list(range(n))
+            assert (np.diff(b["keys"].astype(np.uint64)) >= 0).all() if n > 1 else True
+            if n >= 2:
+                left, right, parent, bounds = b["left"], b["right"], b["parent"], b["bounds"]
+                kids = np.concatenate([left, right])
+                assert sorted((~kids[kids < 0]).tolist()) == list(range(n))
+                assert sorted(kids[kids >= 0].tolist()) == list(range(1, n - 1))
+                for i in range(n - 1):
+                    for c in (left[i], right[i]):
+                        if c >= 0:
+                            assert parent[c] == i
+                            assert (bounds[c, :3] >= bounds[i, :3]).all() and (bounds[c, 3:] <= bounds[i, 3:]).all()
+            nodes, prims = e.wide(0)
+            assert sorted(prims.tolist()) == list(range(n)) and len(nodes) >= 1
+            out = e.render(SEED, threads=1)
+            assert out["overflow"] == 0 and np.isfinite(out["radiance"]).all()
+        finally:
+            e.close()
+
+    check()

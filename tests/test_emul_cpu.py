@@ -354,3 +354,34 @@ def test_instanced_meshes_under_extreme_transforms_hypothesis(pkg, port):
             assert got["rays"] == rays and np.array_equal(got["radiance"], rad)
 
     check()
+
+
+def test_camera_and_sampling_parameters_hypothesis(pkg, port):
+    """Frame parameters at the edges: odd window sizes (the pixel index uses the reference's padded pitch), sample counts
+    that are not perfect squares (floored to a square, Q7), depth 1, narrow and wide fields of view, a defocus disk,
+    other frame seeds.  The product cores must give the oracle's frame bit for bit."""
+    hyp = pytest.importorskip("hypothesis")
+    st = pytest.importorskip("hypothesis.strategies")
+    S = pkg.scenes
+
+    @hyp.settings(max_examples=25, deadline=None)
+    @hyp.given(st.sampled_from([1, 15, 16, 17, 33, 40]), st.sampled_from([1, 2, 9, 16, 21]), st.sampled_from([1, 2, 3, 4, 5, 9, 10]),
+               st.sampled_from([1, 2, 5]), st.sampled_from([20.0, 90.0, 150.0]), st.sampled_from([0.0, 0.3]),
+               st.sampled_from([0, 1, SEED, 2 ** 40 + 7, 2 ** 64 - 1]), st.booleans())
+    def check(width, height, spp, depth, fov, disk, seed, demo):
+        sc = S.c1a(frame=7, width=width, height=height, spp=spp, depth=depth) if demo else S.c1b(width=width, height=height, spp=spp, depth=depth)
+        sc.fov, sc.focus_disk_radius = fov, disk
+        e = ec.Emul(sc)
+        try:
+            got = e.render(seed, threads=1)
+        finally:
+            e.close()
+        h = port.scene(sc, 3)
+        img, rad, rays = h.render(seed)
+        t, inst, prim = h.primary(seed)
+        h.close()
+        assert got["overflow"] == 0 and got["rays"] == rays
+        assert np.array_equal(got["rgba8"], img) and np.array_equal(got["radiance"], rad)
+        assert np.array_equal(got["inst"], inst) and np.array_equal(got["prim"], prim) and np.array_equal(got["t"], t)
+
+    check()

@@ -385,3 +385,61 @@ def test_camera_and_sampling_parameters_hypothesis(pkg, port):
         assert np.array_equal(got["inst"], inst) and np.array_equal(got["prim"], prim) and np.array_equal(got["t"], t)
 
     check()
+
+
+def test_primitive_and_material_edges_hypothesis(pkg, port):
+    """Primitives and materials at the edges: tiny / huge / overlapping spheres, thin and slanted parallelograms (with the
+    reference's wrong box, Q10), sliver triangles, black and over-bright albedos, fuzz 0 and 1.  The
+    product cores must give the oracle's frame bit for bit (NaNs, if the reference's arithmetic makes any, included)."""
+    hyp = pytest.importorskip("hypothesis")
+    st = pytest.importorskip("hypothesis.strategies")
+    S, abi = pkg.scenes, pkg.abi
+    pos = st.tuples(st.sampled_from([-2.0, 0.0, 0.5, 3.0]), st.sampled_from([0.0, 1.0, 2.5]), st.sampled_from([-3.0, 0.0, 1.0]))
+    vec = st.tuples(st.sampled_from([0.0, 1.0, -2.0, 1e-3]), st.sampled_from([0.0, 3.0, 1e-3]), st.sampled_from([0.0, 1.0, -1.0]))
+    albedo = st.sampled_from([(0.0, 0.0, 0.0), (0.73, 0.73, 0.73), (1.5, 0.2, 0.9)])
+
+    @hyp.settings(max_examples=30, deadline=None)
+    @hyp.given(st.lists(st.tuples(pos, st.sampled_from([1e-3, 0.4, 1.0, 6.0])), min_size=1, max_size=4),
+               st.lists(st.tuples(pos, vec, vec), min_size=1, max_size=3),
+               st.lists(st.tuples(pos, pos, pos), min_size=1, max_size=3),
+               albedo, albedo, st.sampled_from([0.0, 0.25, 1.0]))
+    def check(spheres, quads, tris, a0, a1, fuzz):
+        sc = S.Scene(name="edges", width=28, height=16, sample_count=4, ray_trace_depth=4, center=(0.3, 1.2, 7.0), target=(0.0, 1.0, 0.0), fov=70.0)
+        sc.spheres = np.zeros(len(spheres), abi.sphere_dt)
+        for k, (c, r) in enumerate(spheres):        # (no two spheres exactly coincident: exact duplicates tie everywhere, Q1)
+            sc.spheres[k] = ((c[0] + 0.137 * k, c[1], c[2] - 0.059 * k), r * (1.0 + 0.11 * k), abi.ROUGH if k % 2 == 0 else abi.METAL, 0)
+        sc.parallelograms = np.zeros(len(quads), abi.parallelogram_dt)
+        for k, (q, u, v) in enumerate(quads):
+            sc.parallelograms[k] = (q, u, v, abi.METAL if k % 2 == 0 else abi.ROUGH, k % 2)
+        sc.triangles = np.zeros(len(tris), abi.triangle_dt)
+        for k, (a, b, c) in enumerate(tris):
+            sc.triangles[k]["v"] = [a, b, c]
+            sc.triangles[k]["material_type"], sc.triangles[k]["material_index"] = abi.ROUGH, 1
+        sc.roughs = np.zeros(2, abi.rough_dt)
+        sc.roughs["albedo"] = [a0, a1]
+        sc.metals = np.zeros(2, abi.metal_dt)
+        sc.metals[0] = (a1, fuzz)
+        sc.metals[1] = ((0.8, 0.85, 0.88), 0.0)
+        kinds = [(abi.SPHERE, k) for k in range(len(spheres))] + [(abi.PARALLELOGRAM, k) for k in range(len(quads))] + [(abi.TRIANGLE, k) for k in range(len(tris))]
+        sc.instances = S.single_instances(kinds)
+        sc.xforms = S.identity_xforms(len(kinds))
+        e = ec.Emul(sc)
+        try:
+            got = e.render(SEED, threads=1)
+        finally:
+            e.close()
+        h = port.scene(sc, 3)
+        img, rad, rays = h.render(SEED)
+        t, inst, prim = h.primary(SEED)
+        h.close()
+        same = (got["inst"] == inst) & (got["prim"] == prim)
+        assert got["overflow"] == 0
+        # overlapping primitives tie within epsilon on a few pixels (Q1: the id kept there follows the reference's own
+        # traversal order); everywhere else, and for the whole frame when nothing ties, the results are identical
+        assert same.mean() >= 0.97
+        hit = same & (inst >= 0)
+        assert np.array_equal(got["t"][hit], t[hit])
+        if same.all() and got["rays"] == rays:
+            assert np.array_equal(got["radiance"], rad, equal_nan=True) and np.array_equal(got["rgba8"], img)
+
+    check()

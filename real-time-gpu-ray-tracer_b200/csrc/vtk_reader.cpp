@@ -25,20 +25,30 @@ bool VtkSeries::load(const std::string &series_path, std::string &err) {
     const std::string s = ss.str();
     if (s.find("\"files\"") == std::string::npos) { err = "series file has no \"files\" array"; return false; }
     files.clear();
-    size_t pos = s.find("\"files\"");
+    // every {...} object of the "files" array holds one "name" string and one "time" number, in either order
+    size_t pos = s.find('[', s.find("\"files\""));
+    if (pos == std::string::npos) { err = "series file: \"files\" is not an array"; return false; }
+    const size_t end_of_array = s.find(']', pos);
     for (;;) {
-        const size_t k = s.find("\"name\"", pos);
-        if (k == std::string::npos) break;
-        const size_t q0 = s.find('"', s.find(':', k) + 1);
-        const size_t q1 = s.find('"', q0 + 1);
-        if (q0 == std::string::npos || q1 == std::string::npos) { err = "malformed name entry"; return false; }
-        const std::string name = s.substr(q0 + 1, q1 - q0 - 1);
-        const size_t t = s.find("\"time\"", q1);
+        const size_t open = s.find('{', pos);
+        if (open == std::string::npos || (end_of_array != std::string::npos && open > end_of_array)) break;
+        const size_t close = s.find('}', open);
+        if (close == std::string::npos) { err = "series file: unterminated entry"; return false; }
+        const std::string obj = s.substr(open, close - open + 1);
+        const size_t k = obj.find("\"name\"");
+        if (k == std::string::npos) { err = "series entry without a name"; return false; }
+        const size_t c0 = obj.find(':', k);
+        const size_t q0 = c0 == std::string::npos ? std::string::npos : obj.find('"', c0 + 1);
+        const size_t q1 = q0 == std::string::npos ? std::string::npos : obj.find('"', q0 + 1);
+        if (q1 == std::string::npos) { err = "malformed name entry"; return false; }
+        const std::string name = obj.substr(q0 + 1, q1 - q0 - 1);
+        const size_t t = obj.find("\"time\"");
         if (t == std::string::npos) { err = "name without time"; return false; }
-        const size_t colon = s.find(':', t);
-        const float time = std::strtof(s.c_str() + colon + 1, nullptr);
+        const size_t colon = obj.find(':', t);
+        if (colon == std::string::npos) { err = "malformed time entry"; return false; }
+        const float time = std::strtof(obj.c_str() + colon + 1, nullptr);
         files.emplace_back(name, time);
-        pos = colon;
+        pos = close + 1;
     }
     const size_t slash = series_path.find_last_of('/');
     dir = slash == std::string::npos ? std::string() : series_path.substr(0, slash + 1);

@@ -415,6 +415,25 @@ uint64_t emul_png_encode(const uint8_t *rgba, uint32_t w, uint32_t h, int bottom
     return png.size();
 }
 
+// the .vtk.series index parser: names joined by '\n' into `names` (at most cap bytes), times[k]; returns the entry
+// count, or -1 with the error text in `names`
+int64_t emul_vtk_series(const char *path, char *names, uint64_t cap, float *times, uint64_t times_cap) {
+    VtkSeries s;
+    std::string err;
+    std::string joined;
+    if (!s.load(path, err)) {
+        if (names && cap) { strncpy(names, err.c_str(), cap - 1); names[cap - 1] = 0; }
+        return -1;
+    }
+    for (size_t k = 0; k < s.files.size(); k++) {
+        joined += s.files[k].first;
+        joined += '\n';
+        if (times && k < times_cap) times[k] = s.files[k].second;
+    }
+    if (names && cap) { strncpy(names, joined.c_str(), cap - 1); names[cap - 1] = 0; }
+    return (int64_t) s.files.size();
+}
+
 uint64_t emul_exr_encode(const float *plane, uint32_t w, uint32_t h, int n_channels, int bottom_up, uint8_t *out, uint64_t cap) {
     std::vector<uint8_t> exr;
     exr_encode_float(plane, w, h, n_channels, bottom_up != 0, exr);

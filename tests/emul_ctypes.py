@@ -39,7 +39,20 @@ def load():
     lib.emul_png_encode.restype = u64
     lib.emul_exr_encode.argtypes = [vp, C.c_uint32, C.c_uint32, i32, i32, vp, u64]
     lib.emul_exr_encode.restype = u64
+    lib.emul_vtk_series.argtypes = [C.c_char_p, C.c_char_p, u64, vp, u64]
+    lib.emul_vtk_series.restype = C.c_int64
     return lib
+
+
+def vtk_series(path: str):
+    """The product's .vtk.series parser: returns ([names], times float32 array); raises RuntimeError with its message."""
+    lib = load()
+    buf = C.create_string_buffer(1 << 16)
+    times = np.zeros(4096, np.float32)
+    n = lib.emul_vtk_series(path.encode(), buf, len(buf), times.ctypes.data, len(times))
+    if n < 0:
+        raise RuntimeError(buf.value.decode())
+    return [x for x in buf.value.decode().split("\n") if x], times[:n].copy()
 
 
 def exr_encode(plane: np.ndarray, bottom_up: bool = True) -> bytes:

@@ -446,3 +446,28 @@ def test_primitive_and_material_edges_hypothesis(pkg, port):
         assert id_ok.mean() >= 0.97 and rad_ok.mean() >= 0.97
 
     check()
+
+
+def test_vtk_series_index_parser(tmp_path):
+    """The .vtk.series index (the reference reads it with a JSON library, Renderer.cu:394-443): entries in either key
+    order, any whitespace, extra keys; errors are reported, not fatal."""
+    import json
+    entries = [{"name": f"particle_mesh/particle_{k * 100:015d}.vtk", "time": 0.01 * k} for k in range(5)]
+    variants = {
+        "pretty": json.dumps({"file-series-version": "1.0", "files": entries}, indent=2),
+        "compact": json.dumps({"file-series-version": "1.0", "files": entries}, separators=(",", ":")),
+        "time_first": json.dumps({"files": [{"time": e["time"], "name": e["name"]} for e in entries], "file-series-version": "1.0"}),
+        "extra_keys_crlf": json.dumps({"file-series-version": "1.0", "files": [dict(e, note="x") for e in entries]}, indent=1).replace("\n", "\r\n"),
+    }
+    for tag, text in variants.items():
+        p = tmp_path / f"{tag}.vtk.series"
+        p.write_text(text)
+        names, times = ec.vtk_series(str(p))
+        assert names == [e["name"] for e in entries], tag
+        assert np.allclose(times, [e["time"] for e in entries], atol=1e-7), tag
+    (tmp_path / "empty.series").write_text('{"file-series-version": "1.0", "files": []}')
+    (tmp_path / "nofiles.series").write_text('{"file-series-version": "1.0"}')
+    (tmp_path / "noname.series").write_text('{"files": [{"time": 0.0}]}')
+    for bad in ("empty.series", "nofiles.series", "noname.series", "missing.series"):
+        with pytest.raises(RuntimeError):
+            ec.vtk_series(str(tmp_path / bad))

@@ -471,3 +471,24 @@ def test_vtk_series_index_parser(tmp_path):
     for bad in ("empty.series", "nofiles.series", "noname.series", "missing.series"):
         with pytest.raises(RuntimeError):
             ec.vtk_series(str(tmp_path / bad))
+
+
+@pytest.mark.parametrize("frame", [0, 137, 400])
+def test_reference_particle_frames(pkg, frame):
+    """The reference's own data (files/particle_mesh/*.vtk, 25..500 particles; present in this container only): the C++
+    reader with both conversions against the numpy parse, bit for bit, on whole frames."""
+    import os
+    path = f"/root/reference/files/particle_mesh/particle_{frame * 100:015d}.vtk"
+    if not os.path.exists(path):
+        pytest.skip("the reference's particle frames are not on this machine")
+    S = pkg.scenes
+    tris, ins, xf = S.vtk_particles(*S.read_vtk_frame(path))
+    host, dev = ec.vtk_frame(path, 0), ec.vtk_frame(path, 1)
+    for a, b in zip(host, dev):
+        assert a.tobytes() == b.tobytes()
+    verts, shade, inst, xforms = dev
+    assert len(verts) == len(tris) and len(verts) % 1258 == 0
+    assert np.array_equal(verts.view(np.uint32), np.ascontiguousarray(tris["v"]).reshape(len(tris), 9).view(np.uint32))
+    n = np.stack([shade[:, 0:3], shade[:, 4:7], shade[:, 8:11]], axis=1).reshape(len(tris), 9)
+    assert np.array_equal(n, np.ascontiguousarray(tris["n"]).reshape(len(tris), 9).view(np.uint32))
+    assert inst.tobytes() == ins.tobytes() and xforms.tobytes() == xf.tobytes()

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Summarise an ncu report's source page by CUDA source line: share of stall samples, of executed warp instructions,
 average active threads, top stall reason.  Usage: hotlines.py report.ncu-rep [kernel-regex] [top-N]"""
-import csv, io, re, subprocess, sys
+import csv, io, subprocess, sys
 
 rep = sys.argv[1]
 pat = sys.argv[2] if len(sys.argv) > 2 else None

@@ -1,6 +1,5 @@
 """`not gpu`: the C-ABI library loads, exports every symbol include/rtb200.h declares, agrees with the Python mirror on
 struct sizes, and fails loudly (no CPU fallback) without a CUDA device.  No compute calls."""
-import ctypes as C
 import os
 import re
 

@@ -32,6 +32,8 @@ typedef struct oracle_scene {
     rt_window window;
     rt_camera_input camera;
     uint64_t build_seed;                    /* seeds the (otherwise unseeded) axis RNG of the BVH build, Q13 */
+    /* EXTENSION, parity unpinned (no reference counterpart): used by the port only; the compiled reference ignores it */
+    const rt_dielectric *dielectrics;       size_t dielectric_count;
 } oracle_scene;
 
 typedef struct oracle_timing {

@@ -27,7 +27,8 @@ class OracleScene(C.Structure):
                 ("roughs", C.c_void_p), ("rough_count", C.c_size_t),
                 ("metals", C.c_void_p), ("metal_count", C.c_size_t),
                 ("instances", C.c_void_p), ("xforms", C.c_void_p), ("instance_count", C.c_size_t),
-                ("window", abi.Window), ("camera", abi.CameraInput), ("build_seed", C.c_uint64)]
+                ("window", abi.Window), ("camera", abi.CameraInput), ("build_seed", C.c_uint64),
+                ("dielectrics", C.c_void_p), ("dielectric_count", C.c_size_t)]      # extension, parity unpinned
 
 
 class OracleTiming(C.Structure):
@@ -76,6 +77,11 @@ class Oracle:
         return OracleSceneHandle(self, sc, build_seed)
 
 
+def _dielectrics(sc):
+    d = getattr(sc, "dielectrics", None)
+    return (abi.ptr(d), len(d)) if d is not None and len(d) else (None, 0)
+
+
 class OracleSceneHandle:
     def __init__(self, oracle: Oracle, sc, build_seed: int):
         self.o = oracle
@@ -83,7 +89,9 @@ class OracleSceneHandle:
         s = OracleScene(abi.ptr(sc.spheres), len(sc.spheres), abi.ptr(sc.parallelograms), len(sc.parallelograms),
                         abi.ptr(sc.triangles), len(sc.triangles), abi.ptr(sc.roughs), len(sc.roughs),
                         abi.ptr(sc.metals), len(sc.metals), abi.ptr(sc.instances), abi.ptr(sc.xforms), len(sc.instances),
-                        sc.window(), sc.camera_input(), build_seed)
+                        sc.window(), sc.camera_input(), build_seed, *_dielectrics(sc))
+        if len(getattr(sc, "dielectrics", ())) and oracle.kind != "port":
+            raise ValueError("the compiled reference has no dielectric material (extension: port only)")
         self.timing = OracleTiming()
         self.h = oracle._create(C.byref(s), C.byref(self.timing))
         self.W, self.H = sc.width, sc.height

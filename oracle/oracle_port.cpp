@@ -3,7 +3,7 @@
  *
  * From-scratch CPU restatement of the reference's per-frame ray-tracing hot path
  * (3169651074/real-time-gpu-ray-tracer), written against the reference sources and PINNED against
- * them: tests/test_oracle_vs_ref.py checks every export bit-for-bit against oracle/_ref/libref_oracle.so
+ * them: tests/test_oracle_cpu.py checks every export bit-for-bit against oracle/_ref/libref_oracle.so
  * (the reference's own .cu files compiled as C++), and tests/golden/ holds vectors generated from that
  * library by tests/golden/make_golden.py.  Same operation order as the reference everywhere; this file
  * must be compiled WITHOUT fp contraction / fast-math (plain g++ -O2 on x86-64).
@@ -223,6 +223,8 @@ struct Hit {                                                  // include/Basic/B
     V3 point, normal;
     float t;
     bool front;
+    bool primFront;     // Prim::hit's own hitFrontFace (outward normal against the local ray), before Instance::hit overwrites
+                        // it with a test against the already flipped normal — kept for the dielectric extension only
     uint32_t matType, matIndex;
     int32_t prim;       // (type << 28) | index — not in the reference record
     int32_t instance;   // not in the reference record
@@ -273,6 +275,7 @@ bool sphereHit(const SphereP &s, const RayF &ray, const Rng &range, Hit &rec) { 
     rec.matType = s.mt; rec.matIndex = s.mi;
     const V3 outward = unit(sub(rec.point, s.c));
     rec.front = dot(ray.d, outward) < 0.0f;
+    rec.primFront = rec.front;
     rec.normal = rec.front ? outward : neg(outward);
     return true;                                              // uv (Sphere.cu:41-47) is never consumed
 }
@@ -298,6 +301,7 @@ bool quadHit(const QuadP &p, const RayF &ray, const Rng &range, Hit &rec) { // s
     rec.point = x;
     rec.matType = p.mt; rec.matIndex = p.mi;
     rec.front = dot(ray.d, p.n) < 0.0;
+    rec.primFront = rec.front;
     rec.normal = rec.front ? p.n : neg(p.n);
     return true;
 }
@@ -325,6 +329,7 @@ bool triHit(const TriP &tr, const RayF &ray, const Rng &range, Hit &rec) { // sr
     rec.matType = tr.mt; rec.matIndex = tr.mi;
     const V3 n = unit(add(add(mul(tr.n[0], 1.0f - u - v), mul(tr.n[1], u)), mul(tr.n[2], v)));
     rec.front = dot(ray.d, n) < 0.0f;
+    rec.primFront = rec.front;
     rec.normal = rec.front ? n : neg(n);
     return true;
 }
@@ -357,6 +362,7 @@ struct Scene {
     std::vector<TriP> tris;
     std::vector<rt_rough> roughs;
     std::vector<rt_metal> metals;
+    std::vector<rt_dielectric> dielectrics;                   // extension, no reference counterpart
     std::vector<InstanceP> instances;
     std::vector<Bvh> blas;
     Bvh tlas;                                                 // refs[].index = instance id
@@ -550,6 +556,39 @@ bool metalScatter(const rt_metal &m, curandState *st, const RayF &in, const Hit 
     return dot(out.d, rec.normal) > 0.0f;
 }
 
+// EXTENSION — PARITY UNPINNED: the reference has no dielectric (include/Basic/BasicTypes.cuh:14-16 lists ROUGH, METAL).
+// Restated from the standard formulation (Snell refraction, Schlick reflectance, total internal reflection) in the
+// conventions of Metal::scatter (include/Material/Metal.cuh:15-32): the incoming direction is normalised first (ray
+// directions are not unit after a rough bounce, Q5), `normal` is the record's normal (already turned against the ray),
+// the side of the surface comes from Prim::hit's own hitFrontFace, ONE uniform decides reflect / refract and is always
+// drawn, (1 - cos)^5 is five multiplications (no pow), the outgoing direction is not re-normalised, always scatters.
+bool dielectricScatter(const rt_dielectric &m, curandState *st, const RayF &in, const Hit &rec, V3 &attenuation, RayF &out) {
+    const V3 v = unit(in.d), n = rec.normal;
+    const float ri = rec.primFront ? 1.0f / m.ior : m.ior;
+    float cosT = -dot(v, n);
+    if (cosT > 1.0f) cosT = 1.0f;
+    const float sin2 = 1.0f - cosT * cosT;
+    const float sinT = std::sqrt(sin2 > 0.0f ? sin2 : 0.0f);
+    float r0 = (1.0f - ri) / (1.0f + ri);
+    r0 = r0 * r0;
+    const float c1 = 1.0f - cosT;
+    const float c5 = ((c1 * c1) * (c1 * c1)) * c1;
+    const float reflectance = r0 + (1.0f - r0) * c5;
+    const float xi = uniform01(st);
+    V3 dir;
+    if (ri * sinT > 1.0f || reflectance > xi) {
+        dir = sub(v, mul(n, 2 * dot(v, n)));
+    } else {
+        const V3 perp = mul(add(v, mul(n, cosT)), ri);
+        const float k = 1.0f - len2(perp);
+        const V3 par = mul(n, -std::sqrt(std::fabs(k)));
+        dir = add(perp, par);
+    }
+    out = {rec.point, dir};
+    attenuation = {m.albedo.x, m.albedo.y, m.albedo.z};
+    return true;
+}
+
 // src/Global/Kernel.cu:64-102 (live branch of rayColor)
 V3 rayColor(const Scene &s, const RayF &ray, curandState *st, uint64_t &segments) {
     Hit rec{};
@@ -563,6 +602,7 @@ V3 rayColor(const Scene &s, const RayF &ray, curandState *st, uint64_t &segments
             V3 att{};
             if (rec.matType == RT_ROUGH) roughScatter(s.roughs[rec.matIndex], st, rec, att, out);
             else if (rec.matType == RT_METAL) { if (!metalScatter(s.metals[rec.matIndex], st, cur, rec, att, out)) return result; }
+            else if (rec.matType == RT_DIELECTRIC) dielectricScatter(s.dielectrics[rec.matIndex], st, cur, rec, att, out);   // extension
             cur = out;
             result.x *= att.x; result.y *= att.y; result.z *= att.z;
         } else {
@@ -625,6 +665,7 @@ void *port_create(const oracle_scene *sc, oracle_timing *timing) {
     for (size_t i = 0; i < sc->triangle_count; i++) s->tris.push_back(makeTri(sc->triangles[i]));
     s->roughs.assign(sc->roughs, sc->roughs + sc->rough_count);
     s->metals.assign(sc->metals, sc->metals + sc->metal_count);
+    if (sc->dielectric_count) s->dielectrics.assign(sc->dielectrics, sc->dielectrics + sc->dielectric_count);
 
     auto primBox = [&](uint32_t type, size_t i) {
         return type == RT_SPHERE ? sphereBox(s->spheres[i]) : type == RT_PARALLELOGRAM ? quadBox(s->quads[i]) : triBox(s->tris[i]);

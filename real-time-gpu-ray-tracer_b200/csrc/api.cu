@@ -408,6 +408,10 @@ int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_
 int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_out *out) {
     RT_API_BEGIN(ctx)
     if (!ctx->built || !ctx->camera_set || !ctx->materials_committed) return fail(ctx, RT_ERR_STATE, "rt_render_frame: scene not built / camera or materials missing");
+    {
+        const std::string e = ctx->hs.check_materials();
+        if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, "rt_render_frame: " + e);
+    }
     cudaStream_t s = ctx->stream;
     if (ctx->update_cb) ctx->update_cb(ctx->hs.xforms.data(), ctx->n_user_inst, (size_t) frame_index, ctx->update_user);
     CUDA_CHECK(cudaEventRecord(ctx->ev[0], s));
@@ -453,7 +457,9 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     launch_rng_init(ctx->d_rng.get(), seed, ctx->hs.cam, fr, s, ctx->d_rng_tables.get(), ctx->rng_tables_ready);
     CUDA_CHECK(cudaEventRecord(ctx->ev[2], s));
     WaveStats ws{};
-    const bool mega = ctx->flags & RT_FLAG_MEGAKERNEL;
+    // ray_trace_depth == 0: rayColor's loop body never runs (reference src/Global/Kernel.cu:64), every sample returns (1,1,1)
+    // without tracing; the one-thread-per-pixel kernel has that loop shape, the queue-driven kernels always trace one ray
+    const bool mega = (ctx->flags & RT_FLAG_MEGAKERNEL) || ctx->hs.cam.depth == 0;
     const bool persist = !mega && ctx->path_mode == 1 && !fr.traverse_bvh2;
     if (mega) {
         launch_render(sc, ctx->hs.cam, fr, s);
@@ -705,6 +711,7 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
         ctx->d_vtk_ids.upload(vc.ids.data(), vc.ids.size(), s);
         ctx->d_vtk_first_tri.upload(vc.strip_first_tri.data(), vc.strip_first_tri.size(), s);
         ctx->d_vtk_first_id.upload(vc.strip_first_id.data(), vc.strip_first_id.size(), s);
+        ctx->hs.note_material(RT_METAL, 0u);                    // every particle triangle is METAL #0 (reference src/Global/VTKReader.cu:178)
         launch_expand_strips(ctx->d_vtk_points.get(), ctx->d_vtk_normals.get(), ctx->d_vtk_ids.get(), ctx->d_vtk_first_tri.get(), ctx->d_vtk_first_id.get(),
                              (int) vc.strip_first_id.size(), (uint32_t) n_vtk_tris, RT_METAL, 0u, ctx->d_tri_verts.get(), ctx->d_tri_shade.get(), s);
         if (n_user) {
@@ -749,6 +756,7 @@ int sync_lane(rt_ctx *src, rt_ctx *c) {
     h.flags = g.flags;
     h.spheres = g.spheres; h.quads = g.quads; h.sphere_rec = g.sphere_rec; h.quad_rec = g.quad_rec;
     h.roughs = g.roughs; h.metals = g.metals; h.dielectrics = g.dielectrics;
+    for (int k = 0; k < 3; k++) h.max_mat_index[k] = g.max_mat_index[k];
     h.xforms.assign(g.xforms.begin(), g.xforms.begin() + src->n_user_inst);
     h.window = g.window; h.cam = g.cam;
     c->user_tris = src->user_tris;

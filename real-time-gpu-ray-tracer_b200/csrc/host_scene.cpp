@@ -52,6 +52,12 @@ int tlas_morton_bits(size_t n_instances) {
 std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_parallelogram *p, size_t np, const rt_triangle *t, size_t nt) {
     if ((ns && !s) || (np && !p) || (nt && !t)) return "rt_commit_geometry: null array with non-zero count";
     if (nt > RT_REF_POS_MASK || ns > RT_REF_POS_MASK || np > RT_REF_POS_MASK) return "rt_commit_geometry: more than 2^29 primitives of one type";
+    long long mm[3] = {-1, -1, -1};
+    auto note = [&mm](uint32_t type, uint32_t index) { if (type <= RT_DIELECTRIC) { if ((long long) index > mm[type]) mm[type] = index; return true; } return false; };
+    for (size_t i = 0; i < ns; i++) if (!note(s[i].material_type, s[i].material_index)) return "rt_commit_geometry: sphere with an unknown material type";
+    for (size_t i = 0; i < np; i++) if (!note(p[i].material_type, p[i].material_index)) return "rt_commit_geometry: parallelogram with an unknown material type";
+    for (size_t i = 0; i < nt; i++) if (!note(t[i].material_type, t[i].material_index)) return "rt_commit_geometry: triangle with an unknown material type";
+    for (int k = 0; k < 3; k++) max_mat_index[k] = mm[k];
     spheres.assign(s, s + ns);
     quads.assign(p, p + np);
     n_tris = nt;
@@ -89,6 +95,10 @@ std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_p
 std::string HostScene::commit_triangle_tail(size_t n_head, const rt_triangle *t, size_t nt) {
     if (nt && !t) return "commit_triangle_tail: null array with non-zero count";
     if (n_head + nt > RT_REF_POS_MASK) return "rt_commit_geometry: more than 2^29 primitives of one type";
+    for (size_t i = 0; i < nt; i++) {
+        if (t[i].material_type > RT_DIELECTRIC) return "rt_commit_geometry: triangle with an unknown material type";
+        note_material(t[i].material_type, t[i].material_index);
+    }
     n_tris = n_head + nt;
     tri_verts.resize(n_tris * 9);
     tri_shade.resize(n_tris);
@@ -128,6 +138,16 @@ std::string HostScene::commit_dielectrics(const rt_dielectric *d, size_t n) {
     if (n && !d) return "rt_commit_dielectrics: null array";
     dielectrics.resize(n);
     for (size_t i = 0; i < n; i++) dielectrics[i] = make_float4(d[i].albedo.x, d[i].albedo.y, d[i].albedo.z, d[i].ior);
+    return "";
+}
+
+std::string HostScene::check_materials() const {
+    const size_t have[3] = {roughs.size(), metals.size(), dielectrics.size()};
+    static const char *name[3] = {"rough", "metal", "dielectric"};
+    for (int k = 0; k < 3; k++)
+        if (max_mat_index[k] >= (long long) have[k])
+            return std::string("geometry refers to ") + name[k] + " material #" + std::to_string(max_mat_index[k]) + " but only " +
+                   std::to_string(have[k]) + " are committed";
     return "";
 }
 
@@ -221,6 +241,9 @@ std::string HostScene::plan_blas() {
 std::string HostScene::configure_camera(const rt_window &w, const rt_camera_input &in) {
     if (w.width == 0 || w.height == 0) return "rt_configure_camera: bad window";
     if (in.sample_count == 0) return "rt_configure_camera: sample_count must be >= 1";
+    // the path kernels carry (sample index, depth) of a path in one 32-bit word, 16 bits each
+    if (in.sample_count >= 256ull * 256ull) return "rt_configure_camera: sample_count must be below 65536 (255 x 255 strata)";
+    if (in.ray_trace_depth > 65535ull) return "rt_configure_camera: ray_trace_depth must be at most 65535";
     window = w;
     const f3 center = V(in.center), target = V(in.target), up = V(in.up);
     float d2 = 0.0f;

@@ -24,6 +24,11 @@ struct HostScene {
     std::vector<QuadD> quad_rec;
     std::vector<TriShade> tri_shade;
     std::vector<float4> roughs, metals, dielectrics;
+    // highest material index the committed geometry uses, per rt_material_type (-1: type unused); checked against the
+    // committed material counts before a frame is rendered (check_materials)
+    long long max_mat_index[3] = {-1, -1, -1};
+    void note_material(uint32_t type, uint32_t index) { if (type < 3u && (long long) index > max_mat_index[type]) max_mat_index[type] = index; }
+    std::string check_materials() const;
     // instances
     std::vector<rt_instance_desc> inst_desc;
     std::vector<rt_instance_xform> xforms;

@@ -197,20 +197,24 @@ RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const 
     const f3 lp = ray_at(lray, hit.t);
     f3 ln;
     uint32_t mt, mi;
+    bool front;                 // Prim::hit's hitFrontFace: the outward normal faces the (local) ray
     if (type == 2u) {
         const TriShade ts = sc.tri_shade[prim];
         const f3 n = unit3((ld3(ts.n0_mt) * (1.0f - hit.u - hit.v) + ld3(ts.n1_mi) * hit.u) + ld3(ts.n2) * hit.v);
-        ln = dot3(lray.d, n) < 0.0f ? n : -n;
+        front = dot3(lray.d, n) < 0.0f;
+        ln = front ? n : -n;
         mt = f2u(ts.n0_mt.w); mi = f2u(ts.n1_mi.w);
     } else if (type == 0u) {
         const SphereD s = sc.spheres[prim];
         const f3 outward = unit3(lp - ld3(s.c_r));
-        ln = dot3(lray.d, outward) < 0.0f ? outward : -outward;
+        front = dot3(lray.d, outward) < 0.0f;
+        ln = front ? outward : -outward;
         mt = s.mat_type; mi = s.mat_index;
     } else {
         const QuadD q = sc.quads[prim];
         const f3 n = ld3(q.n_flag);
-        ln = dot3(lray.d, n) < 0.0 ? n : -n;
+        front = dot3(lray.d, n) < 0.0;
+        ln = front ? n : -n;
         mt = q.mat_type; mi = q.mat_index;
     }
     const f3 wp = xf_point(ins.fwd, lp);
@@ -218,9 +222,9 @@ RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const 
     // Rough::scatter and Metal::scatter (fuzz > 0) both draw ONE random unit vector; it is drawn at a single place so
     // that the lanes of a warp that shade different materials run the rejection loop together (the stream position
     // and every value are the same as drawing it inside each branch: nothing else consumes the stream in between).
-    const bool rough = mt == 0u, metal = mt == 1u;
+    const bool rough = mt == 0u, metal = mt == 1u, glass = mt == 2u;
     float4 m = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    if (rough) m = sc.roughs[mi]; else if (metal) m = sc.metals[mi];
+    if (rough) m = sc.roughs[mi]; else if (metal) m = sc.metals[mi]; else if (glass) m = sc.dielectrics[mi];
     f3 rv = mk3(0.0f, 0.0f, 0.0f);
     if (rough || (metal && m.w > 0.0f)) rv = rng_space_vector(rng);
     if (rough) {                                                     // Rough::scatter
@@ -239,8 +243,36 @@ RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const 
         throughput.x *= m.x; throughput.y *= m.y; throughput.z *= m.z;
         return true;
     }
-    // MaterialType outside the reference's enum: rayColor's `default:;` leaves `out`/`attenuation`
-    // uninitialised in the reference; we end the path instead.
+    if (glass) {
+        // EXTENSION — PARITY UNPINNED: the reference has no dielectric (include/Basic/BasicTypes.cuh:14-16).  Snell refraction
+        // with Schlick reflectance in Metal::scatter's conventions: incoming direction normalised first (Q5 leaves ray
+        // directions un-normalised), `wn` already faces the ray, the side of the surface is Prim::hit's hitFrontFace, one
+        // uniform (always drawn) decides reflect / refract, outgoing direction not re-normalised.  m.w = index of refraction.
+        const f3 v = unit3(ray.d);
+        const float ri = front ? 1.0f / m.w : m.w;
+        float cosT = -dot3(v, wn);
+        if (cosT > 1.0f) cosT = 1.0f;
+        const float sin2 = 1.0f - cosT * cosT;
+        const float sinT = sqrtf(sin2 > 0.0f ? sin2 : 0.0f);
+        float r0 = (1.0f - ri) / (1.0f + ri);
+        r0 = r0 * r0;
+        const float c1 = 1.0f - cosT;
+        const float c5 = ((c1 * c1) * (c1 * c1)) * c1;
+        const float reflectance = r0 + (1.0f - r0) * c5;
+        const float xi = rng_uniform(rng);
+        f3 dir;
+        if (ri * sinT > 1.0f || reflectance > xi) {
+            dir = v - wn * (2 * dot3(v, wn));
+        } else {
+            const f3 perp = (v + wn * cosT) * ri;
+            const float k = 1.0f - len2(perp);
+            dir = perp + wn * (-sqrtf(fabsf(k)));
+        }
+        ray.o = wp; ray.d = dir;
+        throughput.x *= m.x; throughput.y *= m.y; throughput.z *= m.z;
+        return true;
+    }
+    // MaterialType outside {ROUGH, METAL, DIELECTRIC} is rejected at commit time (host_scene.cpp); unreachable.
     return false;
 }
 

@@ -89,7 +89,7 @@ class Renderer:
     def commitScene(self, sc, update=None):
         """Convenience: the whole start-up sequence of src/Global/Main.cu:111-123 for a scenes.Scene."""
         self.commitGeometryData(sc.spheres, sc.parallelograms, sc.triangles)
-        self.commitMaterialData(sc.roughs, sc.metals)
+        self.commitMaterialData(sc.roughs, sc.metals, getattr(sc, "dielectrics", None))
         self.configureInstances(sc.instances, sc.xforms, update)
         st = self.buildAccelerationStructure()
         self.configureCamera(sc.window(), sc.camera_input())

@@ -23,6 +23,7 @@ class Scene:
     triangles: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.triangle_dt))
     roughs: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.rough_dt))
     metals: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.metal_dt))
+    dielectrics: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.dielectric_dt))   # extension, parity unpinned
     instances: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.instance_desc_dt))
     xforms: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.instance_xform_dt))
     width: int = 640
@@ -132,6 +133,55 @@ def c1b(width: int = 640, height: int = 360, spp: int = 1, depth: int = 4, seed:
     return sc
 
 
+def c1_mixed(width: int = 160, height: int = 90, spp: int = 4, depth: int = 8, seed: int = 3) -> Scene:
+    """All three materials on all three primitive types (the dielectric is an EXTENSION with no reference counterpart —
+    parity unpinned): C1b's layout with a third of the spheres made of glass (index of refraction 1.5, one of 1 / 1.5 = an
+    air bubble), a glass parallelogram pane, a glass triangle and a rotated, non-uniformly scaled glass sphere instance."""
+    rs = np.random.RandomState(seed)
+    sc = Scene(name="C1-mixed-materials", width=width, height=height, sample_count=spp, ray_trace_depth=depth,
+               center=(0.0, 3.0, 9.0), target=(0.0, 0.5, 0.0), fov=70.0)
+    sc.parallelograms = np.zeros(2, abi.parallelogram_dt)
+    sc.parallelograms[0] = ((-50, 0, -50), (100, 0, 0), (0, 0, 100), abi.ROUGH, 0)
+    sc.parallelograms[1] = ((-2.0, 0.2, 3.0), (4.0, 0.0, 0.0), (0.0, 2.5, -0.4), abi.DIELECTRIC, 1)
+    sc.triangles = np.zeros(1, abi.triangle_dt)
+    sc.triangles[0]["v"] = [(-4.0, 0.3, 1.0), (-2.5, 0.3, 2.0), (-3.2, 2.4, 1.2)]
+    sc.triangles[0]["material_type"] = abi.DIELECTRIC
+    sc.triangles[0]["material_index"] = 0
+    roughs, metals = [(0.5, 0.5, 0.5)], []
+    diel = [((1.0, 1.0, 1.0), 1.5), ((0.9, 0.95, 1.0), 1.33), ((1.0, 1.0, 1.0), 1.0 / 1.5)]
+    n = 48
+    sc.spheres = np.zeros(n + 1, abi.sphere_dt)
+    for k in range(n):
+        gx, gz = k % 8, k // 8
+        r = f32(rs.uniform(0.25, 0.55))
+        cx = f32((gx - 3.5) * 1.7 + rs.uniform(-0.3, 0.3))
+        cz = f32((gz - 3) * 1.7 - 1.0 + rs.uniform(-0.3, 0.3))
+        u = rs.uniform()
+        if u < 0.34:
+            roughs.append(tuple(rs.uniform(0, 1, 3)))
+            sc.spheres[k] = ((cx, r, cz), r, abi.ROUGH, len(roughs) - 1)
+        elif u < 0.67:
+            metals.append((tuple(rs.uniform(0.5, 1, 3)), rs.uniform(0, 0.3)))
+            sc.spheres[k] = ((cx, r, cz), r, abi.METAL, len(metals) - 1)
+        else:
+            sc.spheres[k] = ((cx, r, cz), r, abi.DIELECTRIC, int(rs.randint(0, 3)))
+    sc.spheres[n] = ((0.0, 0.0, 0.0), 1.0, abi.DIELECTRIC, 0)
+    sc.roughs = np.zeros(len(roughs), abi.rough_dt)
+    sc.roughs["albedo"] = roughs
+    sc.metals = np.zeros(max(len(metals), 1), abi.metal_dt)
+    for i, (a, fz) in enumerate(metals):
+        sc.metals[i] = (a, fz)
+    sc.dielectrics = np.zeros(len(diel), abi.dielectric_dt)
+    for i, (a, ior) in enumerate(diel):
+        sc.dielectrics[i] = (a, ior)
+    sc.instances = single_instances([(abi.PARALLELOGRAM, 0), (abi.PARALLELOGRAM, 1), (abi.TRIANGLE, 0)] + [(abi.SPHERE, i) for i in range(n + 1)])
+    sc.xforms = identity_xforms(len(sc.instances))
+    sc.xforms[-1]["shift"] = (3.0, 1.6, 3.5)
+    sc.xforms[-1]["rotate_deg"] = (20.0, 35.0, 10.0)
+    sc.xforms[-1]["scale"] = (1.3, 0.8, 1.0)
+    return sc
+
+
 def heightfield_triangles(nx: int, nz: int, x_range, z_range, seed: int, material_tile: int = 25) -> np.ndarray:
     """Displaced height-field of nx*nz quads (2 triangles each), SURVEY §8d C2.
 
@@ -187,6 +237,19 @@ def c2(width: int = 1920, height: int = 1080, spp: int = 64, depth: int = 10, nx
     """1 M-triangle height-field, camera (0,6,9)->(0,0,0), fov 60.  nx/nz shrink it for tests."""
     tris = heightfield_triangles(nx, nz, (-10.0, 10.0), (-5.0, 5.0), seed=2)
     return _mesh_scene(tris, f"C2[{len(tris)} tris]", width, height, spp, depth, (0.0, 6.0, 9.0), (0.0, 0.0, 0.0), 60.0)
+
+
+def c2_dielectric(**kw) -> Scene:
+    """The EXTENDED config 2 of SURVEY 8d: the same height-field with the metal third of the quads made of glass
+    (index of refraction 1.5) instead — 'diffuse/metal/dielectric' of BASELINE.json configs[1].  The dielectric is an
+    extension with no reference counterpart: parity unpinned, reported separately from the headline line."""
+    sc = c2(**kw)
+    glass = sc.triangles["material_type"] == abi.METAL
+    sc.triangles["material_type"][glass] = abi.DIELECTRIC
+    sc.dielectrics = np.zeros(1, abi.dielectric_dt)
+    sc.dielectrics[0] = ((1.0, 1.0, 1.0), 1.5)
+    sc.name = sc.name.replace("C2", "C2-dielectric")
+    return sc
 
 
 def c4(width: int = 3840, height: int = 2160, spp: int = 256, depth: int = 10, nx: int = 5000, nz: int = 1000) -> Scene:

@@ -195,6 +195,7 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     hs.flags = flags;
     if (!hs.commit_geometry(s->spheres, s->sphere_count, s->parallelograms, s->parallelogram_count, s->triangles, s->triangle_count).empty() ||
         !hs.commit_materials(s->roughs, s->rough_count, s->metals, s->metal_count).empty() ||
+        !hs.commit_dielectrics(s->dielectrics, s->dielectric_count).empty() || !hs.check_materials().empty() ||
         !hs.configure_instances(s->instances, s->instance_count, s->xforms).empty() || !hs.plan_blas().empty() ||
         !hs.configure_camera(s->window, s->camera).empty()) { delete e; return nullptr; }
 

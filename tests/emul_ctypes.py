@@ -171,7 +171,7 @@ class Emul:
         s = oc.OracleScene(abi.ptr(sc.spheres), len(sc.spheres), abi.ptr(sc.parallelograms), len(sc.parallelograms),
                            abi.ptr(sc.triangles), len(sc.triangles), abi.ptr(sc.roughs), len(sc.roughs),
                            abi.ptr(sc.metals), len(sc.metals), abi.ptr(sc.instances), abi.ptr(sc.xforms), len(sc.instances),
-                           sc.window(), sc.camera_input(), 0)
+                           sc.window(), sc.camera_input(), 0, *oc._dielectrics(sc))
         self.h = self.lib.emul_create(C.byref(s), flags)
         assert self.h, "emul_create failed"
         self.W, self.H = sc.width, sc.height

@@ -492,3 +492,78 @@ def test_reference_particle_frames(pkg, frame):
     n = np.stack([shade[:, 0:3], shade[:, 4:7], shade[:, 8:11]], axis=1).reshape(len(tris), 9)
     assert np.array_equal(n, np.ascontiguousarray(tris["n"]).reshape(len(tris), 9).view(np.uint32))
     assert inst.tobytes() == ins.tobytes() and xforms.tobytes() == xf.tobytes()
+
+
+# ---- dielectric: an EXTENSION with no reference counterpart — PARITY UNPINNED ------------------------------------------
+# (reference include/Basic/BasicTypes.cuh:14-16 lists ROUGH and METAL only).  What these tests pin is that the product's
+# cores and the oracle port, two independent restatements of the same Snell / Schlick formulation, agree bit for bit.
+@pytest.mark.parametrize("which", ["mixed", "c2"])
+def test_dielectric_cores_match_port(pkg, port, which):
+    sc = pkg.scenes.c1_mixed() if which == "mixed" else pkg.scenes.c2_dielectric(width=160, height=90, spp=4, depth=10, nx=100, nz=50)
+    assert (sc.triangles["material_type"] == pkg.abi.DIELECTRIC).any()
+    r = ec.Emul(sc).render(SEED)
+    h = port.scene(sc, 11)
+    img, rad, rays = h.render(SEED)
+    t, inst, prim = h.primary(SEED)
+    assert r["overflow"] == 0 and r["rays"] == rays
+    assert np.array_equal(r["rgba8"], img) and np.array_equal(r["radiance"], rad)
+    assert np.array_equal(r["inst"], inst) and np.array_equal(r["prim"], prim) and np.array_equal(r["t"], t)
+
+
+def test_dielectric_physics(pkg, port):
+    """A glass slab in front of the camera: with index of refraction 1 the slab is invisible apart from the Schlick term
+    (r0 = 0, reflectance = (1 - cos)^5 ~ 0 at normal incidence), so the frame equals the empty scene's almost everywhere;
+    with 1.5 the refraction shifts what is seen, and every path still ends on the background (albedo 1 everywhere)."""
+    S = pkg.scenes
+
+    def slab(ior):
+        sc = S.Scene(name=f"slab-{ior}", width=64, height=36, sample_count=4, ray_trace_depth=12, center=(0.0, 0.0, 5.0), target=(0.0, 0.0, 0.0), fov=60.0)
+        sc.spheres = np.zeros(1, pkg.abi.sphere_dt)
+        sc.spheres[0] = ((0.0, 0.0, 0.0), 1.5, pkg.abi.DIELECTRIC, 0)
+        sc.roughs = np.zeros(1, pkg.abi.rough_dt)
+        sc.dielectrics = np.zeros(1, pkg.abi.dielectric_dt)
+        sc.dielectrics[0] = ((1.0, 1.0, 1.0), ior)
+        sc.instances = S.single_instances([(pkg.abi.SPHERE, 0)])
+        sc.xforms = S.identity_xforms(1)
+        return sc
+
+    bg = np.array([0.7, 0.8, 0.9], np.float32)
+    for ior in (1.0, 1.5):
+        r = ec.Emul(slab(ior)).render(SEED)
+        # white glass, nothing else in the scene: whatever the path does, it ends on the background or runs out of depth
+        # (Q6: a path that runs out of depth returns its throughput, here (1,1,1)) -> every sample is the background or white
+        assert (r["radiance"] >= bg - 1e-5).all() and (r["radiance"] <= 1.0 + 1e-6).all()
+    inside = ec.Emul(slab(1.0)).render(SEED)
+    centre = inside["radiance"][18, 32]
+    assert np.allclose(centre, bg, atol=1e-5)          # straight through: two refractions with ratio 1
+
+
+def test_material_validation(pkg):
+    """Unknown material types and out-of-range material indices are refused before any kernel reads them."""
+    sc = pkg.scenes.c1b(width=32, height=18, spp=1, depth=2)
+    ec.Emul(sc)                                         # fine as committed
+    bad = pkg.scenes.c1b(width=32, height=18, spp=1, depth=2)
+    bad.spheres[3]["material_type"] = 7
+    with pytest.raises(AssertionError):
+        ec.Emul(bad)
+    bad = pkg.scenes.c1b(width=32, height=18, spp=1, depth=2)
+    bad.spheres[3]["material_type"] = pkg.abi.METAL
+    bad.spheres[3]["material_index"] = 10_000
+    with pytest.raises(AssertionError):
+        ec.Emul(bad)
+    bad = pkg.scenes.c1b(width=32, height=18, spp=1, depth=2)
+    bad.spheres[3]["material_type"] = pkg.abi.DIELECTRIC      # no dielectrics committed
+    bad.spheres[3]["material_index"] = 0
+    with pytest.raises(AssertionError):
+        ec.Emul(bad)
+
+
+@pytest.mark.parametrize("spp,depth,ok", [(255 * 255, 10, True), (256 * 256, 10, False), (4, 65535, True), (4, 65536, False), (0, 4, False)])
+def test_camera_limits(pkg, spp, depth, ok):
+    """The path kernels carry (sample, depth) in 16 bits each: configure_camera refuses what would wrap."""
+    sc = pkg.scenes.c1a(width=16, height=9, spp=spp, depth=depth)
+    if ok:
+        ec.Emul(sc)
+    else:
+        with pytest.raises(AssertionError):
+            ec.Emul(sc)

@@ -43,6 +43,8 @@ def check_against_oracle(g, h, sc):
     rmse = float(np.sqrt(np.mean((g["radiance"] - rad) ** 2)))
     assert rmse <= 1e-3, f"{sc.name}: radiance RMSE {rmse:.3e} > 1e-3"
     diff8 = np.abs(g["rgba8"].astype(int) - img.astype(int)).max()
+    # the bar for byte work is bit-exact: castToUchar4's output (reference include/Basic/Color3.cuh:99-114) compared directly
+    assert np.array_equal(g["rgba8"], img), f"{sc.name}: RGBA8 frame differs from the oracle's (max byte difference {diff8})"
     bitexact = np.array_equal(g["radiance"], rad) and np.array_equal(g["t"], t) and g["out"].rays == rays
     print(f"{sc.name}: id-agreement={agree:.6f} rmse={rmse:.3e} max|rgba8 diff|={diff8} rays gpu={g['out'].rays} cpu={rays} bit-exact={bitexact}")
     return bitexact
@@ -54,6 +56,17 @@ def test_frame_matches_oracle(pkg, port, idx):
     g = gpu_frame(pkg, sc)
     h = port.scene(sc, 4321)
     check_against_oracle(g, h, sc)
+
+
+@pytest.mark.parametrize("variant", ["c1a", "c1b"])
+def test_config1_at_its_quoted_size(pkg, port, variant):
+    """BASELINE.json configs[0] whole: 640x360, 1 spp, depth 4, seed 0x5EED (SURVEY 8d C1a = the reference's Main.cu
+    fixture, C1b = ~100 primitives), every pixel against the oracle (reference src/Global/Kernel.cu:105-147)."""
+    sc = getattr(pkg.scenes, variant)(width=640, height=360, spp=1, depth=4)
+    g = gpu_frame(pkg, sc)
+    h = port.scene(sc, 2024)
+    check_against_oracle(g, h, sc)
+    h.close()
 
 
 @pytest.mark.parametrize("idx", [0, 3, 4])
@@ -111,6 +124,51 @@ def test_parallelogram_fix_flag(pkg, port):
     compat = gpu_frame(pkg, sc)
     fixed = gpu_frame(pkg, sc, flags=pkg.abi.FLAG_FIX_PARALLELOGRAM_BBOX)
     assert (fixed["inst"] == 0).sum() > (compat["inst"] == 0).sum()
+
+
+@pytest.mark.parametrize("which", ["mixed", "c2"])
+def test_dielectric_matches_port(pkg, port, which):
+    """EXTENSION — PARITY UNPINNED (the reference has ROUGH and METAL only, include/Basic/BasicTypes.cuh:14-16): the CUDA
+    path against the oracle port's independent restatement of the same Snell / Schlick scatter, all three materials on
+    all three primitive types, and the extended config 2 (glass instead of metal) at test size."""
+    sc = pkg.scenes.c1_mixed() if which == "mixed" else pkg.scenes.c2_dielectric(width=160, height=90, spp=4, depth=10, nx=100, nz=50)
+    for flags in (0, pkg.abi.FLAG_WAVEFRONT, pkg.abi.FLAG_MEGAKERNEL):
+        assert check_against_oracle(gpu_frame(pkg, sc, flags=flags), port.scene(sc, 77), sc)
+
+
+def test_argument_limits(pkg):
+    """what the kernels cannot represent is refused with RT_ERR_ARGUMENT instead of hanging or reading out of bounds."""
+    r = pkg.Renderer(device=0)
+    try:
+        sc = pkg.scenes.c1b(width=32, height=18, spp=1, depth=2)
+        r.commitScene(sc)
+        for spp, depth in ((256 * 256, 4), (4, 65536)):
+            bad = pkg.scenes.c1b(width=32, height=18, spp=spp, depth=depth)
+            with pytest.raises(pkg.RtError) as e:
+                r.configureCamera(bad.window(), bad.camera_input())
+            assert e.value.code == -2
+        # a material index beyond the committed materials
+        sc.spheres[5]["material_type"] = pkg.abi.METAL
+        sc.spheres[5]["material_index"] = 4096
+        r.commitScene(sc)
+        with pytest.raises(pkg.RtError) as e:
+            r.renderFrame(0, SEED)
+        assert e.value.code == -2 and "metal" in str(e.value)
+        sc.spheres[5]["material_type"] = 9
+        with pytest.raises(pkg.RtError) as e:
+            r.commitGeometryData(sc.spheres, sc.parallelograms, sc.triangles)
+        assert e.value.code == -2
+    finally:
+        r.cleanup()
+
+
+def test_depth_zero_is_white(pkg, port):
+    """ray_trace_depth = 0: rayColor's loop never runs (reference src/Global/Kernel.cu:64), every sample is (1,1,1)."""
+    sc = pkg.scenes.c1a(width=64, height=36, spp=4, depth=0)
+    g = gpu_frame(pkg, sc)
+    img, rad, rays = port.scene(sc, 1).render(SEED)
+    assert g["out"].rays == rays == 0
+    assert np.array_equal(g["radiance"], rad) and np.array_equal(g["rgba8"], img) and (rad == 1.0).all()
 
 
 def test_error_codes(pkg):

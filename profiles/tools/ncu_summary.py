@@ -1,8 +1,11 @@
 #!/usr/bin/env python
 """Summarise one kernel of an ncu report (--set full) as JSON: duration, DRAM/L2 traffic, issue/ALU utilisation,
-lane efficiency, stall mix.  Usage: ncu_summary.py report.ncu-rep kernel-regex out.json [traffic_latest.json]
+lane efficiency, stall mix.  Usage: ncu_summary.py report.ncu-rep kernel-regex out.json [traffic_latest.json config [spp]]
 
-The optional 4th argument also writes {"dram_bytes_per_launch": ...} which bench.py reads into roofline.traffic."""
+With the optional arguments the DRAM bytes per launch are also recorded in traffic_latest.json under `config` ("c2", "c4",
+...) together with the hash of the kernel's sources (tools/kernel_hash.py); bench.py reads that into roofline.traffic and
+drops it when the sources no longer hash the same.  `spp`: the capture ran at that many samples per pixel (bench.py
+scales the bytes to the workload's sample count)."""
 import csv, io, json, subprocess, sys
 
 rep, pat, out = sys.argv[1], sys.argv[2], sys.argv[3]
@@ -40,6 +43,19 @@ s = {
 }
 s["dram_bytes_per_launch"] = s["dram_bytes_read"] + s["dram_bytes_write"]
 json.dump(s, open(out, "w"), indent=1)
-if len(sys.argv) > 4:
-    json.dump({"dram_bytes_per_launch": s["dram_bytes_per_launch"], "kernel": s["kernel"], "from": out}, open(sys.argv[4], "w"), indent=1)
+if len(sys.argv) > 5:
+    import os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from kernel_hash import kernel_source_hash
+    try:
+        allrec = json.load(open(sys.argv[4]))
+        if "dram_bytes_per_launch" in allrec:
+            allrec = {}
+    except Exception:
+        allrec = {}
+    rec = {"dram_bytes_per_launch": s["dram_bytes_per_launch"], "kernel": s["kernel"], "from": out, "kernel_source_sha256": kernel_source_hash()}
+    if len(sys.argv) > 6:
+        rec["scale_to_spp"] = int(sys.argv[6])
+    allrec[sys.argv[5]] = rec
+    json.dump(allrec, open(sys.argv[4], "w"), indent=1)
 print(json.dumps(s, indent=1))

@@ -795,11 +795,6 @@ struct AnimationShared {
     std::string err;
     rt_frame_sink sink = nullptr;
     void *user = nullptr;
-    // The collapse kernel of a rebuild needs its whole grid resident (2 CTAs per SM, its items poll on one another).
-    // Up to five such grids fit on an SM side by side (48 registers x 128 threads each); with more lanes than that the
-    // rebuilds take turns, so that two half-resident grids can never wait for each other's SM space.
-    std::mutex build_mu;
-    bool serialise_builds = false;
 };
 
 void run_lane(rt_ctx *c, const std::vector<size_t> &frames, uint64_t seed, AnimationShared *sh) {
@@ -817,12 +812,7 @@ void run_lane(rt_ctx *c, const std::vector<size_t> &frames, uint64_t seed, Anima
     int rc = rt_prefetch_vtk_frame(c, frames[0]);
     for (size_t j = 0; rc == RT_OK && j < frames.size() && sh->stop.load() == 0; j++) {
         clk::time_point t = clk::now();
-        if (sh->serialise_builds) {
-            std::lock_guard<std::mutex> g(sh->build_mu);
-            rc = rt_set_vtk_frame(c, frames[j]);
-        } else {
-            rc = rt_set_vtk_frame(c, frames[j]);
-        }
+        rc = rt_set_vtk_frame(c, frames[j]);       // rebuilds of different lanes may overlap freely (the collapse claims its items by ticket)
         if (rc != RT_OK) break;
         const double set_ms = ms_since(t), parse_ms = c->vtk_parse_ms;
         if (j + 1 < frames.size()) rc = rt_prefetch_vtk_frame(c, frames[j + 1]);     // parsed while this frame renders
@@ -897,7 +887,6 @@ extern "C" int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t fram
     AnimationShared sh;
     sh.sink = sink;
     sh.user = user;
-    sh.serialise_builds = L > 4;
     const auto t0 = std::chrono::steady_clock::now();
     std::vector<std::thread> th;
     for (int l = 1; l < L; l++) th.emplace_back(run_lane, lane_ctx[l], std::cref(lane_frames[l]), seed, &sh);

@@ -24,6 +24,7 @@
 namespace {
 
 constexpr int PT = 128;
+constexpr uint32_t PID_MASK = 0x0FFFFFFFu;      // path state: tile-major pixel id in the low 28 bits, frame of the window above
 constexpr uint32_t NG_INNER = 0x00FFFFFFu;      // node group has pending inner hits iff .y > NG_INNER
 #ifndef RT_PERSIST_MIN_BLOCKS
 #define RT_PERSIST_MIN_BLOCKS 6   /* 80 registers: no spills; measured faster than 8 blocks x 64 registers */
@@ -63,8 +64,8 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
         // ---- cheap transitions: nothing pending in registers -> leave instance / ray finished / pop -----------------
         if (state == ST_TRACE && tg.y == 0u && ng.y <= NG_INNER) {
             if (inst >= 0 && sp == inst_sp && sp != 0) {         // BLAS exhausted, TLAS work left: back to world space
-                inst = -1;
                 const float4 o = pb.ray_o[slot], d = pb.ray_d[slot];
+                inst = -1 - (int) __float_as_uint(d.w);          // inst < 0: on the TLAS of frame -1 - inst of the window
                 r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);
                 wide_setup_ray(r);
             }
@@ -111,10 +112,10 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                     n.n0 = make_float4(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z), __uint_as_float(a.w));
                     n.n1 = q[1]; n.n2 = q[2]; n.n3 = q[3]; n.n4 = q[4];
                 } else {
-                    n = load_node8(inst < 0 ? sc.tlas_nodes8 : sc.blas_nodes8, base + rel);
+                    n = load_node8(inst < 0 ? sc.tlas_nodes8 + (size_t) (uint32_t) (-1 - inst) * pb.tlas_node_stride : sc.blas_nodes8, base + rel);
                 }
 #else
-                const BvhNode8 n = load_node8(inst < 0 ? sc.tlas_nodes8 : sc.blas_nodes8, base + rel);
+                const BvhNode8 n = load_node8(inst < 0 ? sc.tlas_nodes8 + (size_t) (uint32_t) (-1 - inst) * pb.tlas_node_stride : sc.blas_nodes8, base + rel);
 #endif
                 if (COUNT) stats.nodes++;
                 const uint32_t hm = node8_intersect(n, r, RT_TMIN, hit.tc);
@@ -136,11 +137,12 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                     // TLAS leaf: enter one instance, keep the rest of the group and the node group for later
                     if (tg.y) { if (sp < RT_WIDE_STACK) { stk[sp * PT] = tg; sp++; } else overflow = 1u; }
                     if (ng.y > NG_INNER) { if (sp < RT_WIDE_STACK) { stk[sp * PT] = ng; sp++; } else overflow = 1u; }
-                    inst = (int) __ldg(&sc.tlas_leaf_inst[tg.x + (uint32_t) idx]);
+                    const uint32_t fw = (uint32_t) (-1 - inst);      // frame of the window this ray belongs to
+                    inst = (int) __ldg(&sc.tlas_leaf_inst[(size_t) fw * pb.tlas_leaf_stride + tg.x + (uint32_t) idx]);
                     if (COUNT) stats.insts++;
                     float inv[12];
                     int root8;
-                    load_instance_wide(sc, inst, inv, root8, prim_type);
+                    load_instance_wide(sc, inst, inv, root8, prim_type, fw * pb.inst_stride);
                     const f3 wo = r.ray.o, wd = r.ray.d;
                     r.ray.o = xf_point(inv, wo);                     // Instance::hit: origin as point, direction as vector,
                     r.ray.d = xf_vector(inv, wd);                    // not re-normalised (reference src/AS/Instance.cu:26-28)
@@ -160,6 +162,7 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
             RayD ray{};
             f3 thr = mk3(1.f, 1.f, 1.f);
             uint32_t sample = 0, depth = 0, pix_rays = 0;
+            // pid = tile-major pixel id | frame of the window << 28 (PID_MASK / FW below)
             bool need_pixel = shading && fresh;
             bool need_primary = false, acc_dirty = false;
             if (shading && !fresh) {
@@ -174,16 +177,17 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 const uint32_t sd = __float_as_uint(t4.w);
                 sample = sd >> 16; depth = sd & 0xFFFFu;
                 pix_rays = __float_as_uint(o.w);                     // rays of this pixel so far
+                const uint32_t fw = pid >> 28;
                 if (fr.aov_t && sample == 0u && depth == 0u) {       // primary hit of the pixel's first sample
                     uint32_t lx, ly;
-                    pixel_coords(pid, pb.tiles_x, lx, ly);
-                    const uint32_t lp = ly * cam.width + lx;
+                    pixel_coords(pid & PID_MASK, pb.tiles_x, lx, ly);
+                    const size_t lp = (size_t) fw * pb.frame_px + ly * cam.width + lx;
                     const bool has = hit.inst >= 0;
                     fr.aov_t[lp] = has ? hit.t : RT_INF;
                     fr.aov_inst[lp] = has ? hit.inst : -1;
                     fr.aov_prim[lp] = has ? (int) ((ref_type(hit.leaf) << 28) | sc.leaf_prims8[ref_pos(hit.leaf)]) : -1;
                 }
-                const bool alive = shade_scatter<true>(sc, cam, ray, hit, thr, rng);
+                const bool alive = shade_scatter<true>(sc, cam, ray, hit, thr, rng, fw * pb.inst_stride);
                 depth++;
                 if (!(alive && depth < cam.depth)) {
                     // path over: rayColor returns the throughput (Q6); next sample or next pixel
@@ -192,16 +196,27 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                     sample++;
                     if (sample == cam.sqrtSamples * cam.sqrtSamples) {
                         uint32_t lx, ly;
-                        pixel_coords(pid, pb.tiles_x, lx, ly);
-                        const uint32_t lp = ly * cam.width + lx;
+                        pixel_coords(pid & PID_MASK, pb.tiles_x, lx, ly);
+                        const size_t lp = (size_t) fw * pb.frame_px + ly * cam.width + lx;
                         const float w = cam.rcpSqrtSamples * cam.rcpSqrtSamples;
                         const float cr = acc.x * w, cg = acc.y * w, cb = acc.z * w;
-                        fr.radiance[3 * (size_t) lp + 0] = cr;
-                        fr.radiance[3 * (size_t) lp + 1] = cg;
-                        fr.radiance[3 * (size_t) lp + 2] = cb;
-                        const size_t op = fr.rgba8_is_full_frame ? (size_t) global_row(fr, ly) * cam.width + lx : (size_t) lp;
+                        fr.radiance[3 * lp + 0] = cr;
+                        fr.radiance[3 * lp + 1] = cg;
+                        fr.radiance[3 * lp + 2] = cb;
+                        const size_t op = fr.rgba8_is_full_frame ? (size_t) fw * pb.full_px + (size_t) global_row(fr, ly) * cam.width + lx : lp;
                         reinterpret_cast<uchar4 *>(fr.rgba8)[op] = make_uchar4(to_byte(cr), to_byte(cg), to_byte(cb), 255);
-                        atomicAdd(&pb.tile_cost[pid >> 5], pix_rays);      // next frame hands the dear tiles out first
+                        if (fw == 0u) atomicAdd(&pb.tile_cost[(pid & PID_MASK) >> 5], pix_rays);      // the next launch hands the dear tiles out first
+                        if (pb.frame_done) {
+                            // frame completion: the pixel's stores, then its count; the lane that counts the frame's last pixel
+                            // publishes the frame (system-wide fence, then the flags the host / rank 0 wait on)
+                            if (pb.frame_rays) atomicAdd(&pb.frame_rays[fw], (unsigned long long) pix_rays);
+                            __threadfence();
+                            if (atomicAdd(&pb.frame_done[fw], 1u) + 1u == pb.valid_pixels) {
+                                __threadfence_system();
+                                if (pb.peer_flags) pb.peer_flags[fw] = pb.ticket;
+                                pb.host_flags[fw] = pb.ticket;
+                            }
+                        }
                         need_pixel = true;
                     } else {
                         need_primary = true;
@@ -215,16 +230,18 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 if (any == 0u) break;
                 const uint32_t cand = warp_append(pb.next_pixel, need_pixel);
                 if (need_pixel) {
-                    if (cand >= pb.n_pixels) {
+                    const uint32_t cf = cand / pb.n_pixels;          // frame of the window (its queue follows the previous frame's)
+                    if (cf >= pb.n_frames) {
                         state = ST_DEAD; need_pixel = false;
                     } else {
-                        const uint32_t tile = __ldg(&pb.tile_order[cand >> 5]);
-                        const uint32_t gp = (tile << 5) | (cand & 31u);
+                        const uint32_t cp = cand - cf * pb.n_pixels;
+                        const uint32_t tile = __ldg(&pb.tile_order[cp >> 5]);
+                        const uint32_t gp = (tile << 5) | (cp & 31u);
                         uint32_t lx, ly;
                         pixel_coords(gp, pb.tiles_x, lx, ly);
                         if (lx < cam.width && ly < fr.local_rows && global_row(fr, ly) < cam.height) {
-                            pid = gp; need_pixel = false; need_primary = true;
-                            rng = fr.rng[ly * cam.width + lx];
+                            pid = gp | (cf << 28); need_pixel = false; need_primary = true;
+                            rng = fr.rng[(size_t) cf * pb.frame_px + ly * cam.width + lx];
                             acc = make_float4(0.f, 0.f, 0.f, __uint_as_float(pid));
                             acc_dirty = true;
                             sample = 0;
@@ -236,7 +253,7 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
             if (shading && state != ST_DEAD) {
                 if (need_primary) {
                     uint32_t lx, ly;
-                    pixel_coords(pid, pb.tiles_x, lx, ly);
+                    pixel_coords(pid & PID_MASK, pb.tiles_x, lx, ly);
                     const uint32_t si = sample / cam.sqrtSamples, sj = sample % cam.sqrtSamples;
                     ray = primary_ray(cam, lx, global_row(fr, ly), si, sj, rng);
                     thr = mk3(1.f, 1.f, 1.f);
@@ -245,14 +262,14 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 if (acc_dirty) pb.acc[slot] = acc;
                 // every lane that is still alive here starts a ray: the path's next segment or a new primary ray
                 pb.ray_o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(pix_rays + 1u));
-                pb.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
+                pb.ray_d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(pid >> 28));
                 pb.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float((sample << 16) | depth));
                 pb.rng_a[slot] = make_uint4(rng.d, rng.v0, rng.v1, rng.v2);
                 pb.rng_b[slot] = make_uint2(rng.v3, rng.v4);
                 r.ray = ray;
                 wide_setup_ray(r);
                 hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.f; hit.v = 0.f; hit.inst = -1; hit.leaf = 0;
-                sp = 0; inst = -1; inst_sp = 0;
+                sp = 0; inst = -1 - (int) (pid >> 28); inst_sp = 0;
                 ng = make_uint2(0u, 0x80000000u);           // TLAS root: one pending inner hit at relative index 0
                 tg = make_uint2(0u, 0u);
                 state = ST_TRACE;
@@ -309,7 +326,7 @@ __global__ void __launch_bounds__(256) tile_keys_kernel(uint32_t *__restrict__ t
 
 } // namespace
 
-void PersistRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count) {
+void PersistRenderer::render_window(const SceneD &sc, const CameraD &cam, const FrameD &fr, const PersistBuffers *win, cudaStream_t stream, int sm_count) {
     if (blocks_per_sm_[0] == 0) {
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm_[0], persist8_kernel<false>, PT, 0));
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm_[1], persist8_kernel<true>, PT, 0));
@@ -348,6 +365,14 @@ void PersistRenderer::render(const SceneD &sc, const CameraD &cam, const FrameD 
     pb.rng_a = rng_a_.get(); pb.rng_b = rng_b_.get(); pb.next_pixel = counter_.get();
     pb.tile_order = vals; pb.tile_cost = tile_cost_.get();
     pb.n_blas_nodes = n_blas_nodes;
+    pb.n_frames = 1u;
+    pb.frame_px = cam.width * fr.local_rows;
+    if (win) {
+        pb.n_frames = win->n_frames; pb.frame_px = win->frame_px; pb.full_px = win->full_px;
+        pb.tlas_node_stride = win->tlas_node_stride; pb.tlas_leaf_stride = win->tlas_leaf_stride; pb.inst_stride = win->inst_stride;
+        pb.valid_pixels = win->valid_pixels; pb.ticket = win->ticket;
+        pb.frame_rays = win->frame_rays; pb.frame_done = win->frame_done; pb.host_flags = win->host_flags; pb.peer_flags = win->peer_flags;
+    }
     CUDA_CHECK(cudaMemsetAsync(counter_.get(), 0, sizeof(uint32_t), stream));
     if (count) persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
     else persist8_kernel<false><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);

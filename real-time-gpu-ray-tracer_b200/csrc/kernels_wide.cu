@@ -2,9 +2,12 @@
 //
 // One persistent launch.  Work item i = wide node i; the thread that encodes node i allocates consecutive node
 // slots for its inner children and consecutive leaf-order positions for its leaf primitives (two atomic
-// counters) and publishes the children's binary roots into queue[child_base ..].  Threads own the items
-// tid, tid + T, tid + 2T, ... and poll queue[i] until the producer (always an item with a smaller index, so a
-// resident or finished thread) has written it.  Termination: finished == allocated.
+// counters) and publishes the children's binary roots into queue[child_base ..].  Items are CLAIMED in increasing
+// order from a ticket counter (one warp-aggregated atomic per 32 items) and a thread polls queue[i] of the item it
+// claimed until the producer has written it.  The producer of item i is an item j < i, and every ticket below a
+// claimed one was claimed earlier, by a thread that is running or has finished — so a wait always ends, whatever
+// part of the grid is resident (no co-residency assumption: other tenants of the GPU, concurrent builds of other
+// contexts and partially scheduled grids only make it slower).  Termination: finished == allocated.
 // The node contents are a pure function of the binary tree (rt_wide_core.h); only the memory layout depends on
 // the order of the atomics, and the parity tests compare the trees canonically against the serial twin.
 #include "build.h"
@@ -38,58 +41,67 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
                                                       BvhNode8 *__restrict__ nodes8, uint32_t *__restrict__ leaf_pos8) {
     volatile int *vq = queue;
     volatile uint32_t *vc = counters;
-    const int stride = gridDim.x * blockDim.x;
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t backoff = 32u;
-    bool allocated = false;                        // item i is known to be allocated (so it will be published)
+    const uint32_t lane = threadIdx.x & 31u;
     for (;;) {
-        if (i < capacity) {
-            const int root = vq[i];
-            if (root != QUEUE_EMPTY) {
-                WideChildren w;
-                wide_expand(view, root, leaf_max, w);
-                const int k = wide_inner_count(w), m = wide_prim_count(w);
-                const uint32_t child_base = k ? atomicAdd(&counters[0], (uint32_t) k) : 0u;
-                const uint32_t prim_base = m ? atomicAdd(&counters[1], (uint32_t) m) : 0u;
-                BvhNode8 node;
-                int child_in_slot[8];
-                wide_encode(w, child_base, prim_base, node, child_in_slot);
-                nodes8[i] = node;
-                uint32_t j = 0, off = 0;
-                for (int sl = 0; sl < 8; sl++) {
-                    const int c = child_in_slot[sl];
-                    if (c < 0) continue;
-                    if (w.ref[c] >= 0) {
-                        vq[child_base + j] = w.ref[c];
-                        j++;
-                    } else {
+        // ---- claim the next 32 items for this warp (tickets only grow: everything below them is in someone's hands) ----
+        uint32_t base = 0;
+        if (lane == 0u) base = atomicAdd(&counters[3], 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const int i = (int) (base + lane);
+        bool finished_all = false;
+        uint32_t backoff = 32u;
+        bool allocated = false;                    // item i is known to be allocated (so it will be published)
+        for (;;) {
+            if (i < capacity) {
+                const int root = vq[i];
+                if (root != QUEUE_EMPTY) {
+                    WideChildren w;
+                    wide_expand(view, root, leaf_max, w);
+                    const int k = wide_inner_count(w), m = wide_prim_count(w);
+                    const uint32_t child_base = k ? atomicAdd(&counters[0], (uint32_t) k) : 0u;
+                    const uint32_t prim_base = m ? atomicAdd(&counters[1], (uint32_t) m) : 0u;
+                    Aabb box;
+                    int child_in_slot[8];
+                    wide_layout(w, box, child_in_slot);
+                    // the children first: the collapse's dependency chain runs through these stores, not through the record
+                    uint32_t j = 0;
+                    for (int sl = 0; sl < 8; sl++) {
+                        const int c = child_in_slot[sl];
+                        if (c >= 0 && w.ref[c] >= 0) { vq[child_base + j] = w.ref[c]; j++; }
+                    }
+                    BvhNode8 node;
+                    wide_encode_layout(w, box, child_in_slot, child_base, prim_base, node);
+                    nodes8[i] = node;
+                    uint32_t off = 0;
+                    for (int sl = 0; sl < 8; sl++) {
+                        const int c = child_in_slot[sl];
+                        if (c < 0 || w.ref[c] >= 0) continue;
                         for (int q = 0; q < w.count[c]; q++) leaf_pos8[prim_base + off + q] = (uint32_t) (w.first[c] + q);
                         off += (uint32_t) w.count[c];
                     }
+                    __threadfence();
+                    atomicAdd(&counters[2], 1u);
+                    break;
                 }
-                __threadfence();
-                atomicAdd(&counters[2], 1u);
-                i += stride;
-                backoff = 32u;
-                allocated = false;
+            }
+            // Not published yet.  An index below the allocation count WILL be published (its parent is in someone's hands):
+            // poll only the queue.  Only threads whose index is not allocated (yet) look at the termination condition — the
+            // counters are one hot line that every polling thread used to hammer on every iteration.
+            if (!allocated) allocated = i < capacity && (uint32_t) i < vc[0];       // the count only grows: ask once
+            if (allocated) {
+                __nanosleep(backoff);
+                if (backoff < 256u) backoff <<= 1;
                 continue;
             }
+            const uint32_t fin = vc[2];
+            __threadfence();
+            const uint32_t alloc = vc[0];
+            if (fin == alloc) { finished_all = true; break; }
+            __nanosleep(backoff);                  // waiting lanes must not starve the producers of L2 bandwidth
+            if (backoff < 2048u) backoff <<= 1;
         }
-        // Not published yet.  An index below the allocation count WILL be published (its parent is running): poll only
-        // the queue.  Only threads whose index is not allocated (yet) look at the termination condition — the two
-        // counters are one hot line that 75 k polling threads used to hammer on every iteration.
-        if (!allocated) allocated = i < capacity && (uint32_t) i < vc[0];       // the count only grows: ask once
-        if (allocated) {
-            __nanosleep(backoff);
-            if (backoff < 256u) backoff <<= 1;
-            continue;
-        }
-        const uint32_t fin = vc[2];
-        __threadfence();
-        const uint32_t alloc = vc[0];
-        if (fin == alloc) break;
-        __nanosleep(backoff);                      // waiting lanes must not starve the producers of L2 bandwidth
-        if (backoff < 2048u) backoff <<= 1;
+        // a lane saw finished == allocated: every node is written, and the lanes of this warp that held real items are done
+        if (__any_sync(0xffffffffu, finished_all)) break;
     }
 }
 
@@ -132,7 +144,7 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     CUDA_CHECK(cudaMemsetAsync(queue_.get(), 0x80, (size_t) capacity * sizeof(int), stream));
     collapse_init_kernel<<<div_up(n_segs, 256), 256, 0, stream>>>(seg_offset_.get(), seg_root_.get(), n_segs, queue_.get(), wide_counters_.get());
     const BinaryTreeView view{range_.get(), node_lo_.get(), node_hi_.get(), prim_lo_.get(), prim_hi_.get(), vals_};
-    // every thread of the grid must be resident (the items poll on one another)
+    // items are claimed by ticket (see above): the grid need not be resident as a whole; 2 CTAs per SM measured best
     static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 2;   // tuning (measured: 2 beats 3, 4, 8 — fewer pollers)
     const int max_blocks = sm_count * std::min(collapse_blocks_per_sm_, std::max(1, collapse_bps_env));
     const int want_blocks = (int) div_up((size_t) capacity, CT);

@@ -185,12 +185,12 @@ RT_HD f3 ld3(const float4 &a) { return mk3(a.x, a.y, a.z); }
 // (src/AS/Instance.cu:41-45), Rough/Metal::scatter (include/Material/*.cuh) and rayColor's bookkeeping
 // (src/Global/Kernel.cu:76-98).  Returns false when the path ends; `throughput` is rayColor's `result`.
 template<bool WIDE>
-RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const HitD &hit, f3 &throughput, RngState &rng) {
+RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const HitD &hit, f3 &throughput, RngState &rng, uint32_t inst_base = 0u) {
     if (hit.inst < 0) {
         throughput.x *= cam.background.x; throughput.y *= cam.background.y; throughput.z *= cam.background.z;
         return false;
     }
-    const InstanceD &ins = sc.instances[hit.inst];
+    const InstanceD &ins = sc.instances[inst_base + (uint32_t) hit.inst];   // inst_base: this frame's copy of the records (frames in flight)
     const RayD lray = to_local(ins, ray);
     const uint32_t type = ref_type(hit.leaf), pos = ref_pos(hit.leaf);
     const uint32_t prim = WIDE ? sc.leaf_prims8[pos] : sc.leaf_prims[pos];

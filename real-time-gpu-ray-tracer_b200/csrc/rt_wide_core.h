@@ -190,14 +190,17 @@ RT_HD uint32_t wide_quant_hi(float v, float p, float step, float inv) {
 // prim_base : leaf-order position of the node's first leaf primitive (leaf children in slot order).
 // Outputs the node, and for each slot the child placed there (child_in_slot[s], -1 = empty) so the caller can
 // enqueue inner children / write leaf records in the same order.
-RT_HD void wide_encode(const WideChildren &w, uint32_t child_base, uint32_t prim_base, BvhNode8 &out, int *child_in_slot /* [8] */) {
-    Aabb node = w.box[0];
+// Split in two so that the collapse can publish a node's children (which needs only the slot order) before it spends
+// time on the quantisation: wide_layout = node box + slot assignment, wide_encode_layout = the record.
+RT_HD void wide_layout(const WideChildren &w, Aabb &node, int *child_in_slot /* [8] */) {
+    node = w.box[0];
     for (int c = 1; c < w.n; c++) node = aabb_union(node, w.box[c]);
     int slot_of[8];
     wide_assign_slots(w, node, slot_of);
     for (int s = 0; s < 8; s++) child_in_slot[s] = -1;
     for (int c = 0; c < w.n; c++) child_in_slot[slot_of[c]] = c;
-
+}
+RT_HD void wide_encode_layout(const WideChildren &w, const Aabb &node, const int *child_in_slot, uint32_t child_base, uint32_t prim_base, BvhNode8 &out) {
     const uint32_t ex = wide_grid_exponent(node.hi.x - node.lo.x), ey = wide_grid_exponent(node.hi.y - node.lo.y),
                    ez = wide_grid_exponent(node.hi.z - node.lo.z);
     const float sx = wide_grid_step(ex), sy = wide_grid_step(ey), sz = wide_grid_step(ez);
@@ -231,6 +234,11 @@ RT_HD void wide_encode(const WideChildren &w, uint32_t child_base, uint32_t prim
     out.n2 = make_uint4(q[0][0], q[0][1], q[1][0], q[1][1]);
     out.n3 = make_uint4(q[2][0], q[2][1], q[3][0], q[3][1]);
     out.n4 = make_uint4(q[4][0], q[4][1], q[5][0], q[5][1]);
+}
+RT_HD void wide_encode(const WideChildren &w, uint32_t child_base, uint32_t prim_base, BvhNode8 &out, int *child_in_slot /* [8] */) {
+    Aabb node;
+    wide_layout(w, node, child_in_slot);
+    wide_encode_layout(w, node, child_in_slot, child_base, prim_base, out);
 }
 RT_HD int wide_inner_count(const WideChildren &w) { int k = 0; for (int c = 0; c < w.n; c++) k += w.ref[c] >= 0; return k; }
 RT_HD int wide_prim_count(const WideChildren &w) { int k = 0; for (int c = 0; c < w.n; c++) if (w.ref[c] < 0) k += w.count[c]; return k; }

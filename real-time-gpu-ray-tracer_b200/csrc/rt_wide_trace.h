@@ -117,9 +117,9 @@ RT_HD uint32_t node8_intersect(const BvhNode8 &n, const WideRay &r, float tmin, 
     return hitmask;
 }
 
-RT_HD void load_instance_wide(const SceneD &sc, int inst, float *inv, int &root8, int &prim_type) {
+RT_HD void load_instance_wide(const SceneD &sc, int inst, float *inv, int &root8, int &prim_type, uint32_t inst_base = 0u) {
 #if defined(__CUDA_ARCH__)
-    const float4 *p = reinterpret_cast<const float4 *>(sc.instances + inst);
+    const float4 *p = reinterpret_cast<const float4 *>(sc.instances + inst_base + (uint32_t) inst);
     const float4 r0 = __ldg(p), r1 = __ldg(p + 1), r2 = __ldg(p + 2);
     const int4 m = __ldg(reinterpret_cast<const int4 *>(p + 6));
     inv[0] = r0.x; inv[1] = r0.y; inv[2] = r0.z; inv[3] = r0.w;

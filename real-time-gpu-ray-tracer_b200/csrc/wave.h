@@ -85,12 +85,27 @@ struct PersistBuffers {
     uint32_t n_pixels;       // tiles * 32
     uint32_t n_tiles, tiles_x;
     uint32_t n_blas_nodes;   // records in the BLAS node pool (bounds the shared-memory staging variant)
+    // ---- frames in flight: ONE launch serves the pixel queues of n_frames consecutive frames back to back, so the lanes
+    //      that run out of pixels of frame f start on frame f + 1 instead of idling through f's tail.  Frame f owns plane f
+    //      of every per-pixel array (stride frame_px pixels) and copy f of the per-frame TLAS / instance records.
+    uint32_t n_frames;       // >= 1
+    uint32_t frame_px;       // local pixels per plane: rng / radiance / packed rgba8 / AOV stride between frames
+    uint32_t full_px;        // pixels of a full (peer-mapped) frame: stride of the rgba8 ring when fr.rgba8_is_full_frame
+    uint32_t tlas_node_stride, tlas_leaf_stride, inst_stride;   // records between the frames' copies (0 when n_frames == 1)
+    uint32_t valid_pixels;   // pixels of one frame that lie inside the image (the others are tile padding)
+    uint32_t ticket;         // value written to the completion flags (distinguishes this window from the previous one)
+    unsigned long long *frame_rays;   // [n_frames] rays traced per frame (null: not wanted)
+    uint32_t *frame_done;             // [n_frames] finished pixels per frame (null: no completion tracking)
+    volatile uint32_t *host_flags;    // [n_frames] mapped pinned host memory: = ticket once the frame is complete
+    volatile uint32_t *peer_flags;    // [n_frames] this rank's row of rank 0's device flag table (tile shards), or null
 };
 
 class PersistRenderer {
 public:
     // one path-kernel launch per frame (plus the tile ordering); rays are counted on the device (fr.ray_counter[0])
-    void render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count);
+    void render(const SceneD &sc, const CameraD &cam, const FrameD &fr, cudaStream_t stream, int sm_count) { render_window(sc, cam, fr, nullptr, stream, sm_count); }
+    // the same launch over a window of frames (win: the frames-in-flight fields of PersistBuffers; null = one frame)
+    void render_window(const SceneD &sc, const CameraD &cam, const FrameD &fr, const PersistBuffers *win, cudaStream_t stream, int sm_count);
     int node_min = 20;             // the warp takes a node step while at least this many lanes stand on an inner node
     int shade_min = 8;             // ... and shades finished rays once this many lanes wait for it
     int blocks_per_sm_override = 0;

@@ -402,3 +402,55 @@ def test_sah_refinement(pkg, port, idx):
         assert not np.array_equal(plain["left"], g["lbvh"]["left"]), "no rotation was applied"
     assert sorted(g["wide"][1].tolist()) == sorted(e.wide(0)[1].tolist())
     check_against_oracle(g, port.scene(sc, 5), sc)
+
+
+def test_rebuilds_under_sm_pressure(pkg, tmp_path):
+    """The wide-BVH collapse claims its work items by ticket, so it needs no part of its grid to be resident at any given
+    time (VERDICT r1 weak #11 / ADVICE: it used to spin on co-resident CTAs).  Eight lanes rebuild and render concurrently
+    while a second, independent context keeps every SM busy with a heavy frame loop from another host thread; every
+    delivered frame must still be the single-context frame, and nothing may hang (pytest-timeout guards the test)."""
+    import os
+    import threading
+    S = pkg.scenes
+    fixture = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "particle_frame0.vtk")
+    counts = [25, 40, 31, 64, 28, 50, 33, 26, 45, 30, 38, 27, 60, 29, 35, 41]
+    F = len(counts)
+    series = S.synth_vtk_series(fixture, str(tmp_path), counts, frame_ids=list(range(F)))
+    base = S.c1a(frame=0, width=160, height=90, spp=2, depth=10)
+    want = []
+    r = pkg.Renderer(device=0)
+    try:
+        r.commitScene(base)
+        assert r.configureVTKFiles(series) == F
+        for f in range(F):
+            r.setVTKFrame(f)
+            r.renderFrame(f, SEED)
+            want.append(r.readFramebuffer(pkg.abi.BUF_RGBA8).reshape(90, 160, 4).copy())
+        stop = threading.Event()
+        hog_frames = [0]
+
+        def hog():
+            h = pkg.Renderer(device=0)
+            try:
+                h.commitScene(S.c2(width=1920, height=1080, spp=4, depth=10, nx=300, nz=150))
+                while not stop.is_set():
+                    h.renderFrame(hog_frames[0], SEED)
+                    hog_frames[0] += 1
+            finally:
+                h.cleanup()
+
+        t = threading.Thread(target=hog)
+        t.start()
+        try:
+            for rounds in range(3):
+                got = {}
+                r.runVTKAnimation(0, 1, 0, SEED, 8, lambda frame, img, out: got.__setitem__(frame, img.copy()) or 0)
+                assert sorted(got) == list(range(F))
+                for f in range(F):
+                    assert np.array_equal(got[f], want[f]), f"frame {f} differs under SM pressure"
+        finally:
+            stop.set()
+            t.join()
+        assert hog_frames[0] > 0
+    finally:
+        r.cleanup()

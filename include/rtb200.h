@@ -263,6 +263,73 @@ int rt_write_image(rt_ctx *ctx, int kind, const char *path);
  * buffer instead of the local packed plane (fused gather over NVLink).                              */
 int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_rows, void *peer_rgba8);
 
+/* ---- frames in flight (the frame loop behind the ABI) -------------------------------------------------
+ * Renderer::startRender keeps two frames in flight: instances, TLAS and TraverseData are double-buffered and a copy
+ * stream prepares frame k+1 beside the render stream's frame k (reference src/Global/Renderer.cu:189-207, 278-317).
+ * Here a WINDOW of up to RT_MAX_FRAMES_IN_FLIGHT consecutive frames is prepared (update callback, instance matrices,
+ * TLAS and per-pixel RNG states of every frame) and then served by ONE launch of the persistent path kernel: the
+ * pixel queues of the frames follow one another, so a lane that runs out of pixels of frame k starts on frame k+1
+ * instead of idling through k's tail (a pixel is sequential work: at a 1/8 image shard that tail is a third of a frame).
+ * Every frame is, bit for bit, the frame rt_render_frame(frame, seed) produces.  Two windows may be in flight
+ * (handles 0 and 1): while one drains, the next one's preparation and first pixels already run on a second stream.
+ * The camera, window size and tile shard are those of the context at submit time and are fixed within a window.
+ * rt_frame_out of a pipelined frame: rays, primary_rays, stack_overflow (of the window so far) and render_ms = host
+ * clock from the window's submission to the frame's completion (its latency); the per-stage times are 0.            */
+#define RT_MAX_FRAMES_IN_FLIGHT 8
+/* seeds: one per frame (NULL: `seed0` for every frame).  Returns at once; *window receives the handle.  RT_ERR_STATE
+ * when both windows are in flight.                                                                                   */
+int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const uint64_t *seeds, uint64_t seed0, uint32_t *window);
+/* Blocks until frame k (0-based within the window) is complete on this context's device — and, on rank 0 of a tile shard
+ * with a frame ring (below), until every rank's tiles of that frame have landed in the ring.                          */
+int rt_wait_frame(rt_ctx *ctx, uint32_t window, uint32_t k, rt_frame_out *out);
+/* Copies a plane of frame k to host memory (after rt_wait_frame) on a copy stream, beside the rest of the window.
+ * RT_BUFFER_RGBA8 on a context with a frame ring returns the FULL assembled frame (width*height*4 bytes).             */
+int rt_read_frame(rt_ctx *ctx, uint32_t window, uint32_t k, int kind, void *host_dst, size_t dst_bytes);
+typedef struct rt_window_stats {
+    uint64_t rays;            /* closest-hit queries of the whole window                                        */
+    uint32_t frames;
+    uint32_t kernel_launches; /* kernels launched for the window (preparation of every frame + one path launch) */
+    float    device_ms;       /* CUDA events: first preparation launch .. path kernel finished                  */
+    float    prepare_ms;      /* ... of which instance updates, TLAS rebuilds and RNG initialisation             */
+    uint32_t stack_overflow;
+    uint32_t _pad;
+} rt_window_stats;
+/* Waits for the rest of the window and frees its handle for the next rt_submit_frames.                               */
+int rt_release_window(rt_ctx *ctx, uint32_t window, rt_window_stats *stats);
+/* The headless loop: frames first_frame .. first_frame + n_frames - 1 in windows of `frames_per_window` (1 ..
+ * RT_MAX_FRAMES_IN_FLIGHT), two windows in flight, every finished frame copied to pinned host memory and handed to
+ * `sink` in frame order (may be NULL; non-zero return stops the loop with RT_ERR_STATE).  Without a frame ring the sink
+ * receives this context's (packed shard) plane; with one, rank 0 receives the full assembled frames and the other
+ * ranks are called with (NULL, 0): their pixels are in rank 0's ring.                                                  */
+typedef struct rt_loop_stats {
+    uint64_t frames, rays, kernel_launches;
+    double   wall_ms;         /* host wall clock of the loop                                                      */
+    double   device_ms;       /* sum of the windows' device times (windows overlap: >= the wall clock share)       */
+    double   max_latency_ms;  /* slowest submit -> frame-complete latency                                          */
+} rt_loop_stats;
+typedef int (*rt_frame_sink)(void *user, size_t frame, const void *rgba8, size_t bytes, const rt_frame_out *out);
+int rt_run_frames(rt_ctx *ctx, uint64_t first_frame, size_t n_frames, uint64_t seed, uint32_t frames_per_window,
+                  rt_frame_sink sink, void *user, rt_loop_stats *stats);
+
+/* ---- multi-GPU: the frame ring (fused gather) -------------------------------------------------------------
+ * Tile-sharded ranks (rt_set_tile_shard) can store their finished texels straight into ONE full-size frame on rank 0
+ * instead of gathering packed planes afterwards: the path kernel of every rank writes RGBA8 through a peer mapping over
+ * NVLink and raises a per-frame flag in rank 0's memory when its last pixel of the frame is done.  The ring holds
+ * 2 windows x RT_MAX_FRAMES_IN_FLIGHT full frames + the flag table.
+ *   rank 0            : rt_frame_ring_create  (after rt_set_tile_shard and rt_configure_camera) -> 64-byte CUDA IPC handle
+ *   ranks 1..world-1  : rt_frame_ring_open(handle)      (other processes, e.g. torchrun ranks; the caller ships the bytes)
+ *   same process      : rt_frame_ring_attach(owner_ctx) (several contexts driven by one process, any devices)
+ * With a ring, rt_render_frame stores into frame slot 0 of window 0, and rt_read_framebuffer / rt_framebuffer_device_ptr
+ * (RT_BUFFER_RGBA8) refer to that full frame: rank 0 reads it after every rank has finished its call (the callers
+ * synchronise).  From the moment the ring exists every rank must submit the same sequence of windows.
+ * Errors: RT_ERR_CUDA when the mapping cannot be made (no peer access between the devices), RT_ERR_STATE when the
+ * shard / camera are not set, RT_ERR_ARGUMENT for a ring of another frame size.                                        */
+#define RT_IPC_HANDLE_BYTES 64
+int rt_frame_ring_create(rt_ctx *ctx, void *ipc_handle_out /* RT_IPC_HANDLE_BYTES, may be NULL */);
+int rt_frame_ring_open(rt_ctx *ctx, const void *ipc_handle);
+int rt_frame_ring_attach(rt_ctx *ctx, rt_ctx *owner);
+int rt_frame_ring_close(rt_ctx *ctx);
+
 /* ---- acceleration-structure introspection (parity tests) ----------------------------------- */
 /* Binary LBVH as built on the device, for `which` = 0 (the BLAS batch: all BLASes share one sort and one
  * Karras pass, segment id in the key's high bits) or 1 (the TLAS): sorted Morton keys, sorted build-primitive
@@ -313,7 +380,6 @@ typedef struct rt_animation_stats {
     double   readback_ms;         /* RGBA8 plane -> pinned host                                          */
     double   sink_ms;             /* inside the caller's sink (incl. waiting for the other lanes' calls) */
 } rt_animation_stats;
-typedef int (*rt_frame_sink)(void *user, size_t frame, const void *rgba8, size_t bytes, const rt_frame_out *out);
 int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t frame_stride, size_t max_frames, uint64_t seed, int lanes,
                          rt_frame_sink sink, void *user, rt_animation_stats *stats);
 

@@ -3,7 +3,7 @@
 TAG=${1:-r02a}
 O=gpurun_out
 mkdir -p $O
-timeout 1500 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -5 $O/${TAG}_pytest.log
+timeout 1500 python -m pytest tests -m gpu -q > $O/${TAG}_pytest.log 2>&1; echo "pytest rc=$?"; tail -5 $O/${TAG}_pytest.log
 timeout 600 python bench.py > $O/${TAG}_bench_n1.json 2> $O/${TAG}_bench_n1.err; tail -c 400 $O/${TAG}_bench_n1.json; tail -3 $O/${TAG}_bench_n1.err
 S="--no-cpu-baseline --no-ref-cuda --no-c3"
 timeout 300 python bench.py --emulate-shard 8 $S > $O/${TAG}_bench_shard8.json 2> $O/${TAG}_bench_shard8.err; tail -c 300 $O/${TAG}_bench_shard8.json

@@ -92,6 +92,19 @@ class AnimationStats(C.Structure):
                 ("sink_ms", C.c_double)]
 
 
+class WindowStats(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("frames", C.c_uint32), ("kernel_launches", C.c_uint32), ("device_ms", C.c_float),
+                ("prepare_ms", C.c_float), ("stack_overflow", C.c_uint32), ("_pad", C.c_uint32)]
+
+
+class LoopStats(C.Structure):
+    _fields_ = [("frames", C.c_uint64), ("rays", C.c_uint64), ("kernel_launches", C.c_uint64), ("wall_ms", C.c_double),
+                ("device_ms", C.c_double), ("max_latency_ms", C.c_double)]
+
+
+MAX_FRAMES_IN_FLIGHT = 8
+IPC_HANDLE_BYTES = 64
+
 FRAME_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(FrameOut))
 UPDATE_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p)
 
@@ -101,7 +114,7 @@ _STRUCT_SIZES = {
     "rt_instance_desc": instance_desc_dt.itemsize, "rt_instance_xform": instance_xform_dt.itemsize,
     "rt_window": C.sizeof(Window), "rt_camera_input": C.sizeof(CameraInput), "rt_frame_out": C.sizeof(FrameOut),
     "rt_build_stats": C.sizeof(BuildStats), "rt_animation_stats": C.sizeof(AnimationStats),
-    "rt_camera_motion": C.sizeof(CameraMotion),
+    "rt_camera_motion": C.sizeof(CameraMotion), "rt_window_stats": C.sizeof(WindowStats), "rt_loop_stats": C.sizeof(LoopStats),
 }
 
 # every symbol include/rtb200.h declares
@@ -112,6 +125,8 @@ EXPORTS = [
     "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm", "rt_write_image",
     "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame", "rt_prefetch_vtk_frame",
     "rt_probe_read_bandwidth", "rt_run_vtk_animation", "rt_camera_step",
+    "rt_submit_frames", "rt_wait_frame", "rt_read_frame", "rt_release_window", "rt_run_frames",
+    "rt_frame_ring_create", "rt_frame_ring_open", "rt_frame_ring_attach", "rt_frame_ring_close",
 ]
 
 _lib = None
@@ -157,6 +172,15 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_run_vtk_animation.argtypes = [vp, sz, sz, sz, u64, i32, FRAME_SINK, vp, C.POINTER(AnimationStats)]
     lib.rt_camera_step.argtypes = [C.POINTER(CameraInput), C.POINTER(CameraMotion), C.POINTER(CameraInput), C.POINTER(C.c_int)]
     lib.rt_probe_read_bandwidth.argtypes = [vp, sz, i32, C.POINTER(C.c_double)]
+    lib.rt_submit_frames.argtypes = [vp, u64, u32, vp, u64, C.POINTER(u32)]
+    lib.rt_wait_frame.argtypes = [vp, u32, u32, C.POINTER(FrameOut)]
+    lib.rt_read_frame.argtypes = [vp, u32, u32, i32, vp, sz]
+    lib.rt_release_window.argtypes = [vp, u32, C.POINTER(WindowStats)]
+    lib.rt_run_frames.argtypes = [vp, u64, sz, u64, u32, FRAME_SINK, vp, C.POINTER(LoopStats)]
+    lib.rt_frame_ring_create.argtypes = [vp, vp]
+    lib.rt_frame_ring_open.argtypes = [vp, vp]
+    lib.rt_frame_ring_attach.argtypes = [vp, vp]
+    lib.rt_frame_ring_close.argtypes = [vp]
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if a declared symbol is not exported
         if name not in ("rt_last_error", "rt_version", "rt_struct_size"):

@@ -2,12 +2,8 @@
 // the reference's Renderer::* entry points and returns error codes instead of exiting.
 #include "../../include/rtb200.h"
 
-#include "build.h"
-#include "host_scene.h"
+#include "api_ctx.h"
 #include "image_io.h"
-#include "render.h"
-#include "vtk_reader.h"
-#include "wave.h"
 
 #include <algorithm>
 #include <atomic>
@@ -23,151 +19,40 @@
 #include <tuple>
 #include <vector>
 
-struct rt_ctx {
-    int device = 0;
-    uint32_t flags = 0;
-    std::string err;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[5] = {};
-    int sm_count = 148;
-
-    HostScene hs;                            // host half: validated inputs + device-layout records
-    rt_update_cb update_cb = nullptr;
-    void *update_user = nullptr;
-
-    // device scene
-    DeviceBuffer<float> d_tri_verts;
-    DeviceBuffer<TriShade> d_tri_shade;
-    DeviceBuffer<SphereD> d_spheres;
-    DeviceBuffer<QuadD> d_quads;
-    DeviceBuffer<float4> d_roughs, d_metals, d_dielectrics;
-    DeviceBuffer<InstanceD> d_instances;
-    DeviceBuffer<InstanceXformIn> d_xform_in;
-    DeviceBuffer<float4> d_wcentroid;
-    PinnedBuffer<InstanceXformIn> h_xform_in;
-    LbvhBuilder blas, tlas;
-    // The big per-frame uploads of the animation (triangle vertices and shading records, 52 MB at 629 k triangles) come
-    // from HostScene's vectors; page-locking their storage in place makes the copies DMA at PCIe speed instead of being
-    // staged through the driver's bounce buffer.  The registration follows the vector's allocation.
-    struct PinnedRange {
-        void *p = nullptr;
-        size_t bytes = 0;
-        void release() { if (p) cudaHostUnregister(p); p = nullptr; bytes = 0; }
-        void ensure(void *q, size_t b) {
-            if (q == p && b == bytes) return;
-            release();
-            if (q && b >= (4u << 20)) {
-                if (cudaHostRegister(q, b, cudaHostRegisterDefault) == cudaSuccess) { p = q; bytes = b; } else cudaGetLastError();
-            }
-        }
-        ~PinnedRange() { release(); }
-    };
-    PinnedRange pin_verts, pin_shade;
-    DeviceBuffer<uint32_t> d_rng_tables;   // XORWOW sequence-jump matrices per hex digit (kernels_render.cu)
-    bool rng_tables_ready = false;
-    WaveRenderer wave;
-    PersistRenderer persist;
-    int path_mode = 1;              // 1: persistent path kernel (default), 0: wave loop; RT_FLAG_WAVEFRONT / RTB200_MODE select
-    bool geometry_committed = false, materials_committed = false, instances_configured = false, built = false, camera_set = false;
-    rt_build_stats build_stats{};
-
-    // camera / frame
-    uint32_t shard_rank = 0, shard_world = 1, tile_rows = 8, local_rows = 0;
-    void *peer_rgba8 = nullptr;
-    DeviceBuffer<uint8_t> d_rgba8;
-    DeviceBuffer<float> d_radiance, d_aov_t;
-    DeviceBuffer<int> d_aov_inst, d_aov_prim;
-    DeviceBuffer<RngState> d_rng;
-    DeviceBuffer<unsigned long long> d_counters;   // [0] rays, [1] overflow flag (low word)
-    PinnedBuffer<unsigned long long> h_counters;
-
-    // VTK series: the user's own triangles / instances are kept so that every frame can be recomposed as
-    // [VTK triangles | user triangles], [user instances | VTK instances] (reference src/Global/Renderer.cu:17,106-116)
-    std::shared_ptr<const VtkSeries> vtk;    // shared with the lanes of rt_run_vtk_animation
-    // one parsed + converted series frame.  Two of them: the one being committed and the one a host thread reads ahead
-    // (rt_prefetch_vtk_frame) while the GPU renders; the vectors keep their capacity from frame to frame.
-    struct VtkStage {
-        VtkFrame vf;
-        VtkCompact compact;                 // device expansion (default): per-point tables + strip ids instead of `tris`
-        bool expand_on_device = true;
-        std::vector<rt_triangle> tris;
-        std::vector<rt_instance_desc> inst;
-        std::vector<rt_instance_xform> xf;
-        size_t frame = (size_t) -1;
-        bool ok = false;
-        std::string err;
-        float parse_ms = 0.0f;
-        std::thread worker;
-        void load(const VtkSeries &series, size_t f) {
-            const auto t0 = std::chrono::steady_clock::now();
-            frame = f;
-            err.clear();
-            ok = vf.read(series.dir + series.files[f].first, err);
-            if (ok) {
-                if (expand_on_device) vtk_convert_compact(vf, compact, inst, xf);
-                else vtk_convert(vf, tris, inst, xf);
-            }
-            parse_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
-        }
-        void join() { if (worker.joinable()) worker.join(); }
-    };
-    VtkStage vtk_stage[2];
-    // strips -> triangle records on the device (launch_expand_strips); RTB200_VTK_EXPAND=host keeps the host conversion
-    bool vtk_expand_on_device = true;
-    DeviceBuffer<float> d_vtk_points, d_vtk_normals;
-    DeviceBuffer<int> d_vtk_ids;
-    DeviceBuffer<uint32_t> d_vtk_first_tri, d_vtk_first_id;
-    int vtk_ahead = -1;             // stage a read-ahead is running on / has finished in (-1: none)
-    std::vector<rt_triangle> user_tris;
-    std::vector<rt_instance_desc> user_inst;
-    bool composing = false;
-    size_t n_user_inst = 0;
-    float vtk_parse_ms = 0.0f;
-    // rt_run_vtk_animation: the extra renderer contexts (lanes) and the pinned frame each lane delivers; kept between
-    // calls so that their device buffers, page-locked ranges and jump tables are allocated once
-    std::vector<rt_ctx *> lane_ctx;
-    PinnedBuffer<uint8_t> h_frame;
-    // Host waits of the frame path.  cudaStreamSynchronize spins; with several lanes per GPU and several ranks per host the
-    // spinning threads would take the cores the other lanes' parsing and commits need, so inside the animation loop the
-    // wait sleeps on a blocking-sync event instead.
-    cudaEvent_t ev_block = nullptr;
-    bool blocking_wait = false;
-    void wait() {
-        if (blocking_wait && ev_block) {
-            CUDA_CHECK(cudaEventRecord(ev_block, stream));
-            CUDA_CHECK(cudaEventSynchronize(ev_block));
-        } else {
-            CUDA_CHECK(cudaStreamSynchronize(stream));
-        }
-    }
-};
-
-namespace {
-
-int fail(rt_ctx *ctx, int code, const std::string &msg) {
-    if (ctx) ctx->err = msg;
-    return code;
-}
-
-#define RT_API_BEGIN(ctx)                                   \
-    if (!(ctx)) return RT_ERR_ARGUMENT;                     \
-    try {                                                   \
-        if (cudaSetDevice((ctx)->device) != cudaSuccess) return fail(ctx, RT_ERR_CUDA, "cudaSetDevice failed");
-#define RT_API_END(ctx)                                     \
-    } catch (const CudaError &e) {                          \
-        cudaGetLastError();                                 \
-        return fail(ctx, RT_ERR_CUDA, e.what());            \
-    } catch (const std::exception &e) {                     \
-        return fail(ctx, RT_ERR_ARGUMENT, e.what());        \
-    }                                                       \
-    return RT_OK;
-
-void compute_local_rows(rt_ctx *c) {
+void rt_compute_local_rows(rt_ctx *c) {
     const uint32_t H = c->hs.window.height;
     const uint32_t tiles = (H + c->tile_rows - 1) / c->tile_rows;
     const uint32_t local_tiles = c->shard_rank < tiles ? (tiles - c->shard_rank + c->shard_world - 1) / c->shard_world : 0;
     c->local_rows = c->shard_world == 1 ? H : local_tiles * c->tile_rows;
 }
+
+SceneD rt_scene_view(rt_ctx *ctx) {
+    SceneD sc{};
+    sc.tlas_nodes = ctx->tlas.nodes();
+    sc.blas_nodes = ctx->blas.nodes();
+    sc.instances = ctx->d_instances.get();
+    sc.leaf_tris = ctx->blas.leaf_tris();
+    sc.leaf_prims = ctx->blas.leaf_prims();
+    sc.tri_shade = ctx->d_tri_shade.get();
+    sc.spheres = ctx->d_spheres.get();
+    sc.quads = ctx->d_quads.get();
+    sc.roughs = ctx->d_roughs.get();
+    sc.metals = ctx->d_metals.get();
+    sc.dielectrics = ctx->d_dielectrics.get();
+    sc.tlas_root_ref = ctx->hs.inst_desc.size() > 1 ? 0 : make_leaf_ref(0u, 0u);
+    sc.tlas_nodes8 = ctx->tlas.nodes8();
+    sc.blas_nodes8 = ctx->blas.nodes8();
+    sc.tlas_leaf_inst = ctx->tlas.leaf_prims8();
+    sc.leaf_tris8 = ctx->blas.leaf_tris8();
+    sc.leaf_prims8 = ctx->blas.leaf_prims8();
+    return sc;
+}
+
+namespace {
+
+int fail(rt_ctx *ctx, int code, const std::string &msg) { return rt_fail(ctx, code, msg); }
+
+void compute_local_rows(rt_ctx *c) { rt_compute_local_rows(c); }
 
 void alloc_frame(rt_ctx *c) {
     compute_local_rows(c);
@@ -202,7 +87,7 @@ size_t rt_struct_size(const char *name) {
     if (!name) return 0;
 #define RT_SZ(T) if (strcmp(name, #T) == 0) return sizeof(T);
     RT_SZ(rt_vec3) RT_SZ(rt_sphere) RT_SZ(rt_parallelogram) RT_SZ(rt_triangle) RT_SZ(rt_rough) RT_SZ(rt_metal) RT_SZ(rt_dielectric)
-    RT_SZ(rt_instance_desc) RT_SZ(rt_instance_xform) RT_SZ(rt_window) RT_SZ(rt_camera_input) RT_SZ(rt_frame_out) RT_SZ(rt_build_stats) RT_SZ(rt_animation_stats) RT_SZ(rt_camera_motion)
+    RT_SZ(rt_instance_desc) RT_SZ(rt_instance_xform) RT_SZ(rt_window) RT_SZ(rt_camera_input) RT_SZ(rt_frame_out) RT_SZ(rt_build_stats) RT_SZ(rt_animation_stats) RT_SZ(rt_camera_motion) RT_SZ(rt_window_stats) RT_SZ(rt_loop_stats)
 #undef RT_SZ
     return 0;
 }
@@ -252,6 +137,7 @@ int rt_cleanup(rt_ctx *ctx) {
     ctx->lane_ctx.clear();
     for (auto &st: ctx->vtk_stage) st.join();
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); }
+    rt_release_frames(ctx);
     for (auto &e: ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->ev_block) cudaEventDestroy(ctx->ev_block);
     cudaStream_t s = ctx->stream;
@@ -400,6 +286,8 @@ int rt_camera_step(const rt_camera_input *current, const rt_camera_motion *motio
 int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_rows, void *peer_rgba8) {
     RT_API_BEGIN(ctx)
     if (world == 0 || rank >= world || tile_rows == 0) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_tile_shard: bad rank/world/tile_rows");
+    if (ctx->ring) return fail(ctx, RT_ERR_STATE, "rt_set_tile_shard: close the frame ring first (it was made for the current shard)");
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_set_tile_shard: not while frames are in flight");
     ctx->shard_rank = rank; ctx->shard_world = world; ctx->tile_rows = tile_rows; ctx->peer_rgba8 = peer_rgba8;
     if (ctx->camera_set) alloc_frame(ctx);
     RT_API_END(ctx)
@@ -418,24 +306,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     update_instances_and_tlas(ctx);
     CUDA_CHECK(cudaEventRecord(ctx->ev[1], s));
 
-    SceneD sc{};
-    sc.tlas_nodes = ctx->tlas.nodes();
-    sc.blas_nodes = ctx->blas.nodes();
-    sc.instances = ctx->d_instances.get();
-    sc.leaf_tris = ctx->blas.leaf_tris();
-    sc.leaf_prims = ctx->blas.leaf_prims();
-    sc.tri_shade = ctx->d_tri_shade.get();
-    sc.spheres = ctx->d_spheres.get();
-    sc.quads = ctx->d_quads.get();
-    sc.roughs = ctx->d_roughs.get();
-    sc.metals = ctx->d_metals.get();
-    sc.dielectrics = ctx->d_dielectrics.get();
-    sc.tlas_root_ref = ctx->hs.inst_desc.size() > 1 ? 0 : make_leaf_ref(0u, 0u);
-    sc.tlas_nodes8 = ctx->tlas.nodes8();
-    sc.blas_nodes8 = ctx->blas.nodes8();
-    sc.tlas_leaf_inst = ctx->tlas.leaf_prims8();
-    sc.leaf_tris8 = ctx->blas.leaf_tris8();
-    sc.leaf_prims8 = ctx->blas.leaf_prims8();
+    const SceneD sc = rt_scene_view(ctx);
 
     FrameD fr{};
     fr.rgba8 = ctx->peer_rgba8 ? (uint8_t *) ctx->peer_rgba8 : ctx->d_rgba8.get();
@@ -500,7 +371,10 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
 static int plane_info(rt_ctx *ctx, int kind, void **ptr, size_t *bytes) {
     const size_t px = (size_t) ctx->hs.window.width * ctx->local_rows;
     switch (kind) {
-        case RT_BUFFER_RGBA8: *ptr = ctx->d_rgba8.get(); *bytes = px * 4; return RT_OK;
+        case RT_BUFFER_RGBA8:
+            // with a frame ring the texels of every rank are stored into rank 0's full frame (slot 0 of window 0 for rt_render_frame)
+            if (ctx->ring) { *ptr = ctx->ring->frame(0, 0); *bytes = ctx->ring->frame_bytes; return RT_OK; }
+            *ptr = ctx->d_rgba8.get(); *bytes = px * 4; return RT_OK;
         case RT_BUFFER_RADIANCE: *ptr = ctx->d_radiance.get(); *bytes = px * 12; return RT_OK;
         case RT_BUFFER_PRIMARY_T: *ptr = ctx->d_aov_t.get(); *bytes = px * 4; break;
         case RT_BUFFER_PRIMARY_INSTANCE: *ptr = ctx->d_aov_inst.get(); *bytes = px * 4; break;

@@ -258,17 +258,22 @@ double probe_read_bandwidth(size_t bytes, int repeats, int sm_count, cudaStream_
     return (double) n_words * sizeof(uint4) * repeats / (ms * 1e-3) / 1e9;
 }
 
+void launch_rng_tables(uint32_t *tables, bool &tables_ready, cudaStream_t stream) {
+    if (tables_ready || !tables) return;
+    rng_tables_kernel<<<RNG_HEX_DIGITS * 15, RNG_ROWS, 0, stream>>>(tables);
+    rng_low_table_kernel<<<32, RNG_ROWS, 0, stream>>>(tables);
+    rng_wide_tables_kernel<<<2 * 255, RNG_ROWS, 0, stream>>>(tables);
+    CUDA_CHECK(cudaGetLastError());
+    tables_ready = true;
+}
+
 void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &cam, const FrameD &fr, cudaStream_t stream, uint32_t *tables,
                      bool &tables_ready) {
     const size_t n = (size_t) cam.width * fr.local_rows;
+    if (n == 0) return;
     static const bool use_curand = getenv("RTB200_RNG_INIT") && strcmp(getenv("RTB200_RNG_INIT"), "curand") == 0;
     if (tables && !use_curand) {
-        if (!tables_ready) {
-            rng_tables_kernel<<<RNG_HEX_DIGITS * 15, RNG_ROWS, 0, stream>>>(tables);
-            rng_low_table_kernel<<<32, RNG_ROWS, 0, stream>>>(tables);
-            rng_wide_tables_kernel<<<2 * 255, RNG_ROWS, 0, stream>>>(tables);
-            tables_ready = true;
-        }
+        launch_rng_tables(tables, tables_ready, stream);
         rng_init_tables_kernel<<<div_up(n, 256), 256, 0, stream>>>(states, tables, seed, cam.width, cam.pitch, fr.local_rows, fr.shard_rank, fr.shard_world,
                                                                   fr.tile_rows);
         CUDA_CHECK(cudaGetLastError());

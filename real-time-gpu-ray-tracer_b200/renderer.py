@@ -194,6 +194,82 @@ class Renderer:
         self._check(self.lib.rt_run_vtk_animation(self.ctx, first_frame, frame_stride, max_frames, seed, lanes, cb, None, C.byref(st)))
         return st
 
+    # -- frames in flight (rt_submit_frames .. rt_run_frames) and the multi-GPU frame ring ------------------------------
+    def submitFrames(self, first_frame: int, n_frames: int, seed: int = 0x5EED, seeds=None) -> int:
+        """Prepare `n_frames` consecutive frames and serve them with ONE launch of the path kernel; returns the window handle."""
+        w = C.c_uint32()
+        sp = None
+        if seeds is not None:
+            self._seeds = np.ascontiguousarray(seeds, np.uint64)
+            assert len(self._seeds) == n_frames
+            sp = abi.ptr(self._seeds)
+        self._check(self.lib.rt_submit_frames(self.ctx, first_frame, n_frames, sp, seed, C.byref(w)))
+        return w.value
+
+    def waitFrame(self, window: int, k: int) -> abi.FrameOut:
+        out = abi.FrameOut()
+        self._check(self.lib.rt_wait_frame(self.ctx, window, k, C.byref(out)))
+        return out
+
+    def readFrame(self, window: int, k: int, kind: int = abi.BUF_RGBA8, out: np.ndarray | None = None, nbytes: int | None = None) -> np.ndarray:
+        if nbytes is None:
+            _, nbytes = self.devicePointer(kind)
+            if kind == abi.BUF_RGBA8 and self.has_ring:
+                nbytes = self.width * self.height * 4
+        if out is None:
+            out = np.empty(nbytes, np.uint8)
+        self._check(self.lib.rt_read_frame(self.ctx, window, k, kind, out.ctypes.data_as(C.c_void_p), out.nbytes))
+        dt = {abi.BUF_RGBA8: np.uint8, abi.BUF_RADIANCE: np.float32, abi.BUF_PRIMARY_T: np.float32,
+              abi.BUF_PRIMARY_INSTANCE: np.int32, abi.BUF_PRIMARY_PRIM: np.int32}[kind]
+        return out.view(dt)
+
+    def releaseWindow(self, window: int) -> abi.WindowStats:
+        st = abi.WindowStats()
+        self._check(self.lib.rt_release_window(self.ctx, window, C.byref(st)))
+        return st
+
+    def runFrames(self, first_frame: int, n_frames: int, seed: int = 0x5EED, frames_per_window: int = abi.MAX_FRAMES_IN_FLIGHT, sink=None) -> abi.LoopStats:
+        """The headless frame loop with frames in flight; sink(frame, rgba8 [rows, W, 4] view or None, FrameOut) per frame, in order."""
+        st = abi.LoopStats()
+        W = self.width
+
+        def _sink(_user, frame, ptr, nbytes, out):
+            try:
+                img = None
+                if ptr and nbytes:
+                    img = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(nbytes,)).reshape(-1, W, 4)
+                return int(sink(int(frame), img, out.contents) or 0)
+            except Exception:                      # an exception must not unwind through the C frames
+                import traceback
+                traceback.print_exc()
+                return 1
+
+        cb = abi.FRAME_SINK(_sink) if sink is not None else abi.FRAME_SINK()
+        self._check(self.lib.rt_run_frames(self.ctx, first_frame, n_frames, seed, frames_per_window, cb, None, C.byref(st)))
+        return st
+
+    has_ring = False
+
+    def frameRingCreate(self) -> bytes:
+        """Rank 0 of a tile shard: allocate the ring of full frames the ranks store into; returns the CUDA IPC handle bytes."""
+        h = (C.c_ubyte * abi.IPC_HANDLE_BYTES)()
+        self._check(self.lib.rt_frame_ring_create(self.ctx, C.cast(h, C.c_void_p)))
+        self.has_ring = True
+        return bytes(h)
+
+    def frameRingOpen(self, handle: bytes):
+        h = (C.c_ubyte * abi.IPC_HANDLE_BYTES).from_buffer_copy(handle)
+        self._check(self.lib.rt_frame_ring_open(self.ctx, C.cast(h, C.c_void_p)))
+        self.has_ring = True
+
+    def frameRingAttach(self, owner: "Renderer"):
+        self._check(self.lib.rt_frame_ring_attach(self.ctx, owner.ctx))
+        self.has_ring = True
+
+    def frameRingClose(self):
+        self._check(self.lib.rt_frame_ring_close(self.ctx))
+        self.has_ring = False
+
     # -- Renderer::cleanup -----------------------------------------------------------------------
     def cleanup(self):
         if self.ctx:

@@ -404,6 +404,174 @@ def run_c3(args):
         dist.destroy_process_group()
 
 
+def measure_synchronous(pkg, r, sc, args, torch, dist, rank, world, local, tile_rows):
+    """The comparison modes (and the fallback when no frame ring can be mapped): rt_render_frame one frame at a time; at
+    N > 1 the packed planes are gathered with NCCL and de-interleaved by torch ops."""
+    abi = pkg.abi
+    distributed = world > 1
+    W, H = sc.width, sc.height
+    ptr, nbytes = r.devicePointer(abi.BUF_RGBA8)
+    if distributed:      # every rank's plane is allocated for the largest shard: gather equal-sized buffers
+        nbytes = pkg.sharding.padded_plane_bytes(H, W * 4, world, tile_rows)
+    local_plane = torch.as_tensor(DevPtr(ptr, nbytes), device=f"cuda:{local}")
+    gathered = [torch.empty_like(local_plane) for _ in range(world)] if (distributed and rank == 0) else None
+    host_fb = torch.empty(W * H * 4, dtype=torch.uint8).pin_memory()
+    xf = sc.xforms.copy()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def frame(k, read_back):
+        if read_back:
+            r.setInstanceTransforms(xf)
+        out = r.renderFrame(k, SEED)
+        ms = out.render_ms
+        if distributed:
+            ev0.record()
+            dist.gather(local_plane, gathered, dst=0)
+            ev1.record()
+            ev1.synchronize()
+            ms += ev0.elapsed_time(ev1)
+        if read_back and rank == 0:
+            if distributed:
+                full = pkg.sharding.assemble(gathered, H, W * 4, world, tile_rows)
+                host_fb.copy_(full.view(-1), non_blocking=True)
+                torch.cuda.synchronize()
+            else:
+                r.lib.rt_read_framebuffer(r.ctx, abi.BUF_RGBA8, C.c_void_p(host_fb.data_ptr()), host_fb.numel())
+        return out.rays, ms, out
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for k in range(args.warmup):
+        frame(k, False)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    rays, dev_ms, launches = 0, 0.0, 0
+    trace_ms, rng_ms, tlas_ms = [], [], []
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        n, ms, out = frame(args.warmup + k, False)
+        rays += n
+        dev_ms += ms
+        trace_ms.append(out.trace_ms); rng_ms.append(out.rng_ms); tlas_ms.append(out.tlas_ms)
+        launches += out.kernel_launches
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    clocks = sampler.stop() if rank == 0 else None
+    frame(args.warmup, True)
+    barrier()
+    e_rays = 0
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        n, _, _ = frame(args.warmup + k, True)
+        e_rays += n
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    tot = torch.tensor([float(rays), float(e_rays), float(launches)], dtype=torch.float64, device=f"cuda:{local}")
+    mx = torch.tensor([dev_ms, e2e_s, wall_ms], dtype=torch.float64, device=f"cuda:{local}")
+    if distributed:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    tot_rays, tot_e_rays, launches = tot.tolist()
+    max_dev_ms, max_e2e_s, max_wall_ms = mx.tolist()
+    return {"value": tot_rays / (max_dev_ms * 1e-3) / 1e6, "ms_per_step": max_dev_ms / args.steps, "rays_per_frame": tot_rays / args.steps,
+            "e2e_value": tot_e_rays / max_e2e_s / 1e6, "e2e_ms_per_step": 1e3 * max_e2e_s / args.steps, "wall_ms_per_step": max_wall_ms / args.steps,
+            "launches": int(launches), "clocks": clocks,
+            "stage_ms": {"tlas_rebuild": statistics.mean(tlas_ms), "rng_init": statistics.mean(rng_ms), "trace": statistics.mean(trace_ms)}}
+
+
+def exchange_ring(r, dist, torch, rank, world, local):
+    """Frame ring across the torchrun ranks: rank 0 allocates it and ships the 64-byte CUDA IPC handle (plumbing: one
+    broadcast); the others map it.  Returns None on success, else the reason (the caller falls back to an NCCL gather)."""
+    err = None
+    h = torch.zeros(64, dtype=torch.uint8, device=f"cuda:{local}")
+    try:
+        if rank == 0:
+            h = torch.frombuffer(bytearray(r.frameRingCreate()), dtype=torch.uint8).to(f"cuda:{local}")
+    except Exception as e:   # noqa: BLE001
+        err = f"rank 0: {e}"
+    dist.broadcast(h, src=0)
+    if rank != 0 and err is None:
+        try:
+            r.frameRingOpen(bytes(h.cpu().numpy().tobytes()))
+        except Exception as e:   # noqa: BLE001
+            err = f"rank {rank}: {e}"
+    bad = torch.tensor([1.0 if err else 0.0], device=f"cuda:{local}")
+    dist.all_reduce(bad)
+    if bad.item() > 0:
+        if r.has_ring:
+            try:
+                r.frameRingClose()
+            except Exception:   # noqa: BLE001
+                pass
+        return err or "another rank could not map the ring"
+    return None
+
+
+def measure_pipelined(pkg, r, sc, args, torch, dist, rank, world, local, tile_rows, fpw, sync_frames=None, warm_frames=None):
+    """value / e2e of one workload through the library's frame loop (rt_run_frames: windows of `fpw` frames in flight, two
+    windows overlapping).  value: device clock of the loop, frames stay on the device.  e2e: host wall clock of the same
+    loop with the per-frame transform arguments coming from host memory (H2D inside the loop) and every finished frame
+    copied to pinned host memory (rank 0 reads the ring's assembled frame when the ranks share one)."""
+    abi = pkg.abi
+    distributed = world > 1
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    xf = sc.xforms.copy()
+    # untimed: synchronous frames (stage times, single-frame latency) + one pipelined pass (allocations, tile-cost history)
+    sync_ms, stage = [], None
+    for k in range(sync_frames or max(3, args.warmup)):
+        out = r.renderFrame(k, SEED)
+        sync_ms.append(out.render_ms)
+        stage = {"tlas_rebuild": out.tlas_ms, "rng_init": out.rng_ms, "trace": out.trace_ms}
+    sync_rays = out.rays
+    r.runFrames(0, warm_frames or min(2 * fpw, max(fpw, args.warmup)), SEED, fpw, None)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    st = r.runFrames(args.warmup, args.steps, SEED, fpw, None)
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    clocks = sampler.stop() if rank == 0 else None
+    # e2e
+    seen = [0]
+
+    def sink(frame, img, out):
+        seen[0] += 1
+        return 0
+    r.setInstanceTransforms(xf)
+    r.runFrames(0, min(fpw, args.steps), SEED, fpw, sink)        # untimed: first use of the read-back path
+    barrier()
+    seen[0] = 0
+    t0 = time.perf_counter()
+    r.setInstanceTransforms(xf)          # per-frame host input: the loop uploads the transform arguments of every frame (reference: Renderer.cu:269-291)
+    es = r.runFrames(args.warmup, args.steps, SEED, fpw, sink)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    assert seen[0] == args.steps
+    tot = torch.tensor([float(st.rays), float(es.rays), float(st.kernel_launches)], dtype=torch.float64, device=f"cuda:{local}")
+    mx = torch.tensor([st.span_ms, e2e_s, wall_ms, st.max_latency_ms, statistics.median(sync_ms)], dtype=torch.float64, device=f"cuda:{local}")
+    if distributed:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    tot_rays, tot_e_rays, launches = tot.tolist()
+    span_ms, e2e_s, wall_ms, max_lat, sync_med = mx.tolist()
+    return {"value": tot_rays / (span_ms * 1e-3) / 1e6, "ms_per_step": span_ms / args.steps, "rays_per_frame": tot_rays / args.steps,
+            "e2e_value": tot_e_rays / e2e_s / 1e6, "e2e_ms_per_step": 1e3 * e2e_s / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+            "launches": int(launches), "clocks": clocks, "stage_ms": stage, "max_latency_ms": max_lat,
+            "sync_ms_per_frame": sync_med, "sync_rays": sync_rays, "span_ms": span_ms}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -419,6 +587,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg, sc, cfg = workload(args)
     abi = pkg.abi
+    comparison = args.bvh2 or args.megakernel or args.wavefront or args.sync
+    fpw = max(1, min(abi.MAX_FRAMES_IN_FLIGHT, args.frames_per_window, args.steps))
 
     base_flags = (abi.FLAG_TRAVERSE_BVH2 if args.bvh2 else 0) | (abi.FLAG_MEGAKERNEL if args.megakernel else 0) | (abi.FLAG_WAVEFRONT if args.wavefront else 0) | (abi.FLAG_SAH_REFINE if args.sah else 0)
     r = pkg.Renderer(device=local, flags=base_flags)
@@ -426,94 +596,41 @@ def run_ours(args):
     st = r.commitScene(sc)
     commit_s = time.perf_counter() - t0
     tile_rows = args.tile_rows
+    exchange = "none (single GPU)"
     if distributed:
         r.setTileShard(rank, world, tile_rows)
+        why = exchange_ring(r, dist, torch, rank, world, local) if not comparison else "comparison mode"
+        if why is None:
+            exchange = "frame ring: every rank's path kernel stores finished texels into rank 0's full frame through a CUDA IPC peer mapping over NVLink (fused gather)"
+        else:
+            print(f"[bench] frame ring unavailable ({why}); falling back to the synchronous loop with an NCCL gather", file=sys.stderr)
+            comparison = True
+            exchange = f"NCCL gather of packed planes (frame ring unavailable: {why})"
     elif args.emulate_shard > 1:        # tuning aid: this GPU renders rank 0's shard of an N-way split (not a bench line)
         r.setTileShard(0, args.emulate_shard, tile_rows)
     W, H = sc.width, sc.height
-    ptr, nbytes = r.devicePointer(abi.BUF_RGBA8)
-    if distributed:      # every rank's plane is allocated for the largest shard: gather equal-sized buffers
-        nbytes = pkg.sharding.padded_plane_bytes(H, W * 4, world, tile_rows)
-    local_plane = torch.as_tensor(DevPtr(ptr, nbytes), device=f"cuda:{local}")
-    gathered = [torch.empty_like(local_plane) for _ in range(world)] if (distributed and rank == 0) else None
-    host_fb = torch.empty(W * H * 4, dtype=torch.uint8).pin_memory()
-    xf = sc.xforms.copy()
 
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-
-    def frame(k, read_back):
-        """one step; returns (rays, device_ms incl. gather, FrameOut)"""
-        if read_back:
-            r.setInstanceTransforms(xf)          # per-frame host input (reference: updateInstances + H2D, Renderer.cu:269-291)
-        out = r.renderFrame(k, SEED)
-        ms = out.render_ms
-        if distributed:
-            ev0.record()
-            dist.gather(local_plane, gathered, dst=0)
-            ev1.record()
-            ev1.synchronize()
-            ms += ev0.elapsed_time(ev1)
-        if read_back and rank == 0:
-            if distributed:
-                # tiles of rank q are rows [(k*world+q)*tile_rows ...): de-interleave on the device, one D2H copy
-                full = pkg.sharding.assemble(gathered, H, W * 4, world, tile_rows)
-                host_fb.copy_(full.view(-1), non_blocking=True)
-                torch.cuda.synchronize()
-            else:
-                r.lib.rt_read_framebuffer(r.ctx, abi.BUF_RGBA8, C.c_void_p(host_fb.data_ptr()), host_fb.numel())
-        return out.rays, ms, out
-
-    def barrier():
-        if distributed:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- value: device-timed, inputs resident -------------------------------------------------------------------
-    for k in range(args.warmup):
-        frame(k, False)
-    sampler = ClockSampler(local)
-    barrier()
-    if rank == 0:
-        sampler.start()
-    rays = 0
-    dev_ms = 0.0
-    trace_ms, rng_ms, tlas_ms = [], [], []
-    launches = 0
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        n, ms, out = frame(args.warmup + k, False)
-        rays += n
-        dev_ms += ms
-        trace_ms.append(out.trace_ms)
-        rng_ms.append(out.rng_ms)
-        tlas_ms.append(out.tlas_ms)
-        launches += out.kernel_launches
-    barrier()
-    wall_ms = 1e3 * (time.perf_counter() - t0)
-    clocks = sampler.stop() if rank == 0 else None
-
-    # ---- e2e: same steps through the public API with host buffers: transforms H2D, framebuffer D2H ---------------
-    frame(args.warmup, True)        # untimed: first use of the read-back path (torch's de-interleave kernels, allocator, pinned copy)
-    barrier()
-    e_rays = 0
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        n, _, _ = frame(args.warmup + k, True)
-        e_rays += n
-    barrier()
-    e2e_s = time.perf_counter() - t0
-
-    tot = torch.tensor([float(rays), float(e_rays)], dtype=torch.float64, device=f"cuda:{local}")
-    mx = torch.tensor([dev_ms, e2e_s, wall_ms], dtype=torch.float64, device=f"cuda:{local}")
-    if distributed:
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-    tot_rays, tot_e_rays = tot.tolist()
-    max_dev_ms, max_e2e_s, max_wall_ms = mx.tolist()
+    if not comparison:
+        m = measure_pipelined(pkg, r, sc, args, torch, dist, rank, world, local, tile_rows, fpw)
+        value, e2e = m["value"], m["e2e_value"]
+        ms_per_step, e2e_ms, wall_ms_per_step = m["ms_per_step"], m["e2e_ms_per_step"], m["wall_ms_per_step"]
+        launches, clocks, stage_ms = m["launches"], m["clocks"], m["stage_ms"]
+        rays_per_frame = m["rays_per_frame"]
+        t_kernel_frame_ms = max(1e-6, ms_per_step - (stage_ms["tlas_rebuild"] + stage_ms["rng_init"]))
+        loop = {"frames_per_window": fpw, "windows_in_flight": 2, "max_frame_latency_ms": m["max_latency_ms"],
+                "synchronous_frame_ms": m["sync_ms_per_frame"], "synchronous_mrays": m["sync_rays"] / (m["sync_ms_per_frame"] * 1e-3) / 1e6,
+                "what": "rt_run_frames: windows of frames in flight served by one launch of the path kernel each (a lane out of pixels of frame k starts on "
+                        "frame k+1); ms_per_step = device clock of the loop / frames; synchronous_* = rt_render_frame, one frame at a time (its latency)"}
+    else:
+        m = measure_synchronous(pkg, r, sc, args, torch, dist, rank, world, local, tile_rows)
+        value, e2e = m["value"], m["e2e_value"]
+        ms_per_step, e2e_ms, wall_ms_per_step = m["ms_per_step"], m["e2e_ms_per_step"], m["wall_ms_per_step"]
+        launches, clocks, stage_ms = m["launches"], m["clocks"], m["stage_ms"]
+        rays_per_frame = m["rays_per_frame"]
+        t_kernel_frame_ms = stage_ms["trace"]
+        loop = {"frames_per_window": 1, "what": "rt_render_frame, one frame at a time"}
 
     if rank == 0:
-        value = tot_rays / (max_dev_ms * 1e-3) / 1e6
-        e2e = tot_e_rays / max_e2e_s / 1e6
         # ---- roofline of the dominant kernel (trace/shade): algorithmic bytes from an instrumented pass ----------
         roof = None
         try:
@@ -528,7 +645,7 @@ def run_ours(args):
             rc.cleanup()
             node_b, prim_b, inst_b, io_b = (64 if args.bvh2 else 80), 48, 64, 24 + 16 + 12
             alg = (co.node_fetches * node_b + co.prim_fetches * prim_b + co.instance_fetches * inst_b + W * H * io_b) / world
-            t_kernel = statistics.mean(trace_ms) * 1e-3
+            t_kernel = t_kernel_frame_ms * 1e-3
             achieved = alg / t_kernel / 1e9
             # DRAM traffic of one launch: from the committed ncu --set full capture of THIS workload, and only while the
             # kernel's sources still hash as they did when it was captured (profiles/tools/kernel_hash.py); else null
@@ -550,9 +667,8 @@ def run_ours(args):
                     traffic = None
             kname = ("render_pixels_kernel (one thread per pixel)" if args.megakernel else
                      "wave_trace kernels + wave_shade (wave loop)" if (args.wavefront or args.bvh2) else
+                     "persist8_kernel (trace + shade; one launch per window of frames in flight)" if not comparison else
                      "persist8_kernel (trace + shade, one launch per frame)")
-            # the BVH + triangle records of this workload are L2-resident (ncu: DRAM throughput < 1 %), so the HBM figure
-            # is the contract's formal roofline and the L2 read bandwidth measured here is the one that can bind
             l2 = None
             try:
                 l2_gbs = r.probeReadBandwidth(32 << 20, 40)
@@ -597,17 +713,20 @@ def run_ours(args):
             c3 = c3_rebuild(pkg, local)
         metric = METRIC if args.config == "c2" else f"Mrays/s ({cfg['workload'].split(',')[0]})"
         line = {"metric": metric, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": max_dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": cfg,
-                "parallelism": f"image tiles ({tile_rows} rows) x{world}, scene replicated, NCCL gather" if world > 1 else "single GPU",
-                "rays_per_frame": tot_rays / args.steps, "wall_ms_per_step": max_wall_ms / args.steps,
-                "stage_ms": {"tlas_rebuild": statistics.mean(tlas_ms), "rng_init": statistics.mean(rng_ms), "trace": statistics.mean(trace_ms)},
+                "parallelism": f"image tiles ({tile_rows} rows) x{world}, scene replicated; exchange: {exchange}" if world > 1 else "single GPU",
+                "frame_loop": loop,
+                "rays_per_frame": rays_per_frame, "wall_ms_per_step": wall_ms_per_step,
+                "stage_ms": stage_ms,
                 "lbvh_build_ms": {"blas_1M_tris": st.blas_ms, "tlas": st.tlas_ms, "kernel_launches": st.kernel_launches,
                                   "bytes_per_prim_algorithmic": 280, "achieved_gbs": 280 * st.primitive_count / max(st.blas_ms, 1e-6) / 1e6},
                 "commit_s": commit_s,
                 "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": int(len(sc.instances) * 92), "d2h_bytes_per_step": int(W * H * 4 + 64),
-                        "ms_per_step": 1e3 * max_e2e_s / args.steps,
-                        "what": "rt_set_instance_xforms(host) + rt_render_frame + rt_read_framebuffer(RGBA8 -> pinned host), host wall clock"},
+                        "ms_per_step": e2e_ms,
+                        "what": "rt_set_instance_xforms(host) + rt_run_frames with a sink: per frame the transform arguments go host -> device and the finished "
+                                "RGBA8 frame device -> pinned host (rank 0: the assembled full frame), host wall clock" if not comparison else
+                                "rt_set_instance_xforms(host) + rt_render_frame + rt_read_framebuffer(RGBA8 -> pinned host), host wall clock"},
                 "gpu_launches": int(launches), "clocks": clocks}
         if c3:
             line["c3_particle_rebuild"] = c3
@@ -619,10 +738,44 @@ def run_ours(args):
             line["roofline"] = roof
         if cpu:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line))
     r.cleanup()
+    # ---- config 4 beside the headline line (BASELINE.json names it for 2/4/8 GPUs): 1 warm-up + 2 steps ------------------
+    c4 = None
+    if args.config == "c2" and not args.no_c4 and not comparison and args.emulate_shard == 1:
+        try:
+            c4 = config4_line(pkg, args, torch, dist, rank, world, local, tile_rows)
+        except Exception as e:   # noqa: BLE001
+            c4 = {"unavailable": f"{type(e).__name__}: {e}"}
+    if rank == 0:
+        if c4:
+            line["c4"] = c4
+        print(json.dumps(line))
     if distributed:
         dist.destroy_process_group()
+
+
+def config4_line(pkg, args, torch, dist, rank, world, local, tile_rows):
+    """configs[3] (10 M triangles, 3840x2160, 256 spp, image tiles over the GPUs) through the same frame loop: 1 untimed
+    window + 2 timed frames, so that the driver's scaling record carries the configuration BASELINE.json names for 2/4/8 GPUs."""
+    import copy
+    a = copy.copy(args)
+    a.config, a.steps, a.warmup, a.spp = "c4", 2, 1, 64
+    _, sc, cfg = workload(a)
+    r = pkg.Renderer(device=local)
+    try:
+        st = r.commitScene(sc)
+        if world > 1:
+            r.setTileShard(rank, world, tile_rows)
+            why = exchange_ring(r, dist, torch, rank, world, local)
+            if why is not None:
+                return {"unavailable": f"frame ring: {why}"}
+        m = measure_pipelined(pkg, r, sc, a, torch, dist, rank, world, local, tile_rows, 2, sync_frames=1, warm_frames=2)
+    finally:
+        r.cleanup()
+    return {"metric": f"Mrays/s ({cfg['workload'].split(',')[0]})", "value": m["value"], "unit": "Mrays/s", "ms_per_step": m["ms_per_step"],
+            "steps": a.steps, "warmup": a.warmup, "e2e": {"value": m["e2e_value"], "ms_per_step": m["e2e_ms_per_step"]},
+            "rays_per_frame": m["rays_per_frame"], "synchronous_frame_ms": m["sync_ms_per_frame"], "config": cfg,
+            "lbvh_build_ms": {"blas_10M_tris": st.blas_ms, "tlas": st.tlas_ms, "achieved_gbs": 280 * st.primitive_count / max(st.blas_ms, 1e-6) / 1e6}}
 
 
 def main():
@@ -642,6 +795,9 @@ def main():
     ap.add_argument("--nz", type=int, default=500)
     ap.add_argument("--tile-rows", type=int, default=8)
     ap.add_argument("--emulate-shard", type=int, default=1, help="tuning aid: render only rank 0's tiles of an N-way split on one GPU")
+    ap.add_argument("--frames-per-window", type=int, default=8, help="frames in flight per launch of the path kernel (1..8)")
+    ap.add_argument("--sync", action="store_true", help="comparison mode: rt_render_frame one frame at a time (at N > 1 with an NCCL gather) instead of the frame loop")
+    ap.add_argument("--no-c4", action="store_true", help="skip the config-4 sub-line")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-build baseline")
     ap.add_argument("--no-c3", action="store_true", help="skip the config-3 particle rebuild measurement")
@@ -651,7 +807,7 @@ def main():
     ap.add_argument("--bvh2", action="store_true", help="comparison mode: traverse the binary LBVH instead of the wide BVH")
     args = ap.parse_args()
     if args.config != "c2":
-        args.no_ref_cuda = args.no_c3 = args.no_cpu_baseline = True
+        args.no_ref_cuda = args.no_c3 = args.no_cpu_baseline = args.no_c4 = True
     if args.impl == "reference":
         run_reference(args)
     elif args.config == "c3":

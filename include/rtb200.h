@@ -156,7 +156,12 @@ enum rt_flags {
     RT_FLAG_WAVEFRONT               = 1u << 6,
     /* Optional SAH refinement of the LBVH: one tree rotation per node, applied bottom-up inside the refit (measured:
      * -1.5 % node visits on config 2, +0.3 ms build per 629 k triangles — off by default).                          */
-    RT_FLAG_SAH_REFINE              = 1u << 7
+    RT_FLAG_SAH_REFINE              = 1u << 7,
+    /* BLASes built by rt_build_acceleration_structure use PLOC (parallel locally-ordered clustering, Meister & Bittner
+     * 2018: bottom-up agglomeration by smallest merged surface area over the Morton order) instead of the Karras LBVH:
+     * a tree of near top-down-SAH quality for geometry that is built once, at several times the build time.  The
+     * per-frame rebuilds of rt_set_vtk_frame and the TLAS always use the LBVH.                                          */
+    RT_FLAG_SAH_BUILD               = 1u << 8
 };
 
 typedef struct rt_frame_out {
@@ -305,6 +310,7 @@ typedef struct rt_loop_stats {
     uint64_t frames, rays, kernel_launches;
     double   wall_ms;         /* host wall clock of the loop                                                      */
     double   device_ms;       /* sum of the windows' device times (windows overlap: >= the wall clock share)       */
+    double   span_ms;         /* device clock (CUDA events): start of the loop .. last window finished              */
     double   max_latency_ms;  /* slowest submit -> frame-complete latency                                          */
 } rt_loop_stats;
 typedef int (*rt_frame_sink)(void *user, size_t frame, const void *rgba8, size_t bytes, const rt_frame_out *out);

@@ -27,6 +27,7 @@ FLAG_TRAVERSE_BVH2 = 1 << 4
 FLAG_MEGAKERNEL = 1 << 5
 FLAG_WAVEFRONT = 1 << 6
 FLAG_SAH_REFINE = 1 << 7
+FLAG_SAH_BUILD = 1 << 8
 
 BUF_RGBA8, BUF_RADIANCE, BUF_PRIMARY_T, BUF_PRIMARY_INSTANCE, BUF_PRIMARY_PRIM = range(5)
 
@@ -99,7 +100,7 @@ class WindowStats(C.Structure):
 
 class LoopStats(C.Structure):
     _fields_ = [("frames", C.c_uint64), ("rays", C.c_uint64), ("kernel_launches", C.c_uint64), ("wall_ms", C.c_double),
-                ("device_ms", C.c_double), ("max_latency_ms", C.c_double)]
+                ("device_ms", C.c_double), ("span_ms", C.c_double), ("max_latency_ms", C.c_double)]
 
 
 MAX_FRAMES_IN_FLIGHT = 8

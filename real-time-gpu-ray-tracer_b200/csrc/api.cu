@@ -228,6 +228,12 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     ctx->blas.emit_bvh2 = ctx->tlas.emit_bvh2 = (ctx->flags & (RT_FLAG_TRAVERSE_BVH2 | RT_FLAG_KEEP_LBVH)) != 0;
     // rotated subtrees no longer cover one contiguous Morton range, which multi-primitive leaves (a tuning experiment) rely on
     ctx->blas.sah_rotations = ctx->tlas.sah_rotations = (ctx->flags & RT_FLAG_SAH_REFINE) && !getenv("RTB200_LEAF_MAX");
+    {
+        const char *e = getenv("RTB200_PLOC");      // A/B runs
+        const bool want = e ? atoi(e) != 0 : (ctx->flags & RT_FLAG_SAH_BUILD) != 0;
+        ctx->blas.ploc = want && !ctx->composing && !getenv("RTB200_LEAF_MAX");
+        ctx->tlas.ploc = false;
+    }
     ctx->blas.wait_event = ctx->tlas.wait_event = ctx->blocking_wait ? ctx->ev_block : nullptr;
     ctx->blas.prepare_blas(hs.seg_offset, hs.seg_type);          // allocations stay outside the timed build
     ctx->d_instances.reserve(n_inst);

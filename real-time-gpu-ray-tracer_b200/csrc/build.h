@@ -38,6 +38,8 @@ public:
     void prepare_blas(const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type);   // allocations only
     void prepare_tlas(int n_instances);
     bool sah_rotations = false;              // optional SAH refinement (RT_FLAG_SAH_REFINE): one tree rotation per node inside the refit (rt_build_core.h best_rotation)
+    bool ploc = false;                       // build the binary tree with PLOC (kernels_ploc.cu) instead of Karras + refit: BLASes built once
+    int ploc_rounds = 0;                     // rounds the last PLOC build took
     bool emit_bvh2 = false;                  // also emit the 64-byte binary nodes + their leaf-order records (RT_FLAG_TRAVERSE_BVH2)
     void build_tlas(int n_instances, int morton_bits, cudaStream_t stream, int sm_count);
 
@@ -74,6 +76,7 @@ public:
 private:
     void reserve(int n, int n_segs, bool tris);
     void run_tree(int n, int n_segs, int key_bits, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count);
+    void run_ploc(int n, int n_segs, cudaStream_t stream);                                                             // kernels_ploc.cu
     void collapse_wide(int n, int n_segs, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count);   // kernels_wide.cu
     int n_ = 0, n_segs_ = 0;
     RadixSorter sorter_;
@@ -89,6 +92,10 @@ private:
     DeviceBuffer<BvhNode8> nodes8_;
     DeviceBuffer<TriIsect> leaf_tris8_;
     int collapse_blocks_per_sm_ = 0;
+    DeviceBuffer<float4> ploc_lo_a_, ploc_hi_a_, ploc_lo_b_, ploc_hi_b_;
+    DeviceBuffer<int> ploc_nn_, ploc_state_;
+    DeviceBuffer<uint2> ploc_blocks_;
+    PinnedBuffer<int> ploc_state_host_;
     DeviceBuffer<TriIsect> leaf_tris_;
     DeviceBuffer<uint32_t> leaf_prims_;
     uint64_t *keys_ = nullptr, *keys_alt_ = nullptr;

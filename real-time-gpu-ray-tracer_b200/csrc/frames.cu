@@ -379,6 +379,8 @@ int rt_run_frames(rt_ctx *ctx, uint64_t first_frame, size_t n_frames, uint64_t s
         if (ctx->win[q] && ctx->win[q]->in_flight) return rt_fail(ctx, RT_ERR_STATE, "rt_run_frames: release the windows in flight first");
     rt_loop_stats tot{};
     const auto t0 = std::chrono::steady_clock::now();
+    CUDA_CHECK(cudaEventRecord(ctx->ev[0], ctx->stream));          // every window's stream is ordered behind the context's stream
+    FrameWindow *last = nullptr;
     struct Pending { uint32_t window, n; uint64_t first; };
     std::vector<Pending> queue;                 // submitted, not yet drained (at most two)
     size_t next = 0;
@@ -415,6 +417,7 @@ int rt_run_frames(rt_ctx *ctx, uint64_t first_frame, size_t n_frames, uint64_t s
             }
         }
         rt_window_stats ws{};
+        last = ctx->win[p.window];
         const int rr = rt_release_window(ctx, p.window, &ws);
         if (rc == RT_OK) rc = rr;
         tot.device_ms += ws.device_ms;
@@ -422,6 +425,12 @@ int rt_run_frames(rt_ctx *ctx, uint64_t first_frame, size_t n_frames, uint64_t s
     }
     for (const Pending &p: queue) rt_release_window(ctx, p.window, nullptr);      // after an error or a stop
     tot.wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (last && rc == RT_OK && !stopped) {
+        float span = 0.0f;
+        CUDA_CHECK(cudaEventSynchronize(ctx->ev[0]));
+        CUDA_CHECK(cudaEventElapsedTime(&span, ctx->ev[0], last->ev_end));
+        tot.span_ms = span;
+    }
     if (stats) *stats = tot;
     if (rc != RT_OK) return rc;
     if (stopped) return rt_fail(ctx, RT_ERR_STATE, "rt_run_frames: stopped by the frame sink");

@@ -410,6 +410,9 @@ void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const
     keys_ = keys_a_.get(); keys_alt_ = keys_b_.get(); vals_ = vals_a_.get(); vals_alt_ = vals_b_.get();
     if (n > 1) {
         sorter_.sort(keys_, keys_alt_, vals_, vals_alt_, n, key_bits, stream, sm_count, launches);
+        if (ploc) {
+            run_ploc(n, n_segs, stream);
+        } else {
         CUDA_CHECK(cudaMemsetAsync(flags_.get(), 0, (size_t) (n - 1) * sizeof(int), stream));
         karras_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(keys_, n, seg_offset_.get(), n_segs, left_.get(), right_.get(), parent_.get(),
                                                            leaf_parent_.get(), seg_root_.get(), range_.get());
@@ -421,6 +424,7 @@ void LbvhBuilder::run_tree(int n, int n_segs, int key_bits, int leaf_mode, const
             refit_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(), parent_.get(),
                                                           leaf_parent_.get(), n, flags_.get(), node_lo_.get(), node_hi_.get());
         launches += 2;
+        }
         if (emit_bvh2) {
             emit_nodes_kernel<<<div_up(n - 1, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), vals_, left_.get(), right_.get(),
                                                                    node_lo_.get(), node_hi_.get(), seg_offset_.get(), seg_type_.get(), n_segs, n, leaf_mode,

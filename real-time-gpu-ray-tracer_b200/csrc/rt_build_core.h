@@ -47,6 +47,40 @@ RT_HD int best_rotation(const Aabb &L, const Aabb &R, bool l_inner, const Aabb &
     return best;
 }
 
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) — the builder for BLASes that are built once ---
+// Bottom-up agglomeration over the Morton-sorted primitives: in every round each cluster looks at the clusters within
+// RT_PLOC_RADIUS positions of it in the (Morton-ordered) cluster array and picks the one whose union with it has the
+// smallest surface area; two clusters that pick each other merge into a new inner node, the rest wait.  The merged array
+// keeps the Morton order, so the next round sees ever larger neighbourhoods.  The result approaches a top-down SAH build
+// while every step stays a flat data-parallel pass.  Determinism: the distance is symmetric, ties go to the lower
+// position, node ids come from a prefix sum over the merge leaders — the device rounds and the serial twin give the
+// same tree bit for bit.  Clusters of different segments (BLASes of one batch) never merge.
+// A cluster is two float4: lo.xyz | bits(ref) and hi.xyz | bits(segment); ref >= 0 inner node, ref < 0 leaf ~position.
+#ifndef RT_PLOC_RADIUS
+#define RT_PLOC_RADIUS 16
+#endif
+RT_HD int ploc_nearest(const float4 *clo, const float4 *chi, int m, int i, int radius) {
+    const float4 a = clo[i], b = chi[i];
+    int best = -1;
+    float best_area = RT_INF;
+    const int j0 = i - radius < 0 ? 0 : i - radius, j1 = i + radius > m - 1 ? m - 1 : i + radius;
+    for (int j = j0; j <= j1; j++) {
+        if (j == i) continue;
+        const float4 c = clo[j], d = chi[j];
+        if (f2u(d.w) != f2u(b.w)) continue;                      // another BLAS of the batch
+        const float dx = rt_max(b.x, d.x) - rt_min(a.x, c.x), dy = rt_max(b.y, d.y) - rt_min(a.y, c.y), dz = rt_max(b.z, d.z) - rt_min(a.z, c.z);
+        const float area = dx * dy + dy * dz + dz * dx;
+        if (area < best_area) { best_area = area; best = j; }    // strict: the lower position wins ties
+    }
+    return best;
+}
+// what cluster i does in this round: 0 stays, 1 merges with nn[i] and leads (i < nn[i]), 2 is absorbed by nn[i]
+RT_HD int ploc_role(const int *nn, int i) {
+    const int j = nn[i];
+    if (j < 0 || nn[j] != i) return 0;
+    return i < j ? 1 : 2;
+}
+
 // Conservative padding so that the fma-based slab test can never cull a true hit on the box surface.
 // The reference pads only degenerate axes by 1e-6 (ensureVolume, include/AS/BoundingBox.cuh:24-28).
 RT_HD Aabb aabb_pad(const Aabb &a) {

@@ -49,8 +49,53 @@ int find_segment(const std::vector<uint32_t> &off, uint32_t j) {
     return lo;
 }
 
+// serial twin of LbvhBuilder::run_ploc (kernels_ploc.cu): the same rounds, every pass a plain loop
+void build_ploc(Lbvh &b, const std::vector<uint32_t> &seg_offset) {
+    const int n = b.n, n_segs = (int) seg_offset.size() - 1, m_nodes = n > 1 ? n - 1 : 0;
+    std::vector<float4> lo(n), hi(n), lo2(n), hi2(n);
+    for (int pos = 0; pos < n; pos++) {
+        const Aabb &bx = b.prim_box[b.vals[pos]];
+        lo[pos] = make_float4(bx.lo.x, bx.lo.y, bx.lo.z, u2f((uint32_t) ~pos));
+        hi[pos] = make_float4(bx.hi.x, bx.hi.y, bx.hi.z, u2f((uint32_t) find_segment(seg_offset, (uint32_t) pos)));
+    }
+    b.left.assign(m_nodes, -1); b.right.assign(m_nodes, -1); b.parent.assign(m_nodes, -1); b.leaf_parent.assign(n, -1);
+    Aabb zero;
+    zero.lo = mk3(0.f, 0.f, 0.f); zero.hi = zero.lo;
+    b.node_box.assign(m_nodes, zero);
+    std::vector<int> nn(n);
+    int m = n, next_id = 0;
+    while (m > n_segs) {
+        for (int i = 0; i < m; i++) nn[i] = ploc_nearest(lo.data(), hi.data(), m, i, RT_PLOC_RADIUS);
+        int dst = 0;
+        for (int i = 0; i < m; i++) {
+            const int role = ploc_role(nn.data(), i);
+            if (role == 2) continue;
+            float4 a = lo[i], c = hi[i];
+            if (role == 1) {
+                const int j = nn[i], id = next_id++;
+                const int l = (int) f2u(a.w), r = (int) f2u(lo[j].w);
+                a = make_float4(fminf(a.x, lo[j].x), fminf(a.y, lo[j].y), fminf(a.z, lo[j].z), u2f((uint32_t) id));
+                c = make_float4(fmaxf(c.x, hi[j].x), fmaxf(c.y, hi[j].y), fmaxf(c.z, hi[j].z), c.w);
+                b.node_box[id].lo = mk3(a.x, a.y, a.z);
+                b.node_box[id].hi = mk3(c.x, c.y, c.z);
+                b.left[id] = l; b.right[id] = r;
+                if (l >= 0) b.parent[l] = id; else b.leaf_parent[~l] = id;
+                if (r >= 0) b.parent[r] = id; else b.leaf_parent[~r] = id;
+            }
+            lo2[dst] = a; hi2[dst] = c;
+            dst++;
+        }
+        m = dst;
+        lo.swap(lo2); hi.swap(hi2);
+    }
+    for (int i = 0; i < m; i++) {
+        const int ref = (int) f2u(lo[i].w);
+        if (ref >= 0) b.seg_root[(int) f2u(hi[i].w)] = ref;
+    }
+}
+
 // serial twin of LbvhBuilder::run_tree
-void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type, int leaf_mode, bool rotate) {
+void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vector<uint32_t> &seg_type, int leaf_mode, bool rotate, bool ploc = false) {
     const int n = b.n;
     const int n_segs = (int) seg_type.size();
     std::vector<uint32_t> order(n);
@@ -64,7 +109,11 @@ void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vec
     const int m = n > 1 ? n - 1 : 0;
     b.left.assign(m, 0); b.right.assign(m, 0); b.parent.assign(m, -1); b.leaf_parent.assign(n, -1);
     b.node_box.resize(m); b.nodes.resize(m); b.range.resize(m);
-    for (int i = 0; i < m; i++) {
+    if (ploc && m > 0) {
+        for (int i = 0; i < m; i++) b.range[i] = make_int2(0, 0);
+        build_ploc(b, seg_offset);
+    }
+    for (int i = 0; i < m && !ploc; i++) {
         const KarrasNode k = karras_node(b.keys.data(), n, i);
         b.range[i] = make_int2(k.first, k.last);
         b.left[i] = k.left; b.right[i] = k.right;
@@ -77,7 +126,23 @@ void build_tree(Lbvh &b, const std::vector<uint32_t> &seg_offset, const std::vec
         if (seg_offset[s + 1] - seg_offset[s] == 1u)
             b.seg_root[s] = leaf_mode == 0 ? make_leaf_ref(seg_type[s], seg_offset[s]) : make_leaf_ref(0u, b.vals[seg_offset[s]]);
     // refit in post-order (explicit stack)
-    if (m > 0) {
+    if (m > 0 && ploc) {
+        // PLOC made the boxes while merging; only the traversal records of the binary comparison mode are left to write
+        for (int i = 0; i < m; i++) {
+            Aabb bx[2];
+            int ref[2];
+            const int child[2] = {b.left[i], b.right[i]};
+            for (int c = 0; c < 2; c++) {
+                if (child[c] >= 0) { bx[c] = b.node_box[child[c]]; ref[c] = child[c]; }
+                else {
+                    const uint32_t pos = (uint32_t) ~child[c];
+                    bx[c] = b.prim_box[b.vals[pos]];
+                    ref[c] = leaf_mode == 0 ? make_leaf_ref(seg_type[find_segment(seg_offset, pos)], pos) : make_leaf_ref(0u, b.vals[pos]);
+                }
+            }
+            b.nodes[i] = make_node2(bx[0], ref[0], bx[1], ref[1]);
+        }
+    } else if (m > 0) {
         std::vector<char> done(m, 0);
         std::vector<int> st{0};
         auto child_box = [&](int c) { return c >= 0 ? b.node_box[c] : b.prim_box[b.vals[~c]]; };
@@ -223,7 +288,7 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
         const int seg = find_segment(hs.seg_offset, (uint32_t) j);
         b.keys[j] = ((uint64_t) seg << (3 * bits)) | morton_code(b.prim_box[j], seg_bounds[seg], bits);
     }
-    build_tree(b, hs.seg_offset, hs.seg_type, 0, (hs.flags & RT_FLAG_SAH_REFINE) != 0);
+    build_tree(b, hs.seg_offset, hs.seg_type, 0, (hs.flags & RT_FLAG_SAH_REFINE) != 0, (hs.flags & RT_FLAG_SAH_BUILD) != 0);
     e->leaf_prims.resize(n);
     e->leaf_tris.resize(n);
     for (int pos = 0; pos < n; pos++) {
@@ -272,7 +337,7 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     t.keys.resize(ni);
     for (int i = 0; i < ni; i++) t.keys[i] = morton_code(t.prim_box[i], scene, tbits);
     const std::vector<uint32_t> toff{0u, (uint32_t) ni}, ttype{0u};
-    build_tree(t, toff, ttype, 1, (hs.flags & RT_FLAG_SAH_REFINE) != 0);
+    build_tree(t, toff, ttype, 1, (hs.flags & RT_FLAG_SAH_REFINE) != 0, getenv("EMUL_TLAS_PLOC") != nullptr);
     collapse_wide(t, toff, 1);
     e->tlas_leaf_inst.resize(ni);
     for (int q = 0; q < ni; q++) e->tlas_leaf_inst[q] = t.vals[t.leaf_pos8[q]];
@@ -320,6 +385,30 @@ uint32_t emul_render(void *h, uint64_t seed, int y0, int y1, int threads, uint8_
     });
     if (rays) *rays += total.load();
     return ovf.load();
+}
+
+// traversal work of rows [y0, y1): out[0] rays, [1] wide-node fetches, [2] primitive tests, [3] instance entries — the
+// counts the device's RT_FLAG_COUNT_TRAVERSAL kernel reports (same functions, COUNT = true), for tree-quality checks
+void emul_count(void *h, uint64_t seed, int y0, int y1, int threads, uint64_t *out4) {
+    Emul &e = *(Emul *) h;
+    const CameraD &cam = e.hs.cam;
+    std::atomic<uint64_t> tot[4];
+    for (auto &t: tot) t = 0;
+    parallel_rows(y0, y1, threads, [&](int y) {
+        uint64_t acc[4] = {0, 0, 0, 0};
+        for (uint32_t x = 0; x < cam.width; x++) {
+            const uint32_t pixelIndex = cam.pitch * (uint32_t) y + x;
+            curandStateXORWOW_t st;
+            curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &st);
+            RngState r{st.d, st.v[0], st.v[1], st.v[2], st.v[3], st.v[4]};
+            uint32_t overflow = 0;
+            uint2 stack[RT_WIDE_STACK];
+            const PixelOut o = render_pixel<true, true>(e.sc, cam, x, (uint32_t) y, r, overflow, stack, 1);
+            acc[0] += o.rays; acc[1] += o.stats.nodes; acc[2] += o.stats.prims; acc[3] += o.stats.insts;
+        }
+        for (int k = 0; k < 4; k++) tot[k] += acc[k];
+    });
+    for (int k = 0; k < 4; k++) out4[k] = tot[k].load();
 }
 
 void emul_instances(void *h, float *o) {

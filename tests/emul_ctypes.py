@@ -187,6 +187,14 @@ class Emul:
                                    abi.ptr(t), abi.ptr(inst), abi.ptr(prim))
         return dict(rgba8=img, radiance=rad, rays=rays.value, t=t, inst=inst, prim=prim, overflow=ovf)
 
+    def count(self, seed, y0=0, y1=None, threads=None):
+        """traversal work of rows [y0, y1): dict(rays, nodes, prims, insts) — what RT_FLAG_COUNT_TRAVERSAL reports on the device"""
+        out = np.zeros(4, np.uint64)
+        self.lib.emul_count.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        self.lib.emul_count.restype = None
+        self.lib.emul_count(self.h, seed, y0, self.H if y1 is None else y1, threads or os.cpu_count() or 1, abi.ptr(out))
+        return dict(rays=int(out[0]), nodes=int(out[1]), prims=int(out[2]), insts=int(out[3]))
+
     def instances(self):
         out = np.zeros((len(self.sc.instances), 33), np.float32)
         self.lib.emul_instances(self.h, abi.ptr(out))

@@ -567,3 +567,29 @@ def test_camera_limits(pkg, spp, depth, ok):
     else:
         with pytest.raises(AssertionError):
             ec.Emul(sc)
+
+
+@pytest.mark.parametrize("idx", [2, 3, 4, 5])
+def test_ploc_tree_invariants(pkg, port, idx):
+    """RT_FLAG_SAH_BUILD (PLOC): every primitive in exactly one leaf, every inner node under one parent, parent boxes contain
+    their children, segments (BLASes of the batch) never mix; the frame equals the LBVH frame and the oracle's."""
+    sc = parity_scenes(pkg.scenes)[idx]
+    e = ec.Emul(sc, pkg.abi.FLAG_SAH_BUILD)
+    b = e.lbvh(0)
+    n = len(b["keys"])
+    left, right, parent, bounds = b["left"], b["right"], b["parent"], b["bounds"]
+    used = [i for i in range(n - 1) if not (left[i] == -1 and right[i] == -1 and parent[i] == -1 and not bounds[i].any())]
+    kids = np.concatenate([left[used], right[used]])
+    leaves = sorted(int(~c) for c in kids if c < 0)
+    multi = n - len(leaves)                                        # single-primitive BLASes have no inner node
+    assert leaves == sorted(set(leaves)) and len(leaves) + multi == n
+    inner = sorted(int(c) for c in kids if c >= 0)
+    assert inner == sorted(set(inner))
+    for i in used:
+        for c in (left[i], right[i]):
+            if c >= 0:
+                assert parent[c] == i
+                assert (bounds[c, :3] >= bounds[i, :3]).all() and (bounds[c, 3:] <= bounds[i, 3:]).all()
+    r = e.render(SEED)
+    img, rad, rays = port.scene(sc, 9).render(SEED)
+    assert r["rays"] == rays and np.array_equal(r["rgba8"], img)

@@ -454,3 +454,23 @@ def test_rebuilds_under_sm_pressure(pkg, tmp_path):
         assert hog_frames[0] > 0
     finally:
         r.cleanup()
+
+
+@pytest.mark.parametrize("idx", [0, 2, 3, 4, 5])
+def test_sah_build_ploc(pkg, port, idx):
+    """RT_FLAG_SAH_BUILD: BLASes built with PLOC (kernels_ploc.cu).  The tree is the one the serial twin's rounds make — same
+    children, parents and boxes, and the same wide BVH — and the frame still matches the oracle (the closest hit does not
+    depend on the topology)."""
+    import emul_ctypes as ec
+    sc = parity_scenes(pkg.scenes)[idx]
+    g = gpu_frame(pkg, sc, flags=pkg.abi.FLAG_SAH_BUILD | pkg.abi.FLAG_KEEP_LBVH)
+    e = ec.Emul(sc, pkg.abi.FLAG_SAH_BUILD)
+    twin = e.lbvh(0)
+    for name in ("keys", "prim_ids", "left", "right", "parent", "bounds"):
+        assert np.array_equal(g["lbvh"][name], twin[name]), f"{sc.name}: lbvh.{name} differs from the CPU twin"
+    canon = pkg.abi.canonical_wide_bvh
+    assert canon(*g["wide"], range(e.n_blas())) == canon(*e.wide(0), range(e.n_blas())), sc.name
+    plain = ec.Emul(sc).lbvh(0)
+    if len(plain["left"]) > 64:
+        assert not np.array_equal(plain["left"], g["lbvh"]["left"]), "the PLOC tree equals the Karras tree"
+    check_against_oracle(g, port.scene(sc, 5), sc)

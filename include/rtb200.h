@@ -224,6 +224,14 @@ int rt_commit_materials(rt_ctx *ctx,
                         const rt_rough *roughs, size_t rough_count,
                         const rt_metal *metals, size_t metal_count);
 int rt_commit_dielectrics(rt_ctx *ctx, const rt_dielectric *dielectrics, size_t count); /* extension */
+/* ---- adding a geometry type (reference files/AddGeometryType.txt:1-35: ten steps in ten files) -------------------
+ * Here a primitive type is one row of the table in csrc/rt_prims.h + one PrimOps<type> specialisation (bounds, hit,
+ * surface, local box / centroid).  A build compiled with -DRT_EXT_PRIMITIVE='"header.h"' has a fourth type (value 3 in
+ * rt_instance_desc.type); its device records (the header's ExtPrimD, record_bytes = sizeof) are committed here, original
+ * order, like the arrays of rt_commit_geometry.  The standard build returns RT_ERR_ARGUMENT.
+ * rt_primitive_type_count: 3, or 4 in a build with an extension type.                                              */
+int rt_commit_extension_primitives(rt_ctx *ctx, const void *records, size_t record_bytes, size_t count);
+int rt_primitive_type_count(void);
 /* Renderer::configureInstances  include/Global/Renderer.cuh:123-126, src/Global/Renderer.cu:71-121.
  * initial_xforms may be NULL (identity) — the callback, if given, is invoked with frame 0.      */
 int rt_configure_instances(rt_ctx *ctx, const rt_instance_desc *instances, size_t instance_count,

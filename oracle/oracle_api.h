@@ -34,6 +34,9 @@ typedef struct oracle_scene {
     uint64_t build_seed;                    /* seeds the (otherwise unseeded) axis RNG of the BVH build, Q13 */
     /* EXTENSION, parity unpinned (no reference counterpart): used by the port only; the compiled reference ignores it */
     const rt_dielectric *dielectrics;       size_t dielectric_count;
+    /* records of a compile-time extension primitive type (value 3 in rt_instance_desc.type; csrc/rt_prims.h): only the
+     * test builds that know the type read them (tests/ext/) */
+    const void *ext_records;                size_t ext_record_bytes, ext_count;
 } oracle_scene;
 
 typedef struct oracle_timing {

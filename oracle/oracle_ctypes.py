@@ -28,7 +28,8 @@ class OracleScene(C.Structure):
                 ("metals", C.c_void_p), ("metal_count", C.c_size_t),
                 ("instances", C.c_void_p), ("xforms", C.c_void_p), ("instance_count", C.c_size_t),
                 ("window", abi.Window), ("camera", abi.CameraInput), ("build_seed", C.c_uint64),
-                ("dielectrics", C.c_void_p), ("dielectric_count", C.c_size_t)]      # extension, parity unpinned
+                ("dielectrics", C.c_void_p), ("dielectric_count", C.c_size_t),      # extension, parity unpinned
+                ("ext_records", C.c_void_p), ("ext_record_bytes", C.c_size_t), ("ext_count", C.c_size_t)]   # test-only 4th primitive type
 
 
 class OracleTiming(C.Structure):
@@ -78,8 +79,11 @@ class Oracle:
 
 
 def _dielectrics(sc):
+    """trailing fields of oracle_scene: dielectrics, then the records of a test-only extension primitive type"""
     d = getattr(sc, "dielectrics", None)
-    return (abi.ptr(d), len(d)) if d is not None and len(d) else (None, 0)
+    e = getattr(sc, "ext_records", None)
+    return ((abi.ptr(d), len(d)) if d is not None and len(d) else (None, 0)) + \
+        ((abi.ptr(e), e.dtype.itemsize, len(e)) if e is not None and len(e) else (None, 0, 0))
 
 
 class OracleSceneHandle:

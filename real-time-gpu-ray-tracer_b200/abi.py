@@ -127,6 +127,7 @@ EXPORTS = [
     "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame", "rt_prefetch_vtk_frame",
     "rt_probe_read_bandwidth", "rt_run_vtk_animation", "rt_camera_step",
     "rt_submit_frames", "rt_wait_frame", "rt_read_frame", "rt_release_window", "rt_run_frames",
+    "rt_commit_extension_primitives", "rt_primitive_type_count",
     "rt_frame_ring_create", "rt_frame_ring_open", "rt_frame_ring_attach", "rt_frame_ring_close",
 ]
 
@@ -178,6 +179,8 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_read_frame.argtypes = [vp, u32, u32, i32, vp, sz]
     lib.rt_release_window.argtypes = [vp, u32, C.POINTER(WindowStats)]
     lib.rt_run_frames.argtypes = [vp, u64, sz, u64, u32, FRAME_SINK, vp, C.POINTER(LoopStats)]
+    lib.rt_commit_extension_primitives.argtypes = [vp, vp, sz, sz]
+    lib.rt_primitive_type_count.argtypes = []
     lib.rt_frame_ring_create.argtypes = [vp, vp]
     lib.rt_frame_ring_open.argtypes = [vp, vp]
     lib.rt_frame_ring_attach.argtypes = [vp, vp]

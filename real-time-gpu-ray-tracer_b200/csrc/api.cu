@@ -45,6 +45,7 @@ SceneD rt_scene_view(rt_ctx *ctx) {
     sc.tlas_leaf_inst = ctx->tlas.leaf_prims8();
     sc.leaf_tris8 = ctx->blas.leaf_tris8();
     sc.leaf_prims8 = ctx->blas.leaf_prims8();
+    sc.ext_prims = ctx->d_ext.get();
     return sc;
 }
 
@@ -191,6 +192,18 @@ int rt_commit_dielectrics(rt_ctx *ctx, const rt_dielectric *d, size_t count) {
     RT_API_END(ctx)
 }
 
+int rt_commit_extension_primitives(rt_ctx *ctx, const void *records, size_t record_bytes, size_t count) {
+    RT_API_BEGIN(ctx)
+    const std::string e = ctx->hs.commit_extension(records, record_bytes, count);
+    if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
+    ctx->built = false;
+    ctx->d_ext.upload(ctx->hs.ext_rec.data(), ctx->hs.ext_rec.size(), ctx->stream);
+    CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
+    RT_API_END(ctx)
+}
+
+int rt_primitive_type_count(void) { return RT_PRIMITIVE_TYPE_COUNT; }
+
 int rt_configure_instances(rt_ctx *ctx, const rt_instance_desc *instances, size_t instance_count, const rt_instance_xform *initial_xforms,
                            rt_update_cb update, void *user) {
     RT_API_BEGIN(ctx)
@@ -223,7 +236,7 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     const std::string e = hs.plan_blas();
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
     const size_t n_inst = hs.inst_desc.size();
-    const GeometryD geo{ctx->d_tri_verts.get(), ctx->d_spheres.get(), ctx->d_quads.get()};
+    const GeometryD geo{ctx->d_tri_verts.get(), ctx->d_spheres.get(), ctx->d_quads.get(), ctx->d_ext.get()};
     const size_t n_prims = hs.seg_offset.back();
     ctx->blas.emit_bvh2 = ctx->tlas.emit_bvh2 = (ctx->flags & (RT_FLAG_TRAVERSE_BVH2 | RT_FLAG_KEEP_LBVH)) != 0;
     // rotated subtrees no longer cover one contiguous Morton range, which multi-primitive leaves (a tuning experiment) rely on

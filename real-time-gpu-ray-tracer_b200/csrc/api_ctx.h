@@ -55,6 +55,7 @@ struct rt_ctx {
     DeviceBuffer<SphereD> d_spheres;
     DeviceBuffer<QuadD> d_quads;
     DeviceBuffer<float4> d_roughs, d_metals, d_dielectrics;
+    DeviceBuffer<unsigned char> d_ext;       // records of the extension primitive type (rt_prims.h), if the build has one
     DeviceBuffer<InstanceD> d_instances;
     DeviceBuffer<InstanceXformIn> d_xform_in;
     DeviceBuffer<float4> d_wcentroid;

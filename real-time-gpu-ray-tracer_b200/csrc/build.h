@@ -4,6 +4,7 @@
 
 #include "device_util.h"
 #include "rt_build_core.h"
+#include "rt_prims.h"
 #include "rt_wide_core.h"
 
 #include <algorithm>
@@ -18,13 +19,6 @@ public:
               cudaStream_t stream, int sm_count, uint32_t &launches);
 private:
     DeviceBuffer<uint32_t> scratch_;
-};
-
-// Geometry sources of a BLAS batch (device pointers, original order)
-struct GeometryD {
-    const float *tri_verts;     // 9 floats per triangle
-    const SphereD *spheres;
-    const QuadD *quads;
 };
 
 // One batched LBVH build: all segments (BLASes) of the batch share one sort and one Karras pass; segment s

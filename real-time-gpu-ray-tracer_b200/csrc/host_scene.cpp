@@ -92,6 +92,37 @@ std::string HostScene::commit_geometry(const rt_sphere *s, size_t ns, const rt_p
     return "";
 }
 
+size_t HostScene::prim_count_of(uint32_t type) const {
+    if (type == RT_SPHERE) return spheres.size();
+    if (type == RT_PARALLELOGRAM) return quads.size();
+    if (type == RT_TRIANGLE) return n_tris;
+#if defined(RT_EXT_PRIMITIVE)
+    if (type == 3u) return n_ext;
+#endif
+    return 0;
+}
+
+std::string HostScene::commit_extension(const void *records, size_t record_bytes, size_t count) {
+#if defined(RT_EXT_PRIMITIVE)
+    if (record_bytes != sizeof(ExtPrimD)) return std::string("rt_commit_extension_primitives: a ") + RT_EXT_PRIMITIVE_NAME + " record is " + std::to_string(sizeof(ExtPrimD)) + " bytes";
+    if (count && !records) return "rt_commit_extension_primitives: null array with non-zero count";
+    if (count > RT_REF_POS_MASK) return "rt_commit_extension_primitives: more than 2^29 primitives of one type";
+    const ExtPrimD *r = static_cast<const ExtPrimD *>(records);
+    for (size_t i = 0; i < count; i++) {
+        uint32_t mt, mi;
+        PrimOps<3>::material(r[i], mt, mi);
+        if (mt > RT_DIELECTRIC) return "rt_commit_extension_primitives: unknown material type";
+        note_material(mt, mi);
+    }
+    ext_rec.assign(reinterpret_cast<const unsigned char *>(records), reinterpret_cast<const unsigned char *>(records) + count * sizeof(ExtPrimD));
+    n_ext = count;
+    return "";
+#else
+    (void) records; (void) record_bytes; (void) count;
+    return "rt_commit_extension_primitives: this build of librtb200 has no extension primitive type (compile with -DRT_EXT_PRIMITIVE, csrc/rt_prims.h)";
+#endif
+}
+
 std::string HostScene::commit_triangle_tail(size_t n_head, const rt_triangle *t, size_t nt) {
     if (nt && !t) return "commit_triangle_tail: null array with non-zero count";
     if (n_head + nt > RT_REF_POS_MASK) return "rt_commit_geometry: more than 2^29 primitives of one type";
@@ -156,8 +187,8 @@ std::string HostScene::configure_instances(const rt_instance_desc *d, size_t n, 
     if (n > RT_REF_POS_MASK) return "rt_configure_instances: too many instances";
     for (size_t i = 0; i < n; i++) {
         const uint64_t cnt = d[i].prim_count <= 1 ? 1 : d[i].prim_count;
-        const uint64_t limit = d[i].type == RT_SPHERE ? spheres.size() : d[i].type == RT_PARALLELOGRAM ? quads.size() : d[i].type == RT_TRIANGLE ? n_tris : 0;
-        if (d[i].type > RT_TRIANGLE || d[i].first_prim + cnt > limit) return "rt_configure_instances: primitive range out of bounds";
+        const uint64_t limit = prim_count_of(d[i].type);
+        if (d[i].type >= (uint32_t) RT_PRIMITIVE_TYPE_COUNT || d[i].first_prim + cnt > limit) return "rt_configure_instances: primitive range out of bounds";
     }
     inst_desc.assign(d, d + n);
     xforms.resize(n);
@@ -206,6 +237,13 @@ std::string HostScene::plan_blas() {
                 const f3 h = (V(p.u) + V(p.v)) * 0.5f;
                 return ref_box_from_points(V(p.q) + h, V(p.q) - h);
             }
+#if defined(RT_EXT_PRIMITIVE)
+            if (d.type == 3u) {
+                f3 lo, hi;
+                PrimOps<3>::ref_extent(reinterpret_cast<const ExtPrimD *>(ext_rec.data())[k], lo, hi);
+                return ref_box_from_points(lo, hi);
+            }
+#endif
             const float *v = &tri_verts[k * 9];                                   // Triangle.cu:46-62
             const f3 lo = mk3(std::min({v[0], v[3], v[6]}), std::min({v[1], v[4], v[7]}), std::min({v[2], v[5], v[8]}));
             const f3 hi = mk3(std::max({v[0], v[3], v[6]}), std::max({v[1], v[4], v[7]}), std::max({v[2], v[5], v[8]}));
@@ -219,6 +257,10 @@ std::string HostScene::plan_blas() {
             else if (d.type == RT_PARALLELOGRAM) {
                 const rt_parallelogram &p = quads[d.first_prim];
                 centroid = (V(p.q) + V(p.u) * 0.5f) + V(p.v) * 0.5f;              // Parallelogram.cuh:45-47
+#if defined(RT_EXT_PRIMITIVE)
+            } else if (d.type == 3u) {
+                centroid = PrimOps<3>::centroid(reinterpret_cast<const ExtPrimD *>(ext_rec.data())[d.first_prim]);
+#endif
             } else {
                 const float *v = &tri_verts[d.first_prim * 9];                    // Triangle.cuh:52-60
                 float cc[3];
@@ -306,7 +348,11 @@ size_t HostScene::prim_bytes() const {
     size_t b = 0;
     for (size_t s = 0; s < seg_type.size(); s++) {
         const size_t cnt = seg_offset[s + 1] - seg_offset[s];
-        b += cnt * (seg_type[s] == RT_TRIANGLE ? sizeof(TriIsect) : seg_type[s] == RT_SPHERE ? sizeof(SphereD) : sizeof(QuadD));
+        size_t rec = seg_type[s] == RT_TRIANGLE ? sizeof(TriIsect) : seg_type[s] == RT_SPHERE ? sizeof(SphereD) : sizeof(QuadD);
+#if defined(RT_EXT_PRIMITIVE)
+        if (seg_type[s] == 3u) rec = sizeof(ExtPrimD);
+#endif
+        b += cnt * rec;
     }
     return b;
 }

@@ -5,7 +5,7 @@
 #pragma once
 
 #include "../../include/rtb200.h"
-#include "rt_build_core.h"
+#include "rt_prims.h"
 
 #include <string>
 #include <vector>
@@ -24,6 +24,11 @@ struct HostScene {
     std::vector<QuadD> quad_rec;
     std::vector<TriShade> tri_shade;
     std::vector<float4> roughs, metals, dielectrics;
+    // records of the compile-time extension primitive type (rt_prims.h RT_EXT_PRIMITIVE), raw ExtPrimD bytes; empty otherwise
+    std::vector<unsigned char> ext_rec;
+    size_t n_ext = 0;
+    std::string commit_extension(const void *records, size_t record_bytes, size_t count);
+    size_t prim_count_of(uint32_t type) const;    // committed primitives of a type (0 for an unknown type)
     // highest material index the committed geometry uses, per rt_material_type (-1: type unused); checked against the
     // committed material counts before a frame is rendered (check_materials)
     long long max_mat_index[3] = {-1, -1, -1};

@@ -51,17 +51,7 @@ __global__ void __launch_bounds__(BT) prim_bounds_kernel(GeometryD geo, const ui
         seg = find_segment(seg_offset, n_segs, (uint32_t) j);
         const uint32_t type = __ldg(&seg_type[seg]);
         const uint32_t prim = __ldg(&seg_first[seg]) + ((uint32_t) j - __ldg(&seg_offset[seg]));
-        if (type == 2u) {
-            float v9[9];
-            const float *src = geo.tri_verts + (size_t) prim * 9;
-#pragma unroll
-            for (int k = 0; k < 9; k++) v9[k] = __ldg(src + k);
-            box = tri_aabb(v9);
-        } else if (type == 0u) {
-            box = sphere_aabb(geo.spheres[prim]);
-        } else {
-            box = quad_aabb(geo.quads[prim]);
-        }
+        box = prim_bounds(geo, type, prim);                      // the primitive table (rt_prims.h)
         box = aabb_pad(box);
         prim_lo[j] = make_float4(box.lo.x, box.lo.y, box.lo.z, 0.0f);
         prim_hi[j] = make_float4(box.hi.x, box.hi.y, box.hi.z, 0.0f);

@@ -152,7 +152,7 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     static const int leaf_max_env = getenv("RTB200_LEAF_MAX") ? atoi(getenv("RTB200_LEAF_MAX")) : 0;   // tuning experiments only
     const int leaf_max = leaf_mode == 1 ? 1 : (leaf_max_env >= 1 && leaf_max_env <= 3 ? leaf_max_env : RT_WIDE_LEAF_MAX);
     collapse_kernel<<<blocks, CT, 0, stream>>>(view, leaf_max, capacity, queue_.get(), wide_counters_.get(), nodes8_.get(), leaf_pos8_.get());
-    const GeometryD none{nullptr, nullptr, nullptr};
+    const GeometryD none{nullptr, nullptr, nullptr, nullptr};
     emit_leaves8_kernel<<<div_up(n, 256), 256, 0, stream>>>(geo ? *geo : none, leaf_pos8_.get(), vals_, seg_offset_.get(), seg_type_.get(),
                                                            seg_first_.get(), n_segs, n, leaf_mode, leaf_prims8_.get(), leaf_tris8_.get());
     launches += 3;

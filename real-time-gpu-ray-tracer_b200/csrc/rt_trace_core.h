@@ -3,15 +3,8 @@
 // kernels and, compiled by g++, inside the CPU emulation used by the `not gpu` tests.
 #pragma once
 
-#include "rt_intersect.h"
+#include "rt_prims.h"
 #include "rt_rng.h"
-
-struct HitD {
-    float t, u, v;
-    float tc;       // culling / acceptance bound: == t, except after a bug-compatible parallelogram hit (rt_intersect.h quad_hit_t)
-    int inst;       // instance index, -1 = miss
-    int leaf;       // leaf ref of the winning primitive (type + leaf-order position)
-};
 
 struct RaySlabs { f3 idir, ood; };
 
@@ -56,34 +49,9 @@ RT_HD BvhNode2 load_node2(const BvhNode2 *nodes, int idx) {
     return n;
 }
 
-// One leaf primitive against the LOCAL ray; acceptance rule of BLAS::hit's leaf loop
-// (reference src/AS/BLAS.cu:150-175): in_range(t, tmin, best) is ε-closed, an accepted candidate becomes best.
+// One leaf primitive (binary-LBVH leaf order) against the LOCAL ray: dispatched through the primitive table (rt_prims.h)
 RT_HD void leaf_test(const SceneD &sc, int ref, const RayD &lray, float tmin, int inst, HitD &best) {
-    const uint32_t type = ref_type(ref), pos = ref_pos(ref);
-    if (type == 2u) {
-#if defined(__CUDA_ARCH__)
-        const float4 *p = reinterpret_cast<const float4 *>(sc.leaf_tris + pos);
-        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-#else
-        const float4 a = sc.leaf_tris[pos].v0_id, b = sc.leaf_tris[pos].e1, c = sc.leaf_tris[pos].e2;
-#endif
-        float t, u, v;
-        if (tri_hit_t(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), lray, tmin, best.tc, t, u, v)) {
-            best.t = t; best.tc = t; best.u = u; best.v = v; best.inst = inst; best.leaf = ref;
-        }
-    } else if (type == 0u) {
-        const SphereD s = sc.spheres[sc.leaf_prims[pos]];
-        float t;
-        if (sphere_hit_t(mk3(s.c_r.x, s.c_r.y, s.c_r.z), s.c_r.w, lray, tmin, best.tc, t)) {
-            best.t = t; best.tc = t; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = ref;
-        }
-    } else {
-        const QuadD q = sc.quads[sc.leaf_prims[pos]];
-        float t, tc;
-        if (quad_hit_t(q, lray, tmin, best.tc, t, tc)) {
-            best.t = t; best.tc = tc; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = ref;
-        }
-    }
+    prim_hit<false>(sc, ref_type(ref), ref_pos(ref), lray, tmin, inst, best);
 }
 
 RT_HD RayD to_local(const InstanceD &ins, const RayD &w) {
@@ -179,8 +147,6 @@ RT_HD RayD primary_ray(const CameraD &cam, uint32_t x, uint32_t y, uint32_t si, 
     return r;
 }
 
-RT_HD f3 ld3(const float4 &a) { return mk3(a.x, a.y, a.z); }
-
 // Hit record + scatter: Prim::hit's record fields (reference src/Geometry/*.cu), Instance::hit's back-transform
 // (src/AS/Instance.cu:41-45), Rough/Metal::scatter (include/Material/*.cuh) and rayColor's bookkeeping
 // (src/Global/Kernel.cu:76-98).  Returns false when the path ends; `throughput` is rayColor's `result`.
@@ -198,25 +164,7 @@ RT_HD bool shade_scatter(const SceneD &sc, const CameraD &cam, RayD &ray, const 
     f3 ln;
     uint32_t mt, mi;
     bool front;                 // Prim::hit's hitFrontFace: the outward normal faces the (local) ray
-    if (type == 2u) {
-        const TriShade ts = sc.tri_shade[prim];
-        const f3 n = unit3((ld3(ts.n0_mt) * (1.0f - hit.u - hit.v) + ld3(ts.n1_mi) * hit.u) + ld3(ts.n2) * hit.v);
-        front = dot3(lray.d, n) < 0.0f;
-        ln = front ? n : -n;
-        mt = f2u(ts.n0_mt.w); mi = f2u(ts.n1_mi.w);
-    } else if (type == 0u) {
-        const SphereD s = sc.spheres[prim];
-        const f3 outward = unit3(lp - ld3(s.c_r));
-        front = dot3(lray.d, outward) < 0.0f;
-        ln = front ? outward : -outward;
-        mt = s.mat_type; mi = s.mat_index;
-    } else {
-        const QuadD q = sc.quads[prim];
-        const f3 n = ld3(q.n_flag);
-        front = dot3(lray.d, n) < 0.0;
-        ln = front ? n : -n;
-        mt = q.mat_type; mi = q.mat_index;
-    }
+    prim_surface(sc, type, prim, lray, lp, hit, ln, front, mt, mi);       // the primitive table (rt_prims.h)
     const f3 wp = xf_point(ins.fwd, lp);
     const f3 wn = unit3(xf_normal(ins.inv, ln));
     // Rough::scatter and Metal::scatter (fuzz > 0) both draw ONE random unit vector; it is drawn at a single place so

@@ -114,6 +114,7 @@ struct SceneD {
     const uint32_t *tlas_leaf_inst;  // TLAS leaf order -> instance index
     const TriIsect *leaf_tris8;      // wide leaf order
     const uint32_t *leaf_prims8;     // wide leaf order: original primitive index (all types)
+    const void *ext_prims;           // records of the compile-time extension primitive type (rt_prims.h), original order; else null
 };
 
 // XORWOW state (cuRAND curandStateXORWOW_t without the Box-Muller fields): 24 B per pixel

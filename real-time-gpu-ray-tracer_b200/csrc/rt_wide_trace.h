@@ -133,32 +133,9 @@ RT_HD void load_instance_wide(const SceneD &sc, int inst, float *inv, int &root8
 #endif
 }
 
-// One leaf primitive (wide leaf order) against the LOCAL ray — acceptance rule as leaf_test in rt_trace_core.h
+// One leaf primitive (wide leaf order) against the LOCAL ray: dispatched through the primitive table (rt_prims.h)
 RT_HD void leaf_test8(const SceneD &sc, uint32_t type, uint32_t pos, const RayD &lray, float tmin, int inst, HitD &best) {
-    if (type == 2u) {
-#if defined(__CUDA_ARCH__)
-        const float4 *p = reinterpret_cast<const float4 *>(sc.leaf_tris8 + pos);
-        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-#else
-        const float4 a = sc.leaf_tris8[pos].v0_id, b = sc.leaf_tris8[pos].e1, c = sc.leaf_tris8[pos].e2;
-#endif
-        float t, u, v;
-        if (tri_hit_t(mk3(a.x, a.y, a.z), mk3(b.x, b.y, b.z), mk3(c.x, c.y, c.z), lray, tmin, best.tc, t, u, v)) {
-            best.t = t; best.tc = t; best.u = u; best.v = v; best.inst = inst; best.leaf = make_leaf_ref(2u, pos);
-        }
-    } else if (type == 0u) {
-        const SphereD s = sc.spheres[sc.leaf_prims8[pos]];
-        float t;
-        if (sphere_hit_t(mk3(s.c_r.x, s.c_r.y, s.c_r.z), s.c_r.w, lray, tmin, best.tc, t)) {
-            best.t = t; best.tc = t; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = make_leaf_ref(0u, pos);
-        }
-    } else {
-        const QuadD q = sc.quads[sc.leaf_prims8[pos]];
-        float t, tc;
-        if (quad_hit_t(q, lray, tmin, best.tc, t, tc)) {
-            best.t = t; best.tc = tc; best.u = 0.0f; best.v = 0.0f; best.inst = inst; best.leaf = make_leaf_ref(1u, pos);
-        }
-    }
+    prim_hit<true>(sc, type, pos, lray, tmin, inst, best);
 }
 
 // Stack of 8-byte groups; `stride` lets the CUDA kernels interleave the stacks of a block in shared memory.

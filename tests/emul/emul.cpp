@@ -260,7 +260,8 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     hs.flags = flags;
     if (!hs.commit_geometry(s->spheres, s->sphere_count, s->parallelograms, s->parallelogram_count, s->triangles, s->triangle_count).empty() ||
         !hs.commit_materials(s->roughs, s->rough_count, s->metals, s->metal_count).empty() ||
-        !hs.commit_dielectrics(s->dielectrics, s->dielectric_count).empty() || !hs.check_materials().empty() ||
+        !hs.commit_dielectrics(s->dielectrics, s->dielectric_count).empty() ||
+        (s->ext_count && !hs.commit_extension(s->ext_records, s->ext_record_bytes, s->ext_count).empty()) || !hs.check_materials().empty() ||
         !hs.configure_instances(s->instances, s->instance_count, s->xforms).empty() || !hs.plan_blas().empty() ||
         !hs.configure_camera(s->window, s->camera).empty()) { delete e; return nullptr; }
 
@@ -274,7 +275,8 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     for (int j = 0; j < n; j++) {
         const int seg = find_segment(hs.seg_offset, (uint32_t) j);
         const uint32_t prim = hs.seg_first[seg] + ((uint32_t) j - hs.seg_offset[seg]);
-        Aabb box = hs.seg_type[seg] == 2u ? tri_aabb(&hs.tri_verts[(size_t) prim * 9]) : hs.seg_type[seg] == 0u ? sphere_aabb(hs.sphere_rec[prim]) : quad_aabb(hs.quad_rec[prim]);
+        const GeometryD geo{hs.tri_verts.data(), hs.sphere_rec.data(), hs.quad_rec.data(), hs.ext_rec.data()};
+        Aabb box = prim_bounds(geo, hs.seg_type[seg], prim);             // the primitive table (rt_prims.h), as prim_bounds_kernel
         box = aabb_pad(box);
         b.prim_box[j] = box;
         seg_bounds[seg] = aabb_union(seg_bounds[seg], box);
@@ -350,6 +352,7 @@ void *emul_create(const oracle_scene *s, uint32_t flags) {
     sc.tlas_root_ref = ni > 1 ? 0 : make_leaf_ref(0u, 0u);
     sc.tlas_nodes8 = t.nodes8.data(); sc.blas_nodes8 = b.nodes8.data(); sc.tlas_leaf_inst = e->tlas_leaf_inst.data();
     sc.leaf_tris8 = e->leaf_tris8.data(); sc.leaf_prims8 = e->leaf_prims8.data();
+    sc.ext_prims = hs.ext_rec.data();
     e->wide = !(flags & 0x80000000u);     // test-only switch: traverse the binary LBVH instead of the wide BVH
     return e;
 }

@@ -41,11 +41,12 @@ class Oracle:
     """One of the two checkers: kind = 'port' (restatement) or 'ref' (reference sources compiled as C++)."""
 
     def __init__(self, kind: str = "port"):
-        path = PORT_PATH if kind == "port" else REF_PATH
+        # "port_disc": the port compiled with the test-only fourth primitive type of tests/ext/ (make -C oracle port_disc)
+        path = PORT_PATH if kind == "port" else PORT_PATH.replace("liboracle_port.so", "liboracle_port_disc.so") if kind == "port_disc" else REF_PATH
         if not os.path.exists(path):
             raise FileNotFoundError(f"{path} not built (make -C oracle {kind})")
-        self.kind = kind
-        self.prefix = "port_" if kind == "port" else "ref_"
+        self.kind = "port" if kind == "port_disc" else kind
+        self.prefix = "ref_" if kind == "ref" else "port_"
         self.lib = C.CDLL(path)
         vp, sz, u64, i32 = C.c_void_p, C.c_size_t, C.c_uint64, C.c_int
         self._fn("create", [C.POINTER(OracleScene), C.POINTER(OracleTiming)], vp)

@@ -233,6 +233,7 @@ struct Hit {                                                  // include/Basic/B
 struct SphereP { V3 c; float r; uint32_t mt, mi; };
 struct QuadP { V3 q, u, v; float area; V3 n; float d; uint32_t mt, mi; };
 struct TriP { V3 v[3], n[3], e1, e2; uint32_t mt, mi; };
+struct DiscP { V3 c; float r; V3 n; float d; uint32_t mt, mi; };      // test-only fourth type (ORACLE_EXT_DISC)
 
 QuadP makeQuad(const rt_parallelogram &g) {                   // include/Geometry/Parallelogram.cuh:26-39
     QuadP p{{g.q.x, g.q.y, g.q.z}, {g.u.x, g.u.y, g.u.z}, {g.v.x, g.v.y, g.v.z}, 0, {}, 0, g.material_type, g.material_index};
@@ -360,6 +361,7 @@ struct Scene {
     std::vector<SphereP> spheres;
     std::vector<QuadP> quads;
     std::vector<TriP> tris;
+    std::vector<DiscP> discs;
     std::vector<rt_rough> roughs;
     std::vector<rt_metal> metals;
     std::vector<rt_dielectric> dielectrics;                   // extension, no reference counterpart
@@ -424,8 +426,39 @@ Bvh buildMedianSplit(std::vector<BuildItem> &items, size_t leafSize, std::mt1993
     return out;
 }
 
+#ifdef ORACLE_EXT_DISC
+// TEST-ONLY fourth primitive type (tests/ext/): a disc, written here independently of the product's PrimOps<3> — plane hit
+// as Parallelogram::hit (src/Geometry/Parallelogram.cu:4-46), then |x - c|^2 <= r^2.  Record layout = the product's ExtPrimD.
+struct DiscRec { float c[3], r, n[3], d; uint32_t mt, mi, p0, p1; };
+bool discHit(const DiscP &q, const RayF &ray, const Rng &range, Hit &rec) {
+    const float nDotD = dot(q.n, ray.d);
+    if (nearZero(nDotD)) return false;
+    const float nDotP = dot(q.n, ray.o);
+    const float t = (q.d - nDotP) / nDotD;
+    if (!inRange(range, t)) return false;
+    const V3 x = rayAt(ray, t);
+    const V3 pv = sub(x, q.c);
+    if (len2(pv) > q.r * q.r) return false;
+    rec.t = t;
+    rec.point = x;
+    rec.matType = q.mt; rec.matIndex = q.mi;
+    rec.front = dot(ray.d, q.n) < 0.0f;
+    rec.primFront = rec.front;
+    rec.normal = rec.front ? q.n : neg(q.n);
+    return true;
+}
+Box discBox(const DiscP &q) {
+    const float ex = q.r * std::sqrt(std::max(0.0f, 1.0f - q.n.x * q.n.x)), ey = q.r * std::sqrt(std::max(0.0f, 1.0f - q.n.y * q.n.y)),
+                ez = q.r * std::sqrt(std::max(0.0f, 1.0f - q.n.z * q.n.z));
+    return boxFromPoints({q.c.x - ex, q.c.y - ey, q.c.z - ez}, {q.c.x + ex, q.c.y + ey, q.c.z + ez});
+}
+#endif
+
 bool primHit(const Scene &s, const PrimRef &ref, const RayF &ray, const Rng &range, Hit &rec) {
     switch (ref.type) {
+#ifdef ORACLE_EXT_DISC
+        case 3u: return discHit(s.discs[ref.index], ray, range, rec);
+#endif
         case RT_SPHERE: return sphereHit(s.spheres[ref.index], ray, range, rec);
         case RT_PARALLELOGRAM: return quadHit(s.quads[ref.index], ray, range, rec);
         case RT_TRIANGLE: return triHit(s.tris[ref.index], ray, range, rec);
@@ -667,10 +700,22 @@ void *port_create(const oracle_scene *sc, oracle_timing *timing) {
     s->metals.assign(sc->metals, sc->metals + sc->metal_count);
     if (sc->dielectric_count) s->dielectrics.assign(sc->dielectrics, sc->dielectrics + sc->dielectric_count);
 
+#ifdef ORACLE_EXT_DISC
+    for (size_t i = 0; i < sc->ext_count && sc->ext_record_bytes == sizeof(DiscRec); i++) {
+        const DiscRec &r = static_cast<const DiscRec *>(sc->ext_records)[i];
+        s->discs.push_back({{r.c[0], r.c[1], r.c[2]}, r.r, {r.n[0], r.n[1], r.n[2]}, r.d, r.mt, r.mi});
+    }
+#endif
     auto primBox = [&](uint32_t type, size_t i) {
+#ifdef ORACLE_EXT_DISC
+        if (type == 3u) return discBox(s->discs[i]);
+#endif
         return type == RT_SPHERE ? sphereBox(s->spheres[i]) : type == RT_PARALLELOGRAM ? quadBox(s->quads[i]) : triBox(s->tris[i]);
     };
     auto primCentroid = [&](uint32_t type, size_t i) {
+#ifdef ORACLE_EXT_DISC
+        if (type == 3u) return s->discs[i].c;
+#endif
         return type == RT_SPHERE ? s->spheres[i].c : type == RT_PARALLELOGRAM ? quadCentroid(s->quads[i]) : triCentroid(s->tris[i]);
     };
 

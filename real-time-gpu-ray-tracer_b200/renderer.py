@@ -30,8 +30,9 @@ def cameraStep(camera: abi.CameraInput, dx: int = 0, dy: int = 0, keys: int = 0,
 
 
 class Renderer:
-    def __init__(self, device: int = 0, flags: int = 0):
-        self.lib = abi.load_library()
+    def __init__(self, device: int = 0, flags: int = 0, lib_path: str | None = None):
+        # lib_path: another in-tree build of the same sources (csrc/Makefile VARIANT=...), e.g. the test variant with a fourth primitive type
+        self.lib = abi.load_library(lib_path)
         self.ctx = C.c_void_p()
         rc = self.lib.rt_create(C.byref(self.ctx), device, flags)
         if rc != 0:
@@ -49,6 +50,10 @@ class Renderer:
         n = lambda a: 0 if a is None else len(a)
         self._check(self.lib.rt_commit_geometry(self.ctx, abi.ptr(spheres), n(spheres), abi.ptr(parallelograms), n(parallelograms),
                                                 abi.ptr(triangles), n(triangles)))
+
+    def commitExtensionPrimitives(self, records: np.ndarray):
+        """Records of the build's compile-time extension primitive type (csrc/rt_prims.h); RtError(-2) in the standard build."""
+        self._check(self.lib.rt_commit_extension_primitives(self.ctx, abi.ptr(records), records.dtype.itemsize, len(records)))
 
     # -- Renderer::commitMaterialData ------------------------------------------------------------
     def commitMaterialData(self, roughs=None, metals=None, dielectrics=None):
@@ -89,6 +94,8 @@ class Renderer:
     def commitScene(self, sc, update=None):
         """Convenience: the whole start-up sequence of src/Global/Main.cu:111-123 for a scenes.Scene."""
         self.commitGeometryData(sc.spheres, sc.parallelograms, sc.triangles)
+        if getattr(sc, "ext_records", None) is not None and len(sc.ext_records):
+            self.commitExtensionPrimitives(sc.ext_records)
         self.commitMaterialData(sc.roughs, sc.metals, getattr(sc, "dielectrics", None))
         self.configureInstances(sc.instances, sc.xforms, update)
         st = self.buildAccelerationStructure()

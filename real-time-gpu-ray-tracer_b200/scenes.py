@@ -24,6 +24,7 @@ class Scene:
     roughs: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.rough_dt))
     metals: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.metal_dt))
     dielectrics: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.dielectric_dt))   # extension, parity unpinned
+    ext_records: np.ndarray | None = None      # records of a build's extension primitive type (csrc/rt_prims.h); tests only
     instances: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.instance_desc_dt))
     xforms: np.ndarray = field(default_factory=lambda: np.zeros(0, abi.instance_xform_dt))
     width: int = 640

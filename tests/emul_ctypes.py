@@ -20,10 +20,12 @@ abi = oc.abi
 LIB = os.path.join(HERE, "emul", "libemul.so")
 
 
-def load():
-    if not os.path.exists(LIB):
-        subprocess.check_call(["make", "-C", os.path.join(HERE, "emul")])
-    lib = C.CDLL(LIB)
+def load(variant: str = ""):
+    """variant "disc": the twin with the test-only fourth primitive type of tests/ext/ compiled in"""
+    path = LIB.replace("libemul.so", f"libemul_{variant}.so") if variant else LIB
+    if not os.path.exists(path):
+        subprocess.check_call(["make", "-C", os.path.join(HERE, "emul")] + ([variant] if variant else []))
+    lib = C.CDLL(path)
     vp, u64, i32, sz = C.c_void_p, C.c_uint64, C.c_int, C.c_size_t
     lib.emul_create.argtypes = [C.POINTER(oc.OracleScene), C.c_uint32]
     lib.emul_create.restype = vp
@@ -165,8 +167,8 @@ def vtk_frame(path: str, mode: int):
 
 
 class Emul:
-    def __init__(self, sc, flags: int = 0):
-        self.lib = load()
+    def __init__(self, sc, flags: int = 0, variant: str = ""):
+        self.lib = load(variant)
         self.sc = sc
         s = oc.OracleScene(abi.ptr(sc.spheres), len(sc.spheres), abi.ptr(sc.parallelograms), len(sc.parallelograms),
                            abi.ptr(sc.triangles), len(sc.triangles), abi.ptr(sc.roughs), len(sc.roughs),

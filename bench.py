@@ -533,7 +533,9 @@ def measure_pipelined(pkg, r, sc, args, torch, dist, rank, world, local, tile_ro
         sync_ms.append(out.render_ms)
         stage = {"tlas_rebuild": out.tlas_ms, "rng_init": out.rng_ms, "trace": out.trace_ms}
     sync_rays = out.rays
-    r.runFrames(0, warm_frames or min(2 * fpw, max(fpw, args.warmup)), SEED, fpw, None)
+    # both windows once: each has its own stream, buffers and tile-cost history (a launch hands the dear tiles out first,
+    # from the costs the window's previous launch measured), and the first use of a window allocates them
+    r.runFrames(0, warm_frames or 2 * fpw, SEED, fpw, None)
     sampler = ClockSampler(local)
     barrier()
     if rank == 0:
@@ -550,7 +552,7 @@ def measure_pipelined(pkg, r, sc, args, torch, dist, rank, world, local, tile_ro
         seen[0] += 1
         return 0
     r.setInstanceTransforms(xf)
-    r.runFrames(0, min(fpw, args.steps), SEED, fpw, sink)        # untimed: first use of the read-back path
+    r.runFrames(0, min(2 * fpw, max(fpw, args.steps)), SEED, fpw, sink)        # untimed: first use of the read-back path
     barrier()
     seen[0] = 0
     t0 = time.perf_counter()
@@ -769,7 +771,7 @@ def config4_line(pkg, args, torch, dist, rank, world, local, tile_rows):
             why = exchange_ring(r, dist, torch, rank, world, local)
             if why is not None:
                 return {"unavailable": f"frame ring: {why}"}
-        m = measure_pipelined(pkg, r, sc, a, torch, dist, rank, world, local, tile_rows, 2, sync_frames=1, warm_frames=2)
+        m = measure_pipelined(pkg, r, sc, a, torch, dist, rank, world, local, tile_rows, 1, sync_frames=1, warm_frames=2)
     finally:
         r.cleanup()
     return {"metric": f"Mrays/s ({cfg['workload'].split(',')[0]})", "value": m["value"], "unit": "Mrays/s", "ms_per_step": m["ms_per_step"],

@@ -226,6 +226,7 @@ int rt_set_instance_xforms(rt_ctx *ctx, const rt_instance_xform *xforms, size_t 
     RT_API_BEGIN(ctx)
     if (!xforms || (instance_count != ctx->hs.xforms.size() && instance_count != ctx->n_user_inst)) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_instance_xforms: count mismatch");
     std::copy(xforms, xforms + instance_count, ctx->hs.xforms.begin());
+    ctx->tlas_fresh = false;
     RT_API_END(ctx)
 }
 
@@ -276,6 +277,7 @@ int rt_build_acceleration_structure(rt_ctx *ctx) {
     st.prim_bytes = hs.prim_bytes();
     st.kernel_launches = ctx->blas.launches + ctx->tlas.launches + 2;
     ctx->built = true;
+    ctx->tlas_fresh = true;
     RT_API_END(ctx)
 }
 
@@ -322,7 +324,9 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
     cudaStream_t s = ctx->stream;
     if (ctx->update_cb) ctx->update_cb(ctx->hs.xforms.data(), ctx->n_user_inst, (size_t) frame_index, ctx->update_user);
     CUDA_CHECK(cudaEventRecord(ctx->ev[0], s));
-    update_instances_and_tlas(ctx);
+    const bool reuse_tlas = ctx->tlas_fresh && !ctx->update_cb;        // built a moment ago for these very transforms (api_ctx.h)
+    ctx->tlas_fresh = false;
+    if (!reuse_tlas) update_instances_and_tlas(ctx);
     CUDA_CHECK(cudaEventRecord(ctx->ev[1], s));
 
     const SceneD sc = rt_scene_view(ctx);
@@ -382,7 +386,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
         CUDA_CHECK(cudaEventElapsedTime(&out->tlas_ms, ctx->ev[0], ctx->ev[1]));
         CUDA_CHECK(cudaEventElapsedTime(&out->rng_ms, ctx->ev[1], ctx->ev[2]));
         CUDA_CHECK(cudaEventElapsedTime(&out->trace_ms, ctx->ev[2], ctx->ev[3]));
-        out->kernel_launches = ctx->tlas.launches + 3 /*instance update: bounds init, matrices, world boxes*/ + 1 /*rng*/ + (mega ? 1 : ws.launches);
+        out->kernel_launches = (reuse_tlas ? 0 : ctx->tlas.launches + 3 /*instance update: bounds init, matrices, world boxes*/) + 1 /*rng*/ + (mega ? 1 : ws.launches);
     }
     RT_API_END(ctx)
 }

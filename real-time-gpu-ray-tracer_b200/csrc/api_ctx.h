@@ -85,6 +85,10 @@ struct rt_ctx {
     int path_mode = 1;              // 1: persistent path kernel (default), 0: wave loop; RT_FLAG_WAVEFRONT / RTB200_MODE select
     bool geometry_committed = false, materials_committed = false, instances_configured = false, built = false, camera_set = false;
     rt_build_stats build_stats{};
+    // rt_build_acceleration_structure ends with the instance update + TLAS build for the current transform arguments.  The
+    // FIRST frame rendered after it (the animation renders exactly one frame per rebuild) takes that TLAS instead of
+    // building the identical one again; any later frame, a changed transform or an update callback rebuilds as always.
+    bool tlas_fresh = false;
 
     // camera / frame
     uint32_t shard_rank = 0, shard_world = 1, tile_rows = 8, local_rows = 0;

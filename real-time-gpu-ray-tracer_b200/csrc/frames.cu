@@ -200,6 +200,7 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
         CUDA_CHECK(cudaEventRecord(w.ev_fork, ctx->stream));
         CUDA_CHECK(cudaStreamWaitEvent(s, w.ev_fork, 0));
     }
+    ctx->tlas_fresh = false;
     w.ticket++;
     if (w.ticket == 0u) w.ticket = 1u;
     w.n_frames = n_frames;

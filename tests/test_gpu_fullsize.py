@@ -40,9 +40,20 @@ def check_lines_against_oracle(g, port, sc, lines, ids=True, rgba8=True):
     for y in lines:
         img, rad, _ = h.render(SEED, y, y + 1, rgba8=rgba8)
         if not ids:                                     # radiance / bytes only (the primary AOV is the FIRST sample's)
-            assert np.array_equal(g["radiance"][y], rad[y]), f"{sc.name} line {y}: radiance differs from the oracle"
+            # bit-exact per pixel against the oracle; a pixel with an epsilon-tie on one of its paths (Q1: the reference keeps
+            # the hit its randomly built BVH tests last, src/AS/BLAS.cu:84-89) must equal one of its build-seed outcomes
+            bad = (g["radiance"][y] != rad[y]).any(axis=-1)
             if rgba8:
-                assert np.array_equal(g["rgba8"][y], img[y]), f"{sc.name} line {y}: RGBA8 differs from the oracle"
+                bad |= (g["rgba8"][y] != img[y]).any(axis=-1)
+            assert bad.sum() <= 3, f"{sc.name} line {y}: {int(bad.sum())} pixels differ from the oracle"
+            for build_seed in (8, 9, 10, 11):
+                if not bad.any():
+                    break
+                h2 = port.scene(sc, build_seed)
+                img2, rad2, _ = h2.render(SEED, y, y + 1, rgba8=rgba8)
+                h2.close()
+                bad &= (g["radiance"][y] != rad2[y]).any(axis=-1) | ((g["rgba8"][y] != img2[y]).any(axis=-1) if rgba8 else False)
+            assert not bad.any(), f"{sc.name} line {y}: pixels {np.nonzero(bad)[0].tolist()} equal none of the reference's build-seed outcomes"
             continue
         t, inst, prim = h.primary(SEED, y, y + 1)
         same = (g["inst"][y] == inst[y]) & (g["prim"][y] == prim[y])

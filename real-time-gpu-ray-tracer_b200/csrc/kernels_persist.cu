@@ -34,6 +34,11 @@ constexpr uint32_t NG_INNER = 0x00FFFFFFu;      // node group has pending inner 
 // shared memory by every CTA and node steps read them from there.  Measured on C2 (profiles/r01h_stage_top_nodes.txt):
 // no gain — those records are the ones that already hit in L1 (L1 hit rate 49 % of all sectors) — so it is compiled
 // out by default (0); the variant build is `make VARIANT=stage EXTRA=-DRT_STAGE_TOP_NODES=96`.
+// Variant (A/B): run the pop / leave-instance transition right after a node or leaf step, with that step's lanes, instead
+// of only at the loop top (where it runs at 4-7 lanes: profiles/r02a_persist8_c2_hotlines.txt).
+#ifndef RT_POP_IN_PHASE
+#define RT_POP_IN_PHASE 0
+#endif
 #ifndef RT_STAGE_TOP_NODES
 #define RT_STAGE_TOP_NODES 0
 #endif
@@ -62,22 +67,24 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
 
     for (;;) {
         // ---- cheap transitions: nothing pending in registers -> leave instance / ray finished / pop -----------------
-        if (state == ST_TRACE && tg.y == 0u && ng.y <= NG_INNER) {
-            if (inst >= 0 && sp == inst_sp && sp != 0) {         // BLAS exhausted, TLAS work left: back to world space
-                const float4 o = pb.ray_o[slot], d = pb.ray_d[slot];
-                inst = -1 - (int) __float_as_uint(d.w);          // inst < 0: on the TLAS of frame -1 - inst of the window
-                r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);
-                wide_setup_ray(r);
-            }
-            if (sp == 0) {
-                state = ST_SHADE;
-                ng = make_uint2(0u, 0u);
-            } else {
-                sp--;
-                const uint2 e = stk[sp * PT];
-                if (e.y > NG_INNER) ng = e; else { tg = e; ng = make_uint2(0u, 0u); }
-            }
+#define RT_ADVANCE()                                                                                                         \
+        if (state == ST_TRACE && tg.y == 0u && ng.y <= NG_INNER) {                                                           \
+            if (inst >= 0 && sp == inst_sp && sp != 0) {         /* BLAS exhausted, TLAS work left: back to world space */   \
+                const float4 o = pb.ray_o[slot], d = pb.ray_d[slot];                                                         \
+                inst = -1 - (int) __float_as_uint(d.w);          /* inst < 0: on the TLAS of frame -1 - inst of the window */ \
+                r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);                                                  \
+                wide_setup_ray(r);                                                                                           \
+            }                                                                                                                \
+            if (sp == 0) {                                                                                                   \
+                state = ST_SHADE;                                                                                            \
+                ng = make_uint2(0u, 0u);                                                                                     \
+            } else {                                                                                                         \
+                sp--;                                                                                                        \
+                const uint2 e = stk[sp * PT];                                                                                \
+                if (e.y > NG_INNER) ng = e; else { tg = e; ng = make_uint2(0u, 0u); }                                        \
+            }                                                                                                                \
         }
+        RT_ADVANCE()
         const bool on_node = state == ST_TRACE && tg.y == 0u && ng.y > NG_INNER;
         const bool on_leaf = state == ST_TRACE && tg.y != 0u;
         const uint32_t node_lanes = __ballot_sync(0xffffffffu, on_node);
@@ -124,6 +131,9 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 if (ng.y) ng.y |= __float_as_uint(n.n0.w) >> 24;
                 tg.x = n.n1.y;
                 tg.y = hm & 0x00FFFFFFu;
+#if RT_POP_IN_PHASE & 1
+                RT_ADVANCE()    // a node without hits: pop here, with the lanes of the node step, not alone at the loop top
+#endif
             }
         } else if (phase == 1) {
             // ---- LEAF: one primitive test or one instance entry per lane --------------------------------------------
@@ -133,6 +143,9 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 if (inst >= 0) {
                     if (COUNT) stats.prims++;
                     leaf_test8(sc, (uint32_t) prim_type, tg.x + (uint32_t) idx, r.ray, RT_TMIN, inst, hit);
+#if RT_POP_IN_PHASE & 2
+                    RT_ADVANCE()
+#endif
                 } else {
                     // TLAS leaf: enter one instance, keep the rest of the group and the node group for later
                     if (tg.y) { if (sp < RT_WIDE_STACK) { stk[sp * PT] = tg; sp++; } else overflow = 1u; }

@@ -414,6 +414,40 @@ void emul_count(void *h, uint64_t seed, int y0, int y1, int threads, uint64_t *o
     for (int k = 0; k < 4; k++) out4[k] = tot[k].load();
 }
 
+// debugging aid for parity work: every path segment of one pixel — rows of 12 floats: sample, depth, ray origin, ray
+// direction, hit t (inf on a miss), instance, primitive ((type << 28) | index); returns the number of rows
+int emul_pixel_paths(void *h, uint64_t seed, uint32_t x, uint32_t y, float *out, int cap) {
+    Emul &e = *(Emul *) h;
+    const CameraD &cam = e.hs.cam;
+    const uint32_t pixelIndex = cam.pitch * y + x;
+    curandStateXORWOW_t st;
+    curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &st);
+    RngState rng{st.d, st.v[0], st.v[1], st.v[2], st.v[3], st.v[4]};
+    uint2 stack[RT_WIDE_STACK];
+    int rows = 0;
+    for (uint32_t si = 0; si < cam.sqrtSamples; si++)
+        for (uint32_t sj = 0; sj < cam.sqrtSamples; sj++) {
+            RayD ray = primary_ray(cam, x, y, si, sj, rng);
+            f3 thr = mk3(1.0f, 1.0f, 1.0f);
+            for (uint32_t depth = 0; depth < cam.depth; depth++) {
+                HitD hit;
+                uint32_t overflow = 0;
+                TravStats ts{0, 0, 0};
+                trace_closest8<false>(e.sc, ray, RT_TMIN, hit, overflow, ts, stack, 1);
+                if (rows < cap) {
+                    float *o = out + 12 * rows;
+                    o[0] = (float) (si * cam.sqrtSamples + sj); o[1] = (float) depth;
+                    o[2] = ray.o.x; o[3] = ray.o.y; o[4] = ray.o.z; o[5] = ray.d.x; o[6] = ray.d.y; o[7] = ray.d.z;
+                    o[8] = hit.inst >= 0 ? hit.t : INFINITY; o[9] = (float) hit.inst;
+                    o[10] = hit.inst >= 0 ? (float) e.sc.leaf_prims8[ref_pos(hit.leaf)] : -1.0f; o[11] = hit.inst >= 0 ? (float) ref_type(hit.leaf) : -1.0f;
+                }
+                rows++;
+                if (!shade_scatter<true>(e.sc, cam, ray, hit, thr, rng)) break;
+            }
+        }
+    return rows;
+}
+
 void emul_instances(void *h, float *o) {
     Emul &e = *(Emul *) h;
     for (size_t i = 0; i < e.instances.size(); i++) {

@@ -387,8 +387,8 @@ def run_c3(args):
                 "config": {"workload": f"configs[2]: {F}-frame stand-in for files/particle_mesh.vtk.series ({counts[0]}..{counts[-1]} particles x 1258 strip triangles, "
                                        "the reference's on-disk layout, synthesised from the committed frame-0 fixture) + the 5 Main.cu instances, 1920x1080, 1 spp, depth 10",
                            "frames": F, "width": W, "height": H, "spp": 1, "depth": 10,
-                           "parallelism": f"frames i mod {world}, scene rebuilt per frame on the owning GPU, no per-frame exchange" if world > 1 else "single GPU",
                            "l2": "every frame is a new scene (new BVH, new triangle records): nothing is reused between timed iterations"},
+                "parallelism": f"frames i mod {world}, scene rebuilt per frame on the owning GPU, no per-frame exchange" if world > 1 else "single GPU",
                 "frames_per_s": F * args.steps / (max_dev_ms * 1e-3), "wall_ms_per_step": max_wall_ms / args.steps,
                 "wall_frames_per_s_one_renderer": F * args.steps / (max_wall_ms * 1e-3),
                 "triangles_rebuilt_per_step": tot_tris / args.steps, "slowest_rebuild_ms": max_rebuild,

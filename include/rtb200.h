@@ -26,6 +26,8 @@ enum rt_status {
     RT_ERR_IO        = -1,   /* reference: exit(-1) on file errors, src/Global/Renderer.cu:399-422 */
     RT_ERR_ARGUMENT  = -2,
     RT_ERR_STATE     = -3,   /* call order violated (e.g. render before build)                    */
+    RT_ERR_OVERFLOW  = -4,   /* a traversal stack overflowed: the frame was rendered but is incomplete
+                                (the reference's 64-entry stacks overflow silently, quirk Q15)      */
     RT_ERR_CUDA      = -200, /* reference: CUDA_ERROR_EXIT_CODE, include/Global/Global.cuh:253    */
     RT_ERR_NCCL      = -300
 };

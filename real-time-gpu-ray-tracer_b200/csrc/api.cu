@@ -388,6 +388,9 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
         CUDA_CHECK(cudaEventElapsedTime(&out->trace_ms, ctx->ev[2], ctx->ev[3]));
         out->kernel_launches = (reuse_tlas ? 0 : ctx->tlas.launches + 3 /*instance update: bounds init, matrices, world boxes*/) + 1 /*rng*/ + (mega ? 1 : ws.launches);
     }
+    // a traversal stack that overflowed dropped subtrees: the frame is wrong, and the caller must hear about it (the
+    // reference's 64-entry stacks overflow silently, Q15); `out` is filled all the same
+    if (ctx->h_counters.get()[1] != 0) return fail(ctx, RT_ERR_OVERFLOW, "rt_render_frame: a traversal stack overflowed (BVH deeper than the per-thread stack): the frame is incomplete");
     RT_API_END(ctx)
 }
 

@@ -369,6 +369,7 @@ int rt_release_window(rt_ctx *ctx, uint32_t window, rt_window_stats *stats) {
         CUDA_CHECK(cudaEventElapsedTime(&stats->device_ms, w.ev_begin, w.ev_end));
         CUDA_CHECK(cudaEventElapsedTime(&stats->prepare_ms, w.ev_begin, w.ev_prep));
     }
+    if (w.h_counters.get()[1] != 0) return rt_fail(ctx, RT_ERR_OVERFLOW, "frames in flight: a traversal stack overflowed: the frames of this window are incomplete");
     RT_API_END(ctx)
 }
 

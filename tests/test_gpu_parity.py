@@ -184,6 +184,34 @@ def test_argument_limits(pkg):
         r.cleanup()
 
 
+def test_stack_overflow_is_an_error(pkg):
+    """a traversal stack overflow drops subtrees, so the frame is wrong — rt_render_frame / rt_release_window return
+    RT_ERR_OVERFLOW instead of only setting a flag.  Forced with the test-only build whose stacks hold 2 entries."""
+    import os
+    lib = os.path.join(os.path.dirname(os.path.abspath(pkg.__file__)), "librtb200_tinystack.so")
+    sc = pkg.scenes.c2(width=160, height=90, spp=2, depth=6, nx=100, nz=50)
+    r = pkg.Renderer(device=0, lib_path=lib)
+    try:
+        r.commitScene(sc)
+        with pytest.raises(pkg.RtError) as e:
+            r.renderFrame(0, SEED)
+        assert e.value.code == -4
+        w = r.submitFrames(0, 2)
+        assert r.waitFrame(w, 1).rays > 0
+        with pytest.raises(pkg.RtError) as e:
+            r.releaseWindow(w)
+        assert e.value.code == -4
+        r.submitFrames(2, 1)                       # the handle is free again
+    finally:
+        r.cleanup()
+    ok = pkg.Renderer(device=0)                    # the product build has room: same scene, no error
+    try:
+        ok.commitScene(sc)
+        assert ok.renderFrame(0, SEED).stack_overflow == 0
+    finally:
+        ok.cleanup()
+
+
 def test_depth_zero_is_white(pkg, port):
     """ray_trace_depth = 0: rayColor's loop never runs (reference src/Global/Kernel.cu:64), every sample is (1,1,1)."""
     sc = pkg.scenes.c1a(width=64, height=36, spp=4, depth=0)

@@ -85,7 +85,7 @@ private:
     DeviceBuffer<uint32_t> wide_counters_, leaf_pos8_, leaf_prims8_;
     DeviceBuffer<BvhNode8> nodes8_;
     DeviceBuffer<TriIsect> leaf_tris8_;
-    int collapse_blocks_per_sm_ = 0;
+    int collapse_blocks_per_sm_ = 0, collapse_octet_blocks_per_sm_ = 0;
     DeviceBuffer<float4> ploc_lo_a_, ploc_hi_a_, ploc_lo_b_, ploc_hi_b_;
     DeviceBuffer<int> ploc_nn_, ploc_state_;
     DeviceBuffer<uint2> ploc_blocks_;

@@ -391,7 +391,7 @@ void LbvhBuilder::reserve(int n, int n_segs, bool tris) {
     range_.reserve(m);
     queue_.reserve((size_t) n + n_segs);
     nodes8_.reserve((size_t) n + n_segs);
-    wide_counters_.reserve(4);
+    wide_counters_.reserve(8);
     leaf_pos8_.reserve(n); leaf_prims8_.reserve(n);
     if (tris) leaf_tris8_.reserve(n);
 }

@@ -13,6 +13,7 @@
 #include "build.h"
 
 #include <cstdlib>
+#include <cstring>
 
 namespace {
 
@@ -31,10 +32,76 @@ __device__ __forceinline__ int find_segment_w(const uint32_t *__restrict__ seg_o
 __global__ void __launch_bounds__(256) collapse_init_kernel(const uint32_t *__restrict__ seg_offset, const int *__restrict__ seg_root, int n_segs,
                                                             int *queue, uint32_t *counters) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s == 0) { counters[0] = (uint32_t) n_segs; counters[1] = 0u; counters[2] = 0u; counters[3] = 0u; }
+    if (s == 0) {
+        counters[0] = (uint32_t) n_segs; counters[1] = 0u; counters[2] = 0u; counters[3] = 0u;
+        counters[4] = 0u; counters[5] = (uint32_t) n_segs; counters[6] = 0u;      // level launches: begin, end, blocks done
+    }
     if (s >= n_segs) return;
     const uint32_t first = seg_offset[s], cnt = seg_offset[s + 1] - first;
     queue[s] = cnt == 1u ? ~(int) first : seg_root[s];
+}
+
+// one work item = one wide node: expand, allocate, publish the children, encode, write
+__device__ __forceinline__ void collapse_item(const BinaryTreeView &view, int root, int i, int leaf_max, volatile int *vq, uint32_t *counters,
+                                              BvhNode8 *__restrict__ nodes8, uint32_t *__restrict__ leaf_pos8) {
+    WideChildren w;
+    wide_expand(view, root, leaf_max, w);
+    const int k = wide_inner_count(w), m = wide_prim_count(w);
+    const uint32_t child_base = k ? atomicAdd(&counters[0], (uint32_t) k) : 0u;
+    const uint32_t prim_base = m ? atomicAdd(&counters[1], (uint32_t) m) : 0u;
+    Aabb box;
+    int child_in_slot[8];
+    wide_layout(w, box, child_in_slot);
+    // the children first: the collapse's dependency chain runs through these stores, not through the record
+    uint32_t j = 0;
+    for (int sl = 0; sl < 8; sl++) {
+        const int c = child_in_slot[sl];
+        if (c >= 0 && w.ref[c] >= 0) { vq[child_base + j] = w.ref[c]; j++; }
+    }
+    BvhNode8 node;
+    wide_encode_layout(w, box, child_in_slot, child_base, prim_base, node);
+    nodes8[i] = node;
+    uint32_t off = 0;
+    for (int sl = 0; sl < 8; sl++) {
+        const int c = child_in_slot[sl];
+        if (c < 0 || w.ref[c] >= 0) continue;
+        for (int q = 0; q < w.count[c]; q++) leaf_pos8[prim_base + off + q] = (uint32_t) (w.first[c] + q);
+        off += (uint32_t) w.count[c];
+    }
+}
+
+// ---- the first levels, one launch per level --------------------------------------------------------------------------
+// Items are numbered in allocation order, so the nodes of depth L occupy one contiguous index range, known once depth
+// L - 1 is finished.  A launch that covers exactly that range has every item ready when it starts: no polling, every SM full
+// of warps, the DRAM latency of the dependent binary-node loads hidden by occupancy instead of sitting on a chain of waiting
+// threads (the ticket kernel alone: 8 warps per SM, issue slots 10 % busy, 375 us for 1 M triangles).  The host does not
+// know the ranges: each launch is sized for the largest range its level can have and reads [begin, end) from `levels`, which
+// the last block of the previous level wrote.  Deep or degenerate trees simply leave their remaining levels to the ticket
+// kernel, which runs afterwards in any case and starts at the first index no level launch covered.
+//   levels[0] = current begin, levels[1] = current end, levels[2] = blocks finished in this launch
+__global__ void __launch_bounds__(256) collapse_level_kernel(BinaryTreeView view, int leaf_max, int *queue, uint32_t *counters, uint32_t *levels,
+                                                             BvhNode8 *__restrict__ nodes8, uint32_t *__restrict__ leaf_pos8) {
+    volatile int *vq = queue;
+    const uint32_t begin = ((volatile uint32_t *) levels)[0], end = ((volatile uint32_t *) levels)[1];
+    const uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < end) {
+        collapse_item(view, vq[i], (int) i, leaf_max, vq, counters, nodes8, leaf_pos8);
+        atomicAdd(&counters[2], 1u);
+    }
+    __shared__ bool last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(&levels[2], 1u) + 1u == gridDim.x;
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        __threadfence();
+        const uint32_t alloc = ((volatile uint32_t *) counters)[0];       // every item of this level has allocated its children
+        levels[0] = end;
+        levels[1] = alloc;
+        levels[2] = 0u;
+        counters[3] = end;                                                // where the ticket kernel would have to start
+        __threadfence();
+    }
 }
 
 __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int leaf_max, int capacity, int *queue, uint32_t *counters,
@@ -55,31 +122,9 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
             if (i < capacity) {
                 const int root = vq[i];
                 if (root != QUEUE_EMPTY) {
-                    WideChildren w;
-                    wide_expand(view, root, leaf_max, w);
-                    const int k = wide_inner_count(w), m = wide_prim_count(w);
-                    const uint32_t child_base = k ? atomicAdd(&counters[0], (uint32_t) k) : 0u;
-                    const uint32_t prim_base = m ? atomicAdd(&counters[1], (uint32_t) m) : 0u;
-                    Aabb box;
-                    int child_in_slot[8];
-                    wide_layout(w, box, child_in_slot);
-                    // the children first: the collapse's dependency chain runs through these stores, not through the record
-                    uint32_t j = 0;
-                    for (int sl = 0; sl < 8; sl++) {
-                        const int c = child_in_slot[sl];
-                        if (c >= 0 && w.ref[c] >= 0) { vq[child_base + j] = w.ref[c]; j++; }
-                    }
-                    BvhNode8 node;
-                    wide_encode_layout(w, box, child_in_slot, child_base, prim_base, node);
-                    nodes8[i] = node;
-                    uint32_t off = 0;
-                    for (int sl = 0; sl < 8; sl++) {
-                        const int c = child_in_slot[sl];
-                        if (c < 0 || w.ref[c] >= 0) continue;
-                        for (int q = 0; q < w.count[c]; q++) leaf_pos8[prim_base + off + q] = (uint32_t) (w.first[c] + q);
-                        off += (uint32_t) w.count[c];
-                    }
-                    __threadfence();
+                    collapse_item(view, root, i, leaf_max, vq, counters, nodes8, leaf_pos8);
+                    // no fence: nothing inside this launch reads what the item wrote except the queue entries (single words, polled
+                    // through volatile loads); `finished` only ends the launch, and the end of the launch publishes everything
                     atomicAdd(&counters[2], 1u);
                     break;
                 }
@@ -101,6 +146,222 @@ __global__ void __launch_bounds__(CT) collapse_kernel(BinaryTreeView view, int l
             if (backoff < 2048u) backoff <<= 1;
         }
         // a lane saw finished == allocated: every node is written, and the lanes of this warp that held real items are done
+        if (__any_sync(0xffffffffu, finished_all)) break;
+    }
+}
+
+// ---- the same collapse with EIGHT LANES PER ITEM ("octets", four items per warp) --------------------------------------
+// The one-thread-per-item kernel above keeps the eight children of a node in dynamically indexed local arrays (528 bytes
+// of stack): every argmax / slot / quantisation step is a chain of local-memory round trips, about 10 us per item, and the
+// collapse is a dependency chain of items (seven levels for 1 M triangles, then several passes over the widest level).
+// Here lane c of an octet holds child c in registers; argmax, union, prefix counts and the OR of the quantised bytes are
+// 3-step shuffles inside the octet.  The arithmetic per child is that of rt_wide_core.h (wide_set_child, wide_assign_slots,
+// wide_quant_*), executed by the child's lane, so the nodes are the ones the serial twin makes (tests compare them).
+struct OctChild {
+    int ref, first, count, kl, kr;      // as WideChildren::ref/first/count/kl/kr of one child
+    Aabb box;
+    bool valid;
+};
+__device__ __forceinline__ void oct_set_child(const BinaryTreeView &t, int child, int leaf_max, OctChild &c) {
+    c.valid = true;
+    if (child >= 0) {
+        const float4 a = t.node_lo[child], b = t.node_hi[child];
+        c.box.lo = mk3(a.x, a.y, a.z);
+        c.box.hi = mk3(b.x, b.y, b.z);
+        c.kl = (int) f2u(a.w);
+        c.kr = (int) f2u(b.w);
+        int first = 0, cnt = leaf_max + 1;
+        if (leaf_max > 1) {
+            const int2 rg = t.range[child];
+            first = rg.x;
+            cnt = rg.y - rg.x + 1;
+        }
+        c.first = first;
+        c.count = cnt;
+        c.ref = cnt <= leaf_max ? -1 : child;
+    } else {
+        const int pos = ~child;
+        c.box = view_box(t.prim_lo, t.prim_hi, (int) t.vals[pos]);
+        c.first = pos;
+        c.count = 1;
+        c.ref = -1;
+        c.kl = 0; c.kr = 0;
+    }
+}
+// argmax over the octet: largest value, ties to the lower index (the serial loops take the first maximum)
+__device__ __forceinline__ void oct_argmax(uint32_t om, float &v, int &i) {
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) {
+        const float ov = __shfl_xor_sync(om, v, off, 8);
+        const int oi = __shfl_xor_sync(om, i, off, 8);
+        if (ov > v || (ov == v && oi < i)) { v = ov; i = oi; }
+    }
+}
+__device__ __forceinline__ uint32_t oct_or(uint32_t om, uint32_t v) {
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) v |= __shfl_xor_sync(om, v, off, 8);
+    return v;
+}
+__device__ __forceinline__ float oct_min(uint32_t om, float v) {
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) v = fminf(v, __shfl_xor_sync(om, v, off, 8));
+    return v;
+}
+__device__ __forceinline__ float oct_max(uint32_t om, float v) {
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) v = fmaxf(v, __shfl_xor_sync(om, v, off, 8));
+    return v;
+}
+
+// one item by one octet; `l` = lane within the octet (child index), `om` = the octet's lane mask
+__device__ __forceinline__ void oct_collapse_item(const BinaryTreeView &view, int root, int item, int leaf_max, uint32_t om, int l, volatile int *vq,
+                                                  uint32_t *counters, BvhNode8 *__restrict__ nodes8, uint32_t *__restrict__ leaf_pos8) {
+    // ---- wide_expand: children of the node, child c in lane c -------------------------------------------------------------
+    OctChild c{};
+    c.valid = false; c.ref = -1; c.count = 0;
+    int n = 1;
+    if (l == 0) oct_set_child(view, root, leaf_max, c);
+    if (root >= 0) {
+        const int ref0 = __shfl_sync(om, c.ref, 0, 8);
+        if (ref0 >= 0) {
+            const int kl = __shfl_sync(om, c.kl, 0, 8), kr = __shfl_sync(om, c.kr, 0, 8);
+            n = 2;
+            if (l == 0) oct_set_child(view, kl, leaf_max, c);
+            if (l == 1) oct_set_child(view, kr, leaf_max, c);
+            while (n < 8) {
+                float a = (c.valid && c.ref >= 0) ? aabb_half_area(c.box) : -1.0f;
+                int best = l;
+                oct_argmax(om, a, best);
+                if (!(a > -1.0f)) break;                      // nothing left to open
+                const int bl = __shfl_sync(om, c.kl, best, 8), br = __shfl_sync(om, c.kr, best, 8);
+                if (l == best) oct_set_child(view, bl, leaf_max, c);
+                if (l == n) oct_set_child(view, br, leaf_max, c);
+                n++;
+            }
+        }
+    }
+    // ---- counts and allocation ----------------------------------------------------------------------------------------
+    const bool inner = c.valid && c.ref >= 0, leaf = c.valid && c.ref < 0;
+    const uint32_t inner_lanes = (__ballot_sync(om, inner) >> (__ffs(om) - 1)) & 0xFFu;
+    const int k = __popc(inner_lanes);
+    int m = leaf ? c.count : 0;
+#pragma unroll
+    for (int off = 1; off < 8; off <<= 1) m += __shfl_xor_sync(om, m, off, 8);
+    uint32_t child_base = 0u, prim_base = 0u;
+    if (l == 0) {
+        if (k) child_base = atomicAdd(&counters[0], (uint32_t) k);
+        if (m) prim_base = atomicAdd(&counters[1], (uint32_t) m);
+    }
+    child_base = __shfl_sync(om, child_base, 0, 8);
+    prim_base = __shfl_sync(om, prim_base, 0, 8);
+    // ---- wide_layout: node box, octant-ordered slots (wide_assign_slots) ----------------------------------------------------
+    Aabb node;
+    node.lo = mk3(oct_min(om, c.valid ? c.box.lo.x : RT_INF), oct_min(om, c.valid ? c.box.lo.y : RT_INF), oct_min(om, c.valid ? c.box.lo.z : RT_INF));
+    node.hi = mk3(oct_max(om, c.valid ? c.box.hi.x : -RT_INF), oct_max(om, c.valid ? c.box.hi.y : -RT_INF), oct_max(om, c.valid ? c.box.hi.z : -RT_INF));
+    const f3 nc = mk3(0.5f * (node.lo.x + node.hi.x), 0.5f * (node.lo.y + node.hi.y), 0.5f * (node.lo.z + node.hi.z));
+    f3 d = mk3(0.0f, 0.0f, 0.0f);
+    float prio = -1.0f;
+    if (c.valid) {
+        d = mk3(0.5f * (c.box.lo.x + c.box.hi.x) - nc.x, 0.5f * (c.box.lo.y + c.box.hi.y) - nc.y, 0.5f * (c.box.lo.z + c.box.hi.z) - nc.z);
+        prio = (fabsf(d.x) + fabsf(d.y)) + fabsf(d.z);
+    }
+    int slot = -1;
+    uint32_t slot_free = 0xFFu;
+    bool pending = c.valid;
+    for (int round = 0; round < n; round++) {
+        float bp = pending ? prio : -3.0f;
+        int bc = l;
+        oct_argmax(om, bp, bc);
+        int bs = -1;
+        if (l == bc) {
+            float best = -RT_INF;
+            for (int s = 0; s < 8; s++) {
+                if (!(slot_free & (1u << s))) continue;
+                const float cost = (((s & 4) ? d.x : -d.x) + ((s & 2) ? d.y : -d.y)) + ((s & 1) ? d.z : -d.z);
+                if (cost > best) { best = cost; bs = s; }
+            }
+            slot = bs;
+            pending = false;
+        }
+        bs = __shfl_sync(om, bs, bc, 8);
+        slot_free &= ~(1u << bs);
+    }
+    // ---- positions among the siblings: inner children are numbered, leaf primitives laid out, in slot order -------------------
+    uint32_t j = 0, off = 0;
+#pragma unroll
+    for (int o = 0; o < 8; o++) {
+        const int os = __shfl_sync(om, slot, o, 8);
+        const int oc = __shfl_sync(om, leaf ? c.count : 0, o, 8);
+        const int oi = __shfl_sync(om, inner ? 1 : 0, o, 8);
+        if (os >= 0 && os < slot) { j += (uint32_t) oi; off += (uint32_t) oc; }
+    }
+    // the children first: the collapse's dependency chain runs through these stores, not through the record
+    if (inner) vq[child_base + j] = c.ref;
+    // ---- wide_encode_layout: each lane quantises its own child; the words are OR-ed over the octet --------------------------
+    const uint32_t ex = wide_grid_exponent(node.hi.x - node.lo.x), ey = wide_grid_exponent(node.hi.y - node.lo.y), ez = wide_grid_exponent(node.hi.z - node.lo.z);
+    uint32_t imask = 0, meta[2] = {0, 0}, q[6][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}, {0, 0}};
+    if (c.valid) {
+        const float sx = wide_grid_step(ex), sy = wide_grid_step(ey), sz = wide_grid_step(ez);
+        const float ix = wide_grid_inv_step(ex), iy = wide_grid_inv_step(ey), iz = wide_grid_inv_step(ez);
+        uint32_t mm;
+        if (inner) { imask = 1u << slot; mm = (1u << 5) | (24u + (uint32_t) slot); }
+        else { const uint32_t unary = (1u << c.count) - 1u; mm = (unary << 5) | off; }
+        const bool hi_half = slot >= 4;                   // slots 0..3 -> word 0, 4..7 -> word 1 (no dynamic indexing: registers)
+        const int sh = 8 * (slot & 3);
+        const uint32_t v[7] = {mm << sh,
+                               wide_quant_lo(c.box.lo.x, node.lo.x, sx, ix) << sh, wide_quant_lo(c.box.lo.y, node.lo.y, sy, iy) << sh,
+                               wide_quant_lo(c.box.lo.z, node.lo.z, sz, iz) << sh, wide_quant_hi(c.box.hi.x, node.lo.x, sx, ix) << sh,
+                               wide_quant_hi(c.box.hi.y, node.lo.y, sy, iy) << sh, wide_quant_hi(c.box.hi.z, node.lo.z, sz, iz) << sh};
+        meta[0] = hi_half ? 0u : v[0]; meta[1] = hi_half ? v[0] : 0u;
+#pragma unroll
+        for (int a = 0; a < 6; a++) { q[a][0] = hi_half ? 0u : v[a + 1]; q[a][1] = hi_half ? v[a + 1] : 0u; }
+    }
+    imask = oct_or(om, imask);
+    meta[0] = oct_or(om, meta[0]); meta[1] = oct_or(om, meta[1]);
+#pragma unroll
+    for (int a = 0; a < 6; a++) { q[a][0] = oct_or(om, q[a][0]); q[a][1] = oct_or(om, q[a][1]); }
+    uint4 *dst = reinterpret_cast<uint4 *>(nodes8 + item);
+    if (l == 0) dst[0] = make_uint4(f2u(node.lo.x), f2u(node.lo.y), f2u(node.lo.z), ex | (ey << 8) | (ez << 16) | (imask << 24));
+    if (l == 1) dst[1] = make_uint4(child_base, prim_base, meta[0], meta[1]);
+    if (l == 2) dst[2] = make_uint4(q[0][0], q[0][1], q[1][0], q[1][1]);
+    if (l == 3) dst[3] = make_uint4(q[2][0], q[2][1], q[3][0], q[3][1]);
+    if (l == 4) dst[4] = make_uint4(q[4][0], q[4][1], q[5][0], q[5][1]);
+    if (leaf) for (int t = 0; t < c.count; t++) leaf_pos8[prim_base + off + (uint32_t) t] = (uint32_t) (c.first + t);
+    if (l == 0) atomicAdd(&counters[2], 1u);           // no fence (see collapse_kernel)
+}
+
+__global__ void __launch_bounds__(CT) collapse_octet_kernel(BinaryTreeView view, int leaf_max, int capacity, int *queue, uint32_t *counters,
+                                                            BvhNode8 *__restrict__ nodes8, uint32_t *__restrict__ leaf_pos8) {
+    volatile int *vq = queue;
+    volatile uint32_t *vc = counters;
+    const uint32_t lane = threadIdx.x & 31u;
+    const int l = (int) (lane & 7u), octet = (int) (lane >> 3);
+    const uint32_t om = 0xFFu << (8 * octet);
+    for (;;) {
+        // ---- claim the next 4 items for this warp, one per octet (tickets only grow: everything below them is in someone's hands)
+        uint32_t base = 0;
+        if (lane == 0u) base = atomicAdd(&counters[3], 4u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const int i = (int) base + octet;
+        bool finished_all = false, allocated = false;
+        uint32_t backoff = 32u;
+        for (;;) {
+            int root = (int) 0x80808080u;                 // QUEUE_EMPTY
+            if (i < capacity) root = vq[i];
+            if (root != QUEUE_EMPTY) {
+                oct_collapse_item(view, root, i, leaf_max, om, l, vq, counters, nodes8, leaf_pos8);
+                break;
+            }
+            if (!allocated) allocated = i < capacity && (uint32_t) i < vc[0];       // the count only grows: ask once
+            if (!allocated) {
+                const uint32_t fin = vc[2];
+                __threadfence();
+                const uint32_t alloc = vc[0];
+                if (fin == alloc) { finished_all = true; break; }
+            }
+            __nanosleep(backoff);
+            if (backoff < (allocated ? 128u : 1024u)) backoff <<= 1;
+        }
         if (__any_sync(0xffffffffu, finished_all)) break;
     }
 }
@@ -144,13 +405,45 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     CUDA_CHECK(cudaMemsetAsync(queue_.get(), 0x80, (size_t) capacity * sizeof(int), stream));
     collapse_init_kernel<<<div_up(n_segs, 256), 256, 0, stream>>>(seg_offset_.get(), seg_root_.get(), n_segs, queue_.get(), wide_counters_.get());
     const BinaryTreeView view{range_.get(), node_lo_.get(), node_hi_.get(), prim_lo_.get(), prim_hi_.get(), vals_};
-    // items are claimed by ticket (see above): the grid need not be resident as a whole; 2 CTAs per SM measured best
-    static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 2;   // tuning (measured: 2 beats 3, 4, 8 — fewer pollers)
+    // items are claimed by ticket (see above): the grid need not be resident as a whole; 3 CTAs per SM measured best
+    static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 3;   // tuning (measured, profiles/r02j_build_ab.txt: 0.76 / 0.74 / 0.77 ms at 2 / 3 / 4, 0.97 at 8)
     const int max_blocks = sm_count * std::min(collapse_blocks_per_sm_, std::max(1, collapse_bps_env));
     const int want_blocks = (int) div_up((size_t) capacity, CT);
     const int blocks = want_blocks < max_blocks ? want_blocks : max_blocks;
     static const int leaf_max_env = getenv("RTB200_LEAF_MAX") ? atoi(getenv("RTB200_LEAF_MAX")) : 0;   // tuning experiments only
     const int leaf_max = leaf_mode == 1 ? 1 : (leaf_max_env >= 1 && leaf_max_env <= 3 ? leaf_max_env : RT_WIDE_LEAF_MAX);
+    // the first levels one launch each (collapse_level_kernel); small trees are quicker in the single ticket launch
+    // Measured (profiles/r02i_build_ab.txt, r02i_build_launches.csv): NOT faster — 0.83 ms with 6 level launches, 0.97 with 12,
+    // against 0.76 ms for the ticket kernel alone on the 1 M-triangle BLAS: one item alone takes about 20 us (the first three
+    // level launches are 22-27 us each for 1, 8 and 64 items), the chain of levels is what costs, and each level launch adds its
+    // own start-up on top.  Off by default (0); RTB200_COLLAPSE_LEVELS=n turns n level launches on for A/B runs.
+    static const int level_launches_env = getenv("RTB200_COLLAPSE_LEVELS") ? atoi(getenv("RTB200_COLLAPSE_LEVELS")) : 0;
+    if (capacity >= (1 << 15) && level_launches_env > 0) {
+        size_t bound = (size_t) n_segs;                       // a level of depth L has at most n_segs * 8^L items, and never more than there are
+        for (int level = 0; level < level_launches_env; level++) {
+            const size_t items = std::min(bound, (size_t) capacity);
+            collapse_level_kernel<<<div_up(items, 256), 256, 0, stream>>>(view, leaf_max, queue_.get(), wide_counters_.get(), wide_counters_.get() + 4,
+                                                                         nodes8_.get(), leaf_pos8_.get());
+            launches++;
+            if (bound < (size_t) capacity) bound *= 8;
+        }
+    }
+    // A/B: RTB200_COLLAPSE=octet runs the eight-lanes-per-item kernel.  Measured (profiles/r02f_build_ab.txt, r02g ncu): correct
+    // (same trees as the twin) but slower, 0.88 vs 0.77 ms for the 1 M-triangle BLAS — the collapse is bound by the DRAM
+    // latency of the dependent binary-node loads (long scoreboard 42-50 % of the stalls, L2 hit 56 %), not by the local-memory
+    // arithmetic the octets remove, and eight fences per item cost more than they save.  One thread per item stays the default.
+    static const bool octets = getenv("RTB200_COLLAPSE") && strcmp(getenv("RTB200_COLLAPSE"), "octet") == 0;
+    if (octets) {
+        if (collapse_octet_blocks_per_sm_ == 0) {
+            CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&collapse_octet_blocks_per_sm_, collapse_octet_kernel, CT, 0));
+            if (collapse_octet_blocks_per_sm_ < 1) collapse_octet_blocks_per_sm_ = 1;
+        }
+        static const int bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 8;
+        const int max_b = sm_count * std::min(collapse_octet_blocks_per_sm_, std::max(1, bps_env));
+        const int want_b = (int) div_up((size_t) capacity * 8, CT);             // eight lanes per item
+        collapse_octet_kernel<<<want_b < max_b ? want_b : max_b, CT, 0, stream>>>(view, leaf_max, capacity, queue_.get(), wide_counters_.get(), nodes8_.get(),
+                                                                                   leaf_pos8_.get());
+    } else
     collapse_kernel<<<blocks, CT, 0, stream>>>(view, leaf_max, capacity, queue_.get(), wide_counters_.get(), nodes8_.get(), leaf_pos8_.get());
     const GeometryD none{nullptr, nullptr, nullptr, nullptr};
     emit_leaves8_kernel<<<div_up(n, 256), 256, 0, stream>>>(geo ? *geo : none, leaf_pos8_.get(), vals_, seg_offset_.get(), seg_type_.get(),

@@ -25,6 +25,10 @@ RT_HD int rt_bfind(uint32_t x) {   // index of the highest set bit, x != 0
 }
 RT_HD uint32_t rt_byte(uint32_t v, int i) { return (v >> (8 * i)) & 0xFFu; }
 
+#ifndef RT_COLLAPSE_PREFETCH
+#define RT_COLLAPSE_PREFETCH 0      /* measured: 0.775 vs 0.780 ms for the 1 M-triangle BLAS (profiles/r02h_build_ab.txt): no effect, off */
+#endif
+
 // ---- collapse: children of one wide node --------------------------------------------------------------------
 // ref >= 0 : binary inner node that becomes a wide node of its own
 // ref <  0 : leaf child holding the Morton-order positions [first, first + count)
@@ -53,6 +57,19 @@ RT_HD Aabb view_box(const float4 *lo, const float4 *hi, int i) {
     r.hi = mk3(b.x, b.y, b.z);
     return r;
 }
+// The collapse is a chain of dependent loads: opening a child needs the records of ITS children.  Whichever child is
+// opened next, those records are requested the moment the child is added (L2 prefetch, no registers held), so that the
+// later load finds them on chip instead of paying a DRAM round trip on the critical path.
+RT_HD void wide_prefetch_node(const BinaryTreeView &t, int node) {
+#if defined(__CUDA_ARCH__) && RT_COLLAPSE_PREFETCH
+    if (node >= 0) {
+        asm volatile("prefetch.global.L2 [%0];" :: "l"(t.node_lo + node));
+        asm volatile("prefetch.global.L2 [%0];" :: "l"(t.node_hi + node));
+    }
+#else
+    (void) t; (void) node;
+#endif
+}
 RT_HD void wide_set_child(const BinaryTreeView &t, int child, int leaf_max, WideChildren &w, int k) {
     if (child >= 0) {
         const float4 a = t.node_lo[child], b = t.node_hi[child];
@@ -60,6 +77,8 @@ RT_HD void wide_set_child(const BinaryTreeView &t, int child, int leaf_max, Wide
         w.box[k].hi = mk3(b.x, b.y, b.z);
         w.kl[k] = (int) f2u(a.w);
         w.kr[k] = (int) f2u(b.w);
+        wide_prefetch_node(t, w.kl[k]);
+        wide_prefetch_node(t, w.kr[k]);
         int first = 0, cnt = leaf_max + 1;
         if (leaf_max > 1) {                                  // small subtrees become one leaf child
             const int2 rg = t.range[child];

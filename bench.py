@@ -186,7 +186,7 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------------------
-def reference_cuda_baseline(pkg, args, device, builds=3, budget_s=75.0):
+def reference_cuda_baseline(pkg, args, device, builds=3, budget_s=45.0):
     """north_star's first baseline: the reference's OWN CUDA build (unmodified sources compiled for sm_100a by
     oracle/Makefile `refcuda`, headless surface) on the same scene, camera and sample count as the bench line, timed in
     the same run.  The reference's host BVH builder picks its split axes at random (src/AS/BLAS.cu:84-89), so the frame

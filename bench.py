@@ -597,6 +597,10 @@ def run_ours(args):
     t0 = time.perf_counter()
     st = r.commitScene(sc)
     commit_s = time.perf_counter() - t0
+    # the same build again, twice: what a per-frame rebuild costs once the builder's buffers exist (the first build of a
+    # context also allocates them)
+    rebuilds = [r.buildAccelerationStructure() for _ in range(2)]
+    warm_blas_ms = min(x.blas_ms for x in rebuilds)
     tile_rows = args.tile_rows
     exchange = "none (single GPU)"
     if distributed:
@@ -721,8 +725,9 @@ def run_ours(args):
                 "frame_loop": loop,
                 "rays_per_frame": rays_per_frame, "wall_ms_per_step": wall_ms_per_step,
                 "stage_ms": stage_ms,
-                "lbvh_build_ms": {"blas_1M_tris": st.blas_ms, "tlas": st.tlas_ms, "kernel_launches": st.kernel_launches,
-                                  "bytes_per_prim_algorithmic": 280, "achieved_gbs": 280 * st.primitive_count / max(st.blas_ms, 1e-6) / 1e6},
+                "lbvh_build_ms": {"blas_1M_tris": st.blas_ms, "blas_rebuild": warm_blas_ms, "tlas": st.tlas_ms, "kernel_launches": st.kernel_launches,
+                                  "bytes_per_prim_algorithmic": 280, "achieved_gbs": 280 * st.primitive_count / max(warm_blas_ms, 1e-6) / 1e6,
+                                  "what": "blas_1M_tris = first build of the context (allocates the builder's buffers), blas_rebuild = best of two more builds of the same geometry; CUDA events, primitives resident -> wide BVH ready"},
                 "commit_s": commit_s,
                 "e2e": {"value": e2e, "unit": "Mrays/s", "h2d_bytes_per_step": int(len(sc.instances) * 92), "d2h_bytes_per_step": int(W * H * 4 + 64),
                         "ms_per_step": e2e_ms,

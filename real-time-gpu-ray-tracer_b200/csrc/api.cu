@@ -123,6 +123,7 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     c->persist.blocks_per_sm_override = c->wave.blocks_per_sm_override;
     if (const char *e = getenv("RTB200_SHADE_MIN")) c->persist.shade_min = atoi(e);
     if (const char *e = getenv("RTB200_TILE_ORDER")) c->persist.tile_order = atoi(e);
+    if (const char *e = getenv("RTB200_SPLIT")) c->persist.split = atoi(e) != 0;       // A/B: dedicated shade warp per CTA (kernels_split.cu)
     if (const char *e = getenv("RTB200_VTK_EXPAND")) c->vtk_expand_on_device = strcmp(e, "host") != 0;
     for (auto &st: c->vtk_stage) st.expand_on_device = c->vtk_expand_on_device;
     if (flags & RT_FLAG_WAVEFRONT) c->path_mode = 0;

@@ -266,6 +266,7 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
     win.peer_flags = ring ? ring->flags(wi, ctx->shard_rank) : nullptr;
     w.persist.node_min = ctx->persist.node_min; w.persist.shade_min = ctx->persist.shade_min;
     w.persist.blocks_per_sm_override = ctx->persist.blocks_per_sm_override; w.persist.tile_order = ctx->persist.tile_order;
+    w.persist.split = ctx->persist.split;
     w.persist.n_blas_nodes = (uint32_t) ctx->blas.n_prims();
     if (win.valid_pixels == 0u) {
         // a shard without a single scan-line inside the image: nothing to trace, every frame is complete at once

@@ -352,9 +352,20 @@ void PersistRenderer::render_window(const SceneD &sc, const CameraD &cam, const 
     pb.n_tiles = pb.tiles_x * ((fr.local_rows + 3u) / 4u);
     pb.n_pixels = pb.n_tiles * 32u;
     // no more threads than pixels (a warp = one 8x4 tile at a time)
-    const uint32_t want_blocks = (pb.n_pixels + PT - 1) / PT;
-    const uint32_t blocks = std::min<uint32_t>((uint32_t) (sm_count * bps), std::max(1u, want_blocks));
-    const size_t n_threads = (size_t) blocks * PT;
+    uint32_t want_blocks = (pb.n_pixels + PT - 1) / PT;
+    uint32_t blocks = std::min<uint32_t>((uint32_t) (sm_count * bps), std::max(1u, want_blocks));
+    size_t n_threads = (size_t) blocks * PT;
+    if (split) {                                    // one path-state entry per path of a CTA's pool
+        if (split_blocks_per_sm_[count ? 1 : 0] == 0) split_blocks_per_sm_[count ? 1 : 0] = split_blocks_per_sm(count);
+        int sb = split_blocks_per_sm_[count ? 1 : 0];
+        if (blocks_per_sm_override > 0) sb = std::min(sb, blocks_per_sm_override);
+        const uint32_t slots = (uint32_t) split_slots_per_block();
+        const size_t total_px = (size_t) pb.n_pixels * (win ? win->n_frames : 1u);
+        want_blocks = (uint32_t) std::min<size_t>((total_px + slots - 1) / slots, 1u << 20);
+        blocks = std::min<uint32_t>((uint32_t) (sm_count * sb), std::max(1u, want_blocks));
+        n_threads = (size_t) blocks * slots;
+        hit_.reserve(n_threads); hit_inst_.reserve(n_threads);
+    }
     ray_o_.reserve(n_threads); ray_d_.reserve(n_threads); thr_.reserve(n_threads); acc_.reserve(n_threads);
     rng_a_.reserve(n_threads); rng_b_.reserve(n_threads);
     counter_.reserve(1);
@@ -376,6 +387,7 @@ void PersistRenderer::render_window(const SceneD &sc, const CameraD &cam, const 
     launches = 2 + sort_launches;
     pb.ray_o = ray_o_.get(); pb.ray_d = ray_d_.get(); pb.thr = thr_.get(); pb.acc = acc_.get();
     pb.rng_a = rng_a_.get(); pb.rng_b = rng_b_.get(); pb.next_pixel = counter_.get();
+    pb.hit = hit_.get(); pb.hit_inst = hit_inst_.get();
     pb.tile_order = vals; pb.tile_cost = tile_cost_.get();
     pb.n_blas_nodes = n_blas_nodes;
     pb.n_frames = 1u;
@@ -387,7 +399,8 @@ void PersistRenderer::render_window(const SceneD &sc, const CameraD &cam, const 
         pb.frame_rays = win->frame_rays; pb.frame_done = win->frame_done; pb.host_flags = win->host_flags; pb.peer_flags = win->peer_flags;
     }
     CUDA_CHECK(cudaMemsetAsync(counter_.get(), 0, sizeof(uint32_t), stream));
-    if (count) persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+    if (split) launch_persist_split(sc, cam, fr, pb, blocks, node_min, count, stream);
+    else if (count) persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
     else persist8_kernel<false><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
     CUDA_CHECK(cudaGetLastError());
 }

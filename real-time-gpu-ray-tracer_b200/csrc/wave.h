@@ -79,6 +79,8 @@ struct PersistBuffers {
     float4 *acc;             // radiance sum of the finished samples.xyz, w = bits(pixel id, tile-major)
     uint4 *rng_a;            // XORWOW d, v0, v1, v2
     uint2 *rng_b;            // XORWOW v3, v4
+    float4 *hit;             // split kernel only (kernels_split.cu): the finished ray's hit t, u, v, bits(leaf ref) ...
+    int *hit_inst;           // ... and instance (-1 = miss), handed from the trace lane to the shade warp
     uint32_t *next_pixel;    // next unstarted pixel (index into the hand-out order)
     const uint32_t *tile_order;   // k-th 8x4 tile handed out
     uint32_t *tile_cost;     // rays traced per tile in this frame (orders the next frame)
@@ -100,6 +102,12 @@ struct PersistBuffers {
     volatile uint32_t *peer_flags;    // [n_frames] this rank's row of rank 0's device flag table (tile shards), or null
 };
 
+// kernels_split.cu
+int split_slots_per_block();
+int split_blocks_per_sm(bool count);
+void launch_persist_split(const SceneD &sc, const CameraD &cam, const FrameD &fr, const PersistBuffers &pb, uint32_t blocks, int node_min, bool count,
+                          cudaStream_t stream);
+
 class PersistRenderer {
 public:
     // one path-kernel launch per frame (plus the tile ordering); rays are counted on the device (fr.ray_counter[0])
@@ -110,12 +118,16 @@ public:
     int shade_min = 8;             // ... and shades finished rays once this many lanes wait for it
     int blocks_per_sm_override = 0;
     int tile_order = 1;            // 1: dear tiles first (cost = rays of the previous frame), 0: always scan order
+    bool split = false;            // A/B: the kernel with a dedicated shade warp per CTA (kernels_split.cu) instead of persist8_kernel
     uint32_t launches = 0;         // kernels launched by the last render()
     uint32_t n_blas_nodes = 0;     // set by the caller: size of the BLAS wide-node pool
 private:
     DeviceBuffer<float4> ray_o_, ray_d_, thr_, acc_;
     DeviceBuffer<uint4> rng_a_;
     DeviceBuffer<uint2> rng_b_;
+    DeviceBuffer<float4> hit_;
+    DeviceBuffer<int> hit_inst_;
+    int split_blocks_per_sm_[2] = {0, 0};
     DeviceBuffer<uint32_t> counter_, tile_cost_, vals_a_, vals_b_;
     DeviceBuffer<uint64_t> keys_a_, keys_b_;
     RadixSorter sorter_;

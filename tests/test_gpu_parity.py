@@ -524,3 +524,23 @@ def test_sah_build_ploc(pkg, port, idx):
     if len(plain["left"]) > 64:
         assert not np.array_equal(plain["left"], g["lbvh"]["left"]), "the PLOC tree equals the Karras tree"
     check_against_oracle(g, port.scene(sc, 5), sc)
+
+
+@pytest.mark.parametrize("idx", [0, 3, 4, 5])
+def test_split_kernel_variant(pkg, port, idx, monkeypatch):
+    """RTB200_SPLIT=1: the A/B variant of the path kernel with a dedicated shade warp per CTA and a pool of more paths than trace
+    lanes (csrc/kernels_split.cu; measured slower).  A path still consumes its pixel's stream in order, so the frame is
+    the default kernel's and the oracle's, bit for bit — also for a window of frames in flight."""
+    monkeypatch.setenv("RTB200_SPLIT", "1")
+    sc = parity_scenes(pkg.scenes)[idx]
+    g = gpu_frame(pkg, sc)
+    assert check_against_oracle(g, port.scene(sc, 12), sc)
+    r = pkg.Renderer(device=0)
+    try:
+        r.commitScene(sc)
+        w = r.submitFrames(0, 3, seeds=[SEED + 5, SEED, SEED + 9])
+        assert r.waitFrame(w, 1).rays == g["out"].rays
+        assert np.array_equal(r.readFrame(w, 1, pkg.abi.BUF_RGBA8).reshape(sc.height, sc.width, 4), g["rgba8"])
+        r.releaseWindow(w)
+    finally:
+        r.cleanup()

@@ -225,6 +225,26 @@ def reference_cuda_baseline(pkg, args, device, builds=3, budget_s=45.0):
                     "one frame per independent (randomly split) reference build"}
 
 
+def c2_dielectric_line(pkg, args, device, fpw):
+    """The EXTENDED config 2 of SURVEY 8d: the same 1 M-triangle scene with the metal third of the quads made of glass (index of
+    refraction 1.5) — BASELINE.json configs[1] names 'diffuse/metal/dielectric'.  The dielectric is an extension without a
+    reference counterpart (parity unpinned; the CUDA path agrees bit for bit with the oracle port's independent restatement,
+    tests/test_gpu_parity.py::test_dielectric_matches_port), so this line is reported beside the headline, never as it."""
+    sc = pkg.scenes.c2_dielectric(width=args.width, height=args.height, spp=args.spp, depth=args.depth, nx=args.nx, nz=args.nz)
+    r = pkg.Renderer(device=device)
+    try:
+        r.commitScene(sc)
+        sync = r.renderFrame(0, SEED)
+        r.runFrames(0, 2 * fpw, SEED, fpw, None)
+        n = max(fpw, min(args.steps, 2 * fpw))
+        st = r.runFrames(0, n, SEED, fpw, None)
+    finally:
+        r.cleanup()
+    return {"value": st.rays / (st.span_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": st.span_ms / n, "steps": n, "rays_per_frame": st.rays / n,
+            "synchronous_frame_ms": sync.render_ms, "materials": "rough + rough + dielectric (ior 1.5) by quad, as configs[1] with glass in place of metal",
+            "parity": "unpinned: the reference has no dielectric (include/Basic/BasicTypes.cuh:14-16); GPU == oracle port restatement bit for bit"}
+
+
 def c3_rebuild(pkg, device):
     """Config 3's per-frame work on its largest frame shape: 500 particles x 1258 strip triangles = 629 000 triangles
     (synthesised from the committed frame-0 fixture in the reference's on-disk layout): parse + upload + rebuild of all
@@ -256,6 +276,7 @@ def c3_rebuild(pkg, device):
             "build_kernel_launches": int(st.kernel_launches), "achieved_gbs": 280 * st.primitive_count / min(blas[1:]) / 1e6,
             "commit_upload_rebuild_wall_ms": min(wall[1:]), "render_ms_1080p_1spp": min(frame_ms[1:]), "rays": int(rays),
             "animation_loop_wall_ms_per_frame": statistics.median(loop_ms[2:]),
+            "parity": "particle vertex normals and the strip -> triangle rule are restated (the reference calls the VTK library, absent here): unpinned; primary-hit ids and t are not affected",
             "what": "rt_set_vtk_frame on 500-particle frames with rt_prefetch_vtk_frame reading the next one ahead; lbvh_rebuild_ms = CUDA events, "
                     "triangles resident -> wide BVH ready; animation_loop = set frame + rebuild + render 1080p, host wall per frame"}
 
@@ -389,6 +410,7 @@ def run_c3(args):
                            "frames": F, "width": W, "height": H, "spp": 1, "depth": 10,
                            "l2": "every frame is a new scene (new BVH, new triangle records): nothing is reused between timed iterations"},
                 "parallelism": f"frames i mod {world}, scene rebuilt per frame on the owning GPU, no per-frame exchange" if world > 1 else "single GPU",
+                "parity": "particle vertex normals and the strip -> triangle rule are restated (the reference calls the VTK library, absent here): unpinned",
                 "frames_per_s": F * args.steps / (max_dev_ms * 1e-3), "wall_ms_per_step": max_wall_ms / args.steps,
                 "wall_frames_per_s_one_renderer": F * args.steps / (max_wall_ms * 1e-3),
                 "triangles_rebuilt_per_step": tot_tris / args.steps, "slowest_rebuild_ms": max_rebuild,
@@ -717,6 +739,12 @@ def run_ours(args):
         c3 = None
         if world == 1 and not args.no_c3:
             c3 = c3_rebuild(pkg, local)
+        c2d = None
+        if world == 1 and not args.no_c3 and args.config == "c2" and not comparison:
+            try:
+                c2d = c2_dielectric_line(pkg, args, local, fpw)
+            except Exception as e:   # noqa: BLE001
+                c2d = {"unavailable": f"{type(e).__name__}: {e}"}
         metric = METRIC if args.config == "c2" else f"Mrays/s ({cfg['workload'].split(',')[0]})"
         line = {"metric": metric, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
@@ -737,6 +765,8 @@ def run_ours(args):
                 "gpu_launches": int(launches), "clocks": clocks}
         if c3:
             line["c3_particle_rebuild"] = c3
+        if c2d:
+            line["c2_dielectric"] = c2d
         if refcuda:
             line["reference_cuda"] = refcuda
             if "speedup_vs_median" in refcuda:

@@ -122,7 +122,8 @@ typedef struct rt_camera_input {
  * (Rodrigues rotation, include/Basic/Vec3.cuh:140-160), optional pitch clamp, then W/A/S/D in the horizontal
  * plane, SPACE / LSHIFT along `up`, diagonal moves normalised.  The caller feeds the result to
  * rt_configure_camera before the next rt_render_frame (Renderer.cu:247-255 does exactly that every frame).
- * Restated from the reference (its file needs SDL/GL headers to compile): PARITY UNPINNED.                     */
+ * Transliterated from the reference, same variable flow and branch order (its file needs SDL/GL headers to compile,
+ * so it cannot be run here): PARITY UNPINNED.                     */
 enum rt_key { RT_KEY_W = 1, RT_KEY_A = 2, RT_KEY_S = 4, RT_KEY_D = 8, RT_KEY_SPACE = 16, RT_KEY_LSHIFT = 32 };
 typedef struct rt_camera_motion {
     int32_t  dx, dy;             /* relative mouse motion of this step, pixels                                   */

@@ -288,13 +288,19 @@ int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_
  * instead of idling through k's tail (a pixel is sequential work: at a 1/8 image shard that tail is a third of a frame).
  * Every frame is, bit for bit, the frame rt_render_frame(frame, seed) produces.  Two windows may be in flight
  * (handles 0 and 1): while one drains, the next one's preparation and first pixels already run on a second stream.
- * The camera, window size and tile shard are those of the context at submit time and are fixed within a window.
+ * The window size and the tile shard are those of the context at submit time; so is the camera, unless
+ * rt_set_window_cameras gave every frame of the window its own.
  * rt_frame_out of a pipelined frame: rays, primary_rays, stack_overflow (of the window so far) and render_ms = host
  * clock from the window's submission to the frame's completion (its latency); the per-stage times are 0.            */
 #define RT_MAX_FRAMES_IN_FLIGHT 8
 /* seeds: one per frame (NULL: `seed0` for every frame).  Returns at once; *window receives the handle.  RT_ERR_STATE
  * when both windows are in flight.                                                                                   */
 int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const uint64_t *seeds, uint64_t seed0, uint32_t *window);
+/* Cameras of the frames of the NEXT window (n_frames of them, in frame order; consumed by the next rt_submit_frames, which
+ * must have that many frames): the reference re-reads its controller every frame (src/Global/Renderer.cu:247-255), so a
+ * scripted camera path (rt_camera_step) can run inside a window too.  Window size, sample_count and ray_trace_depth stay
+ * those of rt_configure_camera.  Without this call every frame of a window uses the configured camera.                 */
+int rt_set_window_cameras(rt_ctx *ctx, const rt_camera_input *cameras, uint32_t n_frames);
 /* Blocks until frame k (0-based within the window) is complete on this context's device — and, on rank 0 of a tile shard
  * with a frame ring (below), until every rank's tiles of that frame have landed in the ring.                          */
 int rt_wait_frame(rt_ctx *ctx, uint32_t window, uint32_t k, rt_frame_out *out);

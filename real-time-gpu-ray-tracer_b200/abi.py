@@ -126,7 +126,7 @@ EXPORTS = [
     "rt_render_frame", "rt_set_instance_xforms", "rt_read_framebuffer", "rt_framebuffer_device_ptr", "rt_write_ppm", "rt_write_image",
     "rt_set_tile_shard", "rt_read_lbvh", "rt_read_wide_bvh", "rt_load_vtk_series", "rt_set_vtk_frame", "rt_prefetch_vtk_frame",
     "rt_probe_read_bandwidth", "rt_run_vtk_animation", "rt_camera_step",
-    "rt_submit_frames", "rt_wait_frame", "rt_read_frame", "rt_release_window", "rt_run_frames",
+    "rt_submit_frames", "rt_set_window_cameras", "rt_wait_frame", "rt_read_frame", "rt_release_window", "rt_run_frames",
     "rt_commit_extension_primitives", "rt_primitive_type_count",
     "rt_frame_ring_create", "rt_frame_ring_open", "rt_frame_ring_attach", "rt_frame_ring_close",
 ]
@@ -175,6 +175,7 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_camera_step.argtypes = [C.POINTER(CameraInput), C.POINTER(CameraMotion), C.POINTER(CameraInput), C.POINTER(C.c_int)]
     lib.rt_probe_read_bandwidth.argtypes = [vp, sz, i32, C.POINTER(C.c_double)]
     lib.rt_submit_frames.argtypes = [vp, u64, u32, vp, u64, C.POINTER(u32)]
+    lib.rt_set_window_cameras.argtypes = [vp, vp, u32]
     lib.rt_wait_frame.argtypes = [vp, u32, u32, C.POINTER(FrameOut)]
     lib.rt_read_frame.argtypes = [vp, u32, u32, i32, vp, sz]
     lib.rt_release_window.argtypes = [vp, u32, C.POINTER(WindowStats)]

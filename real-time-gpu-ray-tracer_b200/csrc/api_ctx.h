@@ -97,6 +97,7 @@ struct rt_ctx {
     FrameWindow *win[2] = {nullptr, nullptr};
     FrameRing *ring = nullptr;
     uint32_t next_window = 0;
+    std::vector<CameraD> window_cams;        // rt_set_window_cameras: cameras of the frames of the NEXT window (consumed by it)
     DeviceBuffer<uint8_t> d_rgba8;
     DeviceBuffer<float> d_radiance, d_aov_t;
     DeviceBuffer<int> d_aov_inst, d_aov_prim;

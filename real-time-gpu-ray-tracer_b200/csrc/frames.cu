@@ -36,6 +36,8 @@ struct FrameWindow {
     DeviceBuffer<uint32_t> frame_done;
     PinnedBuffer<unsigned long long> h_counters;
     PinnedBuffer<uint32_t> h_peer_flags;           // rank 0: poll target for the ring's flag table
+    DeviceBuffer<CameraD> d_cams;                  // per-frame cameras of the window (rt_set_window_cameras)
+    PinnedBuffer<CameraD> h_cams;
     uint32_t *h_flags = nullptr;                   // mapped pinned: frame k complete <=> h_flags[k] == ticket
     PersistRenderer persist;
     // state of the window in flight
@@ -188,6 +190,12 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
     w.counters.reserve(8 + RT_MAX_FRAMES_IN_FLIGHT);
     w.h_counters.reserve(8 + RT_MAX_FRAMES_IN_FLIGHT);
     w.frame_done.reserve(RT_MAX_FRAMES_IN_FLIGHT);
+    const bool cams = !ctx->window_cams.empty();
+    if (cams && ctx->window_cams.size() != n_frames) {
+        ctx->window_cams.clear();
+        return rt_fail(ctx, RT_ERR_ARGUMENT, "rt_submit_frames: rt_set_window_cameras gave another number of cameras than this window has frames");
+    }
+    if (cams) { w.d_cams.reserve(RT_MAX_FRAMES_IN_FLIGHT); w.h_cams.reserve(RT_MAX_FRAMES_IN_FLIGHT); }
     ctx->d_rng_tables.reserve(RNG_TABLE_WORDS);
 
     cudaStream_t s = w.stream;
@@ -214,6 +222,11 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
     CUDA_CHECK(cudaEventRecord(w.ev_begin, s));
     CUDA_CHECK(cudaMemsetAsync(w.counters.get(), 0, (8 + RT_MAX_FRAMES_IN_FLIGHT) * sizeof(unsigned long long), s));
     CUDA_CHECK(cudaMemsetAsync(w.frame_done.get(), 0, RT_MAX_FRAMES_IN_FLIGHT * sizeof(uint32_t), s));
+    if (cams) {
+        std::copy(ctx->window_cams.begin(), ctx->window_cams.end(), w.h_cams.get());
+        CUDA_CHECK(cudaMemcpyAsync(w.d_cams.get(), w.h_cams.get(), n_frames * sizeof(CameraD), cudaMemcpyHostToDevice, s));
+        ctx->window_cams.clear();                     // the cameras belong to this window only
+    }
 
     FrameD fr{};
     FrameRing *ring = ctx->ring;
@@ -264,6 +277,7 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
     CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void **>(&dev_flags), w.h_flags, 0));
     win.host_flags = dev_flags;
     win.peer_flags = ring ? ring->flags(wi, ctx->shard_rank) : nullptr;
+    win.frame_cams = cams ? w.d_cams.get() : nullptr;
     w.persist.node_min = ctx->persist.node_min; w.persist.shade_min = ctx->persist.shade_min;
     w.persist.blocks_per_sm_override = ctx->persist.blocks_per_sm_override; w.persist.tile_order = ctx->persist.tile_order;
     w.persist.split = ctx->persist.split;
@@ -281,6 +295,23 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
     w.in_flight = true;
     ctx->next_window = wi ^ 1u;
     *window = wi;
+    RT_API_END(ctx)
+}
+
+int rt_set_window_cameras(rt_ctx *ctx, const rt_camera_input *cameras, uint32_t n_frames) {
+    RT_API_BEGIN(ctx)
+    ctx->window_cams.clear();
+    if (n_frames == 0) return RT_OK;
+    if (!ctx->camera_set) return rt_fail(ctx, RT_ERR_STATE, "rt_set_window_cameras: configure the camera first (window size, samples and depth come from it)");
+    if (!cameras || n_frames > RT_MAX_FRAMES_IN_FLIGHT) return rt_fail(ctx, RT_ERR_ARGUMENT, "rt_set_window_cameras: 1 <= n_frames <= RT_MAX_FRAMES_IN_FLIGHT cameras");
+    std::vector<CameraD> cams(n_frames);
+    for (uint32_t k = 0; k < n_frames; k++) {
+        const std::string e = HostScene::make_camera(ctx->hs.window, cameras[k], cams[k]);
+        if (!e.empty()) return rt_fail(ctx, RT_ERR_ARGUMENT, e);
+        if (cams[k].sqrtSamples != ctx->hs.cam.sqrtSamples || cams[k].depth != ctx->hs.cam.depth)
+            return rt_fail(ctx, RT_ERR_ARGUMENT, "rt_set_window_cameras: sample_count and ray_trace_depth are those of the configured camera for every frame of a window");
+    }
+    ctx->window_cams = cams;
     RT_API_END(ctx)
 }
 

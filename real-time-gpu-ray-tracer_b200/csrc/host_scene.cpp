@@ -281,12 +281,20 @@ std::string HostScene::plan_blas() {
 
 // RendererImpl::calculateCameraProperties (reference src/Global/RenderPin.cu:73-95), same operation order
 std::string HostScene::configure_camera(const rt_window &w, const rt_camera_input &in) {
+    CameraD c{};
+    const std::string e = make_camera(w, in, c);
+    if (!e.empty()) return e;
+    window = w;
+    cam = c;
+    return "";
+}
+
+std::string HostScene::make_camera(const rt_window &w, const rt_camera_input &in, CameraD &cam) {
     if (w.width == 0 || w.height == 0) return "rt_configure_camera: bad window";
     if (in.sample_count == 0) return "rt_configure_camera: sample_count must be >= 1";
     // the path kernels carry (sample index, depth) of a path in one 32-bit word, 16 bits each
     if (in.sample_count >= 256ull * 256ull) return "rt_configure_camera: sample_count must be below 65536 (255 x 255 strata)";
     if (in.ray_trace_depth > 65535ull) return "rt_configure_camera: ray_trace_depth must be at most 65535";
-    window = w;
     const f3 center = V(in.center), target = V(in.target), up = V(in.up);
     float d2 = 0.0f;
     d2 += (center.x - target.x) * (center.x - target.x);

@@ -56,6 +56,8 @@ struct HostScene {
     std::string configure_instances(const rt_instance_desc *d, size_t n, const rt_instance_xform *x);
     std::string plan_blas();                      // fills seg_*, inst_blas, inst_box, inst_centroid
     std::string configure_camera(const rt_window &w, const rt_camera_input &c);
+    // the derived camera of (window, input) without touching this scene's own (per-frame cameras of a window of frames in flight)
+    static std::string make_camera(const rt_window &w, const rt_camera_input &c, CameraD &out);
     // per frame: transform arguments -> kernel input records (trig evaluated here with the host libm)
     void fill_xform_in(InstanceXformIn *out, const std::vector<int> &seg_root) const;
     size_t prim_bytes() const;

@@ -43,7 +43,10 @@ constexpr uint32_t NG_INNER = 0x00FFFFFFu;      // node group has pending inner 
 #define RT_STAGE_TOP_NODES 0
 #endif
 enum : uint32_t { ST_DEAD = 0u, ST_TRACE = 1u, ST_SHADE = 2u, ST_FRESH = 3u };
-template<bool COUNT>
+// CAMS: every frame of the window has its own camera pose (pb.frame_cams, global memory, indexed by the path's frame); the
+// default instantiation (false) reads the one camera from the kernel parameters and is, instruction for instruction, the
+// kernel without this option.
+template<bool COUNT, bool CAMS = false>
 __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
                                                                             const __grid_constant__ FrameD fr, const __grid_constant__ PersistBuffers pb,
                                                                             int shade_min, int node_min) {
@@ -200,7 +203,7 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                     fr.aov_inst[lp] = has ? hit.inst : -1;
                     fr.aov_prim[lp] = has ? (int) ((ref_type(hit.leaf) << 28) | sc.leaf_prims8[ref_pos(hit.leaf)]) : -1;
                 }
-                const bool alive = shade_scatter<true>(sc, cam, ray, hit, thr, rng, fw * pb.inst_stride);
+                const bool alive = shade_scatter<true>(sc, CAMS ? pb.frame_cams[fw] : cam, ray, hit, thr, rng, fw * pb.inst_stride);
                 depth++;
                 if (!(alive && depth < cam.depth)) {
                     // path over: rayColor returns the throughput (Q6); next sample or next pixel
@@ -268,7 +271,7 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                     uint32_t lx, ly;
                     pixel_coords(pid & PID_MASK, pb.tiles_x, lx, ly);
                     const uint32_t si = sample / cam.sqrtSamples, sj = sample % cam.sqrtSamples;
-                    ray = primary_ray(cam, lx, global_row(fr, ly), si, sj, rng);
+                    ray = primary_ray(CAMS ? pb.frame_cams[pid >> 28] : cam, lx, global_row(fr, ly), si, sj, rng);
                     thr = mk3(1.f, 1.f, 1.f);
                     depth = 0;
                 }
@@ -355,7 +358,7 @@ void PersistRenderer::render_window(const SceneD &sc, const CameraD &cam, const 
     uint32_t want_blocks = (pb.n_pixels + PT - 1) / PT;
     uint32_t blocks = std::min<uint32_t>((uint32_t) (sm_count * bps), std::max(1u, want_blocks));
     size_t n_threads = (size_t) blocks * PT;
-    if (split) {                                    // one path-state entry per path of a CTA's pool
+    if (split && !(win && win->frame_cams)) {       // one path-state entry per path of a CTA's pool
         if (split_blocks_per_sm_[count ? 1 : 0] == 0) split_blocks_per_sm_[count ? 1 : 0] = split_blocks_per_sm(count);
         int sb = split_blocks_per_sm_[count ? 1 : 0];
         if (blocks_per_sm_override > 0) sb = std::min(sb, blocks_per_sm_override);
@@ -397,9 +400,11 @@ void PersistRenderer::render_window(const SceneD &sc, const CameraD &cam, const 
         pb.tlas_node_stride = win->tlas_node_stride; pb.tlas_leaf_stride = win->tlas_leaf_stride; pb.inst_stride = win->inst_stride;
         pb.valid_pixels = win->valid_pixels; pb.ticket = win->ticket;
         pb.frame_rays = win->frame_rays; pb.frame_done = win->frame_done; pb.host_flags = win->host_flags; pb.peer_flags = win->peer_flags;
+        pb.frame_cams = win->frame_cams;
     }
     CUDA_CHECK(cudaMemsetAsync(counter_.get(), 0, sizeof(uint32_t), stream));
-    if (split) launch_persist_split(sc, cam, fr, pb, blocks, node_min, count, stream);
+    if (pb.frame_cams) persist8_kernel<false, true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);      // per-frame cameras (never with counting / split)
+    else if (split) launch_persist_split(sc, cam, fr, pb, blocks, node_min, count, stream);
     else if (count) persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
     else persist8_kernel<false><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
     CUDA_CHECK(cudaGetLastError());

@@ -100,6 +100,7 @@ struct PersistBuffers {
     uint32_t *frame_done;             // [n_frames] finished pixels per frame (null: no completion tracking)
     volatile uint32_t *host_flags;    // [n_frames] mapped pinned host memory: = ticket once the frame is complete
     volatile uint32_t *peer_flags;    // [n_frames] this rank's row of rank 0's device flag table (tile shards), or null
+    const CameraD *frame_cams;        // [n_frames] camera of every frame of the window (rt_set_window_cameras), or null: the one camera
 };
 
 // kernels_split.cu

@@ -213,6 +213,11 @@ class Renderer:
         self._check(self.lib.rt_submit_frames(self.ctx, first_frame, n_frames, sp, seed, C.byref(w)))
         return w.value
 
+    def setWindowCameras(self, cameras):
+        """Cameras (abi.CameraInput) of the frames of the next submitted window, one per frame."""
+        arr = (abi.CameraInput * len(cameras))(*cameras)
+        self._check(self.lib.rt_set_window_cameras(self.ctx, C.cast(arr, C.c_void_p), len(cameras)))
+
     def waitFrame(self, window: int, k: int) -> abi.FrameOut:
         out = abi.FrameOut()
         self._check(self.lib.rt_wait_frame(self.ctx, window, k, C.byref(out)))

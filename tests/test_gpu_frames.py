@@ -187,3 +187,46 @@ def test_frames_in_flight_need_the_default_kernel(pkg):
             assert e.value.code == -3
         finally:
             r.cleanup()
+
+
+def test_window_with_a_camera_per_frame(pkg):
+    """rt_set_window_cameras: a scripted camera walk (rt_camera_step, the reference's controller) inside ONE window of frames in
+    flight — the reference re-reads its controller every frame (src/Global/Renderer.cu:247-255).  Every frame equals the
+    synchronous frame rendered after rt_configure_camera with that frame's camera."""
+    sc, update = moving_scene(pkg, width=160, height=90, spp=2, depth=6)
+    cams = [sc.camera_input()]
+    for dx, dy, keys in [(40, -10, pkg.abi.KEY_W), (0, 0, pkg.abi.KEY_D | pkg.abi.KEY_SPACE), (-90, 25, 0), (15, 5, pkg.abi.KEY_S), (0, -30, pkg.abi.KEY_A)]:
+        nxt, moved = pkg.cameraStep(cams[-1], dx, dy, keys, move_speed=0.4)
+        assert moved
+        cams.append(nxt)
+    frames = list(range(len(cams)))
+    want = []
+    r = pkg.Renderer(device=0)
+    try:
+        r.commitScene(sc, update)
+        for f, cam in zip(frames, cams):
+            r.configureCamera(sc.window(), cam)
+            out = r.renderFrame(f, SEED + f)
+            want.append((out.rays, r.readFramebuffer(pkg.abi.BUF_RGBA8).copy()))
+        assert not np.array_equal(want[0][1], want[3][1])
+        r.configureCamera(sc.window(), cams[0])
+        r.setWindowCameras(cams)
+        w = r.submitFrames(0, len(cams), seeds=[SEED + f for f in frames])
+        for k in frames:
+            assert r.waitFrame(w, k).rays == want[k][0]
+            assert np.array_equal(r.readFrame(w, k), want[k][1]), f"frame {k}"
+        r.releaseWindow(w)
+        # the cameras were this window's: the next one uses the configured camera again
+        w = r.submitFrames(0, 2, seeds=[SEED, SEED + 1])
+        assert np.array_equal(r.readFrame(w, 0), want[0][1]) and not np.array_equal(r.readFrame(w, 1), want[1][1])
+        r.releaseWindow(w)
+        r.setWindowCameras(cams[:3])
+        with pytest.raises(pkg.RtError) as e:
+            r.submitFrames(0, 4)                   # three cameras for four frames
+        assert e.value.code == -2
+        bad = sc.camera_input()
+        bad.sample_count = 16
+        with pytest.raises(pkg.RtError):
+            r.setWindowCameras([bad])
+    finally:
+        r.cleanup()

@@ -153,6 +153,7 @@ const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->err.c_str() : "
 int rt_commit_geometry(rt_ctx *ctx, const rt_sphere *spheres, size_t sphere_count, const rt_parallelogram *parallelograms,
                        size_t parallelogram_count, const rt_triangle *triangles, size_t triangle_count) {
     RT_API_BEGIN(ctx)
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_commit_geometry: not while frames are in flight (rt_release_window first): the window's kernel is reading the scene");
     // the vectors are about to grow: their old storage must not stay registered when it is freed
     if (triangle_count * 9 > ctx->hs.tri_verts.capacity()) ctx->pin_verts.release();
     if (triangle_count > ctx->hs.tri_shade.capacity()) ctx->pin_shade.release();
@@ -175,6 +176,7 @@ int rt_commit_geometry(rt_ctx *ctx, const rt_sphere *spheres, size_t sphere_coun
 
 int rt_commit_materials(rt_ctx *ctx, const rt_rough *roughs, size_t rough_count, const rt_metal *metals, size_t metal_count) {
     RT_API_BEGIN(ctx)
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_commit_materials: not while frames are in flight (rt_release_window first): the window's kernel is reading the scene");
     const std::string e = ctx->hs.commit_materials(roughs, rough_count, metals, metal_count);
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
     ctx->d_roughs.upload(ctx->hs.roughs.data(), ctx->hs.roughs.size(), ctx->stream);
@@ -233,6 +235,7 @@ int rt_set_instance_xforms(rt_ctx *ctx, const rt_instance_xform *xforms, size_t 
 
 int rt_build_acceleration_structure(rt_ctx *ctx) {
     RT_API_BEGIN(ctx)
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_build_acceleration_structure: not while frames are in flight (rt_release_window first): the window's kernel is reading the scene");
     if (!ctx->geometry_committed || !ctx->instances_configured) return fail(ctx, RT_ERR_STATE, "rt_build_acceleration_structure: commit geometry and instances first");
     HostScene &hs = ctx->hs;
     const std::string e = hs.plan_blas();
@@ -290,6 +293,7 @@ int rt_get_build_stats(const rt_ctx *ctx, rt_build_stats *out) {
 
 int rt_configure_camera(rt_ctx *ctx, const rt_window *window, const rt_camera_input *camera) {
     RT_API_BEGIN(ctx)
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_configure_camera: not while frames are in flight (rt_release_window first): the window's kernel is reading the scene");
     if (!window || !camera) return fail(ctx, RT_ERR_ARGUMENT, "rt_configure_camera: null argument");
     const std::string e = ctx->hs.configure_camera(*window, *camera);
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);

@@ -84,6 +84,11 @@ def test_two_windows_in_flight_and_the_loop(pkg):
         with pytest.raises(pkg.RtError) as e:
             r.submitFrames(7, 2)                    # both windows are in flight
         assert e.value.code == -3
+        for call in (lambda: r.buildAccelerationStructure(), lambda: r.configureCamera(sc.window(), sc.camera_input()),
+                     lambda: r.commitGeometryData(sc.spheres, sc.parallelograms, sc.triangles)):
+            with pytest.raises(pkg.RtError) as e:   # the scene a window's kernel reads cannot be replaced under it
+                call()
+            assert e.value.code == -3
         for w, first, n in ((b, 4, 3), (a, 0, 4)):
             for k in range(n):
                 assert r.waitFrame(w, k).rays == want[first + k]["rays"]

@@ -51,6 +51,32 @@ for rounds in range(3):
             if not same:
                 print(f"round {rounds} frame {k}: {int((got[k] != want).sum())} bytes differ")
         ref.cleanup()
+# the library's loop with a SLOW consumer on rank 0 (its sink sleeps): the other ranks run ahead and must wait for rank 0 to release
+# a window slot before they store into it again (the ring's back-pressure), or rank 0 would read overwritten frames
+import time
+n_loop = 24
+delivered = {}
+
+
+def sink(frame, img, out):
+    if rank == 0:
+        time.sleep(0.03)
+        delivered[frame] = img.copy()
+    return 0
+
+
+r.runFrames(0, n_loop, SEED, 4, sink)
+dist.barrier()
+if rank == 0:
+    ref = pkg.Renderer(device=local)
+    ref.commitScene(sc)
+    for k in range(n_loop):
+        ref.renderFrame(k, SEED)
+        same = k in delivered and np.array_equal(delivered[k].reshape(-1), ref.readFramebuffer(pkg.abi.BUF_RGBA8))
+        ok = ok and same
+        if not same:
+            print(f"loop frame {k}: differs or missing")
+    ref.cleanup()
 # the synchronous frame through the ring as well
 out = r.renderFrame(0, SEED)
 torch.cuda.synchronize()

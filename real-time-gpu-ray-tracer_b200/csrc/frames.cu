@@ -85,6 +85,12 @@ void rt_release_frames(rt_ctx *ctx) {
 
 namespace {
 
+// Back-pressure of the frame ring.  A rank may not store into window slot w again before rank 0 has let go of the frames the
+// slot held: rank 0 publishes, per slot, the ticket of the last window it RELEASED (two words behind the flag table, inside
+// the allocation's slack), and the other ranks wait for it before they submit the slot's next window.  Without it a rank
+// that runs ahead of a slow consumer on rank 0 (a sink that writes files) would overwrite frames rank 0 has not read yet.
+uint32_t *ring_ack(const FrameRing *r, uint32_t window) { return r->flag_table() + FrameRing::flag_words(r->world) + window; }
+
 uint32_t max_shard_rows(const rt_ctx *c) {
     const uint32_t tiles = (c->hs.window.height + c->tile_rows - 1) / c->tile_rows;
     return c->shard_world == 1 ? c->hs.window.height : ((tiles + c->shard_world - 1) / c->shard_world) * c->tile_rows;
@@ -209,6 +215,19 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
         CUDA_CHECK(cudaStreamWaitEvent(s, w.ev_fork, 0));
     }
     ctx->tlas_fresh = false;
+    if (ctx->ring && ctx->shard_rank != 0 && w.ticket != 0u) {
+        // rank 0 must have released this slot's previous window (ring_ack)
+        w.h_peer_flags.reserve(FrameRing::flag_words(ctx->ring->world));
+        const auto t0 = std::chrono::steady_clock::now();
+        for (;;) {
+            CUDA_CHECK(cudaMemcpyAsync(w.h_peer_flags.get(), ring_ack(ctx->ring, wi), sizeof(uint32_t), cudaMemcpyDeviceToHost, w.copy_stream));
+            CUDA_CHECK(cudaStreamSynchronize(w.copy_stream));
+            if (w.h_peer_flags.get()[0] >= w.ticket) break;
+            if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 120.0)
+                return rt_fail(ctx, RT_ERR_STATE, "frame ring: rank 0 did not release the previous window of this slot within 120 s");
+            std::this_thread::yield();
+        }
+    }
     w.ticket++;
     if (w.ticket == 0u) w.ticket = 1u;
     w.n_frames = n_frames;
@@ -400,6 +419,12 @@ int rt_release_window(rt_ctx *ctx, uint32_t window, rt_window_stats *stats) {
         stats->stack_overflow = (uint32_t) w.h_counters.get()[1];
         CUDA_CHECK(cudaEventElapsedTime(&stats->device_ms, w.ev_begin, w.ev_end));
         CUDA_CHECK(cudaEventElapsedTime(&stats->prepare_ms, w.ev_begin, w.ev_prep));
+    }
+    if (ctx->ring && ctx->shard_rank == 0 && ctx->ring->world > 1) {       // the slot's frames may be overwritten now (ring_ack)
+        w.h_peer_flags.reserve(FrameRing::flag_words(ctx->ring->world));
+        w.h_peer_flags.get()[0] = w.ticket;
+        CUDA_CHECK(cudaMemcpyAsync(ring_ack(ctx->ring, window), w.h_peer_flags.get(), sizeof(uint32_t), cudaMemcpyHostToDevice, w.copy_stream));
+        CUDA_CHECK(cudaStreamSynchronize(w.copy_stream));
     }
     if (w.h_counters.get()[1] != 0) return rt_fail(ctx, RT_ERR_OVERFLOW, "frames in flight: a traversal stack overflowed: the frames of this window are incomplete");
     RT_API_END(ctx)

@@ -292,7 +292,9 @@ int rt_set_tile_shard(rt_ctx *ctx, uint32_t rank, uint32_t world, uint32_t tile_
  * rt_set_window_cameras gave every frame of the window its own.
  * rt_frame_out of a pipelined frame: rays, primary_rays, stack_overflow (of the window so far) and render_ms = host
  * clock from the window's submission to the frame's completion (its latency); the per-stage times are 0.            */
-#define RT_MAX_FRAMES_IN_FLIGHT 8
+#ifndef RT_MAX_FRAMES_IN_FLIGHT
+#define RT_MAX_FRAMES_IN_FLIGHT 8     /* at most 16: a path carries its frame in four bits */
+#endif
 /* seeds: one per frame (NULL: `seed0` for every frame).  Returns at once; *window receives the handle.  RT_ERR_STATE
  * when both windows are in flight.                                                                                   */
 int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const uint64_t *seeds, uint64_t seed0, uint32_t *window);

@@ -103,7 +103,7 @@ class LoopStats(C.Structure):
                 ("device_ms", C.c_double), ("span_ms", C.c_double), ("max_latency_ms", C.c_double)]
 
 
-MAX_FRAMES_IN_FLIGHT = 8
+MAX_FRAMES_IN_FLIGHT = int(os.environ.get("RTB200_MAX_WINDOW", "8"))      # RT_MAX_FRAMES_IN_FLIGHT of the loaded build (8 unless a variant build says otherwise)
 IPC_HANDLE_BYTES = 64
 
 FRAME_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(FrameOut))

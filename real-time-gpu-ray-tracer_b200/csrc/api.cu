@@ -119,7 +119,11 @@ int rt_create(rt_ctx **out, int cuda_device, uint32_t flags) {
     if (const char *e = getenv("RTB200_GROUPS")) c->wave.n_groups = atoi(e);
     if (const char *e = getenv("RTB200_GRAPHS")) c->wave.use_graphs = atoi(e) != 0;
     if (const char *e = getenv("RTB200_FINISH_DIVISOR")) c->wave.finish_divisor = atoi(e);
-    c->persist.node_min = c->wave.node_min;
+    // Vote thresholds of the path kernel, re-tuned under frames in flight (profiles/r02s_sweep.txt, r02t_sweep.txt): a node step
+    // while >= 18 lanes stand on a node, a shade step once >= 10 lanes wait (round 1, one frame at a time: 20 / 8).
+    // C2 1903 -> 1928 Mrays/s, 1/8 shard 21.51 -> 21.32 ms, C5 unchanged.  The wave comparison mode keeps its own 20.
+    c->persist.node_min = getenv("RTB200_NODE_MIN") ? c->wave.node_min : 18;
+    c->persist.shade_min = 10;
     c->persist.blocks_per_sm_override = c->wave.blocks_per_sm_override;
     if (const char *e = getenv("RTB200_SHADE_MIN")) c->persist.shade_min = atoi(e);
     if (const char *e = getenv("RTB200_TILE_ORDER")) c->persist.tile_order = atoi(e);

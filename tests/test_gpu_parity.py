@@ -544,3 +544,40 @@ def test_split_kernel_variant(pkg, port, idx, monkeypatch):
         r.releaseWindow(w)
     finally:
         r.cleanup()
+
+
+def test_vtk_real_mid_animation_frame(pkg, port, tmp_path):
+    """Config 3 on a REAL frame from the middle of the reference's animation (files/particle_mesh/particle_..4000.vtk, series entry 40,
+    100 particles: committed as tests/golden/particle_frame40.vtk) next to frame 0: series loader -> strips expanded on the device ->
+    batched LBVH -> render, against the oracle given the numpy parse of the same file.  (The vertex normals and the strip rule are
+    restated — the reference calls the VTK library: parity unpinned for the shading of particles, pinned for ids and t.)"""
+    import json
+    import os
+    import shutil
+    S = pkg.scenes
+    golden = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    os.makedirs(tmp_path / "particle_mesh")
+    names = []
+    for k, f in enumerate(("particle_frame0.vtk", "particle_frame40.vtk")):
+        name = f"particle_mesh/particle_{k:015d}.vtk"
+        shutil.copy(os.path.join(golden, f), tmp_path / name)
+        names.append({"name": name, "time": 0.4 * k})
+    (tmp_path / "particle_mesh.vtk.series").write_text(json.dumps({"file-series-version": "1.0", "files": names}))
+    base = S.c1a(frame=40, width=320, height=180, spp=1, depth=10)
+    r = pkg.Renderer(device=0, flags=pkg.abi.FLAG_RECORD_PRIMARY_AOV)
+    try:
+        r.commitScene(base)
+        assert r.configureVTKFiles(str(tmp_path / "particle_mesh.vtk.series")) == 2
+        st = r.setVTKFrame(1)
+        sc = S.c3(os.path.join(golden, "particle_frame40.vtk"), frame=40, width=320, height=180, spp=1, depth=10)
+        n_particles = (len(sc.triangles) - 1) // 1258
+        assert n_particles > 25 and st.primitive_count == len(sc.triangles) - 1 + 4
+        out = r.renderFrame(0, SEED)
+        H, W = 180, 320
+        g = dict(out=out, radiance=r.readFramebuffer(pkg.abi.BUF_RADIANCE).reshape(H, W, 3).copy(), rgba8=r.readFramebuffer(pkg.abi.BUF_RGBA8).reshape(H, W, 4).copy(),
+                 t=r.readFramebuffer(pkg.abi.BUF_PRIMARY_T).reshape(H, W).copy(), inst=r.readFramebuffer(pkg.abi.BUF_PRIMARY_INSTANCE).reshape(H, W).copy(),
+                 prim=r.readFramebuffer(pkg.abi.BUF_PRIMARY_PRIM).reshape(H, W).copy())
+        assert (g["inst"] >= 5).sum() > 500, "the particles are not visible"
+        check_against_oracle(g, port.scene(sc, 40), sc)
+    finally:
+        r.cleanup()

@@ -11,6 +11,9 @@
 #include <cstdint>
 #include <vector>
 
+// a TLAS of at most this many instances is rebuilt by one block in one launch (kernels_wide.cu tlas_small_kernel)
+#define RT_TLAS_SMALL_MAX 1024
+
 class RadixSorter {
 public:
     // Sorts n (key, value) pairs by the low `key_bits` bits of the key.  On return `keys`/`vals` point at the
@@ -70,6 +73,7 @@ public:
 private:
     void reserve(int n, int n_segs, bool tris);
     void run_tree(int n, int n_segs, int key_bits, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count);
+    bool tlas_small(int n, int morton_bits, cudaStream_t stream);                                                      // kernels_wide.cu: one block, one launch
     void run_ploc(int n, int n_segs, cudaStream_t stream);                                                             // kernels_ploc.cu
     void collapse_wide(int n, int n_segs, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count);   // kernels_wide.cu
     int n_ = 0, n_segs_ = 0;

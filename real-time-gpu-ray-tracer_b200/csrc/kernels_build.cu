@@ -475,6 +475,7 @@ void LbvhBuilder::prepare_tlas(int n_instances) {
 void LbvhBuilder::build_tlas(int n_instances, int morton_bits, cudaStream_t stream, int sm_count) {
     const int n = n_instances;
     n_ = n; n_segs_ = 1; launches = 0;
+    if (tlas_small(n, morton_bits, stream)) return;        // up to RT_TLAS_SMALL_MAX instances: the whole rebuild is one launch
     set_single_segment_kernel<<<1, 1, 0, stream>>>(seg_offset_.get(), seg_type_.get(), (uint32_t) n);
     launches++;
     morton_kernel<<<div_up(n, BT), BT, 0, stream>>>(prim_lo_.get(), prim_hi_.get(), seg_offset_.get(), 1, seg_bounds_.get(), n, morton_bits,

@@ -394,7 +394,145 @@ __global__ void __launch_bounds__(256) emit_leaves8_kernel(GeometryD geo, const 
     }
 }
 
+// ---- small TLAS: the whole per-frame rebuild in ONE block, ONE launch -------------------------------------------------------
+// The TLAS of every config but C5 has at most a few hundred instances.  As a chain of general kernels (Morton keys, four
+// radix passes, Karras, refit, collapse, leaf emission: 16 launches, each of them a few microseconds of work behind a launch
+// gap) it cost 0.22 ms per frame of config 3.  Here one block of 512 threads does the same steps between __syncthreads():
+// keys and the sort in shared memory (bitonic on (key, instance index): the order a stable radix sort gives), Karras from the
+// shared keys, the atomic refit with its arrival flags in shared memory, the collapse level by level (the items of one level
+// are ready when the previous level's barrier has passed: no polling), the leaf-order instance indices.  Every array the long
+// path leaves behind (sorted keys, binary topology, boxes, counters) is written too, so introspection sees the same tree;
+// the node contents are those of the serial twin (same per-element functions), which the parity tests compare.
+struct TlasSmallArgs {
+    const float4 *prim_lo, *prim_hi;
+    const uint32_t *bounds;
+    int n, bits;
+    uint64_t *keys;
+    uint32_t *vals;
+    int *left, *right, *parent, *leaf_parent, *seg_root;
+    int2 *range;
+    float4 *node_lo, *node_hi;
+    uint32_t *seg_offset, *seg_type;
+    int *queue;
+    uint32_t *counters;
+    BvhNode8 *nodes8;
+    uint32_t *leaf_pos8, *leaf_prims8;
+};
+constexpr int TS_THREADS = 512;
+
+__global__ void __launch_bounds__(TS_THREADS) tlas_small_kernel(TlasSmallArgs a) {
+    __shared__ uint64_t skey[RT_TLAS_SMALL_MAX];
+    __shared__ uint32_t sval[RT_TLAS_SMALL_MAX];
+    __shared__ int sflag[RT_TLAS_SMALL_MAX];
+    const int tid = threadIdx.x, n = a.n;
+    int N = 2;
+    while (N < n) N <<= 1;
+    // ---- Morton keys over the instance centres' bounds (morton_kernel), padding sorts last ----
+    Aabb scene;
+    scene.lo = mk3(ordered_to_float(a.bounds[0]), ordered_to_float(a.bounds[1]), ordered_to_float(a.bounds[2]));
+    scene.hi = mk3(ordered_to_float(a.bounds[3]), ordered_to_float(a.bounds[4]), ordered_to_float(a.bounds[5]));
+    for (int j = tid; j < N; j += TS_THREADS) {
+        if (j < n) {
+            skey[j] = morton_code(view_box(a.prim_lo, a.prim_hi, j), scene, a.bits);
+            sval[j] = (uint32_t) j;
+        } else {
+            skey[j] = ~0ull;
+            sval[j] = 0xFFFFFFFFu;
+        }
+        sflag[j] = 0;
+    }
+    if (tid == 0) {
+        a.seg_offset[0] = 0u; a.seg_offset[1] = (uint32_t) n; a.seg_type[0] = 0u;
+        a.counters[0] = 1u; a.counters[1] = 0u; a.counters[2] = 0u; a.counters[3] = 0u;
+        a.counters[4] = 0u; a.counters[5] = 1u; a.counters[6] = 0u;
+    }
+    __syncthreads();
+    // ---- bitonic sort by (key, instance index) ----
+    for (int k = 2; k <= N; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int p = tid; p < (N >> 1); p += TS_THREADS) {
+                const int i = 2 * p - (p & (j - 1)), q = i + j;
+                const uint64_t ki = skey[i], kq = skey[q];
+                const uint32_t vi = sval[i], vq2 = sval[q];
+                const bool greater = ki > kq || (ki == kq && vi > vq2);
+                if (greater == ((i & k) == 0)) { skey[i] = kq; skey[q] = ki; sval[i] = vq2; sval[q] = vi; }
+            }
+            __syncthreads();
+        }
+    }
+    for (int j = tid; j < n; j += TS_THREADS) { a.keys[j] = skey[j]; a.vals[j] = sval[j]; }
+    // ---- Karras hierarchy (karras_kernel) ----
+    for (int i = tid; i < n - 1; i += TS_THREADS) {
+        const KarrasNode k = karras_node(skey, n, i);
+        a.left[i] = k.left;
+        a.right[i] = k.right;
+        a.range[i] = make_int2(k.first, k.last);
+        if (k.left >= 0) a.parent[k.left] = i; else a.leaf_parent[~k.left] = i;
+        if (k.right >= 0) a.parent[k.right] = i; else a.leaf_parent[~k.right] = i;
+        if (i == 0) a.parent[0] = -1;
+    }
+    volatile int *vq = a.queue;
+    if (tid == 0) {
+        a.seg_root[0] = n > 1 ? 0 : make_leaf_ref(0u, sval[0]);
+        vq[0] = n > 1 ? 0 : ~0;
+    }
+    __syncthreads();
+    // ---- bottom-up refit (refit_kernel): the second child to arrive computes the node ----
+    if (n > 1) {
+        for (int pos = tid; pos < n; pos += TS_THREADS) {
+            int cur = a.leaf_parent[pos];
+            while (cur >= 0) {
+                __threadfence_block();
+                if (atomicAdd(&sflag[cur], 1) == 0) break;
+                __threadfence_block();
+                const int l = a.left[cur], r = a.right[cur];
+                float4 llo, lhi, rlo, rhi;
+                if (l >= 0) { llo = __ldcg(&a.node_lo[l]); lhi = __ldcg(&a.node_hi[l]); } else { const uint32_t p = sval[~l]; llo = a.prim_lo[p]; lhi = a.prim_hi[p]; }
+                if (r >= 0) { rlo = __ldcg(&a.node_lo[r]); rhi = __ldcg(&a.node_hi[r]); } else { const uint32_t p = sval[~r]; rlo = a.prim_lo[p]; rhi = a.prim_hi[p]; }
+                __stcg(&a.node_lo[cur], make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), __int_as_float(l)));
+                __stcg(&a.node_hi[cur], make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), __int_as_float(r)));
+                cur = a.parent[cur];
+            }
+        }
+    }
+    __syncthreads();
+    // ---- collapse into 8-wide nodes, one level per round (collapse_item; items [begin, end) were published by the previous round) ----
+    const BinaryTreeView view{a.range, a.node_lo, a.node_hi, a.prim_lo, a.prim_hi, a.vals};
+    uint32_t begin = 0u, end = 1u;
+    while (begin < end) {
+        for (uint32_t i = begin + (uint32_t) tid; i < end; i += TS_THREADS) collapse_item(view, vq[i], (int) i, 1, vq, a.counters, a.nodes8, a.leaf_pos8);
+        __syncthreads();
+        begin = end;
+        end = ((volatile uint32_t *) a.counters)[0];
+        __syncthreads();                       // everyone has read the count before the next round's allocations move it
+    }
+    if (tid == 0) { a.counters[2] = end; a.counters[3] = end; }
+    // ---- leaf-order instance indices (emit_leaves8_kernel, leaf_mode 1) ----
+    for (int q = tid; q < n; q += TS_THREADS) a.leaf_prims8[q] = sval[a.leaf_pos8[q]];
+}
+
 } // namespace
+
+bool LbvhBuilder::tlas_small(int n, int morton_bits, cudaStream_t stream) {
+    // RTB200_TLAS_FUSED=0: the general kernels for every size (A/B runs)
+    static const bool enabled = !(getenv("RTB200_TLAS_FUSED") && atoi(getenv("RTB200_TLAS_FUSED")) == 0);
+    if (!enabled || n < 1 || n > RT_TLAS_SMALL_MAX || emit_bvh2 || sah_rotations || ploc) return false;
+    keys_ = keys_a_.get(); keys_alt_ = keys_b_.get(); vals_ = vals_a_.get(); vals_alt_ = vals_b_.get();
+    TlasSmallArgs a;
+    a.prim_lo = prim_lo_.get(); a.prim_hi = prim_hi_.get(); a.bounds = seg_bounds_.get();
+    a.n = n; a.bits = morton_bits;
+    a.keys = keys_; a.vals = vals_;
+    a.left = left_.get(); a.right = right_.get(); a.parent = parent_.get(); a.leaf_parent = leaf_parent_.get(); a.seg_root = seg_root_.get();
+    a.range = range_.get();
+    a.node_lo = node_lo_.get(); a.node_hi = node_hi_.get();
+    a.seg_offset = seg_offset_.get(); a.seg_type = seg_type_.get();
+    a.queue = queue_.get(); a.counters = wide_counters_.get();
+    a.nodes8 = nodes8_.get(); a.leaf_pos8 = leaf_pos8_.get(); a.leaf_prims8 = leaf_prims8_.get();
+    tlas_small_kernel<<<1, TS_THREADS, 0, stream>>>(a);
+    CUDA_CHECK(cudaGetLastError());
+    launches++;
+    return true;
+}
 
 void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const GeometryD *geo, cudaStream_t stream, int sm_count) {
     if (collapse_blocks_per_sm_ == 0) {

@@ -20,7 +20,7 @@
 // A fourth type plugs in at compile time: -DRT_EXT_PRIMITIVE='"header.h"' names a header that defines ExtPrimD (its
 // 16-byte-aligned device record), RT_EXT_PRIMITIVE_NAME and PrimOps<3>; its records arrive through
 // rt_commit_extension_primitives.  tests/ext/rt_prim_disc.h is such a type (a disc), built only into the test variant
-// librtb200_disc.so and checked against the oracle port's independent disc (tests/test_gpu_ext_primitive.py).
+// librtb200_disc.so and checked against the oracle port's independent disc (tests/test_ext_primitive.py).
 #pragma once
 
 #include "rt_build_core.h"

@@ -414,6 +414,25 @@ void emul_count(void *h, uint64_t seed, int y0, int y1, int threads, uint64_t *o
     for (int k = 0; k < 4; k++) out4[k] = tot[k].load();
 }
 
+// rays traced by every pixel of rows [y0, y1) (row-major, width entries per row): the distribution of the sequential work a pixel
+// is (profiles/tools/tail_evidence.py: critical path of a frame / of a shard)
+void emul_pixel_rays(void *h, uint64_t seed, int y0, int y1, int threads, uint32_t *out) {
+    Emul &e = *(Emul *) h;
+    const CameraD &cam = e.hs.cam;
+    parallel_rows(y0, y1, threads, [&](int y) {
+        for (uint32_t x = 0; x < cam.width; x++) {
+            const uint32_t pixelIndex = cam.pitch * (uint32_t) y + x;
+            curandStateXORWOW_t st;
+            curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &st);
+            RngState r{st.d, st.v[0], st.v[1], st.v[2], st.v[3], st.v[4]};
+            uint32_t overflow = 0;
+            uint2 stack[RT_WIDE_STACK];
+            const PixelOut o = render_pixel<false, true>(e.sc, cam, x, (uint32_t) y, r, overflow, stack, 1);
+            out[(size_t) (y - y0) * cam.width + x] = o.rays;
+        }
+    });
+}
+
 // debugging aid for parity work: every path segment of one pixel — rows of 12 floats: sample, depth, ray origin, ray
 // direction, hit t (inf on a miss), instance, primitive ((type << 28) | index); returns the number of rows
 int emul_pixel_paths(void *h, uint64_t seed, uint32_t x, uint32_t y, float *out, int cap) {

@@ -197,6 +197,14 @@ class Emul:
         self.lib.emul_count(self.h, seed, y0, self.H if y1 is None else y1, threads or os.cpu_count() or 1, abi.ptr(out))
         return dict(rays=int(out[0]), nodes=int(out[1]), prims=int(out[2]), insts=int(out[3]))
 
+    def pixel_rays(self, seed, y0, y1, threads=None):
+        """rays traced by every pixel of rows [y0, y1): uint32 [y1 - y0, W]"""
+        out = np.zeros((y1 - y0, self.W), np.uint32)
+        self.lib.emul_pixel_rays.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        self.lib.emul_pixel_rays.restype = None
+        self.lib.emul_pixel_rays(self.h, seed, y0, y1, threads or os.cpu_count() or 1, abi.ptr(out))
+        return out
+
     def instances(self):
         out = np.zeros((len(self.sc.instances), 33), np.float32)
         self.lib.emul_instances(self.h, abi.ptr(out))

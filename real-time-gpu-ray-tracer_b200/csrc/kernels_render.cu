@@ -119,25 +119,27 @@ __device__ __forceinline__ void xorwow_matvec_low(const uint32_t *__restrict__ l
     v[0] = r0; v[1] = r1; v[2] = r2; v[3] = r3; v[4] = r4;
 }
 
-__global__ void __launch_bounds__(256) rng_init_tables_kernel(RngState *__restrict__ states, const uint32_t *__restrict__ tables, unsigned long long seed,
-                                                              uint32_t width, uint32_t pitch, uint32_t local_rows, uint32_t rank, uint32_t world,
-                                                              uint32_t tile_rows) {
-    const uint32_t lp0 = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool valid = lp0 < width * local_rows;
-    const uint32_t lp = valid ? lp0 : width * local_rows - 1u;          // lanes past the end shadow the last pixel (warp collectives below)
+// pixelIndex of local pixel lp (tile-interleaved shard rows, cam.pitch)
+__device__ __forceinline__ uint32_t rng_pixel_index(uint32_t lp, uint32_t width, uint32_t pitch, uint32_t rank, uint32_t world, uint32_t tile_rows) {
     const uint32_t lx = lp % width, ly = lp / width;
     const uint32_t gy = ((ly / tile_rows) * world + rank) * tile_rows + (ly % tile_rows);
-    const uint32_t pixelIndex = pitch * gy + lx;
-    // _curand_init_scratch (curand_kernel.h): seed scrambling, then the sequence jump
+    return pitch * gy + lx;
+}
+// _curand_init_scratch (curand_kernel.h): seed scrambling; returns the state's d word
+__device__ __forceinline__ uint32_t rng_seed_vector(uint32_t pixelIndex, unsigned long long seed, uint32_t v[5]) {
     const unsigned long long sd = (unsigned long long) ((long long) pixelIndex ^ (long long) seed);
     const uint32_t s0 = ((uint32_t) sd) ^ 0xaad26b49u, s1 = (uint32_t) (sd >> 32) ^ 0xf7dcefddu;
     const uint32_t t0 = 1099087573u * s0, t1 = 2591861531u * s1;
-    uint32_t v[5] = {123456789u + t0, 362436069u ^ t0, 521288629u + t1, 88675123u ^ t1, 5783321u + t0};
-    // Lanes of a warp hold neighbouring pixels: their indices differ in a few low bits and agree above.  A product whose
-    // matrix differs from lane to lane is a 16-way gather in L1 (it bound the first version of this kernel), so the
-    // bits that vary across the warp are applied one at a time with the warp-uniform single-bit matrix T[b / 4][1 << b % 4]
-    // (every lane computes, lanes whose bit is clear keep their vector), and only the bits all lanes share go through
-    // the hex-digit tables.
+    v[0] = 123456789u + t0; v[1] = 362436069u ^ t0; v[2] = 521288629u + t1; v[3] = 88675123u ^ t1; v[4] = 5783321u + t0;
+    return 6615241u + t1 + t0;
+}
+// The sequence jump by pixelIndex for ANY assignment of pixels to lanes (all 32 lanes call it together).
+// Lanes of a warp hold neighbouring pixels: their indices differ in a few low bits and agree above.  A product whose
+// matrix differs from lane to lane is a 16-way gather in L1 (it bound the first version of this kernel), so the
+// bits that vary across the warp are applied one at a time with the warp-uniform single-bit matrix T[b / 4][1 << b % 4]
+// (every lane computes, lanes whose bit is clear keep their vector), and only the bits all lanes share go through
+// the hex-digit tables.
+__device__ __forceinline__ void rng_jump_generic(const uint32_t *__restrict__ tables, uint32_t pixelIndex, uint32_t v[5]) {
     // the low 5 bits: one product with the lane's own matrix from the lane-interleaved table (coalesced when the warp's
     // pixels are consecutive; correct in any case)
     xorwow_matvec_low(tables + RNG_HEX_TABLE_WORDS, pixelIndex & 31u, v);
@@ -158,9 +160,111 @@ __global__ void __launch_bounds__(256) rng_init_tables_kernel(RngState *__restri
         const uint32_t d = p & 15u;
         if (d) xorwow_matvec(tables + (size_t) (h * 15 + (int) d - 1) * RNG_MAT_WORDS, v);
     }
+}
+
+// One pixel per thread (RTB200_RNG_INIT=single; the kernel of round 1)
+__global__ void __launch_bounds__(256) rng_init_tables_kernel(RngState *__restrict__ states, const uint32_t *__restrict__ tables, unsigned long long seed,
+                                                              uint32_t width, uint32_t pitch, uint32_t local_rows, uint32_t rank, uint32_t world,
+                                                              uint32_t tile_rows) {
+    const uint32_t lp0 = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = lp0 < width * local_rows;
+    const uint32_t lp = valid ? lp0 : width * local_rows - 1u;          // lanes past the end shadow the last pixel (warp collectives below)
+    const uint32_t pixelIndex = rng_pixel_index(lp, width, pitch, rank, world, tile_rows);
+    uint32_t v[5];
     RngState r;
-    r.d = 6615241u + t1 + t0; r.v0 = v[0]; r.v1 = v[1]; r.v2 = v[2]; r.v3 = v[3]; r.v4 = v[4];
-    if (valid) states[lp] = r;
+    r.d = rng_seed_vector(pixelIndex, seed, v);
+    rng_jump_generic(tables, pixelIndex, v);
+    r.v0 = v[0]; r.v1 = v[1]; r.v2 = v[2]; r.v3 = v[3]; r.v4 = v[4];
+    if (valid) states[lp0] = r;
+}
+
+// ---- four pixels per thread: the rows of a matrix are loaded once for four vectors ---------------------------------------
+// The one-pixel kernel issues 9 loads per matrix row index and pixel (5 for the lane's own low-bits matrix, 2 + 2 for the two
+// byte-digit matrices) against 15 logic operations: it is bound as much by L1 wavefronts (1 440 per warp) as by issue slots.
+// A thread here takes the pixels lp, lp + 32, lp + 64, lp + 96 of its warp's 128 consecutive pixels: same lane, hence the SAME
+// low-bits matrix, and — 128 aligned pixels never straddle an 8 192-pixel block — the same high byte digit; only the middle
+// digit differs (consecutive values).  Loads per row index and pixel: 5/4 + 2 + 2/4 = 3.75.  The bit of the vector that selects
+// a row is taken from the top of a bit-reversed copy that shifts left once per row (sign-extending shift = the mask: two
+// instructions instead of four).  Same products, same order per pixel as the one-pixel kernel: the states are bit-identical
+// (every parity test depends on them).  Warps whose 128 pixels are not that regular (shard boundaries of odd geometries, the
+// end of the frame, indices beyond 2^21) take the generic path pixel by pixel.
+constexpr int RNG_K = 4;
+template<int K, bool LOW>
+__device__ __forceinline__ void xorwow_matvec_k(const uint32_t *__restrict__ m, uint32_t v[K][5]) {
+    uint32_t r[K][5];
+#pragma unroll
+    for (int k = 0; k < K; k++) { r[k][0] = 0u; r[k][1] = 0u; r[k][2] = 0u; r[k][3] = 0u; r[k][4] = 0u; }
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        uint32_t wr[K];
+#pragma unroll
+        for (int k = 0; k < K; k++) wr[k] = __brev(v[k][i]);
+#pragma unroll 4
+        for (int j = 0; j < 32; j++) {
+            uint32_t a0, a1, a2, a3, a4;
+            if (LOW) {                      // m = lane table + lane: word w of row at [(5 * row + w) * 32]
+                const uint32_t *row = m + (size_t) (5 * (32 * i + j)) * 32;
+                a0 = __ldg(row); a1 = __ldg(row + 32); a2 = __ldg(row + 64); a3 = __ldg(row + 96); a4 = __ldg(row + 128);
+            } else {
+                const uint32_t *row = m + RNG_ROW_WORDS * (32 * i + j);
+                const uint4 a = __ldg(reinterpret_cast<const uint4 *>(row));
+                a0 = a.x; a1 = a.y; a2 = a.z; a3 = a.w; a4 = __ldg(row + 4);
+            }
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                const uint32_t mask = (uint32_t) ((int32_t) wr[k] >> 31);
+                wr[k] <<= 1;
+                r[k][0] ^= a0 & mask; r[k][1] ^= a1 & mask; r[k][2] ^= a2 & mask; r[k][3] ^= a3 & mask; r[k][4] ^= a4 & mask;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; k++) { v[k][0] = r[k][0]; v[k][1] = r[k][1]; v[k][2] = r[k][2]; v[k][3] = r[k][3]; v[k][4] = r[k][4]; }
+}
+
+__global__ void __launch_bounds__(256) rng_init_tables4_kernel(RngState *__restrict__ states, const uint32_t *__restrict__ tables, unsigned long long seed,
+                                                               uint32_t width, uint32_t pitch, uint32_t local_rows, uint32_t rank, uint32_t world,
+                                                               uint32_t tile_rows) {
+    const uint32_t n = width * local_rows;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    const uint32_t base = warp * (32u * RNG_K);
+    if (base >= n) return;                                             // the whole warp
+    uint32_t pix[RNG_K], d[RNG_K], v[RNG_K][5];
+    bool regular = true;
+#pragma unroll
+    for (int k = 0; k < RNG_K; k++) {
+        const uint32_t lp0 = base + 32u * k + lane;
+        pix[k] = rng_pixel_index(lp0 < n ? lp0 : n - 1u, width, pitch, rank, world, tile_rows);      // lanes past the end shadow the last pixel
+        d[k] = rng_seed_vector(pix[k], seed, v[k]);
+    }
+    const uint32_t p0 = __shfl_sync(0xffffffffu, pix[0], 0);
+#pragma unroll
+    for (int k = 0; k < RNG_K; k++) regular = regular && pix[k] == p0 + 32u * k + lane;
+    const uint32_t last = p0 + 32u * RNG_K - 1u;
+    regular = __all_sync(0xffffffffu, regular) && (p0 & 31u) == 0u && (p0 >> 13) == (last >> 13) && last < (1u << 21);
+    if (regular) {
+        const uint32_t *wide = tables + RNG_HEX_TABLE_WORDS + RNG_LOW_TABLE_WORDS;
+        xorwow_matvec_k<RNG_K, true>(tables + RNG_HEX_TABLE_WORDS + lane, v);                       // bits 0..4: the lane's matrix, four vectors
+#pragma unroll
+        for (int k = 0; k < RNG_K; k++) {                                                    // bits 5..12: one matrix per 32 pixels
+            const uint32_t da = ((p0 >> 5) + (uint32_t) k) & 255u;
+            if (da) xorwow_matvec_k<1, false>(wide + (size_t) (da - 1u) * RNG_MAT_WORDS, &v[k]);
+        }
+        const uint32_t db = (p0 >> 13) & 255u;                                               // bits 13..20: one matrix, four vectors
+        if (db) xorwow_matvec_k<RNG_K, false>(wide + (size_t) (255u + db - 1u) * RNG_MAT_WORDS, v);
+    } else {
+#pragma unroll
+        for (int k = 0; k < RNG_K; k++) rng_jump_generic(tables, pix[k], v[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < RNG_K; k++) {
+        const uint32_t lp0 = base + 32u * k + lane;
+        if (lp0 < n) {
+            RngState r;
+            r.d = d[k]; r.v0 = v[k][0]; r.v1 = v[k][1]; r.v2 = v[k][2]; r.v3 = v[k][3]; r.v4 = v[k][4];
+            states[lp0] = r;
+        }
+    }
 }
 
 // v1: one thread per pixel, 8x4-pixel warps, all samples and bounces of the pixel in the thread
@@ -274,8 +378,13 @@ void launch_rng_init(RngState *states, unsigned long long seed, const CameraD &c
     static const bool use_curand = getenv("RTB200_RNG_INIT") && strcmp(getenv("RTB200_RNG_INIT"), "curand") == 0;
     if (tables && !use_curand) {
         launch_rng_tables(tables, tables_ready, stream);
-        rng_init_tables_kernel<<<div_up(n, 256), 256, 0, stream>>>(states, tables, seed, cam.width, cam.pitch, fr.local_rows, fr.shard_rank, fr.shard_world,
-                                                                  fr.tile_rows);
+        static const bool single = getenv("RTB200_RNG_INIT") && strcmp(getenv("RTB200_RNG_INIT"), "single") == 0;       // A/B: one pixel per thread
+        if (single)
+            rng_init_tables_kernel<<<div_up(n, 256), 256, 0, stream>>>(states, tables, seed, cam.width, cam.pitch, fr.local_rows, fr.shard_rank, fr.shard_world,
+                                                                      fr.tile_rows);
+        else
+            rng_init_tables4_kernel<<<div_up(div_up(n, (size_t) 32 * RNG_K) * 32, 256), 256, 0, stream>>>(states, tables, seed, cam.width, cam.pitch, fr.local_rows,
+                                                                                                        fr.shard_rank, fr.shard_world, fr.tile_rows);
         CUDA_CHECK(cudaGetLastError());
         return;
     }

@@ -544,8 +544,12 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     collapse_init_kernel<<<div_up(n_segs, 256), 256, 0, stream>>>(seg_offset_.get(), seg_root_.get(), n_segs, queue_.get(), wide_counters_.get());
     const BinaryTreeView view{range_.get(), node_lo_.get(), node_hi_.get(), prim_lo_.get(), prim_hi_.get(), vals_};
     // items are claimed by ticket (see above): the grid need not be resident as a whole; 3 CTAs per SM measured best
-    static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 3;   // tuning (measured, profiles/r02j_build_ab.txt: 0.76 / 0.74 / 0.77 ms at 2 / 3 / 4, 0.97 at 8)
-    const int max_blocks = sm_count * std::min(collapse_blocks_per_sm_, std::max(1, collapse_bps_env));
+    // tuning (measured): one 1 M-triangle BLAS 0.76 / 0.74 / 0.77 ms at 2 / 3 / 4 CTAs per SM, 0.97 at 8 (profiles/r02j_build_ab.txt); a batch
+    // of 504 particle BLASes 0.62 / 0.58 / 0.62 / 0.67 / 0.86 at 1 / 2 / 3 / 4 / 6 (profiles/r02_c3_build_ab.txt, r02_bps_ab.txt): many roots
+    // are ready at once there and the waiting threads of a larger grid only take L2 bandwidth from the working ones
+    static const int collapse_bps_env = getenv("RTB200_COLLAPSE_BLOCKS_PER_SM") ? atoi(getenv("RTB200_COLLAPSE_BLOCKS_PER_SM")) : 0;
+    const int collapse_bps = collapse_bps_env > 0 ? collapse_bps_env : (n_segs >= 64 ? 2 : 3);
+    const int max_blocks = sm_count * std::min(collapse_blocks_per_sm_, collapse_bps);
     const int want_blocks = (int) div_up((size_t) capacity, CT);
     const int blocks = want_blocks < max_blocks ? want_blocks : max_blocks;
     static const int leaf_max_env = getenv("RTB200_LEAF_MAX") ? atoi(getenv("RTB200_LEAF_MAX")) : 0;   // tuning experiments only

@@ -414,6 +414,30 @@ int rt_run_vtk_animation(rt_ctx *ctx, size_t first_frame, size_t frame_stride, s
  * bandwidth that bounds node/triangle fetches of an L2-resident BVH; bytes well above it measures HBM reads.     */
 int rt_probe_read_bandwidth(rt_ctx *ctx, size_t bytes, int repeats, double *gbs);
 
+/* ---- TLAS build that allocates nothing ----------------------------------------------------------------------------
+ * This entry point has NO COUNTERPART IN THE REFERENCE; it was added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  It is the per-frame
+ * TLAS rebuild of the frame path (one block, one launch: csrc/kernels_wide.cu tlas_small_kernel, the kernel rt_render_frame /
+ * rt_submit_frames use for up to 1024 instances) with its scratch memory in a file-scope static device array instead of the
+ * context's buffers.  It needs no rt_ctx, calls no cudaMalloc / cudaFree / allocating routine, and does not synchronise: two
+ * kernel launches and one 4-byte device-to-device copy are enqueued on `cuda_stream` (a cudaStream_t; NULL = default stream)
+ * of the CURRENT device, and the call returns.
+ *   boxes_dev               in   n_instances x 6 floats (lo x y z, hi x y z): the world boxes the TLAS leaves are to have
+ *   nodes_out_dev           out  room for (n_instances + 1) records of 80 bytes (BvhNode8, csrc/rt_types.h), 16-byte aligned;
+ *                                node 0 is the root
+ *   leaf_instances_out_dev  out  n_instances words: instance index per leaf-order position
+ *   n_nodes_out_dev         out  one word: number of wide nodes written (may be NULL)
+ * All four are device memory of the current device.  The node contents are those rt_read_wide_bvh(ctx, 1, ...) returns for
+ * the same leaf boxes; as there, only their placement depends on the order of the build's atomics.
+ * LIMITS: n_instances in 1 .. RT_TLAS_NO_ALLOC_MAX_INSTANCES, else RT_ERR_ARGUMENT with the reason in error_text (error_cap bytes,
+ * may be NULL).  The scratch is RT_TLAS_NO_ALLOC_SCRATCH_BYTES (112 KiB) per GPU that loads the library, held until the process
+ * exits.  Every call on a device shares that array (it keeps the previous call's contents; the kernels rewrite or reset what
+ * they read): calls that overlap on the GPU — two streams, two host threads — RACE and must be serialised by the caller.      */
+#define RT_TLAS_NO_ALLOC_MAX_INSTANCES 1024
+#define RT_TLAS_NO_ALLOC_SCRATCH_BYTES (112 * 1024)
+int rt_build_tlas_no_alloc(const float *boxes_dev, uint32_t n_instances, void *nodes_out_dev, uint32_t *leaf_instances_out_dev,
+                           uint32_t *n_nodes_out_dev, void *cuda_stream, char *error_text, size_t error_cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -129,6 +129,7 @@ EXPORTS = [
     "rt_submit_frames", "rt_set_window_cameras", "rt_wait_frame", "rt_read_frame", "rt_release_window", "rt_run_frames",
     "rt_commit_extension_primitives", "rt_primitive_type_count",
     "rt_frame_ring_create", "rt_frame_ring_open", "rt_frame_ring_attach", "rt_frame_ring_close",
+    "rt_build_tlas_no_alloc",
 ]
 
 _lib = None
@@ -174,6 +175,8 @@ def load_library(path: str | None = None) -> C.CDLL:
     lib.rt_run_vtk_animation.argtypes = [vp, sz, sz, sz, u64, i32, FRAME_SINK, vp, C.POINTER(AnimationStats)]
     lib.rt_camera_step.argtypes = [C.POINTER(CameraInput), C.POINTER(CameraMotion), C.POINTER(CameraInput), C.POINTER(C.c_int)]
     lib.rt_probe_read_bandwidth.argtypes = [vp, sz, i32, C.POINTER(C.c_double)]
+    # no rt_ctx, no allocation: device pointers of the current device + an optional error-text buffer (include/rtb200.h)
+    lib.rt_build_tlas_no_alloc.argtypes = [vp, u32, vp, vp, vp, vp, C.c_char_p, sz]
     lib.rt_submit_frames.argtypes = [vp, u64, u32, vp, u64, C.POINTER(u32)]
     lib.rt_set_window_cameras.argtypes = [vp, vp, u32]
     lib.rt_wait_frame.argtypes = [vp, u32, u32, C.POINTER(FrameOut)]

@@ -593,3 +593,126 @@ void LbvhBuilder::collapse_wide(int n, int n_segs, int leaf_mode, const Geometry
     launches += 3;
     CUDA_CHECK(cudaGetLastError());
 }
+
+#include "../../include/rtb200.h"
+
+#include <cstdio>
+#include <mutex>
+
+// ---- rt_build_tlas_no_alloc: the one-block TLAS build for callers that cannot allocate ---------------------------------------
+// No counterpart in the reference (include/rtb200.h).  The kernel is
+// tlas_small_kernel above, unchanged; what differs is where its scratch lives: every intermediate array (leaf boxes as float4,
+// Morton keys, sorted ids, Karras topology, node boxes, collapse queue and counters, leaf positions) is a field of ONE file-scope
+// device array of RT_TLAS_NO_ALLOC_SCRATCH_BYTES, which every GPU that loads the library holds until the process exits.  The
+// caller passes the input (instance boxes) and the outputs (wide nodes, leaf-order instance indices, node count), all device
+// memory of the current device.  Nothing here calls cudaMalloc / cudaFree or an allocating routine, and nothing synchronises: two
+// kernel launches and one 4-byte device-to-device copy on the caller's stream.
+//
+// In host code `g_tlas_no_alloc_scratch` is a host-side stand-in, not a device address: the address is taken once per device
+// with cudaGetSymbolAddress (that device current) and that pointer is what the kernels receive.
+// Every call on a device shares the array and finds the previous call's contents in it.  Nothing has to start at zero between
+// calls: the prep kernel rewrites the boxes and the bounds, tlas_small_kernel resets its counters and its arrival flags (shared
+// memory) and reads only queue / topology entries it wrote in the same launch.  Calls that OVERLAP on the GPU (two streams, two
+// host threads, two processes' contexts do not share it — two streams of one process do) race on the array: serialise them.
+namespace {
+
+struct TlasNoAllocScratch {
+    float4 prim_lo[RT_TLAS_SMALL_MAX], prim_hi[RT_TLAS_SMALL_MAX], node_lo[RT_TLAS_SMALL_MAX], node_hi[RT_TLAS_SMALL_MAX];
+    uint64_t keys[RT_TLAS_SMALL_MAX];
+    int2 range[RT_TLAS_SMALL_MAX];
+    uint32_t vals[RT_TLAS_SMALL_MAX], leaf_pos8[RT_TLAS_SMALL_MAX];
+    int left[RT_TLAS_SMALL_MAX], right[RT_TLAS_SMALL_MAX], parent[RT_TLAS_SMALL_MAX], leaf_parent[RT_TLAS_SMALL_MAX];
+    int queue[RT_TLAS_SMALL_MAX + 8];
+    uint32_t bounds[8], counters[8], seg_offset[4], seg_type[4];
+    int seg_root[4];
+};
+static_assert(RT_TLAS_NO_ALLOC_MAX_INSTANCES == RT_TLAS_SMALL_MAX, "the no-alloc entry point serves what the one-block kernel serves");
+static_assert(sizeof(TlasNoAllocScratch) <= RT_TLAS_NO_ALLOC_SCRATCH_BYTES, "scratch layout exceeds the stated size");
+
+static __device__ __align__(256) unsigned char g_tlas_no_alloc_scratch[RT_TLAS_NO_ALLOC_SCRATCH_BYTES];
+
+constexpr int NA_MAX_DEVICES = 64;
+std::mutex g_na_mutex;
+TlasNoAllocScratch *g_na_scratch[NA_MAX_DEVICES];     // device address of the array on each device, taken on first use
+
+// caller's boxes (6 floats: lo xyz, hi xyz) -> the builder's float4 leaf boxes + the bounds of the box centres (ordered uints):
+// what instance_bounds_kernel leaves for tlas_small_kernel in the frame path
+__global__ void __launch_bounds__(TS_THREADS) tlas_no_alloc_prep_kernel(const float *__restrict__ boxes, int n, float4 *__restrict__ prim_lo,
+                                                                        float4 *__restrict__ prim_hi, uint32_t *__restrict__ bounds) {
+    __shared__ uint32_t sb[6];
+    if (threadIdx.x < 6) sb[threadIdx.x] = threadIdx.x < 3 ? 0xFFFFFFFFu : 0u;
+    __syncthreads();
+    for (int j = threadIdx.x; j < n; j += TS_THREADS) {
+        const float *b = boxes + 6 * (size_t) j;
+        Aabb box;
+        box.lo = mk3(b[0], b[1], b[2]);
+        box.hi = mk3(b[3], b[4], b[5]);
+        prim_lo[j] = make_float4(box.lo.x, box.lo.y, box.lo.z, 0.0f);
+        prim_hi[j] = make_float4(box.hi.x, box.hi.y, box.hi.z, 0.0f);
+        const Aabb c = aabb_centre_box(box);
+        atomicMin(&sb[0], float_to_ordered(c.lo.x)); atomicMin(&sb[1], float_to_ordered(c.lo.y)); atomicMin(&sb[2], float_to_ordered(c.lo.z));
+        atomicMax(&sb[3], float_to_ordered(c.hi.x)); atomicMax(&sb[4], float_to_ordered(c.hi.y)); atomicMax(&sb[5], float_to_ordered(c.hi.z));
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) bounds[threadIdx.x] = sb[threadIdx.x];
+}
+
+int na_fail(char *error_text, size_t error_cap, int code, const char *msg, const char *detail = nullptr) {
+    if (error_text && error_cap) snprintf(error_text, error_cap, "rt_build_tlas_no_alloc: %s%s%s", msg, detail ? ": " : "", detail ? detail : "");
+    return code;
+}
+
+} // namespace
+
+extern "C" int rt_build_tlas_no_alloc(const float *boxes_dev, uint32_t n_instances, void *nodes_out_dev, uint32_t *leaf_instances_out_dev,
+                                      uint32_t *n_nodes_out_dev, void *cuda_stream, char *error_text, size_t error_cap) {
+    if (error_text && error_cap) error_text[0] = 0;
+    if (n_instances < 1u) return na_fail(error_text, error_cap, RT_ERR_ARGUMENT, "n_instances must be at least 1");
+    if (n_instances > (uint32_t) RT_TLAS_NO_ALLOC_MAX_INSTANCES) {
+        char d[96];
+        snprintf(d, sizeof(d), "%u instances, the static scratch array holds at most %d", n_instances, RT_TLAS_NO_ALLOC_MAX_INSTANCES);
+        return na_fail(error_text, error_cap, RT_ERR_ARGUMENT, "too many instances", d);
+    }
+    if (!boxes_dev || !nodes_out_dev || !leaf_instances_out_dev) return na_fail(error_text, error_cap, RT_ERR_ARGUMENT, "null input or output pointer");
+    if (((uintptr_t) boxes_dev & 3u) || ((uintptr_t) leaf_instances_out_dev & 3u) || ((uintptr_t) n_nodes_out_dev & 3u))
+        return na_fail(error_text, error_cap, RT_ERR_ARGUMENT, "boxes / leaf_instances_out / n_nodes_out must be 4-byte aligned");
+    if ((uintptr_t) nodes_out_dev & 15u) return na_fail(error_text, error_cap, RT_ERR_ARGUMENT, "nodes_out must be 16-byte aligned (80-byte records written as 128-bit words)");
+    int dev = -1;
+    cudaError_t rc = cudaGetDevice(&dev);
+    if (rc != cudaSuccess) return na_fail(error_text, error_cap, RT_ERR_CUDA, "cudaGetDevice", cudaGetErrorString(rc));
+    if (dev < 0 || dev >= NA_MAX_DEVICES) return na_fail(error_text, error_cap, RT_ERR_ARGUMENT, "device ordinal beyond the table of scratch addresses (64)");
+    TlasNoAllocScratch *sc = nullptr;
+    {
+        // set-up, once per device, with that device current: the array's name is a host-side stand-in here, its device address
+        // comes from cudaGetSymbolAddress and is what the kernels get
+        std::lock_guard<std::mutex> lock(g_na_mutex);
+        if (!g_na_scratch[dev]) {
+            void *p = nullptr;
+            rc = cudaGetSymbolAddress(&p, g_tlas_no_alloc_scratch);
+            if (rc != cudaSuccess || !p) return na_fail(error_text, error_cap, RT_ERR_CUDA, "cudaGetSymbolAddress(scratch)", cudaGetErrorString(rc));
+            g_na_scratch[dev] = static_cast<TlasNoAllocScratch *>(p);
+        }
+        sc = g_na_scratch[dev];
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    const int n = (int) n_instances;
+    tlas_no_alloc_prep_kernel<<<1, TS_THREADS, 0, stream>>>(boxes_dev, n, sc->prim_lo, sc->prim_hi, sc->bounds);
+    TlasSmallArgs a;
+    a.prim_lo = sc->prim_lo; a.prim_hi = sc->prim_hi; a.bounds = sc->bounds;
+    a.n = n; a.bits = 10;                                  // tlas_morton_bits(n) for every n <= 1024 (host_scene.cpp)
+    a.keys = sc->keys; a.vals = sc->vals;
+    a.left = sc->left; a.right = sc->right; a.parent = sc->parent; a.leaf_parent = sc->leaf_parent; a.seg_root = sc->seg_root;
+    a.range = sc->range;
+    a.node_lo = sc->node_lo; a.node_hi = sc->node_hi;
+    a.seg_offset = sc->seg_offset; a.seg_type = sc->seg_type;
+    a.queue = sc->queue; a.counters = sc->counters;
+    a.nodes8 = static_cast<BvhNode8 *>(nodes_out_dev); a.leaf_pos8 = sc->leaf_pos8; a.leaf_prims8 = leaf_instances_out_dev;
+    tlas_small_kernel<<<1, TS_THREADS, 0, stream>>>(a);
+    rc = cudaGetLastError();
+    if (rc != cudaSuccess) return na_fail(error_text, error_cap, RT_ERR_CUDA, "kernel launch", cudaGetErrorString(rc));
+    if (n_nodes_out_dev) {
+        rc = cudaMemcpyAsync(n_nodes_out_dev, &sc->counters[0], sizeof(uint32_t), cudaMemcpyDeviceToDevice, stream);
+        if (rc != cudaSuccess) return na_fail(error_text, error_cap, RT_ERR_CUDA, "cudaMemcpyAsync(node count)", cudaGetErrorString(rc));
+    }
+    return RT_OK;
+}

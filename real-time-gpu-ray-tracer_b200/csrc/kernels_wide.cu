@@ -417,6 +417,7 @@ struct TlasSmallArgs {
     uint32_t *counters;
     BvhNode8 *nodes8;
     uint32_t *leaf_pos8, *leaf_prims8;
+    int octets;             // collapse with eight lanes per item (oct_collapse_item): a level's latency instead of its throughput
 };
 constexpr int TS_THREADS = 512;
 
@@ -500,7 +501,14 @@ __global__ void __launch_bounds__(TS_THREADS) tlas_small_kernel(TlasSmallArgs a)
     const BinaryTreeView view{a.range, a.node_lo, a.node_hi, a.prim_lo, a.prim_hi, a.vals};
     uint32_t begin = 0u, end = 1u;
     while (begin < end) {
-        for (uint32_t i = begin + (uint32_t) tid; i < end; i += TS_THREADS) collapse_item(view, vq[i], (int) i, 1, vq, a.counters, a.nodes8, a.leaf_pos8);
+        if (a.octets) {
+            const int l = tid & 7;
+            const uint32_t om = 0xFFu << (8 * ((tid & 31) >> 3));
+            for (uint32_t i = begin + (uint32_t) (tid >> 3); i < end; i += TS_THREADS / 8)
+                oct_collapse_item(view, vq[i], (int) i, 1, om, l, vq, a.counters, a.nodes8, a.leaf_pos8);
+        } else {
+            for (uint32_t i = begin + (uint32_t) tid; i < end; i += TS_THREADS) collapse_item(view, vq[i], (int) i, 1, vq, a.counters, a.nodes8, a.leaf_pos8);
+        }
         __syncthreads();
         begin = end;
         end = ((volatile uint32_t *) a.counters)[0];
@@ -512,6 +520,15 @@ __global__ void __launch_bounds__(TS_THREADS) tlas_small_kernel(TlasSmallArgs a)
 }
 
 } // namespace
+
+// The collapse inside the one-block TLAS kernel: eight lanes per item (default) or one thread per item (RTB200_TLAS_OCTETS=0).
+// For the big builds the octets lost (throughput: three times the instructions); here a level is a handful of items and what
+// counts is the latency of ONE item — children in registers instead of dynamically indexed local arrays: 0.152 -> 0.129 ms for
+// the TLAS step of a config-3 frame (505 instances; profiles/r02_tlas_octets_ab.txt), same trees (twin equality tests).
+static int tlas_small_octets() {
+    static const int v = getenv("RTB200_TLAS_OCTETS") ? atoi(getenv("RTB200_TLAS_OCTETS")) : 1;
+    return v;
+}
 
 bool LbvhBuilder::tlas_small(int n, int morton_bits, cudaStream_t stream) {
     // RTB200_TLAS_FUSED=0: the general kernels for every size (A/B runs)
@@ -528,6 +545,7 @@ bool LbvhBuilder::tlas_small(int n, int morton_bits, cudaStream_t stream) {
     a.seg_offset = seg_offset_.get(); a.seg_type = seg_type_.get();
     a.queue = queue_.get(); a.counters = wide_counters_.get();
     a.nodes8 = nodes8_.get(); a.leaf_pos8 = leaf_pos8_.get(); a.leaf_prims8 = leaf_prims8_.get();
+    a.octets = tlas_small_octets();
     tlas_small_kernel<<<1, TS_THREADS, 0, stream>>>(a);
     CUDA_CHECK(cudaGetLastError());
     launches++;
@@ -707,6 +725,7 @@ extern "C" int rt_build_tlas_no_alloc(const float *boxes_dev, uint32_t n_instanc
     a.seg_offset = sc->seg_offset; a.seg_type = sc->seg_type;
     a.queue = sc->queue; a.counters = sc->counters;
     a.nodes8 = static_cast<BvhNode8 *>(nodes_out_dev); a.leaf_pos8 = sc->leaf_pos8; a.leaf_prims8 = leaf_instances_out_dev;
+    a.octets = tlas_small_octets();
     tlas_small_kernel<<<1, TS_THREADS, 0, stream>>>(a);
     rc = cudaGetLastError();
     if (rc != cudaSuccess) return na_fail(error_text, error_cap, RT_ERR_CUDA, "kernel launch", cudaGetErrorString(rc));

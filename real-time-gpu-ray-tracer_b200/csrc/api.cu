@@ -368,6 +368,7 @@ int rt_render_frame(rt_ctx *ctx, uint64_t frame_index, uint64_t seed, rt_frame_o
         launch_render(sc, ctx->hs.cam, fr, s);
     } else if (persist) {
         ctx->persist.n_blas_nodes = (uint32_t) ctx->blas.n_prims();      // <= allocated records of the node pool
+        ctx->persist.single_instance = rt_single_instance(ctx);
         ctx->persist.render(sc, ctx->hs.cam, fr, s, ctx->sm_count);
         ws.launches = ctx->persist.launches;
     } else {

@@ -11,6 +11,7 @@
 #include "wave.h"
 
 #include <chrono>
+#include <cstdlib>
 #include <memory>
 #include <string>
 #include <thread>
@@ -184,6 +185,12 @@ inline int rt_fail(rt_ctx *ctx, int code, const std::string &msg) {
         return rt_fail(ctx, RT_ERR_ARGUMENT, e.what());     \
     }                                                       \
     return RT_OK;
+
+// a scene of one instance runs the path kernel's SINGLE instantiation (kernels_persist.cu); RTB200_SINGLE_INSTANCE=0: A/B runs
+inline bool rt_single_instance(const rt_ctx *ctx) {
+    static const bool enabled = !(getenv("RTB200_SINGLE_INSTANCE") && atoi(getenv("RTB200_SINGLE_INSTANCE")) == 0);
+    return enabled && ctx->hs.inst_desc.size() == 1;
+}
 
 // shared between api.cu and frames.cu
 void rt_compute_local_rows(rt_ctx *c);

@@ -301,6 +301,7 @@ int rt_submit_frames(rt_ctx *ctx, uint64_t first_frame, uint32_t n_frames, const
     w.persist.blocks_per_sm_override = ctx->persist.blocks_per_sm_override; w.persist.tile_order = ctx->persist.tile_order;
     w.persist.split = ctx->persist.split;
     w.persist.n_blas_nodes = (uint32_t) ctx->blas.n_prims();
+    w.persist.single_instance = rt_single_instance(ctx);
     if (win.valid_pixels == 0u) {
         // a shard without a single scan-line inside the image: nothing to trace, every frame is complete at once
         for (uint32_t k = 0; k < n_frames; k++) w.h_flags[k] = w.ticket;

@@ -46,7 +46,12 @@ enum : uint32_t { ST_DEAD = 0u, ST_TRACE = 1u, ST_SHADE = 2u, ST_FRESH = 3u };
 // CAMS: every frame of the window has its own camera pose (pb.frame_cams, global memory, indexed by the path's frame); the
 // default instantiation (false) reads the one camera from the kernel parameters and is, instruction for instruction, the
 // kernel without this option.
-template<bool COUNT, bool CAMS = false>
+// SINGLE: the scene is ONE instance (configs 2 and 4).  A top level over one box only prunes rays that miss the scene, and entering
+// the instance costs every ray a node step on the TLAS root plus a LEAF step of its own; here the ray is taken into the
+// instance's space where it starts (in the SHADE step, with the lanes that start rays together) and begins at the BLAS root.  The
+// candidates, their order and the acceptance arithmetic are those of the two-level walk, so the frames are the same bit for bit
+// (the parity tests run on it: every C2 / C4 test); the TLAS-leaf branch and the leave-instance transition compile away.
+template<bool COUNT, bool CAMS = false, bool SINGLE = false>
 __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(const __grid_constant__ SceneD sc, const __grid_constant__ CameraD cam,
                                                                             const __grid_constant__ FrameD fr, const __grid_constant__ PersistBuffers pb,
                                                                             int shade_min, int node_min) {
@@ -72,7 +77,7 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
         // ---- cheap transitions: nothing pending in registers -> leave instance / ray finished / pop -----------------
 #define RT_ADVANCE()                                                                                                         \
         if (state == ST_TRACE && tg.y == 0u && ng.y <= NG_INNER) {                                                           \
-            if (inst >= 0 && sp == inst_sp && sp != 0) {         /* BLAS exhausted, TLAS work left: back to world space */   \
+            if (!SINGLE && inst >= 0 && sp == inst_sp && sp != 0) { /* BLAS exhausted, TLAS work left: back to world space */ \
                 const float4 o = pb.ray_o[slot], d = pb.ray_d[slot];                                                         \
                 inst = -1 - (int) __float_as_uint(d.w);          /* inst < 0: on the TLAS of frame -1 - inst of the window */ \
                 r.ray.o = mk3(o.x, o.y, o.z); r.ray.d = mk3(d.x, d.y, d.z);                                                  \
@@ -122,10 +127,10 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                     n.n0 = make_float4(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z), __uint_as_float(a.w));
                     n.n1 = q[1]; n.n2 = q[2]; n.n3 = q[3]; n.n4 = q[4];
                 } else {
-                    n = load_node8(inst < 0 ? sc.tlas_nodes8 + (size_t) (uint32_t) (-1 - inst) * pb.tlas_node_stride : sc.blas_nodes8, base + rel);
+                    n = load_node8(!SINGLE && inst < 0 ? sc.tlas_nodes8 + (size_t) (uint32_t) (-1 - inst) * pb.tlas_node_stride : sc.blas_nodes8, base + rel);
                 }
 #else
-                const BvhNode8 n = load_node8(inst < 0 ? sc.tlas_nodes8 + (size_t) (uint32_t) (-1 - inst) * pb.tlas_node_stride : sc.blas_nodes8, base + rel);
+                const BvhNode8 n = load_node8(!SINGLE && inst < 0 ? sc.tlas_nodes8 + (size_t) (uint32_t) (-1 - inst) * pb.tlas_node_stride : sc.blas_nodes8, base + rel);
 #endif
                 if (COUNT) stats.nodes++;
                 const uint32_t hm = node8_intersect(n, r, RT_TMIN, hit.tc);
@@ -143,9 +148,9 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
             if (on_leaf) {
                 const int idx = rt_bfind(tg.y);
                 tg.y &= ~(1u << idx);
-                if (inst >= 0) {
+                if (SINGLE || inst >= 0) {
                     if (COUNT) stats.prims++;
-                    leaf_test8(sc, (uint32_t) prim_type, tg.x + (uint32_t) idx, r.ray, RT_TMIN, inst, hit);
+                    leaf_test8(sc, (uint32_t) prim_type, tg.x + (uint32_t) idx, r.ray, RT_TMIN, SINGLE ? 0 : inst, hit);
 #if RT_POP_IN_PHASE & 2
                     RT_ADVANCE()
 #endif
@@ -282,11 +287,25 @@ __global__ void __launch_bounds__(PT, RT_PERSIST_MIN_BLOCKS) persist8_kernel(con
                 pb.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float((sample << 16) | depth));
                 pb.rng_a[slot] = make_uint4(rng.d, rng.v0, rng.v1, rng.v2);
                 pb.rng_b[slot] = make_uint2(rng.v3, rng.v4);
-                r.ray = ray;
-                wide_setup_ray(r);
                 hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.f; hit.v = 0.f; hit.inst = -1; hit.leaf = 0;
-                sp = 0; inst = -1 - (int) (pid >> 28); inst_sp = 0;
-                ng = make_uint2(0u, 0x80000000u);           // TLAS root: one pending inner hit at relative index 0
+                sp = 0; inst_sp = 0;
+                if (SINGLE) {
+                    // straight into the one instance (Instance::hit: origin as point, direction as vector, not re-normalised)
+                    float inv[12];
+                    int root8;
+                    load_instance_wide(sc, 0, inv, root8, prim_type, (pid >> 28) * pb.inst_stride);
+                    if (COUNT) stats.insts++;
+                    r.ray.o = xf_point(inv, ray.o);
+                    r.ray.d = xf_vector(inv, ray.d);
+                    wide_setup_ray(r);
+                    inst = 0;
+                    ng = make_uint2((uint32_t) root8, 0x80000000u);
+                } else {
+                    r.ray = ray;
+                    wide_setup_ray(r);
+                    inst = -1 - (int) (pid >> 28);
+                    ng = make_uint2(0u, 0x80000000u);       // TLAS root: one pending inner hit at relative index 0
+                }
                 tg = make_uint2(0u, 0u);
                 state = ST_TRACE;
                 rays++;
@@ -403,9 +422,17 @@ void PersistRenderer::render_window(const SceneD &sc, const CameraD &cam, const 
         pb.frame_cams = win->frame_cams;
     }
     CUDA_CHECK(cudaMemsetAsync(counter_.get(), 0, sizeof(uint32_t), stream));
-    if (pb.frame_cams) persist8_kernel<false, true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);      // per-frame cameras (never with counting / split)
-    else if (split) launch_persist_split(sc, cam, fr, pb, blocks, node_min, count, stream);
-    else if (count) persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
-    else persist8_kernel<false><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+    const bool single = single_instance && !split;
+    if (pb.frame_cams) {                                    // per-frame cameras (never with counting / split)
+        if (single) persist8_kernel<false, true, true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+        else persist8_kernel<false, true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+    } else if (split) launch_persist_split(sc, cam, fr, pb, blocks, node_min, count, stream);
+    else if (count) {
+        if (single) persist8_kernel<true, false, true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+        else persist8_kernel<true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+    } else {
+        if (single) persist8_kernel<false, false, true><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+        else persist8_kernel<false><<<blocks, PT, 0, stream>>>(sc, cam, fr, pb, shade_min, node_min);
+    }
     CUDA_CHECK(cudaGetLastError());
 }

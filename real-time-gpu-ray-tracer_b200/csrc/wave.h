@@ -122,6 +122,7 @@ public:
     bool split = false;            // A/B: the kernel with a dedicated shade warp per CTA (kernels_split.cu) instead of persist8_kernel
     uint32_t launches = 0;         // kernels launched by the last render()
     uint32_t n_blas_nodes = 0;     // set by the caller: size of the BLAS wide-node pool
+    bool single_instance = false;  // set by the caller: the scene is one instance -> persist8_kernel<.., .., SINGLE> (no top-level walk)
 private:
     DeviceBuffer<float4> ray_o_, ray_d_, thr_, acc_;
     DeviceBuffer<uint4> rng_a_;

@@ -250,6 +250,58 @@ void parallel_rows(int y0, int y1, int threads, F f) {
     for (auto &t: pool) t.join();
 }
 
+// The SINGLE instantiation of the path kernel (kernels_persist.cu) on the CPU: a scene of ONE instance is traced without its
+// top level — the world ray goes into the instance's space at once and starts on the BLAS root.  Written here (not in the product
+// headers) from the same pieces the kernel uses: load_instance_wide, xf_point / xf_vector, wide_setup_ray, node8_intersect,
+// leaf_test8.  emul_single_check runs every ray of rows [y0, y1) through BOTH walks and compares the hit records bit for bit.
+template<bool COUNT>
+void trace_single8(const SceneD &sc, const RayD &wray, float tmin, HitD &hit, uint32_t &overflow, TravStats &stats, uint2 *stack_mem) {
+    hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.0f; hit.v = 0.0f; hit.inst = -1; hit.leaf = 0;
+    WideStack st;
+    st.base = stack_mem; st.stride = 1; st.sp = 0;
+    float inv[12];
+    int root8, prim_type;
+    load_instance_wide(sc, 0, inv, root8, prim_type);
+    if (COUNT) stats.insts++;
+    WideRay r;
+    r.ray.o = xf_point(inv, wray.o);
+    r.ray.d = xf_vector(inv, wray.d);
+    wide_setup_ray(r);
+    uint2 ng = make_uint2((uint32_t) root8, 0x80000000u);
+    uint2 tg = make_uint2(0u, 0u);
+    for (;;) {
+        if (ng.y > 0x00FFFFFFu) {
+            const uint32_t hits_imask = ng.y;
+            const int bit = rt_bfind(hits_imask);
+            const uint32_t base = ng.x;
+            ng.y &= ~(1u << bit);
+            if (ng.y > 0x00FFFFFFu) wide_push(st, ng, overflow);
+            const uint32_t slot = ((uint32_t) bit - 24u) ^ (r.oct_inv4 & 0xFFu);
+            const uint32_t rel = (uint32_t) rt_popc(hits_imask & ~(0xFFFFFFFFu << slot));
+            const BvhNode8 n = load_node8(sc.blas_nodes8, base + rel);
+            if (COUNT) stats.nodes++;
+            const uint32_t hm = node8_intersect(n, r, tmin, hit.tc);
+            ng.x = n.n1.x;
+            ng.y = (hm & 0xFF000000u) | (f2u(n.n0.w) >> 24);
+            tg.x = n.n1.y;
+            tg.y = hm & 0x00FFFFFFu;
+        } else {
+            tg = ng;
+            ng = make_uint2(0u, 0u);
+        }
+        while (tg.y) {
+            const int idx = rt_bfind(tg.y);
+            tg.y &= ~(1u << idx);
+            if (COUNT) stats.prims++;
+            leaf_test8(sc, (uint32_t) prim_type, tg.x + (uint32_t) idx, r.ray, tmin, 0, hit);
+        }
+        if (ng.y <= 0x00FFFFFFu) {
+            if (st.sp == 0) break;
+            ng = wide_pop(st);
+        }
+    }
+}
+
 } // namespace
 
 extern "C" {
@@ -412,6 +464,48 @@ void emul_count(void *h, uint64_t seed, int y0, int y1, int threads, uint64_t *o
         for (int k = 0; k < 4; k++) tot[k] += acc[k];
     });
     for (int k = 0; k < 4; k++) out4[k] = tot[k].load();
+}
+
+// out[0] rays, [1] rays whose hit records differ between the two walks (must be 0), [2] wide-node fetches of the two-level walk,
+// [3] of the single-level walk, [4] rays that miss the scene's top-level box (the only rays the top level saves work on), [5] primitive
+// tests two-level, [6] single-level.  Returns -1 unless the scene is exactly one instance.
+int emul_single_check(void *h, uint64_t seed, int y0, int y1, int threads, uint64_t *out7) {
+    Emul &e = *(Emul *) h;
+    if (e.hs.inst_desc.size() != 1 || !e.wide) return -1;
+    const CameraD &cam = e.hs.cam;
+    std::atomic<uint64_t> tot[7];
+    for (auto &t: tot) t = 0;
+    parallel_rows(y0, y1, threads, [&](int y) {
+        uint64_t acc[7] = {0, 0, 0, 0, 0, 0, 0};
+        for (uint32_t x = 0; x < cam.width; x++) {
+            const uint32_t pixelIndex = cam.pitch * (uint32_t) y + x;
+            curandStateXORWOW_t cs;
+            curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &cs);
+            RngState rng{cs.d, cs.v[0], cs.v[1], cs.v[2], cs.v[3], cs.v[4]};
+            uint2 stack[RT_WIDE_STACK];
+            for (uint32_t si = 0; si < cam.sqrtSamples; si++) {
+                for (uint32_t sj = 0; sj < cam.sqrtSamples; sj++) {
+                    RayD ray = primary_ray(cam, x, (uint32_t) y, si, sj, rng);
+                    f3 thr = mk3(1.0f, 1.0f, 1.0f);
+                    for (uint32_t depth = 0; depth < cam.depth; depth++) {
+                        HitD a, b;
+                        TravStats sa{0, 0, 0}, sb{0, 0, 0};
+                        uint32_t ovf = 0;
+                        trace_closest8<true>(e.sc, ray, RT_TMIN, a, ovf, sa, stack, 1);
+                        trace_single8<true>(e.sc, ray, RT_TMIN, b, ovf, sb, stack);
+                        acc[0]++;
+                        if (std::memcmp(&a.t, &b.t, 4) || std::memcmp(&a.tc, &b.tc, 4) || std::memcmp(&a.u, &b.u, 4) || std::memcmp(&a.v, &b.v, 4) ||
+                            a.inst != b.inst || a.leaf != b.leaf) acc[1]++;
+                        acc[2] += sa.nodes; acc[3] += sb.nodes; acc[4] += sa.insts == 0; acc[5] += sa.prims; acc[6] += sb.prims;
+                        if (!shade_scatter<true>(e.sc, cam, ray, a, thr, rng)) break;
+                    }
+                }
+            }
+        }
+        for (int k = 0; k < 7; k++) tot[k] += acc[k];
+    });
+    for (int k = 0; k < 7; k++) out7[k] = tot[k].load();
+    return 0;
 }
 
 // rays traced by every pixel of rows [y0, y1) (row-major, width entries per row): the distribution of the sequential work a pixel

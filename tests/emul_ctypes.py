@@ -197,6 +197,18 @@ class Emul:
         self.lib.emul_count(self.h, seed, y0, self.H if y1 is None else y1, threads or os.cpu_count() or 1, abi.ptr(out))
         return dict(rays=int(out[0]), nodes=int(out[1]), prims=int(out[2]), insts=int(out[3]))
 
+    def single_check(self, seed, y0=0, y1=None, threads=None):
+        """every ray of rows [y0, y1) through the two-level walk AND the single-level walk of the path kernel's SINGLE
+        instantiation (one-instance scenes): dict(rays, mismatches, nodes_two_level, nodes_single, rays_missing_top_box,
+        prims_two_level, prims_single)"""
+        out = np.zeros(7, np.uint64)
+        self.lib.emul_single_check.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        self.lib.emul_single_check.restype = C.c_int
+        rc = self.lib.emul_single_check(self.h, seed, y0, self.H if y1 is None else y1, threads or os.cpu_count() or 1, abi.ptr(out))
+        assert rc == 0, "emul_single_check: the scene is not exactly one instance"
+        keys = ("rays", "mismatches", "nodes_two_level", "nodes_single", "rays_missing_top_box", "prims_two_level", "prims_single")
+        return {k: int(v) for k, v in zip(keys, out)}
+
     def pixel_rays(self, seed, y0, y1, threads=None):
         """rays traced by every pixel of rows [y0, y1): uint32 [y1 - y0, W]"""
         out = np.zeros((y1 - y0, self.W), np.uint32)

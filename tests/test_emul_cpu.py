@@ -593,3 +593,39 @@ def test_ploc_tree_invariants(pkg, port, idx):
     r = e.render(SEED)
     img, rad, rays = port.scene(sc, 9).render(SEED)
     assert r["rays"] == rays and np.array_equal(r["rgba8"], img)
+
+
+def _one_instance_scenes(scenes):
+    """one-instance scenes: what the path kernel's SINGLE instantiation runs on (configs 2 and 4 are of this shape)"""
+    out = []
+    out.append(("c2-small", scenes.c2(width=128, height=72, spp=4, depth=6, nx=60, nz=30)))
+    sc = scenes.c2(width=96, height=54, spp=4, depth=8, nx=40, nz=20)          # rotated, non-uniformly scaled, shifted
+    sc.xforms[0]["shift"] = (0.5, -0.25, 1.0); sc.xforms[0]["rotate_deg"] = (20.0, 35.0, -10.0); sc.xforms[0]["scale"] = (1.5, 0.75, 1.2)
+    out.append(("c2-transformed", sc))
+    sc = scenes.c2(width=96, height=54, spp=1, depth=4, nx=30, nz=15)          # camera that sees mostly sky: rays that miss the top box
+    sc.target = (6.0, 2.5, 0.0)
+    out.append(("c2-looking-up", sc))
+    sc = scenes.c4(width=128, height=72, spp=1, depth=10, nx=80, nz=16)
+    out.append(("c4-small", sc))
+    return out
+
+
+@pytest.mark.parametrize("which", range(4))
+def test_single_level_walk_equals_two_level_walk(pkg, which):
+    """The claim behind persist8_kernel<.., .., SINGLE> (csrc/kernels_persist.cu; reference walk: src/AS/TLAS.cu:131-201 ->
+    src/AS/Instance.cu:19-49 -> src/AS/BLAS.cu:119-206): in a scene of ONE instance, starting the ray on the BLAS root in the instance's
+    space finds the same hit record, bit for bit, as walking the top level first; the top level only saves work for rays that miss
+    the scene's box.  Checked here on the CPU twin for every ray of every path of small frames; the GPU parity tests of configs 2
+    and 4 run on the kernel itself."""
+    name, sc = _one_instance_scenes(pkg.scenes)[which]
+    e = ec.Emul(sc)
+    r = e.single_check(SEED)
+    assert r["rays"] >= sc.width * sc.height * sc.sample_count and r["mismatches"] == 0, (name, r)
+    # two-level = single-level + one TLAS-root fetch per ray that enters the instance; rays that miss the top box fetch only that root
+    entered = r["rays"] - r["rays_missing_top_box"]
+    assert r["prims_two_level"] == r["prims_single"], (name, r)
+    assert r["nodes_two_level"] - r["rays"] <= r["nodes_single"], (name, r)
+    assert r["nodes_single"] - (r["nodes_two_level"] - r["rays"]) <= r["rays_missing_top_box"] * 64, (name, r)
+    if name == "c2-looking-up":
+        assert r["rays_missing_top_box"] > 0
+    assert entered > 0

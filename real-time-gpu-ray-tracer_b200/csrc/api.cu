@@ -192,6 +192,7 @@ int rt_commit_materials(rt_ctx *ctx, const rt_rough *roughs, size_t rough_count,
 
 int rt_commit_dielectrics(rt_ctx *ctx, const rt_dielectric *d, size_t count) {
     RT_API_BEGIN(ctx)
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_commit_dielectrics: not while frames are in flight (rt_release_window first): the window's kernel is reading the scene");
     const std::string e = ctx->hs.commit_dielectrics(d, count);
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
     ctx->d_dielectrics.upload(ctx->hs.dielectrics.data(), ctx->hs.dielectrics.size(), ctx->stream);
@@ -201,6 +202,7 @@ int rt_commit_dielectrics(rt_ctx *ctx, const rt_dielectric *d, size_t count) {
 
 int rt_commit_extension_primitives(rt_ctx *ctx, const void *records, size_t record_bytes, size_t count) {
     RT_API_BEGIN(ctx)
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_commit_extension_primitives: not while frames are in flight (rt_release_window first): the window's kernel is reading the scene");
     const std::string e = ctx->hs.commit_extension(records, record_bytes, count);
     if (!e.empty()) return fail(ctx, RT_ERR_ARGUMENT, e);
     ctx->built = false;
@@ -456,9 +458,14 @@ int rt_probe_read_bandwidth(rt_ctx *ctx, size_t bytes, int repeats, double *gbs)
 int rt_write_ppm(rt_ctx *ctx, const char *path) {
     RT_API_BEGIN(ctx)
     if (!ctx->camera_set || !path) return fail(ctx, RT_ERR_STATE, "rt_write_ppm: no frame");
-    const uint32_t W = ctx->hs.window.width, H = ctx->local_rows;
+    // the plane rt_read_framebuffer returns: this context's rows, or — with a frame ring — the assembled full frame on rank 0
+    void *src = nullptr;
+    size_t n_bytes = 0;
+    const int rc = plane_info(ctx, RT_BUFFER_RGBA8, &src, &n_bytes);
+    if (rc != RT_OK) return rc;
+    const uint32_t W = ctx->hs.window.width, H = (uint32_t) (n_bytes / ((size_t) W * 4));
     std::vector<uint8_t> img((size_t) W * H * 4);
-    CUDA_CHECK(cudaMemcpyAsync(img.data(), ctx->d_rgba8.get(), img.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_CHECK(cudaMemcpyAsync(img.data(), src, img.size(), cudaMemcpyDeviceToHost, ctx->stream));
     CUDA_CHECK(cudaStreamSynchronize(ctx->stream));
     FILE *f = fopen(path, "wb");
     if (!f) return fail(ctx, RT_ERR_IO, std::string("cannot open ") + path);
@@ -473,12 +480,14 @@ int rt_write_ppm(rt_ctx *ctx, const char *path) {
     }
     fprintf(f, "P6\n%u %u\n255\n", W, H);
     std::vector<uint8_t> row((size_t) W * 3);
+    bool ok = true;
     for (uint32_t y = 0; y < H; y++) {   // row 0 of the framebuffer is the bottom scan-line: flip
-        const uint8_t *src = &img[(size_t) (H - 1 - y) * W * 4];
-        for (uint32_t x = 0; x < W; x++) { row[3 * x] = src[4 * x]; row[3 * x + 1] = src[4 * x + 1]; row[3 * x + 2] = src[4 * x + 2]; }
-        fwrite(row.data(), 1, row.size(), f);
+        const uint8_t *line = &img[(size_t) (H - 1 - y) * W * 4];
+        for (uint32_t x = 0; x < W; x++) { row[3 * x] = line[4 * x]; row[3 * x + 1] = line[4 * x + 1]; row[3 * x + 2] = line[4 * x + 2]; }
+        ok = ok && fwrite(row.data(), 1, row.size(), f) == row.size();
     }
-    fclose(f);
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) return fail(ctx, RT_ERR_IO, std::string("short write to ") + path);
     RT_API_END(ctx)
 }
 
@@ -576,6 +585,7 @@ int rt_set_vtk_frame(rt_ctx *ctx, size_t frame) {
     if (!ctx->vtk) return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: load a series first");
     if (!ctx->geometry_committed || !ctx->instances_configured) return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: commit geometry and instances first");
     if (frame >= ctx->vtk->files.size()) return fail(ctx, RT_ERR_ARGUMENT, "rt_set_vtk_frame: frame out of range");
+    for (int q = 0; q < 2; q++) if (rt_window_in_flight(ctx, q)) return fail(ctx, RT_ERR_STATE, "rt_set_vtk_frame: not while frames are in flight (rt_release_window first): the window's kernel is reading the scene");
     // the frame may have been read ahead by rt_prefetch_vtk_frame; otherwise read it now
     int cur = -1;
     if (ctx->vtk_ahead >= 0) {

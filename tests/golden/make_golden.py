@@ -5,7 +5,7 @@ C++ into oracle/_ref/libref_oracle.so by oracle/Makefile) on the small parity sc
 
     python tests/golden/make_golden.py
 
-Each file holds, for one scene of tests/conftest.py::parity_scenes: the RGBA8 frame written by the reference's own
+Each file holds, for one scene of tests/conftest.py::parity_scenes (scene*.npz) or ::edge_scenes (edge*.npz): the RGBA8 frame written by the reference's own
 `render` kernel body (src/Global/Kernel.cu:105-147) through the surf2Dwrite shim, the float radiance and ray count
 of the rayColor loop, the primary-hit AOVs (t, instance, primitive) recorded by the id-recording copy of
 TLAS::hit/BLAS::hit, the derived camera, the instance matrices/boxes, and a few closest-hit probes.
@@ -22,7 +22,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
     sys.path.insert(0, p)
 import oracle_ctypes as oc  # noqa: E402
-from conftest import parity_scenes  # noqa: E402
+from conftest import edge_scenes, parity_scenes  # noqa: E402
 
 SEED = 0x5EED
 BUILD_SEED = 20261104
@@ -40,7 +40,8 @@ def probe_rays(sc, n=512, seed=7):
 def main():
     pkg = importlib.import_module("real-time-gpu-ray-tracer_b200")
     ref = oc.Oracle("ref")
-    for k, sc in enumerate(parity_scenes(pkg.scenes)):
+    sets = [(f"scene{k}", sc) for k, sc in enumerate(parity_scenes(pkg.scenes))] + [(f"edge{k}", sc) for k, sc in enumerate(edge_scenes(pkg.scenes))]
+    for stem, sc in sets:
         h = ref.scene(sc, BUILD_SEED)
         rgba_kernel = h.render_kernel(SEED)
         rgba, rad, rays = h.render(SEED)
@@ -48,10 +49,10 @@ def main():
         t, inst, prim = h.primary(SEED)
         pr = probe_rays(sc)
         pt, pi, pp, pn = h.trace(pr)
-        np.savez_compressed(os.path.join(HERE, f"scene{k}.npz"), name=sc.name, seed=SEED, rgba8=rgba, radiance=rad, rays=np.uint64(rays),
+        np.savez_compressed(os.path.join(HERE, f"{stem}.npz"), name=sc.name, seed=SEED, rgba8=rgba, radiance=rad, rays=np.uint64(rays),
                             t=t, inst=inst, prim=prim, camera=h.camera(), instances=h.instances(),
                             probe_rays=pr, probe_t=pt, probe_inst=pi, probe_prim=pp, probe_normal=pn)
-        print(f"scene{k}.npz  {sc.name}: rays={rays} hit-pixels={(inst >= 0).mean():.3f}")
+        print(f"{stem}.npz  {sc.name}: rays={rays} hit-pixels={(inst >= 0).mean():.3f}")
         h.close()
     pairs = [(0, 0), (0x5EED, 0), (0x5EED ^ 1234, 1234), (0x5EED ^ 57599, 57599), (2 ** 40 + 17, 2 ** 20 + 3), (12345678901234567, 2073599)]
     np.savez_compressed(os.path.join(HERE, "xorwow.npz"), pairs=np.array(pairs, np.uint64),

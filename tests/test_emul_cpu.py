@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import emul_ctypes as ec
-from conftest import N_PARITY, parity_scenes
+from conftest import N_EDGE, N_PARITY, edge_scenes, parity_scenes
 
 SEED = 0x5EED
 
@@ -629,3 +629,15 @@ def test_single_level_walk_equals_two_level_walk(pkg, which):
     if name == "c2-looking-up":
         assert r["rays_missing_top_box"] > 0
     assert entered > 0
+
+
+@pytest.mark.parametrize("idx", range(N_EDGE))
+def test_cores_match_reference_golden_edge(pkg, idx):
+    """The product's device cores on the CPU against the REFERENCE's own output (tests/golden/edge*.npz, no port in between)."""
+    sc = edge_scenes(pkg.scenes)[idx]
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"edge{idx}.npz"))
+    assert str(g["name"]) == sc.name
+    r = ec.Emul(sc).render(SEED)
+    assert r["overflow"] == 0 and r["rays"] == int(g["rays"])
+    assert np.array_equal(r["rgba8"], g["rgba8"]) and np.array_equal(r["radiance"], g["radiance"])
+    assert np.array_equal(r["inst"], g["inst"]) and np.array_equal(r["prim"], g["prim"]) and np.array_equal(r["t"], g["t"])

@@ -239,6 +239,9 @@ struct Emul {
     std::vector<Aabb> wbox;
     std::vector<f3> wcentroid;
     SceneD sc{};
+    // emul_simt_tokens / emul_simt_run: per pixel (tile-major within rows [tok_y0, tok_y1)) the steps its lane takes in the path kernel
+    std::vector<std::vector<uint8_t>> tok;
+    int tok_y0 = 0, tok_y1 = 0;
 };
 
 template<class F>
@@ -466,6 +469,58 @@ void emul_count(void *h, uint64_t seed, int y0, int y1, int threads, uint64_t *o
     for (int k = 0; k < 4; k++) out4[k] = tot[k].load();
 }
 
+// ---- a trace-driven model of the path kernel's warp votes (profiles/tools/simt_model.py) ----------------------------------------
+// Token stream of one ray in the SINGLE instantiation of persist8_kernel: one TOK_NODE per wide-node step, one TOK_LEAF per primitive
+// test (the kernel tests ONE primitive per lane and LEAF step), closed by the SHADE step that ends the ray and starts the next.
+enum : uint8_t { TOK_NODE = 0, TOK_LEAF = 1, TOK_SHADE_GO_ON = 2, TOK_SHADE_PATH_END = 3 };
+
+void trace_single8_tokens(const SceneD &sc, const RayD &wray, float tmin, HitD &hit, uint2 *stack_mem, std::vector<uint8_t> &tok) {
+    hit.t = RT_INF; hit.tc = RT_INF; hit.u = 0.0f; hit.v = 0.0f; hit.inst = -1; hit.leaf = 0;
+    WideStack st;
+    st.base = stack_mem; st.stride = 1; st.sp = 0;
+    uint32_t overflow = 0;
+    float inv[12];
+    int root8, prim_type;
+    load_instance_wide(sc, 0, inv, root8, prim_type);
+    WideRay r;
+    r.ray.o = xf_point(inv, wray.o);
+    r.ray.d = xf_vector(inv, wray.d);
+    wide_setup_ray(r);
+    uint2 ng = make_uint2((uint32_t) root8, 0x80000000u);
+    uint2 tg = make_uint2(0u, 0u);
+    for (;;) {
+        if (ng.y > 0x00FFFFFFu) {
+            const uint32_t hits_imask = ng.y;
+            const int bit = rt_bfind(hits_imask);
+            const uint32_t base = ng.x;
+            ng.y &= ~(1u << bit);
+            if (ng.y > 0x00FFFFFFu) wide_push(st, ng, overflow);
+            const uint32_t slot = ((uint32_t) bit - 24u) ^ (r.oct_inv4 & 0xFFu);
+            const uint32_t rel = (uint32_t) rt_popc(hits_imask & ~(0xFFFFFFFFu << slot));
+            const BvhNode8 n = load_node8(sc.blas_nodes8, base + rel);
+            tok.push_back(TOK_NODE);
+            const uint32_t hm = node8_intersect(n, r, tmin, hit.tc);
+            ng.x = n.n1.x;
+            ng.y = (hm & 0xFF000000u) | (f2u(n.n0.w) >> 24);
+            tg.x = n.n1.y;
+            tg.y = hm & 0x00FFFFFFu;
+        } else {
+            tg = ng;
+            ng = make_uint2(0u, 0u);
+        }
+        while (tg.y) {
+            const int idx = rt_bfind(tg.y);
+            tg.y &= ~(1u << idx);
+            tok.push_back(TOK_LEAF);
+            leaf_test8(sc, (uint32_t) prim_type, tg.x + (uint32_t) idx, r.ray, tmin, 0, hit);
+        }
+        if (ng.y <= 0x00FFFFFFu) {
+            if (st.sp == 0) break;
+            ng = wide_pop(st);
+        }
+    }
+}
+
 // out[0] rays, [1] rays whose hit records differ between the two walks (must be 0), [2] wide-node fetches of the two-level walk,
 // [3] of the single-level walk, [4] rays that miss the scene's top-level box (the only rays the top level saves work on), [5] primitive
 // tests two-level, [6] single-level.  Returns -1 unless the scene is exactly one instance.
@@ -505,6 +560,125 @@ int emul_single_check(void *h, uint64_t seed, int y0, int y1, int threads, uint6
         for (int k = 0; k < 7; k++) tot[k] += acc[k];
     });
     for (int k = 0; k < 7; k++) out7[k] = tot[k].load();
+    return 0;
+}
+
+// Token streams of every pixel of rows [y0, y1) (y0, y1 multiples of 4; a one-instance scene), kept in the handle for emul_simt_run.
+// NOTE for variant 1 / 2 runs on two_level streams: the instance entry is a LEAF token of its own run (a node token follows it).
+// Returns the number of tokens, -1 on a scene that is not one instance.
+long long emul_simt_tokens(void *h, uint64_t seed, int y0, int y1, int threads, int two_level) {
+    Emul &e = *(Emul *) h;
+    if (e.hs.inst_desc.size() != 1 || !e.wide || (y0 & 3) || (y1 & 3)) return -1;
+    const CameraD &cam = e.hs.cam;
+    const uint32_t tiles_x = (cam.width + 7u) / 8u;
+    const int tile_rows = (y1 - y0) / 4;
+    e.tok.assign((size_t) tiles_x * tile_rows * 32u, std::vector<uint8_t>());
+    e.tok_y0 = y0; e.tok_y1 = y1;
+    std::atomic<long long> total{0};
+    parallel_rows(y0, y1, threads, [&](int y) {
+        long long n = 0;
+        for (uint32_t x = 0; x < cam.width; x++) {
+            const uint32_t pixelIndex = cam.pitch * (uint32_t) y + x;
+            curandStateXORWOW_t cs;
+            curand_init((unsigned long long) ((long long) pixelIndex ^ (long long) seed), pixelIndex, 0, &cs);
+            RngState rng{cs.d, cs.v[0], cs.v[1], cs.v[2], cs.v[3], cs.v[4]};
+            uint2 stack[RT_WIDE_STACK];
+            const uint32_t ly = (uint32_t) (y - y0);
+            std::vector<uint8_t> &tok = e.tok[((size_t) (ly / 4u) * tiles_x + x / 8u) * 32u + (ly & 3u) * 8u + (x & 7u)];
+            for (uint32_t si = 0; si < cam.sqrtSamples; si++) {
+                for (uint32_t sj = 0; sj < cam.sqrtSamples; sj++) {
+                    RayD ray = primary_ray(cam, x, (uint32_t) y, si, sj, rng);
+                    f3 thr = mk3(1.0f, 1.0f, 1.0f);
+                    for (uint32_t depth = 0; depth < cam.depth; depth++) {
+                        HitD hit;
+                        // two_level: the general kernel's walk of a one-instance scene — a node step on the TLAS root and the instance
+                        // entry (a LEAF step) in front of every ray (approximation: also for the few rays that miss the top box)
+                        if (two_level) { tok.push_back(TOK_NODE); tok.push_back(TOK_LEAF); }
+                        trace_single8_tokens(e.sc, ray, RT_TMIN, hit, stack, tok);
+                        const bool alive = shade_scatter<true>(e.sc, cam, ray, hit, thr, rng);
+                        const bool go_on = alive && depth + 1 < cam.depth;
+                        tok.push_back(go_on ? TOK_SHADE_GO_ON : TOK_SHADE_PATH_END);
+                        if (!alive) break;
+                    }
+                }
+            }
+            n += (long long) tok.size();
+        }
+        total += n;
+    });
+    return total.load();
+}
+
+// The warp votes of persist8_kernel replayed on those token streams: `n_warps` warps of 32 lanes step in turn; every lane carries
+// one pixel, takes the next unstarted one from the shared queue (tile order) inside a SHADE step, and the warp runs ONE phase per
+// iteration, chosen as the kernel does (kernels_persist.cu: node while >= node_min lanes stand on a node, else shade once
+// >= shade_min lanes wait, else leaf, else node, else shade).
+// variant 0: the kernel as it is.  variant 1: a LEAF step hands ALL pending primitive tests of the warp out to its 32 lanes
+// (ceil(pending / 32) rounds).  variant 2: a lane tests all pending primitives of its own group in one LEAF step (the rejected
+// RT_LEAF_LOOP variant, as a cross-check of the model).
+// out[0..2] steps of node / leaf / shade phases, out[3..5] the lanes that took part, summed, out[6] leaf ROUNDS (variant 1 / 2: the
+// issue cost of a leaf step is its rounds), out[7] lane-rounds of leaf work, out[8] iterations, out[9] tokens consumed.
+int emul_simt_run(void *h, int n_warps, int node_min, int shade_min, int variant, uint64_t *out) {
+    Emul &e = *(Emul *) h;
+    if (e.tok.empty() || n_warps < 1) return -1;
+    struct Lane { const std::vector<uint8_t> *t = nullptr; size_t i = 0; };
+    std::vector<Lane> lanes((size_t) n_warps * 32);
+    size_t next = 0;
+    auto take = [&](Lane &l) {
+        while (next < e.tok.size() && e.tok[next].empty()) next++;        // ids outside the image (edge tiles)
+        if (next < e.tok.size()) { l.t = &e.tok[next++]; l.i = 0; } else l.t = nullptr;
+    };
+    for (Lane &l: lanes) take(l);
+    for (int k = 0; k < 10; k++) out[k] = 0;
+    size_t live = 0;
+    for (const Lane &l: lanes) live += l.t != nullptr;
+    while (live) {
+        for (int w = 0; w < n_warps; w++) {
+            Lane *L = &lanes[(size_t) w * 32];
+            int nn = 0, nl = 0, ns = 0;
+            for (int k = 0; k < 32; k++) {
+                if (!L[k].t) continue;
+                const uint8_t t = (*L[k].t)[L[k].i];
+                if (t == TOK_NODE) nn++; else if (t == TOK_LEAF) nl++; else ns++;
+            }
+            if (nn + nl + ns == 0) continue;
+            out[8]++;
+            int phase;
+            if (nn >= node_min) phase = 0;
+            else if (ns >= shade_min) phase = 2;
+            else if (nl) phase = 1;
+            else if (nn) phase = 0;
+            else phase = 2;
+            if (phase == 0) {
+                out[0]++; out[3] += (uint64_t) nn; out[9] += (uint64_t) nn;
+                for (int k = 0; k < 32; k++) if (L[k].t && (*L[k].t)[L[k].i] == TOK_NODE) L[k].i++;
+            } else if (phase == 1) {
+                out[1]++; out[4] += (uint64_t) nl;
+                if (variant == 0) {
+                    out[6]++; out[7] += (uint64_t) nl; out[9] += (uint64_t) nl;
+                    for (int k = 0; k < 32; k++) if (L[k].t && (*L[k].t)[L[k].i] == TOK_LEAF) L[k].i++;
+                } else {
+                    uint64_t pending = 0, longest = 0;
+                    for (int k = 0; k < 32; k++) {
+                        if (!L[k].t) continue;
+                        uint64_t run = 0;
+                        while ((*L[k].t)[L[k].i] == TOK_LEAF) { L[k].i++; run++; }
+                        pending += run;
+                        if (run > longest) longest = run;
+                    }
+                    out[9] += pending; out[7] += pending;
+                    out[6] += variant == 1 ? (pending + 31u) / 32u : longest;
+                }
+            } else {
+                out[2]++; out[5] += (uint64_t) ns; out[9] += (uint64_t) ns;
+                for (int k = 0; k < 32; k++) {
+                    if (!L[k].t || (*L[k].t)[L[k].i] < TOK_SHADE_GO_ON) continue;
+                    L[k].i++;
+                    if (L[k].i == L[k].t->size()) { take(L[k]); if (!L[k].t) live--; }
+                }
+            }
+        }
+    }
     return 0;
 }
 

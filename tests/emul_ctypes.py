@@ -209,6 +209,25 @@ class Emul:
         keys = ("rays", "mismatches", "nodes_two_level", "nodes_single", "rays_missing_top_box", "prims_two_level", "prims_single")
         return {k: int(v) for k, v in zip(keys, out)}
 
+    def simt_tokens(self, seed, y0, y1, threads=None, two_level=False):
+        """token streams (node / leaf / shade steps of the path kernel's SINGLE instantiation) of every pixel of rows [y0, y1),
+        kept in the handle for simt_run; returns the number of tokens"""
+        self.lib.emul_simt_tokens.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int]
+        self.lib.emul_simt_tokens.restype = C.c_longlong
+        n = self.lib.emul_simt_tokens(self.h, seed, y0, y1, threads or os.cpu_count() or 1, 1 if two_level else 0)
+        assert n >= 0, "emul_simt_tokens: one-instance scenes, rows in multiples of 4"
+        return int(n)
+
+    def simt_run(self, n_warps, node_min=18, shade_min=10, variant=0):
+        """the path kernel's warp votes replayed on the token streams (tests/emul/emul.cpp emul_simt_run)"""
+        out = np.zeros(10, np.uint64)
+        self.lib.emul_simt_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        self.lib.emul_simt_run.restype = C.c_int
+        assert self.lib.emul_simt_run(self.h, n_warps, node_min, shade_min, variant, abi.ptr(out)) == 0
+        o = [int(v) for v in out]
+        return dict(node_steps=o[0], leaf_steps=o[1], shade_steps=o[2], node_lanes=o[3], leaf_lanes=o[4], shade_lanes=o[5],
+                    leaf_rounds=o[6], leaf_lane_rounds=o[7], iterations=o[8], tokens=o[9])
+
     def pixel_rays(self, seed, y0, y1, threads=None):
         """rays traced by every pixel of rows [y0, y1): uint32 [y1 - y0, W]"""
         out = np.zeros((y1 - y0, self.W), np.uint32)

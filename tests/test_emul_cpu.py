@@ -641,3 +641,22 @@ def test_cores_match_reference_golden_edge(pkg, idx):
     assert r["overflow"] == 0 and r["rays"] == int(g["rays"])
     assert np.array_equal(r["rgba8"], g["rgba8"]) and np.array_equal(r["radiance"], g["radiance"])
     assert np.array_equal(r["inst"], g["inst"]) and np.array_equal(r["prim"], g["prim"]) and np.array_equal(r["t"], g["t"])
+
+
+def test_simt_model_replays_every_step(pkg):
+    """profiles/tools/simt_model.py stands on two twin functions: the per-pixel step streams of the path kernel's SINGLE instantiation
+    (their node / primitive counts must be the traversal counts of the same rows) and the replay of the kernel's warp votes (every
+    step of every stream is consumed exactly once, whatever the thresholds or the leaf-step variant)."""
+    sc = pkg.scenes.c2(width=64, height=32, spp=4, depth=6, nx=40, nz=20)
+    e = ec.Emul(sc)
+    n = e.simt_tokens(SEED, 8, 24)
+    chk = e.single_check(SEED, 8, 24)
+    for nm, sm, variant in ((18, 10, 0), (24, 4, 0), (1, 32, 0), (18, 10, 1), (18, 10, 2)):
+        r = e.simt_run(3, nm, sm, variant)
+        assert r["tokens"] == n
+        assert r["node_lanes"] == chk["nodes_single"] and r["leaf_lane_rounds"] == chk["prims_single"] and r["shade_lanes"] == chk["rays"]
+        assert r["node_steps"] + r["leaf_steps"] + r["shade_steps"] == r["iterations"]
+        if variant == 0:
+            assert r["leaf_rounds"] == r["leaf_steps"] and r["leaf_lanes"] == r["leaf_lane_rounds"]
+    shared, own = e.simt_run(3, 18, 10, 1), e.simt_run(3, 18, 10, 2)
+    assert shared["leaf_rounds"] <= own["leaf_rounds"]          # 32 lanes share the work vs the longest group decides
